@@ -1,0 +1,559 @@
+/*
+ * hnsw_build.c — host-side HNSW graph construction in the reference's format.
+ *
+ * The search path this repo accelerates runs "over the graph the reference builds"
+ * (BASELINE.json north_star).  The reference's own hnsw_insert is quadratic in two
+ * places (linear-scan VisitedSet, src/hnsw_algo.c:318-325; O(deg²) mutual-neighbour
+ * count evaluated for every entry of every over-full list, :460-475 + :608-617), so it
+ * cannot produce the 1M–10M node graphs of BASELINE.json configs 2–4 in practical time
+ * (SURVEY.md finding 7, risk R1).  This file implements the same construction
+ * algorithm from scratch on flat arrays:
+ *
+ *   random level        src/hnsw_algo.c:19-30, :240-248   xorshift32 seed 42, floor(-ln(u)/ln(M))
+ *   greedy descent      src/hnsw_algo.c:257-282           list-order scan with in-loop switch
+ *   beam per level      src/hnsw_algo.c:347-448           ef = ef_construction, patience rule included
+ *   closest-M select    src/hnsw_algo.c:497-516
+ *   bidirectional link  src/hnsw_algo.c:582-591
+ *   MN-RU prune         src/hnsw_algo.c:601-646           distance asc, mutual-neighbour count desc on ties
+ *
+ * Two modes:
+ *   exact  (batch = 0): one insert at a time. O(1) visited stamps and a lazily evaluated
+ *          mutual-neighbour count (it only matters when two distances are bit-equal) are
+ *          pure representation changes, so the graph is IDENTICAL to the reference's —
+ *          entry point, levels and ordered neighbour lists (tests/test_builder.py diffs it
+ *          against the real reference).
+ *   batch  (batch > 0): nodes are inserted in id order in groups; each group searches the
+ *          graph as it stood before the group (parallel, read-only) and is then linked in
+ *          id order, reverse edges grouped per target so every list has one writer.  The
+ *          result is deterministic for a given batch size, independent of thread count,
+ *          and is a graph of the reference's construction rule but not its exact
+ *          sequential graph.  Used only to make full-size benchmark inputs in minutes.
+ *
+ * Distances are evaluated in the reference's SSE order (src/vec_math.c:78-143) so that
+ * the exact mode reproduces its comparisons bit for bit.
+ */
+#define _POSIX_C_SOURCE 200809L
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+#include <xmmintrin.h>
+
+enum { MB_L2 = 0, MB_COSINE = 1, MB_IP = 2 };
+#define MB_MAX_LEVELS 32 /* src/hnsw_algo.h:14 */
+
+typedef struct { int32_t slot; float key; } HItem;
+typedef struct { HItem *a; int size, cap; } Heap;
+
+typedef struct {
+    uint32_t *stamp; uint32_t cur;
+    Heap cand, res;
+    int32_t *r_slot; float *r_dist; /* beam output, ascending, capacity efc */
+    int32_t *sel;                   /* per level selected: [MB_MAX_LEVELS][M0] */
+    int32_t *sel_cnt;               /* [MB_MAX_LEVELS] */
+} Scratch;
+
+typedef struct {
+    int dim, metric, M, M0, efc;
+    int64_t n, cap;
+    const float *vecs;
+    int32_t *level;
+    int32_t *nbr0; int32_t *cnt0;       /* layer 0: stride M0+1 */
+    int64_t *upper_base;                /* first upper list of a node, or -1 */
+    int32_t *nbrU; int32_t *cntU;       /* upper lists: stride M+1 */
+    int64_t n_upper, cap_upper;
+    int32_t entry; int max_level;
+    uint32_t rng; double level_mult;
+    int n_scratch; Scratch *scratch;
+    int lazy_mn_parallel_skip;
+} Builder;
+
+/* ───────────── distances, reference SSE order ───────────── */
+
+static inline float hsum(__m128 v) {
+    float t[4];
+    _mm_storeu_ps(t, v);
+    return t[0] + t[1] + t[2] + t[3];
+}
+
+static float dist_l2(const float *a, const float *b, int dim) {
+    __m128 acc = _mm_setzero_ps();
+    int i = 0;
+    for (; i + 4 <= dim; i += 4) {
+        __m128 d = _mm_sub_ps(_mm_loadu_ps(a + i), _mm_loadu_ps(b + i));
+        acc = _mm_add_ps(acc, _mm_mul_ps(d, d));
+    }
+    float s = hsum(acc);
+    for (; i < dim; i++) { float d = a[i] - b[i]; float p = d * d; s = s + p; }
+    return s;
+}
+
+static float dist_ip(const float *a, const float *b, int dim) {
+    __m128 acc = _mm_setzero_ps();
+    int i = 0;
+    for (; i + 4 <= dim; i += 4) acc = _mm_add_ps(acc, _mm_mul_ps(_mm_loadu_ps(a + i), _mm_loadu_ps(b + i)));
+    float s = hsum(acc);
+    for (; i < dim; i++) { float p = a[i] * b[i]; s = s + p; }
+    return -s;
+}
+
+static float dist_cos(const float *a, const float *b, int dim) {
+    __m128 ad = _mm_setzero_ps(), aa = _mm_setzero_ps(), ab = _mm_setzero_ps();
+    int i = 0;
+    for (; i + 4 <= dim; i += 4) {
+        __m128 va = _mm_loadu_ps(a + i), vb = _mm_loadu_ps(b + i);
+        ad = _mm_add_ps(ad, _mm_mul_ps(va, vb));
+        aa = _mm_add_ps(aa, _mm_mul_ps(va, va));
+        ab = _mm_add_ps(ab, _mm_mul_ps(vb, vb));
+    }
+    float dot = hsum(ad), na = hsum(aa), nb = hsum(ab);
+    for (; i < dim; i++) {
+        float p;
+        p = a[i] * b[i]; dot = dot + p;
+        p = a[i] * a[i]; na = na + p;
+        p = b[i] * b[i]; nb = nb + p;
+    }
+    float denom = sqrtf(na) * sqrtf(nb);
+    if (denom < 1e-30f) return 1.0f;
+    return 1.0f - (dot / denom);
+}
+
+static inline float dist(const Builder *b, const float *x, const float *y) {
+    return b->metric == MB_L2 ? dist_l2(x, y, b->dim) : b->metric == MB_COSINE ? dist_cos(x, y, b->dim)
+                                                                                : dist_ip(x, y, b->dim);
+}
+
+/* ───────────── heap with the reference's sift rules (src/priority_queue.c:18-42) ───────────── */
+
+static void hp_reset(Heap *h, int cap) {
+    if (cap < 4) cap = 4;
+    if (!h->a || h->cap < cap) { free(h->a); h->a = (HItem *)malloc((size_t)(cap + 1) * sizeof(HItem)); h->cap = cap; }
+    h->size = 0;
+}
+static void hp_push(Heap *h, int32_t slot, float key) {
+    if (h->size >= h->cap) { h->cap *= 2; h->a = (HItem *)realloc(h->a, (size_t)(h->cap + 1) * sizeof(HItem)); }
+    int i = ++h->size;
+    h->a[i].slot = slot; h->a[i].key = key;
+    while (i > 1) {
+        int p = i >> 1;
+        if (h->a[p].key <= h->a[i].key) break;
+        HItem t = h->a[p]; h->a[p] = h->a[i]; h->a[i] = t;
+        i = p;
+    }
+}
+static HItem hp_pop(Heap *h) {
+    HItem top = h->a[1];
+    h->a[1] = h->a[h->size--];
+    int i = 1;
+    while (h->size > 0) {
+        int m = i, l = 2 * i, r = l + 1;
+        if (l <= h->size && h->a[l].key < h->a[m].key) m = l;
+        if (r <= h->size && h->a[r].key < h->a[m].key) m = r;
+        if (m == i) break;
+        HItem t = h->a[i]; h->a[i] = h->a[m]; h->a[m] = t;
+        i = m;
+    }
+    return top;
+}
+
+/* ───────────── adjacency ───────────── */
+
+static inline const float *vec_of(const Builder *b, int32_t s) { return b->vecs + (size_t)s * (size_t)b->dim; }
+
+static inline int32_t *list_ptr(const Builder *b, int32_t s, int l, int32_t **cnt) {
+    if (l == 0) { *cnt = &b->cnt0[s]; return b->nbr0 + (size_t)s * (size_t)(b->M0 + 1); }
+    int64_t u = b->upper_base[s] + (l - 1);
+    *cnt = &b->cntU[u];
+    return b->nbrU + (size_t)u * (size_t)(b->M + 1);
+}
+
+static int list_add(int32_t *lst, int32_t *cnt, int32_t t) { /* src/hnsw_algo.c:142-163 */
+    for (int i = 0; i < *cnt; i++) if (lst[i] == t) return 0;
+    lst[(*cnt)++] = t;
+    return 1;
+}
+
+static int mutual_count(const Builder *b, int32_t x, int32_t y, int l) { /* src/hnsw_algo.c:460-475 */
+    if (l > b->level[x] || l > b->level[y]) return 0;
+    int32_t *cx, *cy;
+    const int32_t *lx = list_ptr(b, x, l, &cx), *ly = list_ptr(b, y, l, &cy);
+    int c = 0;
+    for (int i = 0; i < *cx; i++)
+        for (int j = 0; j < *cy; j++)
+            if (ly[j] == lx[i]) { c++; break; }
+    return c;
+}
+
+/* MN-RU prune of s's over-full list at level l (src/hnsw_algo.c:601-646). The reference
+ * evaluates the mutual-neighbour count of every entry up front; it is consulted only
+ * when two distances compare equal, so it is evaluated on demand here (use_mn = 0 in the
+ * batch linker, where other lists are being written concurrently: ties keep the earlier
+ * entry there). */
+static void prune(Builder *b, int32_t s, int l, int M_max, int use_mn) {
+    int32_t *cnt;
+    int32_t *lst = list_ptr(b, s, l, &cnt);
+    int nc = *cnt;
+    float d[2 * 64 + 8];
+    int mn[2 * 64 + 8];
+    int32_t id[2 * 64 + 8];
+    float *dp = d; int *mp = mn; int32_t *ip = id;
+    if (nc > (int)(sizeof(d) / sizeof(d[0]))) {
+        dp = (float *)malloc((size_t)nc * sizeof(float));
+        mp = (int *)malloc((size_t)nc * sizeof(int));
+        ip = (int32_t *)malloc((size_t)nc * sizeof(int32_t));
+    }
+    const float *vs = vec_of(b, s);
+    for (int j = 0; j < nc; j++) { ip[j] = lst[j]; dp[j] = dist(b, vs, vec_of(b, lst[j])); mp[j] = -2; }
+    for (int a = 0; a < M_max && a < nc; a++) {
+        int best = a;
+        for (int c = a + 1; c < nc; c++) {
+            if (dp[c] < dp[best]) best = c;
+            else if (dp[c] == dp[best] && use_mn) {
+                if (mp[c] == -2) mp[c] = mutual_count(b, s, ip[c], l);
+                if (mp[best] == -2) mp[best] = mutual_count(b, s, ip[best], l);
+                if (mp[c] > mp[best]) best = c;
+            }
+        }
+        if (best != a) {
+            float td = dp[a]; dp[a] = dp[best]; dp[best] = td;
+            int tm = mp[a]; mp[a] = mp[best]; mp[best] = tm;
+            int32_t ti = ip[a]; ip[a] = ip[best]; ip[best] = ti;
+        }
+    }
+    memcpy(lst, ip, (size_t)M_max * sizeof(int32_t));
+    *cnt = M_max;
+    if (dp != d) { free(dp); free(mp); free(ip); }
+}
+
+/* ───────────── search primitives over the growing graph ───────────── */
+
+static int32_t greedy(const Builder *b, const float *q, int32_t entry, int l) {
+    int32_t cur = entry;
+    float cur_d = dist(b, q, vec_of(b, cur));
+    int changed = 1;
+    while (changed) {
+        changed = 0;
+        int32_t *cnt;
+        const int32_t *lst = list_ptr(b, cur, l, &cnt);
+        for (int i = 0; i < *cnt; i++) {
+            int32_t t = lst[i];
+            float d = dist(b, q, vec_of(b, t));
+            if (d < cur_d) { cur_d = d; cur = t; changed = 1; lst = list_ptr(b, cur, l, &cnt); }
+        }
+    }
+    return cur;
+}
+
+static int beam(const Builder *b, Scratch *sc, const float *q, int32_t entry, int l, int ef) {
+    hp_reset(&sc->cand, ef * 2);
+    hp_reset(&sc->res, ef * 2);
+    if (++sc->cur == 0) { memset(sc->stamp, 0, (size_t)b->cap * sizeof(uint32_t)); sc->cur = 1; }
+    float d0 = dist(b, q, vec_of(b, entry));
+    hp_push(&sc->cand, entry, d0);
+    hp_push(&sc->res, entry, -d0);
+    sc->stamp[entry] = sc->cur;
+    int patience_max = ef / 4 < 10 ? 10 : ef / 4, stale = 0;
+    while (sc->cand.size > 0) {
+        HItem c = hp_pop(&sc->cand);
+        if (sc->res.size >= ef && c.key > -sc->res.a[1].key) break;
+        if (stale >= patience_max && sc->res.size >= ef) break;
+        int32_t *cnt;
+        const int32_t *lst = list_ptr(b, c.slot, l, &cnt);
+        int n = *cnt, improved = 0;
+        for (int i = 0; i < n; i++) {
+            int32_t t = lst[i];
+            if (sc->stamp[t] == sc->cur) continue;
+            __builtin_prefetch(vec_of(b, t));
+        }
+        for (int i = 0; i < n; i++) {
+            int32_t t = lst[i];
+            if (sc->stamp[t] == sc->cur) continue;
+            sc->stamp[t] = sc->cur;
+            float d = dist(b, q, vec_of(b, t));
+            if (sc->res.size < ef) { hp_push(&sc->cand, t, d); hp_push(&sc->res, t, -d); improved = 1; }
+            else if (d < -sc->res.a[1].key) { hp_push(&sc->cand, t, d); hp_pop(&sc->res); hp_push(&sc->res, t, -d); improved = 1; }
+        }
+        stale = improved ? 0 : stale + 1;
+    }
+    int count = sc->res.size;
+    for (int i = count - 1; i >= 0; i--) { HItem it = hp_pop(&sc->res); sc->r_slot[i] = it.slot; sc->r_dist[i] = -it.key; }
+    return count;
+}
+
+/* ───────────── level generator (src/hnsw_algo.c:19-30, :240-248) ───────────── */
+
+static int next_level(Builder *b) {
+    uint32_t x = b->rng;
+    x ^= x << 13; x ^= x >> 17; x ^= x << 5;
+    b->rng = x;
+    double r = (double)x / (double)0xFFFFFFFFu;
+    if (r == 0.0) r = 1e-10;
+    int lv = (int)(-log(r) * b->level_mult);
+    if (lv >= MB_MAX_LEVELS) lv = MB_MAX_LEVELS - 1;
+    return lv;
+}
+
+static void alloc_node(Builder *b, int32_t s, int lv) {
+    b->level[s] = lv;
+    b->cnt0[s] = 0;
+    b->upper_base[s] = -1;
+    if (lv > 0) {
+        if (b->n_upper + lv > b->cap_upper) {
+            int64_t nc = b->cap_upper * 2 + lv + 1024;
+            b->nbrU = (int32_t *)realloc(b->nbrU, (size_t)nc * (size_t)(b->M + 1) * sizeof(int32_t));
+            b->cntU = (int32_t *)realloc(b->cntU, (size_t)nc * sizeof(int32_t));
+            b->cap_upper = nc;
+        }
+        b->upper_base[s] = b->n_upper;
+        for (int l = 0; l < lv; l++) b->cntU[b->n_upper + l] = 0;
+        b->n_upper += lv;
+    }
+}
+
+/* phase A of an insert: find the per-level selected neighbours of node s (read-only on
+ * every other node). Levels searched: min(level, max_level) .. 0 (src/hnsw_algo.c:553-579). */
+static void find_links(const Builder *b, Scratch *sc, int32_t s) {
+    const float *q = vec_of(b, s);
+    int lv = b->level[s];
+    int32_t cur = b->entry;
+    for (int l = b->max_level; l > lv; l--) cur = greedy(b, q, cur, l);
+    int start = lv < b->max_level ? lv : b->max_level;
+    for (int l = 0; l < MB_MAX_LEVELS; l++) sc->sel_cnt[l] = 0;
+    for (int l = start; l >= 0; l--) {
+        int M_max = l == 0 ? b->M0 : b->M;
+        int found = beam(b, sc, q, cur, l, b->efc);
+        int k = found < M_max ? found : M_max;
+        memcpy(sc->sel + (size_t)l * (size_t)b->M0, sc->r_slot, (size_t)k * sizeof(int32_t));
+        sc->sel_cnt[l] = k;
+        if (found > 0) cur = sc->r_slot[0];
+    }
+}
+
+/* exact sequential insert (src/hnsw_algo.c:520-666). The search of level l-1 must see the
+ * links made at level l, so search and link are interleaved exactly as in the reference. */
+static void insert_exact(Builder *b, int32_t s, int lv) {
+    Scratch *sc = &b->scratch[0];
+    alloc_node(b, s, lv);
+    if (b->entry < 0) { b->entry = s; b->max_level = lv; return; }
+    const float *q = vec_of(b, s);
+    int32_t cur = b->entry;
+    for (int l = b->max_level; l > lv; l--) cur = greedy(b, q, cur, l);
+    int start = lv < b->max_level ? lv : b->max_level;
+    for (int l = start; l >= 0; l--) {
+        int M_max = l == 0 ? b->M0 : b->M;
+        int found = beam(b, sc, q, cur, l, b->efc);
+        int k = found < M_max ? found : M_max;
+        int32_t *mycnt;
+        int32_t *mine = list_ptr(b, s, l, &mycnt);
+        for (int i = 0; i < k; i++) {
+            int32_t t = sc->r_slot[i];
+            list_add(mine, mycnt, t);
+            if (l <= b->level[t]) {
+                int32_t *tc;
+                int32_t *tl = list_ptr(b, t, l, &tc);
+                list_add(tl, tc, s);
+                if (*tc > M_max) prune(b, t, l, M_max, 1);
+            }
+        }
+        if (found > 0) cur = sc->r_slot[0];
+    }
+    if (lv > b->max_level) { b->entry = s; b->max_level = lv; }
+}
+
+typedef struct { int32_t target, level, src; } RevReq;
+
+static int cmp_req(const void *a, const void *b) {
+    const RevReq *x = (const RevReq *)a, *y = (const RevReq *)b;
+    if (x->target != y->target) return x->target < y->target ? -1 : 1;
+    if (x->level != y->level) return x->level < y->level ? -1 : 1;
+    return x->src < y->src ? -1 : x->src > y->src;
+}
+
+/* ───────────── public C API ───────────── */
+
+static void scratch_init(Builder *b, Scratch *sc) {
+    memset(sc, 0, sizeof(*sc));
+    sc->stamp = (uint32_t *)calloc((size_t)b->cap, sizeof(uint32_t));
+    sc->r_slot = (int32_t *)malloc((size_t)b->efc * sizeof(int32_t));
+    sc->r_dist = (float *)malloc((size_t)b->efc * sizeof(float));
+    sc->sel = (int32_t *)malloc((size_t)MB_MAX_LEVELS * (size_t)b->M0 * sizeof(int32_t));
+    sc->sel_cnt = (int32_t *)calloc(MB_MAX_LEVELS, sizeof(int32_t));
+}
+
+void *muninn_build_create(int dim, int metric, int M, int ef_construction, int64_t capacity, const float *vectors) {
+    Builder *b = (Builder *)calloc(1, sizeof(Builder));
+    if (!b) return NULL;
+    b->dim = dim; b->metric = metric; b->M = M; b->M0 = 2 * M; /* src/hnsw_algo.c:188 */
+    b->efc = ef_construction; b->cap = capacity; b->vecs = vectors;
+    b->level = (int32_t *)malloc((size_t)capacity * sizeof(int32_t));
+    b->nbr0 = (int32_t *)malloc((size_t)capacity * (size_t)(b->M0 + 1) * sizeof(int32_t));
+    b->cnt0 = (int32_t *)calloc((size_t)capacity, sizeof(int32_t));
+    b->upper_base = (int64_t *)malloc((size_t)capacity * sizeof(int64_t));
+    b->entry = -1; b->max_level = -1;
+    b->rng = 42; /* src/hnsw_algo.c:205 */
+    b->level_mult = 1.0 / log((double)M);
+    if (!b->level || !b->nbr0 || !b->cnt0 || !b->upper_base) return NULL;
+    return b;
+}
+
+void muninn_build_seed(void *h, uint32_t seed) { ((Builder *)h)->rng = seed ? seed : 1; } /* src/hnsw_algo.c:222-224 */
+
+/* Insert the next `count` vectors (slots n .. n+count-1, in order).
+ * batch = 0 → exact sequential mode; batch > 0 → batch-synchronous mode once the graph
+ * holds at least `warm` nodes (earlier nodes are inserted exactly). */
+int muninn_build_insert(void *h, int64_t count, int batch, int64_t warm, int nthreads) {
+    Builder *b = (Builder *)h;
+    if (b->n + count > b->cap) return -1;
+    if (nthreads < 1) nthreads = 1;
+    if (b->n_scratch < nthreads) {
+        b->scratch = (Scratch *)realloc(b->scratch, (size_t)nthreads * sizeof(Scratch));
+        for (int t = b->n_scratch; t < nthreads; t++) scratch_init(b, &b->scratch[t]);
+        b->n_scratch = nthreads;
+    }
+    int64_t end = b->n + count;
+    RevReq *req = NULL; int64_t req_cap = 0;
+    int64_t *grp = NULL; int64_t grp_cap = 0;
+    while (b->n < end) {
+        if (batch <= 0 || b->n < warm) {
+            int lv = next_level(b);
+            insert_exact(b, (int32_t)b->n, lv);
+            b->n++;
+            continue;
+        }
+        /* form a group; a node that would raise max_level is inserted alone, exactly */
+        int64_t g0 = b->n, g1 = g0;
+        int raise = 0;
+        while (g1 < end && g1 - g0 < batch) {
+            int lv = next_level(b);
+            if (lv > b->max_level) {
+                if (g1 == g0) { insert_exact(b, (int32_t)g1, lv); b->n++; g0 = g1 = b->n; continue; }
+                /* close the group before this node; remember its level by allocating now */
+                alloc_node(b, (int32_t)g1, lv);
+                raise = 1;
+                break;
+            }
+            alloc_node(b, (int32_t)g1, lv);
+            g1++;
+        }
+        int64_t gn = g1 - g0;
+        if (gn > 0) {
+            /* phase A: parallel read-only searches; each node writes only its own lists */
+            int64_t max_req = gn * ((int64_t)b->M0 + (int64_t)b->M * MB_MAX_LEVELS);
+            if (max_req > req_cap) { req = (RevReq *)realloc(req, (size_t)max_req * sizeof(RevReq)); req_cap = max_req; }
+            int64_t *req_off = (int64_t *)malloc((size_t)(gn + 1) * sizeof(int64_t));
+            int64_t per = (int64_t)b->M0 + (int64_t)b->M * MB_MAX_LEVELS;
+            int32_t *req_n = (int32_t *)calloc((size_t)gn, sizeof(int32_t));
+#pragma omp parallel for schedule(dynamic, 4) num_threads(nthreads)
+            for (int64_t i = 0; i < gn; i++) {
+#ifdef _OPENMP
+                Scratch *sc = &b->scratch[omp_get_thread_num()];
+#else
+                Scratch *sc = &b->scratch[0];
+#endif
+                int32_t s = (int32_t)(g0 + i);
+                find_links(b, sc, s);
+                RevReq *r = req + i * per;
+                int nr = 0;
+                for (int l = b->level[s] < b->max_level ? b->level[s] : b->max_level; l >= 0; l--) {
+                    int32_t *mycnt;
+                    int32_t *mine = list_ptr(b, s, l, &mycnt);
+                    for (int j = 0; j < sc->sel_cnt[l]; j++) {
+                        int32_t t = sc->sel[(size_t)l * (size_t)b->M0 + j];
+                        list_add(mine, mycnt, t);
+                        r[nr++] = (RevReq){t, l, s};
+                    }
+                }
+                req_n[i] = nr;
+            }
+            /* compact + sort requests by (target, level, src) */
+            int64_t tot = 0;
+            for (int64_t i = 0; i < gn; i++) {
+                if (tot != i * per) memmove(req + tot, req + i * per, (size_t)req_n[i] * sizeof(RevReq));
+                tot += req_n[i];
+            }
+            free(req_off); free(req_n);
+            qsort(req, (size_t)tot, sizeof(RevReq), cmp_req);
+            /* group boundaries per target */
+            if (tot + 1 > grp_cap) { grp = (int64_t *)realloc(grp, (size_t)(tot + 1) * sizeof(int64_t)); grp_cap = tot + 1; }
+            int64_t ng = 0;
+            for (int64_t i = 0; i < tot; i++)
+                if (i == 0 || req[i].target != req[i - 1].target) grp[ng++] = i;
+            grp[ng] = tot;
+            /* phase B: one writer per target list */
+#pragma omp parallel for schedule(dynamic, 16) num_threads(nthreads)
+            for (int64_t gi = 0; gi < ng; gi++) {
+                for (int64_t i = grp[gi]; i < grp[gi + 1]; i++) {
+                    int32_t t = req[i].target; int l = req[i].level;
+                    int M_max = l == 0 ? b->M0 : b->M;
+                    int32_t *tc;
+                    int32_t *tl = list_ptr(b, t, l, &tc);
+                    list_add(tl, tc, req[i].src);
+                    if (*tc > M_max) prune(b, t, l, M_max, 0);
+                }
+            }
+            b->n = g1;
+        }
+        if (raise) {
+            /* the pending node: level already drawn and allocated; insert it exactly */
+            int32_t s = (int32_t)b->n;
+            int lv = b->level[s];
+            /* undo alloc so insert_exact can redo it identically */
+            if (lv > 0) b->n_upper -= lv;
+            insert_exact(b, s, lv);
+            b->n++;
+        }
+    }
+    free(req); free(grp);
+    return 0;
+}
+
+void muninn_build_sizes(void *h, int64_t *n, int64_t *n_lists, int64_t *n_edges, int32_t *entry, int32_t *max_level) {
+    Builder *b = (Builder *)h;
+    int64_t nl = 0, ne = 0;
+    for (int64_t s = 0; s < b->n; s++) {
+        nl += b->level[s] + 1;
+        ne += b->cnt0[s];
+        for (int l = 1; l <= b->level[s]; l++) ne += b->cntU[b->upper_base[s] + l - 1];
+    }
+    *n = b->n; *n_lists = nl; *n_edges = ne; *entry = b->entry; *max_level = b->max_level;
+}
+
+static int cmp_i32(const void *a, const void *b) {
+    int32_t x = *(const int32_t *)a, y = *(const int32_t *)b;
+    return (x > y) - (x < y);
+}
+
+/* Export in the list-CSR layout of include/muninn_cuda.h. sort_lists = 1 gives the
+ * "reloaded from shadow tables" neighbour order (ascending target id,
+ * src/hnsw_vtab.c:163-169 + :322), which is the state the parity contract pins. */
+void muninn_build_export(void *h, int32_t *levels, int64_t *list_offsets, int32_t *targets, int sort_lists) {
+    Builder *b = (Builder *)h;
+    int64_t li = 0, e = 0;
+    list_offsets[0] = 0;
+    for (int64_t s = 0; s < b->n; s++) {
+        levels[s] = b->level[s];
+        for (int l = 0; l <= b->level[s]; l++) {
+            int32_t *cnt;
+            const int32_t *lst = list_ptr(b, (int32_t)s, l, &cnt);
+            memcpy(targets + e, lst, (size_t)*cnt * sizeof(int32_t));
+            if (sort_lists && *cnt > 1) qsort(targets + e, (size_t)*cnt, sizeof(int32_t), cmp_i32);
+            e += *cnt;
+            list_offsets[++li] = e;
+        }
+    }
+}
+
+void muninn_build_destroy(void *h) {
+    Builder *b = (Builder *)h;
+    if (!b) return;
+    for (int t = 0; t < b->n_scratch; t++) {
+        Scratch *sc = &b->scratch[t];
+        free(sc->stamp); free(sc->cand.a); free(sc->res.a); free(sc->r_slot); free(sc->r_dist); free(sc->sel); free(sc->sel_cnt);
+    }
+    free(b->scratch);
+    free(b->level); free(b->nbr0); free(b->cnt0); free(b->upper_base); free(b->nbrU); free(b->cntU);
+    free(b);
+}
