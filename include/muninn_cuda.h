@@ -1,0 +1,146 @@
+/*
+ * muninn_cuda.h — C ABI of libmuninn_cuda: the B200 (sm_100a) implementation of
+ * sqlite-muninn's vector-search hot path.
+ *
+ * Every entry point below replaces, or is the batched form of, one reference interface
+ * (paths relative to /root/reference/):
+ *
+ *   muninn_cuda_index_create / _destroy   hnsw_create / hnsw_destroy         src/hnsw_algo.h:56-59
+ *   muninn_cuda_index_upload              load_index_from_shadow             src/hnsw_vtab.c:286-341
+ *   muninn_cuda_search_batch              hnsw_search, called at             src/hnsw_vtab.c:604
+ *                                         (signature src/hnsw_algo.h:73), for nq queries at once
+ *   muninn_cuda_search_batch_device       same, device-resident queries/results (benchmark `value`)
+ *   muninn_cuda_exact_knn                 brute_force_knn test helper        test/test_hnsw_algo.c:10-34
+ *   muninn_cuda_distance_batch            vec_get_distance_func(metric)(a,b) src/vec_math.c:180-190
+ *   muninn_cuda_parse_metric              vec_parse_metric                   src/vec_math.c:192-204
+ *
+ * Plain C types only: pointers, sizes and ints.  No CPU fallback exists anywhere in the
+ * library: without a CUDA device every compute entry point returns MUNINN_CUDA_E_NODEVICE.
+ *
+ * Threading: entry points are not re-entrant on one handle (the reference has no locks
+ * either; SQLite serialises calls on a connection).  Separate handles are
+ * independent.  Multi-GPU = one process (or at least one handle) per device.
+ */
+#ifndef MUNINN_CUDA_H
+#define MUNINN_CUDA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* VecMetric, src/vec_math.h:13-16 — the integer stored in the _config shadow table */
+enum { MUNINN_METRIC_L2 = 0, MUNINN_METRIC_COSINE = 1, MUNINN_METRIC_INNER_PRODUCT = 2 };
+
+enum {
+    MUNINN_CUDA_OK = 0,
+    MUNINN_CUDA_E_ARG = -1,      /* bad argument (message in muninn_cuda_last_error) */
+    MUNINN_CUDA_E_NODEVICE = -2, /* no usable CUDA device */
+    MUNINN_CUDA_E_CUDA = -3,     /* a CUDA runtime call failed */
+    MUNINN_CUDA_E_NOMEM = -4,    /* host or device allocation failed */
+    MUNINN_CUDA_E_STATE = -5     /* e.g. search before upload */
+};
+
+typedef struct MuninnCudaIndex MuninnCudaIndex;
+
+/* Per-query work counters. n_dist / n_expand are deterministic functions of (graph, query,
+ * ef) and must equal the CPU oracle's; they also define the algorithmic
+ * bytes of the roofline. Layout matches oracle/hnsw_oracle.c OrcStats. */
+typedef struct {
+    int64_t n_dist;         /* distance evaluations the reference would make (dist_func calls) */
+    int64_t n_dist_upper;   /* of which in the greedy descent, src/hnsw_algo.c:257-282 */
+    int32_t n_expand;       /* layer-0 candidates whose neighbour lists were scanned */
+    int32_t n_greedy_steps; /* neighbour lists (re)scanned in the descent */
+    int32_t term;           /* 0 candidates exhausted, 1 distance bound, 2 patience (src/hnsw_algo.c:382-392) */
+    int32_t entry0;         /* slot at which the descent handed over to the layer-0 beam */
+} MuninnSearchStats;
+
+int muninn_cuda_device_count(void);
+const char *muninn_cuda_version(void);
+const char *muninn_cuda_strerror(int code);
+/* "l2" | "cosine" | "inner_product" → metric, else -1 (vec_parse_metric). Host-only. */
+int muninn_cuda_parse_metric(const char *name);
+
+/* hnsw_create: dim, metric, M as in `CREATE VIRTUAL TABLE … USING hnsw_index(dimensions, metric, m, …)`.
+ * M_max0 = 2*M (src/hnsw_algo.c:188). `device` is the CUDA ordinal. */
+int muninn_cuda_index_create(int device, int dim, int metric, int M, MuninnCudaIndex **out);
+void muninn_cuda_index_destroy(MuninnCudaIndex *idx);
+/* Message of the last failure on this handle ("" if none). NULL handle → last create failure. */
+const char *muninn_cuda_last_error(const MuninnCudaIndex *idx);
+
+/*
+ * Upload the graph exactly as load_index_from_shadow leaves it in host memory:
+ *   n             stored rows of <name>_nodes, deleted ones included
+ *   ids[n]        rowids, strictly ascending; the dense "slot" of a node is its rank here
+ *   levels[n]     _nodes.level
+ *   deleted[n]    _nodes.deleted (may be NULL = none)
+ *   vectors       [n × dim] fp32, row-major, packed
+ *   list_offsets  [L+1], L = Σ(levels[s]+1): lists are node-major, level-minor — list
+ *                 (s, l) has index first(s)+l with first(s) = Σ_{t<s}(levels[t]+1)
+ *   targets       slot per edge, in shadow-table order (ascending target_id within a list,
+ *                 src/hnsw_vtab.c:163-169,322); -1 for an edge whose target row is missing
+ *   entry_slot    slot of _config.entry_point, or -1 for an empty index
+ *   max_level     _config.max_level
+ * Device layout built from it: packed fp32 slab (row stride padded to 4 floats), layer-0
+ * neighbour table [n × 2M] int32 (-1 padded), upper-layer lists [·× M], per-row squared
+ * norms for cosine. A second upload replaces the first (the vtab's dirty-flag re-upload).
+ */
+int muninn_cuda_index_upload(MuninnCudaIndex *idx, int64_t n, const int64_t *ids, const int32_t *levels,
+                             const uint8_t *deleted, const float *vectors, const int64_t *list_offsets,
+                             const int32_t *targets, int32_t entry_slot, int32_t max_level);
+
+/*
+ * Batched hnsw_search. Host buffers; the call copies queries to the device, runs the
+ * search kernel, copies results back and returns when they are in place.
+ *   queries   [nq × dim] fp32
+ *   k, ef     as hnsw_search; ef = max(ef, k) is applied here (src/hnsw_algo.c:673). The
+ *             vtab's default ef = 2k (src/hnsw_vtab.c:591) stays in the vtab.
+ *   out_ids   [nq × k] rowids ascending by distance; unused tail = -1
+ *   out_dist  [nq × k] fp32 distances (L2 is squared, as in the reference); unused tail = 0
+ *   out_count [nq] number of results per query (may be < k; 0 for an empty index)
+ *   out_stats [nq] or NULL
+ */
+int muninn_cuda_search_batch(MuninnCudaIndex *idx, const float *queries, int nq, int k, int ef, int64_t *out_ids,
+                             float *out_dist, int32_t *out_count, MuninnSearchStats *out_stats);
+
+/* Same, all buffers device-resident on the handle's device; asynchronous on the handle's
+ * stream (muninn_cuda_set_stream), no host synchronisation. d_stats may be NULL. */
+int muninn_cuda_search_batch_device(MuninnCudaIndex *idx, const float *d_queries, int nq, int k, int ef,
+                                    int64_t *d_ids, float *d_dist, int32_t *d_count, MuninnSearchStats *d_stats);
+
+/* Stream on which the handle launches (a cudaStream_t passed as void*; NULL = the handle's own). */
+int muninn_cuda_set_stream(MuninnCudaIndex *idx, void *stream);
+/* Device time of the handle's most recent search kernel, from CUDA events recorded around
+ * the launch on its stream (synchronises on the end event). < 0 if none. */
+float muninn_cuda_last_kernel_ms(MuninnCudaIndex *idx);
+/* Number of kernels this handle has launched since creation (bench.py's gpu_launches). */
+int64_t muninn_cuda_launch_count(const MuninnCudaIndex *idx);
+/* Launch geometry knobs for tuning: warps cooperating on one query (1, 2 or 4) and query
+ * teams resident per SM (0 = automatic). Results do not depend on them. */
+int muninn_cuda_set_tuning(MuninnCudaIndex *idx, int warps_per_query, int teams_per_sm);
+
+/*
+ * Exact k-NN over the uploaded rows of this handle (deleted rows skipped), reference
+ * distance arithmetic, output ascending by (distance, row index) — the tie rule of
+ * test/test_hnsw_algo.c:10-34. out_idx holds ROW INDICES (slots) + index_base, not rowids,
+ * so a base sharded over several handles merges by plain comparison.
+ */
+int muninn_cuda_exact_knn(MuninnCudaIndex *idx, const float *queries, int nq, int k, int64_t index_base,
+                          int64_t *out_idx, float *out_dist, int32_t *out_count);
+int muninn_cuda_exact_knn_device(MuninnCudaIndex *idx, const float *d_queries, int nq, int k, int64_t index_base,
+                                 int64_t *d_idx, float *d_dist, int32_t *d_count);
+/* Merge `parts` per-shard result lists ([parts × nq × k], as gathered by ncclAllGather) into
+ * the global top-k under the same (distance, index) order. Device buffers. */
+int muninn_cuda_topk_merge_device(MuninnCudaIndex *idx, int parts, int nq, int k, const int64_t *d_idx_parts,
+                                  const float *d_dist_parts, const int32_t *d_count_parts, int64_t *d_idx,
+                                  float *d_dist, int32_t *d_count);
+
+/* n distances metric(a[i], b[i]) with the reference's summation order (src/vec_math.c:78-143).
+ * Host buffers [n × dim]; used by the known-answer tests of test/test_vec_math.c. */
+int muninn_cuda_distance_batch(int device, int metric, int dim, int64_t n, const float *a, const float *b, float *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MUNINN_CUDA_H */

@@ -54,6 +54,9 @@ class Oracle:
         L.orc_graph_destroy.argtypes = [C.c_void_p]
         L.orc_search.restype = C.c_double
         L.orc_search.argtypes = [C.c_void_p, _f32, C.c_int, C.c_int, C.c_int, C.c_int, _i64, _f32, _i32, C.c_void_p]
+        L.orc_search_mode.restype = C.c_double
+        L.orc_search_mode.argtypes = [C.c_void_p, _f32, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _i64, _f32, _i32,
+                                      C.c_void_p]
         L.orc_exact_knn.restype = C.c_double
         L.orc_exact_knn.argtypes = [_f32, C.c_void_p, C.c_int64, C.c_int, C.c_int, _f32, C.c_int, C.c_int, C.c_int,
                                     _i64, _f32, _i32]
@@ -100,7 +103,9 @@ class OracleGraph:
         self.h = orc.L.orc_graph_create(g.dim, g.metric, g.M, g.n, g.ids, g.levels, g.deleted, g.vectors,
                                         g.list_offsets, g.targets, g.entry_slot, g.max_level)
 
-    def search(self, queries, k: int, ef: int, threads: int = 1, want_stats: bool = True):
+    def search(self, queries, k: int, ef: int, threads: int = 1, want_stats: bool = True, canonical: bool = False):
+        """canonical=False: the reference's two-heap loop (pinned against the real reference);
+        canonical=True: the (distance, slot)-ordered list the CUDA kernel is specified to follow."""
         q = np.ascontiguousarray(queries, np.float32)
         nq = q.shape[0]
         ids = np.empty((nq, k), np.int64)
@@ -108,7 +113,7 @@ class OracleGraph:
         cnt = np.empty(nq, np.int32)
         stats = np.zeros(nq, STATS_DTYPE) if want_stats else None
         sp = stats.ctypes.data_as(C.c_void_p) if want_stats else None
-        secs = self.orc.L.orc_search(self.h, q, nq, k, ef, threads, ids, dist, cnt, sp)
+        secs = self.orc.L.orc_search_mode(self.h, q, nq, k, ef, threads, 1 if canonical else 0, ids, dist, cnt, sp)
         return ids, dist, cnt, stats, secs
 
     def close(self):

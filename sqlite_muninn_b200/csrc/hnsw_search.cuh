@@ -1,0 +1,351 @@
+/*
+ * hnsw_search.cuh — batched HNSW search kernel for sm_100a.
+ *
+ * Restates, per query, the reference's hnsw_search (src/hnsw_algo.c:670-704):
+ *   greedy_search_layer  src/hnsw_algo.c:257-282   list-order hill climb with the in-loop switch
+ *   beam_search_layer    src/hnsw_algo.c:347-448   ef-bounded best-first search + patience rule
+ *   distances            src/vec_math.c:78-143     bit-exact summation order
+ *
+ * Execution model (B200): a persistent grid of query teams. A team is one warp (one CTA) that
+ * pulls query indices from a global counter until the batch is drained, so long and short
+ * searches balance across the 148 SMs. Per team, in shared memory: the query, the result list
+ * R (ef entries, ascending (distance, slot) 64-bit keys, bit 0 = "expanded"), and a 4 KB
+ * staging tile for the distance transposition. Per team, in HBM: an open-addressing visited
+ * table of 64-bit (epoch, slot) entries; entries of older epochs read as empty, so the table
+ * is never cleared between queries.
+ *
+ * Distances: for a batch of up to 8 neighbour rows the 32 lanes load one 16-byte chunk of
+ * every row each (fully coalesced 512 B per row at dim 128, eight independent 128-bit loads
+ * in flight per lane), form the per-component products, and transpose them through shared
+ * memory so that lane (n, j) adds chain j of row n in ascending element order — the exact
+ * order of the reference's SSE loop — before the fixed ((s0+s1)+s2)+s3 horizontal sum.
+ *
+ * Result-set semantics ("canonical order"): R' = the ef smallest of R ∪ F under
+ * (distance, slot); next candidate = smallest unexpanded entry of R. On inputs without
+ * bit-equal distances this is exactly the reference's two-heap loop (SURVEY.md finding 4);
+ * with ties the reference's order is heap-dependent and unspecified (test_priority_queue.c:85-99).
+ */
+#pragma once
+#include "muninn_dev.cuh"
+#include "../../include/muninn_cuda.h"
+
+namespace muninn {
+
+constexpr int DB = 8;             /* neighbour rows per distance batch */
+constexpr int PSTRIDE = 128 + 4;  /* floats per staged row: 32 chunks + 4 pad → conflict-free transposed reads */
+constexpr int MAX_M0 = 128;       /* layer-0 list capacity supported (M ≤ 64) */
+
+struct SearchParams {
+    /* graph */
+    const float *vec; const float *norm2; const int32_t *nbr0; const int32_t *upper_base; const int32_t *nbrU;
+    const uint8_t *deleted; const int64_t *ids;
+    int dim, ld, M, M0, entry_slot, max_level;
+    long long n_live;
+    /* batch */
+    const float *queries; int nq, k, ef, patience_max;
+    int64_t *out_ids; float *out_dist; int32_t *out_count; MuninnSearchStats *stats;
+    /* work lists: level 0 processes queries 0..nq-1; level>0 processes in_list[0..*in_count) */
+    const int *in_list; const int *in_count; int *out_list; int *out_count_retry; int *work_counter;
+    /* visited tables */
+    unsigned long long *vis; unsigned vis_shift; unsigned vis_cap; unsigned epoch_base;
+};
+
+struct TeamSmem {
+    unsigned long long *R;   /* [ef] */
+    unsigned long long *Fk;  /* [MAX_M0] keys of this expansion's fresh neighbours */
+    unsigned long long *S;   /* [32] survivors being merged */
+    float *q;                /* [ld] */
+    float *P;                /* [DB * PSTRIDE] */
+    int *Fs;                 /* [MAX_M0] fresh slots */
+};
+
+__host__ __device__ inline size_t search_smem_bytes(int ef, int ld) {
+    size_t b = (size_t)ef * 8 + (size_t)MAX_M0 * 8 + 32 * 8;
+    b += ((size_t)ld * 4 + 15) / 16 * 16;
+    b += (size_t)DB * PSTRIDE * 4;
+    b += (size_t)MAX_M0 * 4;
+    return b;
+}
+
+/*
+ * Distances from the staged query to up to DB rows. bs[0..nb) are slots (shared memory).
+ * Every lane returns the distance of row (lane >> 2) (garbage if that row index ≥ nb).
+ */
+template <int METRIC>
+__device__ __forceinline__ float warp_dist_batch(const SearchParams &p, const TeamSmem &sm, const int *bs, int nb,
+                                                 float q_norm2, int lane) {
+    const int cpr = p.ld >> 2, cfull = p.dim >> 2, rem = p.dim & 3;
+    const int n_me = lane >> 2, j_me = lane & 3;
+    float s = 0.0f, tailv = 0.0f;
+    for (int t0 = 0; t0 < cpr; t0 += 32) {
+        const int c = t0 + lane;
+        float4 x[DB];
+        if (c < cpr) {
+#pragma unroll
+            for (int n = 0; n < DB; n++)
+                if (n < nb) x[n] = ldg_stream_f4(p.vec + (size_t)bs[n] * (size_t)p.ld + 4 * c);
+            const float4 qv = *reinterpret_cast<const float4 *>(sm.q + 4 * c);
+#pragma unroll
+            for (int n = 0; n < DB; n++)
+                if (n < nb) *reinterpret_cast<float4 *>(sm.P + n * PSTRIDE + 4 * lane) = prod4<METRIC>(qv, x[n]);
+        }
+        __syncwarp();
+        int tfull = cfull - t0;
+        tfull = tfull > 32 ? 32 : tfull;
+        if (n_me < nb) {
+            const float *row = sm.P + n_me * PSTRIDE + j_me;
+#pragma unroll 8
+            for (int cc = 0; cc < tfull; cc++) s = __fadd_rn(s, row[4 * cc]);
+            if (rem && cfull >= t0 && cfull < t0 + 32 && j_me < rem) tailv = row[4 * (cfull - t0)];
+        }
+        __syncwarp();
+    }
+    const int g = lane & ~3;
+    float s0 = __shfl_sync(FULL, s, g), s1 = __shfl_sync(FULL, s, g + 1), s2 = __shfl_sync(FULL, s, g + 2),
+          s3 = __shfl_sync(FULL, s, g + 3);
+    float sum = __fadd_rn(__fadd_rn(__fadd_rn(s0, s1), s2), s3);
+    if (rem) {
+        float t0v = __shfl_sync(FULL, tailv, g), t1v = __shfl_sync(FULL, tailv, g + 1),
+              t2v = __shfl_sync(FULL, tailv, g + 2);
+        sum = __fadd_rn(sum, t0v);
+        if (rem > 1) sum = __fadd_rn(sum, t1v);
+        if (rem > 2) sum = __fadd_rn(sum, t2v);
+    }
+    if (METRIC == METRIC_L2) return sum;
+    if (METRIC == METRIC_IP) return -sum;
+    float nb2 = (n_me < nb) ? p.norm2[bs[n_me]] : 1.0f;
+    return cosine_finish(sum, q_norm2, nb2);
+}
+
+/* Σ q_i² in chain order: the `norm_a` accumulator of vec_cosine_distance (src/vec_math.c:104-118) */
+__device__ __forceinline__ float query_norm2(const float *q, int dim) {
+    return chained_sum_serial<METRIC_IP>(q, q, dim);
+}
+
+/* visited test-and-set for one neighbour per lane; returns 1 if the slot was not yet visited.
+ * The table is private to the team: plain L2-level loads/stores, intra-warp claim conflicts
+ * resolved with match.any. */
+__device__ __forceinline__ int visited_test_and_set(const SearchParams &p, unsigned long long *tab, unsigned epoch,
+                                                    int t, bool valid, int lane) {
+    unsigned h = ((unsigned)t * 2654435761u) >> p.vis_shift;
+    const unsigned mask = p.vis_cap - 1;
+    bool active = valid;
+    int fresh = 0;
+    const unsigned long long mine = ((unsigned long long)epoch << 32) | (unsigned)t;
+    while (__any_sync(FULL, active)) {
+        unsigned long long e = active ? __ldcg(tab + h) : 0ull;
+        bool cur = (unsigned)(e >> 32) == epoch;
+        bool claim = false;
+        if (active) {
+            if (cur) {
+                if ((unsigned)e == (unsigned)t) active = false; /* already visited */
+                else h = (h + 1) & mask;
+            } else claim = true;
+        }
+        unsigned cm = __ballot_sync(FULL, claim);
+        if (claim) {
+            unsigned peers = __match_any_sync(cm, h);
+            if ((__ffs(peers) - 1) == lane) {
+                __stcg(tab + h, mine);
+                fresh = 1;
+                active = false;
+            } else h = (h + 1) & mask;
+        }
+        __syncwarp();
+    }
+    return fresh;
+}
+
+template <int METRIC>
+__global__ void __launch_bounds__(32) hnsw_search_kernel(const SearchParams p, const int level) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x;
+    TeamSmem sm;
+    {
+        unsigned char *b = smem_raw;
+        sm.R = reinterpret_cast<unsigned long long *>(b); b += (size_t)p.ef * 8;
+        sm.Fk = reinterpret_cast<unsigned long long *>(b); b += (size_t)MAX_M0 * 8;
+        sm.S = reinterpret_cast<unsigned long long *>(b); b += 32 * 8;
+        sm.q = reinterpret_cast<float *>(b); b += ((size_t)p.ld * 4 + 15) / 16 * 16;
+        sm.P = reinterpret_cast<float *>(b); b += (size_t)DB * PSTRIDE * 4;
+        sm.Fs = reinterpret_cast<int *>(b);
+    }
+    unsigned long long *tab = p.vis + (size_t)blockIdx.x * (size_t)p.vis_cap;
+    const int nwork = level == 0 ? p.nq : *p.in_count;
+    const int ef = p.ef;
+
+    for (;;) {
+        int w = 0;
+        if (lane == 0) w = atomicAdd(p.work_counter, 1);
+        w = __shfl_sync(FULL, w, 0);
+        if (w >= nwork) break;
+        const int qi = level == 0 ? w : p.in_list[w];
+        /* unique per (launch chain, retry level, query): a retry re-lays the arena out with a
+         * larger capacity, so it must not recognise entries its level-0 attempt wrote */
+        const unsigned epoch = p.epoch_base + (unsigned)level * (unsigned)p.nq + (unsigned)qi + 1u;
+
+        /* stage the query (pad lanes to the 4-float row stride with zeros) */
+        const float *qg = p.queries + (size_t)qi * (size_t)p.dim;
+        for (int i = lane; i < p.ld; i += 32) sm.q[i] = i < p.dim ? qg[i] : 0.0f;
+        __syncwarp();
+        float qn2 = 0.0f;
+        if (METRIC == METRIC_COSINE) qn2 = query_norm2(sm.q, p.dim);
+
+        long long n_dist = 0, n_dist_upper = 0;
+        int n_expand = 0, n_greedy = 0, term = 0, entry0 = -1, size = 0;
+        bool overflow = false;
+
+        if (p.entry_slot >= 0 && p.n_live > 0) {
+            /* ── greedy descent, levels max_level..1 (src/hnsw_algo.c:679-681, :257-282) ── */
+            int cur = p.entry_slot;
+            if (lane == 0) sm.Fs[0] = cur;
+            __syncwarp();
+            float cur_d = __shfl_sync(FULL, warp_dist_batch<METRIC>(p, sm, sm.Fs, 1, qn2, lane), 0);
+            __syncwarp();
+            for (int l = p.max_level; l > 0; l--) {
+                n_dist++; n_dist_upper++; /* the reference re-evaluates the entry at every level (:262) */
+                bool changed = true;
+                while (changed) {
+                    changed = false;
+                    n_greedy++;
+                    int i0 = 0;
+                    /* scan positions i0.. of cur's list in order, DB valid entries at a time; on
+                     * the first improvement switch node and keep counting positions (:267-279) */
+                    for (;;) {
+                        const int32_t *lst = p.nbrU + ((size_t)p.upper_base[cur] + (size_t)(l - 1)) * (size_t)p.M;
+                        /* gather up to DB valid entries at positions ≥ i0 */
+                        int nb = 0, last_pos = p.M;
+                        for (int base = i0; base < p.M && nb < DB; base += 32) {
+                            int pos = base + lane;
+                            int t = pos < p.M ? lst[pos] : -1;
+                            unsigned vm = __ballot_sync(FULL, t >= 0);
+                            int r = __popc(vm & ((1u << lane) - 1));
+                            if (t >= 0 && nb + r < DB) { sm.Fs[nb + r] = t; sm.Fs[MAX_M0 / 2 + nb + r] = pos; }
+                            nb += __popc(vm);
+                        }
+                        if (nb > DB) nb = DB;
+                        __syncwarp();
+                        if (nb == 0) break;
+                        last_pos = sm.Fs[MAX_M0 / 2 + nb - 1];
+                        float d = warp_dist_batch<METRIC>(p, sm, sm.Fs, nb, qn2, lane);
+                        bool better = (lane & 3) == 0 && (lane >> 2) < nb && d < cur_d; /* strict, :274 */
+                        unsigned bm = __ballot_sync(FULL, better);
+                        if (bm) {
+                            int src = __ffs(bm) - 1, j = src >> 2;
+                            n_dist += j + 1; n_dist_upper += j + 1;
+                            cur_d = __shfl_sync(FULL, d, src);
+                            cur = sm.Fs[j];
+                            i0 = sm.Fs[MAX_M0 / 2 + j] + 1;
+                            changed = true;
+                            n_greedy++;
+                        } else {
+                            n_dist += nb; n_dist_upper += nb;
+                            i0 = last_pos + 1;
+                        }
+                        __syncwarp();
+                        if (i0 >= p.M) break;
+                    }
+                }
+            }
+            entry0 = cur;
+
+            /* ── layer-0 beam (src/hnsw_algo.c:347-448) ── */
+            if (!p.deleted[cur]) { /* a deleted entry seeds nothing (:358-366) */
+                n_dist++;
+                if (lane == 0) sm.R[0] = make_key(cur_d, (unsigned)cur << 1);
+                size = 1;
+                visited_test_and_set(p, tab, epoch, cur, lane == 0, lane);
+                __syncwarp();
+                int stale = 0, lb = 0, n_ins = 1, evicted_open = 0;
+                for (;;) {
+                    /* closest unexpanded entry of R */
+                    int pos = -1;
+                    for (int base = lb & ~31; base < size; base += 32) {
+                        int idx = base + lane;
+                        bool open = idx < size && idx >= lb && !(sm.R[idx] & 1ull);
+                        unsigned om = __ballot_sync(FULL, open);
+                        if (om) { pos = base + __ffs(om) - 1; break; }
+                    }
+                    if (pos < 0) { term = (size >= ef && evicted_open) ? 1 : 0; break; }
+                    if (stale >= p.patience_max && size >= ef) { term = 2; break; } /* :391-392 */
+                    const int c = (int)((unsigned)sm.R[pos] >> 1);
+                    __syncwarp();
+                    if (lane == 0) sm.R[pos] |= 1ull;
+                    lb = pos + 1;
+                    n_expand++;
+                    if ((unsigned)(n_ins + p.M0) > (p.vis_cap >> 1)) { overflow = true; break; }
+
+                    /* neighbour list → visited filter → fresh slots */
+                    int nf = 0;
+                    const int32_t *lst = p.nbr0 + (size_t)c * (size_t)p.M0;
+                    for (int base = 0; base < p.M0; base += 32) {
+                        int pos0 = base + lane;
+                        int t = pos0 < p.M0 ? lst[pos0] : -1;
+                        int fresh = visited_test_and_set(p, tab, epoch, t, t >= 0, lane);
+                        unsigned fm = __ballot_sync(FULL, fresh);
+                        if (fresh) sm.Fs[nf + __popc(fm & ((1u << lane) - 1))] = t;
+                        nf += __popc(fm);
+                    }
+                    n_ins += nf;
+                    n_dist += nf;
+                    __syncwarp();
+                    /* distances */
+                    for (int b0 = 0; b0 < nf; b0 += DB) {
+                        int nb = nf - b0 < DB ? nf - b0 : DB;
+                        float d = warp_dist_batch<METRIC>(p, sm, sm.Fs + b0, nb, qn2, lane);
+                        if ((lane & 3) == 0 && (lane >> 2) < nb)
+                            sm.Fk[b0 + (lane >> 2)] = make_key(d, (unsigned)sm.Fs[b0 + (lane >> 2)] << 1);
+                    }
+                    __syncwarp();
+                    /* R ← ef smallest of R ∪ F */
+                    bool improved = false;
+                    for (int base = 0; base < nf; base += 32) {
+                        unsigned long long worst = size >= ef ? sm.R[ef - 1] : KEY_NONE;
+                        unsigned long long f = base + lane < nf ? sm.Fk[base + lane] : KEY_NONE;
+                        bool keep = f < worst;
+                        unsigned km = __ballot_sync(FULL, keep);
+                        int ns = __popc(km);
+                        if (ns == 0) continue;
+                        improved = true;
+                        if (keep) sm.S[__popc(km & ((1u << lane) - 1))] = f;
+                        __syncwarp();
+                        int mp;
+                        size = warp_merge_sorted(sm.R, size, ef, sm.S, ns, lane, &mp, &evicted_open);
+                        lb = mp < lb ? mp : lb;
+                    }
+                    stale = improved ? 0 : stale + 1; /* :428-432 */
+                }
+            }
+        }
+
+        if (overflow) {
+            /* visited table too small for this query: hand it to the next, larger level */
+            if (lane == 0) p.out_list[atomicAdd(p.out_count_retry, 1)] = qi;
+            continue;
+        }
+        /* results: first min(size, k) of R (src/hnsw_algo.c:695-699) */
+        const int cnt = size < p.k ? size : p.k;
+        for (int i = lane; i < p.k; i += 32) {
+            int64_t id = -1; float d = 0.0f;
+            if (i < cnt) {
+                unsigned long long e = sm.R[i];
+                id = p.ids[(unsigned)e >> 1];
+                d = okey_inv((unsigned)(e >> 32));
+            }
+            p.out_ids[(size_t)qi * p.k + i] = id;
+            p.out_dist[(size_t)qi * p.k + i] = d;
+        }
+        if (lane == 0) {
+            p.out_count[qi] = cnt;
+            if (p.stats) {
+                MuninnSearchStats st;
+                st.n_dist = n_dist; st.n_dist_upper = n_dist_upper; st.n_expand = n_expand;
+                st.n_greedy_steps = n_greedy; st.term = term; st.entry0 = entry0;
+                p.stats[qi] = st;
+            }
+        }
+        __syncwarp();
+    }
+}
+
+} // namespace muninn

@@ -1,0 +1,542 @@
+/*
+ * muninn_cuda.cu — libmuninn_cuda: handle management, graph upload and the C ABI declared in
+ * include/muninn_cuda.h. Kernels live in hnsw_search.cuh and exact_knn.cuh.
+ *
+ * Upload mirrors what load_index_from_shadow (/root/reference/src/hnsw_vtab.c:286-341) leaves
+ * in host memory, re-laid out for the device:
+ *   vec        [n × ld] fp32, ld = dim rounded up to 4 (16-byte rows for 128-bit gathers)
+ *   nbr0       [n × 2M] int32 layer-0 neighbour slots, -1 padded; a deleted or missing target
+ *              is stored as -1 in place (the reference skips both, src/hnsw_algo.c:270,408)
+ *   upper_base [n] first upper-layer list of a node (or -1); nbrU [lists × M], same convention
+ *   norm2      [n] Σx² in the reference's summation order (cosine only)
+ * There is no CPU path: without a device every entry point fails with MUNINN_CUDA_E_NODEVICE.
+ */
+#include "../../include/muninn_cuda.h"
+#include "exact_knn.cuh"
+#include "hnsw_search.cuh"
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace muninn;
+
+struct MuninnCudaIndex {
+    int device = 0, dim = 0, ld = 0, metric = 0, M = 0, M0 = 0;
+    long long n = 0, n_live = 0;
+    int entry_slot = -1, max_level = -1;
+    bool uploaded = false;
+    /* device graph */
+    float *d_vec = nullptr, *d_norm2 = nullptr;
+    int32_t *d_nbr0 = nullptr, *d_upper_base = nullptr, *d_nbrU = nullptr;
+    uint8_t *d_deleted = nullptr;
+    int64_t *d_ids = nullptr;
+    /* launch state */
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool have_timing = false;
+    int num_sms = 0, teams_per_sm = 0, warps_per_query = 1;
+    int64_t launches = 0;
+    unsigned epoch_base = 0;
+    unsigned long long *d_vis = nullptr; size_t vis_entries = 0;
+    int *d_ctl = nullptr;        /* [8]: work counters ×3, retry counts ×2 */
+    int *d_retry = nullptr; size_t retry_cap = 0; /* 2 × nq */
+    /* staging for the host-buffer entry points */
+    void *d_stage = nullptr; size_t stage_bytes = 0;
+    void *h_pinned = nullptr; size_t pinned_bytes = 0;
+    /* exact k-NN scratch */
+    float *d_panel = nullptr; size_t panel_floats = 0;
+    unsigned long long *d_topk = nullptr; int *d_topk_size = nullptr; size_t topk_cap = 0, topk_q = 0;
+    std::string err;
+};
+
+static thread_local std::string g_create_err;
+
+static int fail(MuninnCudaIndex *h, int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (h) h->err = buf; else g_create_err = buf;
+    return code;
+}
+
+#define CK(h, call)                                                                                       \
+    do {                                                                                                  \
+        cudaError_t e_ = (call);                                                                          \
+        if (e_ != cudaSuccess)                                                                            \
+            return fail(h, e_ == cudaErrorMemoryAllocation ? MUNINN_CUDA_E_NOMEM : MUNINN_CUDA_E_CUDA,    \
+                        "%s: %s", #call, cudaGetErrorString(e_));                                        \
+    } while (0)
+
+extern "C" int muninn_cuda_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+extern "C" const char *muninn_cuda_version(void) { return "muninn-b200 0.1 (sm_100a)"; }
+
+extern "C" const char *muninn_cuda_strerror(int code) {
+    switch (code) {
+    case MUNINN_CUDA_OK: return "ok";
+    case MUNINN_CUDA_E_ARG: return "invalid argument";
+    case MUNINN_CUDA_E_NODEVICE: return "no CUDA device";
+    case MUNINN_CUDA_E_CUDA: return "CUDA runtime error";
+    case MUNINN_CUDA_E_NOMEM: return "out of memory";
+    case MUNINN_CUDA_E_STATE: return "index not uploaded";
+    }
+    return "unknown error";
+}
+
+/* vec_parse_metric, /root/reference/src/vec_math.c:192-204 */
+extern "C" int muninn_cuda_parse_metric(const char *name) {
+    if (!name) return -1;
+    if (!strcmp(name, "l2")) return MUNINN_METRIC_L2;
+    if (!strcmp(name, "cosine")) return MUNINN_METRIC_COSINE;
+    if (!strcmp(name, "inner_product")) return MUNINN_METRIC_INNER_PRODUCT;
+    return -1;
+}
+
+extern "C" const char *muninn_cuda_last_error(const MuninnCudaIndex *h) {
+    return h ? h->err.c_str() : g_create_err.c_str();
+}
+
+static void free_graph(MuninnCudaIndex *h) {
+    cudaFree(h->d_vec); cudaFree(h->d_norm2); cudaFree(h->d_nbr0); cudaFree(h->d_upper_base);
+    cudaFree(h->d_nbrU); cudaFree(h->d_deleted); cudaFree(h->d_ids);
+    h->d_vec = h->d_norm2 = nullptr; h->d_nbr0 = h->d_upper_base = h->d_nbrU = nullptr;
+    h->d_deleted = nullptr; h->d_ids = nullptr;
+    h->uploaded = false;
+}
+
+extern "C" int muninn_cuda_index_create(int device, int dim, int metric, int M, MuninnCudaIndex **out) {
+    if (!out) return fail(nullptr, MUNINN_CUDA_E_ARG, "out is NULL");
+    *out = nullptr;
+    if (dim < 1) return fail(nullptr, MUNINN_CUDA_E_ARG, "dimensions must be >= 1 (got %d)", dim);
+    if (metric < 0 || metric > 2) return fail(nullptr, MUNINN_CUDA_E_ARG, "unknown metric %d", metric);
+    if (M < 2 || 2 * M > MAX_M0) return fail(nullptr, MUNINN_CUDA_E_ARG, "m must be in [2, %d] (got %d)", MAX_M0 / 2, M);
+    int ndev = muninn_cuda_device_count();
+    if (ndev <= 0) return fail(nullptr, MUNINN_CUDA_E_NODEVICE, "no CUDA device visible; libmuninn_cuda has no CPU path");
+    if (device < 0 || device >= ndev) return fail(nullptr, MUNINN_CUDA_E_ARG, "device %d out of range (0..%d)", device, ndev - 1);
+    MuninnCudaIndex *h = new (std::nothrow) MuninnCudaIndex();
+    if (!h) return fail(nullptr, MUNINN_CUDA_E_NOMEM, "host allocation failed");
+    h->device = device; h->dim = dim; h->ld = (dim + 3) & ~3; h->metric = metric; h->M = M; h->M0 = 2 * M;
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
+    if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device);
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_ctl, 8 * sizeof(int));
+    if (e != cudaSuccess) {
+        int rc = fail(nullptr, MUNINN_CUDA_E_CUDA, "device %d setup: %s", device, cudaGetErrorString(e));
+        delete h;
+        return rc;
+    }
+    h->stream = h->own_stream;
+    *out = h;
+    return MUNINN_CUDA_OK;
+}
+
+extern "C" void muninn_cuda_index_destroy(MuninnCudaIndex *h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    free_graph(h);
+    cudaFree(h->d_vis); cudaFree(h->d_ctl); cudaFree(h->d_retry); cudaFree(h->d_stage);
+    cudaFree(h->d_panel); cudaFree(h->d_topk); cudaFree(h->d_topk_size);
+    if (h->h_pinned) cudaFreeHost(h->h_pinned);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->own_stream) cudaStreamDestroy(h->own_stream);
+    delete h;
+}
+
+extern "C" int muninn_cuda_set_stream(MuninnCudaIndex *h, void *stream) {
+    if (!h) return MUNINN_CUDA_E_ARG;
+    h->stream = stream ? (cudaStream_t)stream : h->own_stream;
+    return MUNINN_CUDA_OK;
+}
+
+extern "C" int64_t muninn_cuda_launch_count(const MuninnCudaIndex *h) { return h ? h->launches : 0; }
+
+extern "C" int muninn_cuda_set_tuning(MuninnCudaIndex *h, int warps_per_query, int teams_per_sm) {
+    if (!h) return MUNINN_CUDA_E_ARG;
+    if (warps_per_query != 1) return fail(h, MUNINN_CUDA_E_ARG, "warps_per_query %d not supported (1)", warps_per_query);
+    if (teams_per_sm < 0 || teams_per_sm > 32) return fail(h, MUNINN_CUDA_E_ARG, "teams_per_sm must be in [0, 32]");
+    h->warps_per_query = warps_per_query;
+    h->teams_per_sm = teams_per_sm;
+    return MUNINN_CUDA_OK;
+}
+
+extern "C" float muninn_cuda_last_kernel_ms(MuninnCudaIndex *h) {
+    if (!h || !h->have_timing) return -1.0f;
+    cudaSetDevice(h->device);
+    if (cudaEventSynchronize(h->ev1) != cudaSuccess) return -1.0f;
+    float ms = -1.0f;
+    if (cudaEventElapsedTime(&ms, h->ev0, h->ev1) != cudaSuccess) return -1.0f;
+    return ms;
+}
+
+/* ───────────────────────── upload ───────────────────────── */
+
+template <typename T>
+static cudaError_t to_device(T **dptr, const T *src, size_t count, cudaStream_t s) {
+    cudaError_t e = cudaMalloc((void **)dptr, std::max<size_t>(count, 1) * sizeof(T));
+    if (e != cudaSuccess) return e;
+    if (count) e = cudaMemcpyAsync(*dptr, src, count * sizeof(T), cudaMemcpyHostToDevice, s);
+    return e;
+}
+
+extern "C" int muninn_cuda_index_upload(MuninnCudaIndex *h, int64_t n, const int64_t *ids, const int32_t *levels,
+                                        const uint8_t *deleted, const float *vectors, const int64_t *list_offsets,
+                                        const int32_t *targets, int32_t entry_slot, int32_t max_level) {
+    if (!h) return MUNINN_CUDA_E_ARG;
+    if (n < 0 || n > 0x7ffffff0LL) return fail(h, MUNINN_CUDA_E_ARG, "n = %lld out of range", (long long)n);
+    if (n > 0 && (!ids || !levels || !vectors || !list_offsets)) return fail(h, MUNINN_CUDA_E_ARG, "NULL array");
+    if (entry_slot < -1 || entry_slot >= n) return fail(h, MUNINN_CUDA_E_ARG, "entry_slot %d out of range", entry_slot);
+    CK(h, cudaSetDevice(h->device));
+    CK(h, cudaStreamSynchronize(h->stream));
+    free_graph(h);
+
+    const int M = h->M, M0 = h->M0;
+    /* host re-layout */
+    std::vector<int32_t> nbr0((size_t)n * M0, -1), upper_base((size_t)n, -1);
+    std::vector<uint8_t> del((size_t)n, 0);
+    long long n_upper = 0, n_live = 0;
+    for (int64_t s = 0; s < n; s++) {
+        if (levels[s] < 0 || levels[s] >= 32) /* HNSW_MAX_LEVELS, src/hnsw_algo.h:14 */
+            return fail(h, MUNINN_CUDA_E_ARG, "level %d of slot %lld out of range", levels[s], (long long)s);
+        if (s > 0 && ids[s] <= ids[s - 1]) return fail(h, MUNINN_CUDA_E_ARG, "ids must be strictly ascending");
+        if (levels[s] > 0) { upper_base[s] = (int32_t)n_upper; n_upper += levels[s]; }
+        del[s] = deleted ? (deleted[s] != 0) : 0;
+        if (!del[s]) n_live++;
+        if (n_upper > 0x7ffffff0LL) return fail(h, MUNINN_CUDA_E_ARG, "too many upper-layer lists");
+    }
+    if (entry_slot >= 0 && levels[entry_slot] < max_level)
+        return fail(h, MUNINN_CUDA_E_ARG, "entry node level %d < max_level %d", levels[entry_slot], max_level);
+    if (entry_slot >= 0 && (max_level < 0 || max_level >= 32)) return fail(h, MUNINN_CUDA_E_ARG, "bad max_level");
+    std::vector<int32_t> nbrU((size_t)n_upper * M, -1);
+    int64_t li = 0;
+    for (int64_t s = 0; s < n; s++) {
+        for (int l = 0; l <= levels[s]; l++, li++) {
+            const int64_t b = list_offsets[li], e = list_offsets[li + 1];
+            const int capl = l == 0 ? M0 : M;
+            if (e < b || e - b > capl)
+                return fail(h, MUNINN_CUDA_E_ARG, "list (slot %lld, level %d) has %lld entries, capacity %d",
+                            (long long)s, l, (long long)(e - b), capl);
+            int32_t *dst = l == 0 ? &nbr0[(size_t)s * M0] : &nbrU[((size_t)upper_base[s] + (l - 1)) * M];
+            for (int64_t j = b; j < e; j++) {
+                int32_t t = targets[j];
+                if (t < -1 || t >= n) return fail(h, MUNINN_CUDA_E_ARG, "target %d out of range", t);
+                if (t >= 0 && levels[t] < l) /* the reference would index neighbors[l] out of bounds */
+                    return fail(h, MUNINN_CUDA_E_ARG, "edge to slot %d at level %d above its level %d", t, l, levels[t]);
+                dst[j - b] = (t >= 0 && !del[t]) ? t : -1;
+            }
+        }
+    }
+
+    cudaStream_t st = h->stream;
+    CK(h, cudaMalloc((void **)&h->d_vec, std::max<size_t>((size_t)n * h->ld, 4) * sizeof(float)));
+    if (n) {
+        if (h->ld != h->dim) CK(h, cudaMemsetAsync(h->d_vec, 0, (size_t)n * h->ld * sizeof(float), st));
+        CK(h, cudaMemcpy2DAsync(h->d_vec, (size_t)h->ld * 4, vectors, (size_t)h->dim * 4, (size_t)h->dim * 4, (size_t)n,
+                                cudaMemcpyHostToDevice, st));
+    }
+    CK(h, to_device(&h->d_nbr0, nbr0.data(), nbr0.size(), st));
+    CK(h, to_device(&h->d_upper_base, upper_base.data(), upper_base.size(), st));
+    CK(h, to_device(&h->d_nbrU, nbrU.data(), nbrU.size(), st));
+    CK(h, to_device(&h->d_deleted, del.data(), del.size(), st));
+    CK(h, to_device(&h->d_ids, ids, (size_t)n, st));
+    CK(h, cudaMalloc((void **)&h->d_norm2, std::max<size_t>((size_t)n, 1) * sizeof(float)));
+    if (n) {
+        row_norm2_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(h->d_vec, h->ld, h->dim, n, h->d_norm2);
+        h->launches++;
+        CK(h, cudaGetLastError());
+    }
+    CK(h, cudaStreamSynchronize(st)); /* host vectors above go out of scope */
+    h->n = n; h->n_live = n_live; h->entry_slot = entry_slot; h->max_level = max_level;
+    h->uploaded = true;
+    return MUNINN_CUDA_OK;
+}
+
+/* ───────────────────────── batched HNSW search ───────────────────────── */
+
+static unsigned pow2_at_least(unsigned long long v) {
+    unsigned long long p = 1024;
+    while (p < v) p <<= 1;
+    return (unsigned)p;
+}
+static unsigned log2u(unsigned v) { unsigned l = 0; while ((1u << l) < v) l++; return l; }
+
+template <int METRIC>
+static cudaError_t launch_levels(MuninnCudaIndex *h, SearchParams p, size_t smem, const int teams[3],
+                                 const unsigned caps[3], int nlevels, int nq) {
+    cudaError_t e = cudaFuncSetAttribute(hnsw_search_kernel<METRIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    for (int lv = 0; lv < nlevels; lv++) {
+        p.vis_cap = caps[lv];
+        p.vis_shift = 32 - log2u(caps[lv]);
+        p.work_counter = h->d_ctl + lv;
+        p.in_list = lv == 0 ? nullptr : h->d_retry + (size_t)(lv - 1) * nq;
+        p.in_count = lv == 0 ? nullptr : h->d_ctl + 3 + (lv - 1);
+        p.out_list = h->d_retry + (size_t)(lv < 2 ? lv : 0) * nq;
+        p.out_count_retry = h->d_ctl + 3 + lv;
+        hnsw_search_kernel<METRIC><<<teams[lv], 32, smem, h->stream>>>(p, lv);
+        h->launches++;
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+template <int METRIC>
+static cudaError_t occupancy_of(int *occ, size_t smem) {
+    cudaError_t e = cudaFuncSetAttribute(hnsw_search_kernel<METRIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, hnsw_search_kernel<METRIC>, 32, smem);
+}
+
+extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *d_queries, int nq, int k, int ef,
+                                               int64_t *d_ids, float *d_dist, int32_t *d_count,
+                                               MuninnSearchStats *d_stats) {
+    if (!h) return MUNINN_CUDA_E_ARG;
+    if (!h->uploaded) return fail(h, MUNINN_CUDA_E_STATE, "search before muninn_cuda_index_upload");
+    if (nq < 0 || k < 1) return fail(h, MUNINN_CUDA_E_ARG, "nq must be >= 0 and k >= 1 (nq=%d k=%d)", nq, k);
+    if (nq == 0) return MUNINN_CUDA_OK;
+    if (!d_queries || !d_ids || !d_dist || !d_count) return fail(h, MUNINN_CUDA_E_ARG, "NULL buffer");
+    if (ef < k) ef = k; /* src/hnsw_algo.c:673 */
+    const size_t smem = search_smem_bytes(ef, h->ld);
+    if (smem > 200 * 1024) return fail(h, MUNINN_CUDA_E_ARG, "ef=%d with dim=%d needs %zu B of shared memory per query (limit 200 KiB)", ef, h->dim, smem);
+    CK(h, cudaSetDevice(h->device));
+
+    int occ = 0;
+    cudaError_t oe = h->metric == MUNINN_METRIC_L2       ? occupancy_of<METRIC_L2>(&occ, smem)
+                     : h->metric == MUNINN_METRIC_COSINE ? occupancy_of<METRIC_COSINE>(&occ, smem)
+                                                         : occupancy_of<METRIC_IP>(&occ, smem);
+    CK(h, oe);
+    if (occ < 1) return fail(h, MUNINN_CUDA_E_CUDA, "search kernel does not fit on an SM");
+    int tps = h->teams_per_sm > 0 ? std::min(h->teams_per_sm, occ) : occ;
+    int teams[3];
+    unsigned caps[3];
+    teams[0] = (int)std::min<long long>((long long)h->num_sms * tps, nq);
+    const unsigned cap_all = pow2_at_least(2ull * (unsigned long long)(h->n + h->M0 + 1));
+    caps[0] = std::min(pow2_at_least(4ull * (unsigned long long)ef * h->M0), cap_all);
+    caps[1] = (unsigned)std::min<unsigned long long>(16ull * caps[0], cap_all);
+    caps[2] = cap_all;
+    int nlevels = caps[0] == cap_all ? 1 : (caps[1] == cap_all ? 2 : 3);
+    const size_t arena = std::max<size_t>((size_t)teams[0] * caps[0], cap_all);
+    for (int lv = 1; lv < 3; lv++) teams[lv] = (int)std::max<size_t>(1, std::min<size_t>(arena / caps[lv], (size_t)teams[0]));
+
+    if (arena > h->vis_entries) {
+        CK(h, cudaStreamSynchronize(h->stream));
+        cudaFree(h->d_vis); h->d_vis = nullptr; h->vis_entries = 0;
+        CK(h, cudaMalloc((void **)&h->d_vis, arena * 8));
+        CK(h, cudaMemsetAsync(h->d_vis, 0, arena * 8, h->stream));
+        h->vis_entries = arena; h->epoch_base = 0;
+    }
+    if ((unsigned long long)h->epoch_base + 3ull * (unsigned)nq + 2ull >= 0xffffffffull) {
+        CK(h, cudaMemsetAsync(h->d_vis, 0, h->vis_entries * 8, h->stream));
+        h->epoch_base = 0;
+    }
+    if ((size_t)2 * nq > h->retry_cap) {
+        CK(h, cudaStreamSynchronize(h->stream));
+        cudaFree(h->d_retry); h->d_retry = nullptr;
+        CK(h, cudaMalloc((void **)&h->d_retry, (size_t)2 * nq * sizeof(int)));
+        h->retry_cap = (size_t)2 * nq;
+    }
+    CK(h, cudaMemsetAsync(h->d_ctl, 0, 8 * sizeof(int), h->stream));
+
+    SearchParams p;
+    memset(&p, 0, sizeof p);
+    p.vec = h->d_vec; p.norm2 = h->d_norm2; p.nbr0 = h->d_nbr0; p.upper_base = h->d_upper_base; p.nbrU = h->d_nbrU;
+    p.deleted = h->d_deleted; p.ids = h->d_ids;
+    p.dim = h->dim; p.ld = h->ld; p.M = h->M; p.M0 = h->M0; p.entry_slot = h->entry_slot; p.max_level = h->max_level;
+    p.n_live = h->n_live;
+    p.queries = d_queries; p.nq = nq; p.k = k; p.ef = ef;
+    p.patience_max = std::max(ef / 4, 10); /* src/hnsw_algo.c:372-374 */
+    p.out_ids = d_ids; p.out_dist = d_dist; p.out_count = d_count; p.stats = d_stats;
+    p.vis = h->d_vis; p.epoch_base = h->epoch_base;
+    h->epoch_base += 3u * (unsigned)nq;
+
+    CK(h, cudaEventRecord(h->ev0, h->stream));
+    cudaError_t e = h->metric == MUNINN_METRIC_L2       ? launch_levels<METRIC_L2>(h, p, smem, teams, caps, nlevels, nq)
+                    : h->metric == MUNINN_METRIC_COSINE ? launch_levels<METRIC_COSINE>(h, p, smem, teams, caps, nlevels, nq)
+                                                        : launch_levels<METRIC_IP>(h, p, smem, teams, caps, nlevels, nq);
+    CK(h, e);
+    CK(h, cudaEventRecord(h->ev1, h->stream));
+    h->have_timing = true;
+    return MUNINN_CUDA_OK;
+}
+
+static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+static int ensure_stage(MuninnCudaIndex *h, size_t bytes) {
+    if (bytes <= h->stage_bytes) return MUNINN_CUDA_OK;
+    CK(h, cudaStreamSynchronize(h->stream));
+    cudaFree(h->d_stage); h->d_stage = nullptr; h->stage_bytes = 0;
+    CK(h, cudaMalloc(&h->d_stage, bytes));
+    h->stage_bytes = bytes;
+    return MUNINN_CUDA_OK;
+}
+
+extern "C" int muninn_cuda_search_batch(MuninnCudaIndex *h, const float *queries, int nq, int k, int ef,
+                                        int64_t *out_ids, float *out_dist, int32_t *out_count,
+                                        MuninnSearchStats *out_stats) {
+    if (!h) return MUNINN_CUDA_E_ARG;
+    if (!h->uploaded) return fail(h, MUNINN_CUDA_E_STATE, "search before muninn_cuda_index_upload");
+    if (nq < 0 || k < 1) return fail(h, MUNINN_CUDA_E_ARG, "nq must be >= 0 and k >= 1 (nq=%d k=%d)", nq, k);
+    if (nq == 0) return MUNINN_CUDA_OK;
+    if (!queries || !out_ids || !out_dist || !out_count) return fail(h, MUNINN_CUDA_E_ARG, "NULL buffer");
+    CK(h, cudaSetDevice(h->device));
+    const size_t bq = align256((size_t)nq * h->dim * 4), bi = align256((size_t)nq * k * 8),
+                 bd = align256((size_t)nq * k * 4), bc = align256((size_t)nq * 4),
+                 bs = out_stats ? align256((size_t)nq * sizeof(MuninnSearchStats)) : 0;
+    int rc = ensure_stage(h, bq + bi + bd + bc + bs);
+    if (rc) return rc;
+    char *b = (char *)h->d_stage;
+    float *dq = (float *)b; int64_t *di = (int64_t *)(b + bq); float *dd = (float *)(b + bq + bi);
+    int32_t *dc = (int32_t *)(b + bq + bi + bd);
+    MuninnSearchStats *ds = out_stats ? (MuninnSearchStats *)(b + bq + bi + bd + bc) : nullptr;
+    CK(h, cudaMemcpyAsync(dq, queries, (size_t)nq * h->dim * 4, cudaMemcpyHostToDevice, h->stream));
+    rc = muninn_cuda_search_batch_device(h, dq, nq, k, ef, di, dd, dc, ds);
+    if (rc) return rc;
+    CK(h, cudaMemcpyAsync(out_ids, di, (size_t)nq * k * 8, cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaMemcpyAsync(out_dist, dd, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaMemcpyAsync(out_count, dc, (size_t)nq * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (out_stats) CK(h, cudaMemcpyAsync(out_stats, ds, (size_t)nq * sizeof(MuninnSearchStats), cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    return MUNINN_CUDA_OK;
+}
+
+/* ───────────────────────── exact k-NN ───────────────────────── */
+
+template <int METRIC>
+static void launch_dist_tile(MuninnCudaIndex *h, long long row0, int rows, const float *dq, int nq, int panel_ld) {
+    dim3 grid((rows + XT - 1) / XT, (nq + QT - 1) / QT);
+    exact_dist_tile<METRIC><<<grid, 256, 0, h->stream>>>(h->d_vec, h->d_norm2, h->d_deleted, h->ld, h->dim, row0, rows, dq,
+                                                         nq, h->d_panel, panel_ld);
+}
+
+extern "C" int muninn_cuda_exact_knn_device(MuninnCudaIndex *h, const float *d_queries, int nq, int k,
+                                            int64_t index_base, int64_t *d_idx, float *d_dist, int32_t *d_count) {
+    if (!h) return MUNINN_CUDA_E_ARG;
+    if (!h->uploaded) return fail(h, MUNINN_CUDA_E_STATE, "exact k-NN before muninn_cuda_index_upload");
+    if (nq < 0 || k < 1 || k > 2048) return fail(h, MUNINN_CUDA_E_ARG, "need nq >= 0 and 1 <= k <= 2048 (nq=%d k=%d)", nq, k);
+    if (nq == 0) return MUNINN_CUDA_OK;
+    if (!d_queries || !d_idx || !d_dist || !d_count) return fail(h, MUNINN_CUDA_E_ARG, "NULL buffer");
+    CK(h, cudaSetDevice(h->device));
+    /* distance panel: at most 1 GiB, whole 64-row tiles */
+    long long chunk = (long long)((1ull << 28) / (unsigned long long)nq);
+    chunk = std::max<long long>(XT, chunk / XT * XT);
+    chunk = std::min<long long>(chunk, std::max<long long>(XT, (h->n + XT - 1) / XT * XT));
+    const size_t need = (size_t)nq * (size_t)chunk;
+    if (need > h->panel_floats) {
+        CK(h, cudaStreamSynchronize(h->stream));
+        cudaFree(h->d_panel); h->d_panel = nullptr; h->panel_floats = 0;
+        CK(h, cudaMalloc((void **)&h->d_panel, need * 4));
+        h->panel_floats = need;
+    }
+    if ((size_t)nq * k > h->topk_cap || (size_t)nq > h->topk_q) {
+        CK(h, cudaStreamSynchronize(h->stream));
+        cudaFree(h->d_topk); cudaFree(h->d_topk_size); h->d_topk = nullptr; h->d_topk_size = nullptr;
+        CK(h, cudaMalloc((void **)&h->d_topk, (size_t)nq * k * 8));
+        CK(h, cudaMalloc((void **)&h->d_topk_size, (size_t)nq * 4));
+        h->topk_cap = (size_t)nq * k; h->topk_q = (size_t)nq;
+    }
+    CK(h, cudaMemsetAsync(h->d_topk_size, 0, (size_t)nq * 4, h->stream));
+    const size_t sel_smem = (size_t)4 * (k + 32) * 8;
+    if (sel_smem > 48 * 1024)
+        CK(h, cudaFuncSetAttribute(exact_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sel_smem));
+    CK(h, cudaEventRecord(h->ev0, h->stream));
+    for (long long row0 = 0; row0 < h->n; row0 += chunk) {
+        const int rows = (int)std::min<long long>(chunk, h->n - row0);
+        if (h->metric == MUNINN_METRIC_L2) launch_dist_tile<METRIC_L2>(h, row0, rows, d_queries, nq, (int)chunk);
+        else if (h->metric == MUNINN_METRIC_COSINE) launch_dist_tile<METRIC_COSINE>(h, row0, rows, d_queries, nq, (int)chunk);
+        else launch_dist_tile<METRIC_IP>(h, row0, rows, d_queries, nq, (int)chunk);
+        exact_select<<<(nq + 3) / 4, 128, sel_smem, h->stream>>>(h->d_panel, (int)chunk, rows, (unsigned)row0, nq, k,
+                                                                 h->d_topk, h->d_topk_size);
+        h->launches += 2;
+        CK(h, cudaGetLastError());
+    }
+    exact_emit<<<(unsigned)(((size_t)nq * k + 255) / 256), 256, 0, h->stream>>>(h->d_topk, h->d_topk_size, nq, k, index_base,
+                                                                               d_idx, d_dist, d_count);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    CK(h, cudaEventRecord(h->ev1, h->stream));
+    h->have_timing = true;
+    return MUNINN_CUDA_OK;
+}
+
+extern "C" int muninn_cuda_exact_knn(MuninnCudaIndex *h, const float *queries, int nq, int k, int64_t index_base,
+                                     int64_t *out_idx, float *out_dist, int32_t *out_count) {
+    if (!h) return MUNINN_CUDA_E_ARG;
+    if (!h->uploaded) return fail(h, MUNINN_CUDA_E_STATE, "exact k-NN before muninn_cuda_index_upload");
+    if (nq < 0 || k < 1) return fail(h, MUNINN_CUDA_E_ARG, "nq must be >= 0 and k >= 1");
+    if (nq == 0) return MUNINN_CUDA_OK;
+    if (!queries || !out_idx || !out_dist || !out_count) return fail(h, MUNINN_CUDA_E_ARG, "NULL buffer");
+    CK(h, cudaSetDevice(h->device));
+    const size_t bq = align256((size_t)nq * h->dim * 4), bi = align256((size_t)nq * k * 8),
+                 bd = align256((size_t)nq * k * 4), bc = align256((size_t)nq * 4);
+    int rc = ensure_stage(h, bq + bi + bd + bc);
+    if (rc) return rc;
+    char *b = (char *)h->d_stage;
+    float *dq = (float *)b; int64_t *di = (int64_t *)(b + bq); float *dd = (float *)(b + bq + bi);
+    int32_t *dc = (int32_t *)(b + bq + bi + bd);
+    CK(h, cudaMemcpyAsync(dq, queries, (size_t)nq * h->dim * 4, cudaMemcpyHostToDevice, h->stream));
+    rc = muninn_cuda_exact_knn_device(h, dq, nq, k, index_base, di, dd, dc);
+    if (rc) return rc;
+    CK(h, cudaMemcpyAsync(out_idx, di, (size_t)nq * k * 8, cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaMemcpyAsync(out_dist, dd, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaMemcpyAsync(out_count, dc, (size_t)nq * 4, cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    return MUNINN_CUDA_OK;
+}
+
+extern "C" int muninn_cuda_topk_merge_device(MuninnCudaIndex *h, int parts, int nq, int k, const int64_t *d_idx_parts,
+                                             const float *d_dist_parts, const int32_t *d_count_parts, int64_t *d_idx,
+                                             float *d_dist, int32_t *d_count) {
+    if (!h) return MUNINN_CUDA_E_ARG;
+    if (parts < 1 || nq < 0 || k < 1 || k > 2048) return fail(h, MUNINN_CUDA_E_ARG, "bad parts/nq/k");
+    if (nq == 0) return MUNINN_CUDA_OK;
+    CK(h, cudaSetDevice(h->device));
+    const size_t smem = (size_t)4 * (k + 32) * 8;
+    if (smem > 48 * 1024)
+        CK(h, cudaFuncSetAttribute(topk_merge_parts, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    topk_merge_parts<<<(nq + 3) / 4, 128, smem, h->stream>>>(parts, nq, k, d_idx_parts, d_dist_parts, d_count_parts, d_idx,
+                                                             d_dist, d_count);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    return MUNINN_CUDA_OK;
+}
+
+/* ───────────────────────── distances (known-answer surface) ───────────────────────── */
+
+extern "C" int muninn_cuda_distance_batch(int device, int metric, int dim, int64_t n, const float *a, const float *b,
+                                          float *out) {
+    if (metric < 0 || metric > 2 || dim < 1 || n < 0 || (n > 0 && (!a || !b || !out))) return MUNINN_CUDA_E_ARG;
+    if (muninn_cuda_device_count() <= 0) return MUNINN_CUDA_E_NODEVICE;
+    if (n == 0) return MUNINN_CUDA_OK;
+    if (cudaSetDevice(device) != cudaSuccess) return MUNINN_CUDA_E_ARG;
+    float *da = nullptr, *db = nullptr, *dout = nullptr;
+    const size_t bytes = (size_t)n * dim * 4;
+    int rc = MUNINN_CUDA_OK;
+    if (cudaMalloc((void **)&da, bytes) != cudaSuccess || cudaMalloc((void **)&db, bytes) != cudaSuccess ||
+        cudaMalloc((void **)&dout, (size_t)n * 4) != cudaSuccess)
+        rc = MUNINN_CUDA_E_NOMEM;
+    if (!rc && (cudaMemcpy(da, a, bytes, cudaMemcpyHostToDevice) != cudaSuccess ||
+                cudaMemcpy(db, b, bytes, cudaMemcpyHostToDevice) != cudaSuccess))
+        rc = MUNINN_CUDA_E_CUDA;
+    if (!rc) {
+        distance_pairs_kernel<<<(unsigned)((n + 127) / 128), 128>>>(metric, dim, n, da, db, dout);
+        if (cudaGetLastError() != cudaSuccess || cudaMemcpy(out, dout, (size_t)n * 4, cudaMemcpyDeviceToHost) != cudaSuccess)
+            rc = MUNINN_CUDA_E_CUDA;
+    }
+    cudaFree(da); cudaFree(db); cudaFree(dout);
+    return rc;
+}
