@@ -1,0 +1,113 @@
+"""hnsw_index shadow tables ⇄ FlatGraph.
+
+The on-disk format is the reference's (/root/reference/src/hnsw_vtab.c:138-199):
+  <name>_config(key TEXT PRIMARY KEY, value TEXT)   dimensions, metric (int), m, ef_construction,
+                                                    entry_point, max_level
+  <name>_nodes(id INTEGER PRIMARY KEY, vector BLOB, level, deleted)
+  <name>_edges(source_id, target_id, level, distance, PRIMARY KEY(source_id, level, target_id)) WITHOUT ROWID
+
+`load_from_shadow` reproduces load_index_from_shadow (src/hnsw_vtab.c:286-341): every stored
+node, deleted ones included; an edge is kept only if its source exists and level <= the
+source's level (:334); neighbour lists come back in ascending target_id order. A target id with
+no node row is kept as -1 (the reference keeps the dangling id and skips it at search time).
+
+`write_shadow` is the bulk writer: it stores a FlatGraph in exactly this
+format so that the unmodified reference extension can xConnect to graphs built here.
+"""
+from __future__ import annotations
+
+import sqlite3
+
+import numpy as np
+
+from .graph import FlatGraph
+
+
+def read_config(conn: sqlite3.Connection, name: str) -> dict:
+    rows = conn.execute(f'SELECT key, value FROM "{name}_config"').fetchall()
+    return {k: v for k, v in rows}
+
+
+def load_from_shadow(conn: sqlite3.Connection, name: str) -> FlatGraph:
+    cfg = read_config(conn, name)
+    dim, metric, M = int(cfg["dimensions"]), int(cfg["metric"]), int(cfg["m"])
+    efc = int(cfg["ef_construction"])
+    entry_id, max_level = int(cfg.get("entry_point", -1)), int(cfg.get("max_level", -1))
+    nodes = conn.execute(f'SELECT id, vector, level, deleted FROM "{name}_nodes" ORDER BY id').fetchall()
+    n = len(nodes)
+    ids = np.fromiter((r[0] for r in nodes), np.int64, n)
+    levels = np.fromiter((r[2] for r in nodes), np.int32, n)
+    deleted = np.fromiter((1 if r[3] else 0 for r in nodes), np.uint8, n)
+    vectors = np.empty((n, dim), np.float32)
+    for i, r in enumerate(nodes):
+        vectors[i] = np.frombuffer(r[1], np.float32, dim)
+    first = np.zeros(n + 1, np.int64)
+    np.cumsum(levels.astype(np.int64) + 1, out=first[1:])
+    n_lists = int(first[-1])
+    edges = np.array(conn.execute(
+        f'SELECT source_id, level, target_id FROM "{name}_edges" ORDER BY source_id, level, target_id').fetchall(),
+        dtype=np.int64).reshape(-1, 3)
+    counts = np.zeros(n_lists, np.int64)
+    if edges.shape[0]:
+        src = np.searchsorted(ids, edges[:, 0])
+        src_ok = (src < n) & (ids[np.minimum(src, n - 1)] == edges[:, 0])
+        src = np.where(src_ok, src, 0)
+        keep = src_ok & (edges[:, 1] <= levels[src]) & (edges[:, 1] >= 0)  # src/hnsw_vtab.c:334
+        edges, src = edges[keep], src[keep]
+        li = first[src] + edges[:, 1]
+        tgt = np.searchsorted(ids, edges[:, 2])
+        tgt_ok = (tgt < n) & (ids[np.minimum(tgt, n - 1)] == edges[:, 2])
+        targets = np.where(tgt_ok, tgt, -1).astype(np.int32)
+        np.add.at(counts, li, 1)  # rows are already ordered by (source, level, target) = list order
+    else:
+        targets = np.empty(0, np.int32)
+    offs = np.zeros(n_lists + 1, np.int64)
+    np.cumsum(counts, out=offs[1:])
+    entry_slot = -1
+    if entry_id != -1 and n:
+        p = int(np.searchsorted(ids, entry_id))
+        if p < n and ids[p] == entry_id:
+            entry_slot = p
+    return FlatGraph(dim, metric, M, efc, ids, levels, deleted, vectors, offs, targets, entry_slot, max_level)
+
+
+def write_shadow(conn: sqlite3.Connection, name: str, g: FlatGraph, with_distance: bool = False) -> None:
+    """Create <name>_config/_nodes/_edges holding `g` (bulk, one transaction). The `distance`
+    column is informational in the reference (never read back, src/hnsw_vtab.c:322); it is
+    written as 0.0 unless with_distance."""
+    g.validate()
+    cur = conn.cursor()
+    cur.execute(f'CREATE TABLE IF NOT EXISTS "{name}_config" (key TEXT PRIMARY KEY, value TEXT NOT NULL)')
+    cur.execute(f'CREATE TABLE IF NOT EXISTS "{name}_nodes" (id INTEGER PRIMARY KEY, vector BLOB NOT NULL, '
+                f'level INTEGER NOT NULL, deleted INTEGER NOT NULL DEFAULT 0)')
+    cur.execute(f'CREATE TABLE IF NOT EXISTS "{name}_edges" (source_id INTEGER NOT NULL, target_id INTEGER NOT NULL, '
+                f'level INTEGER NOT NULL, distance REAL NOT NULL, PRIMARY KEY (source_id, level, target_id)) '
+                f'WITHOUT ROWID')
+    cur.execute(f'CREATE INDEX IF NOT EXISTS "{name}_edges_rev" ON "{name}_edges"(target_id, level)')
+    entry_id = int(g.ids[g.entry_slot]) if g.entry_slot >= 0 else -1
+    cur.executemany(f'INSERT OR REPLACE INTO "{name}_config" (key, value) VALUES (?, ?)',
+                    [("dimensions", str(g.dim)), ("metric", str(g.metric)), ("m", str(g.M)),
+                     ("ef_construction", str(g.ef_construction)), ("entry_point", str(entry_id)),
+                     ("max_level", str(g.max_level))])
+    cur.executemany(f'INSERT INTO "{name}_nodes" (id, vector, level, deleted) VALUES (?, ?, ?, ?)',
+                    ((int(g.ids[s]), g.vectors[s].tobytes(), int(g.levels[s]), int(g.deleted[s]))
+                     for s in range(g.n)))
+    first = g.first_list()
+
+    def edge_rows():
+        for s in range(g.n):
+            for l in range(int(g.levels[s]) + 1):
+                li = int(first[s]) + l
+                for e in range(int(g.list_offsets[li]), int(g.list_offsets[li + 1])):
+                    t = int(g.targets[e])
+                    if t < 0:
+                        continue
+                    d = 0.0
+                    if with_distance:
+                        diff = g.vectors[s] - g.vectors[t]
+                        d = float(np.dot(diff, diff))
+                    yield (int(g.ids[s]), int(g.ids[t]), l, d)
+
+    cur.executemany(f'INSERT INTO "{name}_edges" (source_id, target_id, level, distance) VALUES (?, ?, ?, ?)',
+                    edge_rows())
+    conn.commit()

@@ -1,0 +1,194 @@
+"""`-m gpu`: the CUDA path, called through the C ABI (ctypes → libmuninn_cuda.so), against the
+CPU oracle on the same seeded inputs and against the committed reference outputs."""
+import numpy as np
+import pytest
+
+from tests.conftest import assert_results_match, lcg_vectors, uniform
+from tests.helpers import GOLDEN, load_golden
+
+pytestmark = pytest.mark.gpu
+L2, COS, IP = 0, 1, 2
+
+
+@pytest.fixture(scope="module")
+def cuda():
+    from sqlite_muninn_b200 import cuda as c
+    assert c.device_count() > 0, "no CUDA device: the product has no CPU path"
+    return c
+
+
+# ── distances: test/test_vec_math.c known answers and bit-exactness vs the oracle ──
+def test_distance_known_answers(cuda):
+    cases = [(L2, [1, 2, 3], [1, 2, 3], 0.0), (L2, [1, 0, 0], [0, 1, 0], 2.0), (COS, [1, 2, 3], [1, 2, 3], 0.0),
+             (COS, [1, 0, 0], [0, 1, 0], 1.0), (COS, [1, 0, 0], [-1, 0, 0], 2.0), (COS, [0, 0, 0], [1, 2, 3], 1.0),
+             (IP, [1, 2, 3], [4, 5, 6], -32.0), (IP, [1, 0, 0], [0, 1, 0], 0.0)]
+    for metric, a, b, want in cases:
+        got = cuda.distance_batch(metric, np.float32([a]), np.float32([b]))[0]
+        assert abs(float(got) - want) <= 1e-6
+    assert float(cuda.distance_batch(L2, np.float32([[3]]), np.float32([[7]]))[0]) == 16.0
+
+
+@pytest.mark.parametrize("dim", [1, 3, 4, 7, 96, 128, 131, 768])
+@pytest.mark.parametrize("metric", [L2, COS, IP])
+def test_distance_bit_exact(cuda, oracle, metric, dim):
+    a, b = uniform(dim, 200, dim), uniform(dim + 1000, 200, dim)
+    got = cuda.distance_batch(metric, a, b)
+    want = np.array([oracle.distance(metric, a[i], b[i]) for i in range(200)], np.float32)
+    assert got.tobytes() == want.tobytes()
+
+
+# ── search: committed outputs of the unmodified reference ──
+@pytest.mark.parametrize("name", GOLDEN)
+def test_search_reproduces_reference_golden(cuda, name):
+    g, queries, k, cases = load_golden(name)
+    with cuda.HnswIndexCuda.from_graph(g) as idx:
+        for c in cases:
+            ids, dist, cnt, st = idx.search(queries, k, c["ef"], want_stats=True)
+            assert_results_match(ids, dist.astype(np.float64), cnt, c["ids"], c["dist"].astype(np.float64), c["cnt"],
+                                 name)
+            if c["ndist"] is not None:
+                assert np.array_equal(st["n_dist"], c["ndist"]), name
+
+
+# ── search: oracle on seeded inputs; ids, distances AND work counters identical ──
+CONFIGS = [  # metric, M, dim, n, efc
+    (L2, 16, 128, 6000, 100), (L2, 8, 16, 3000, 60), (COS, 32, 768, 1500, 60), (IP, 32, 96, 4000, 80),
+    (COS, 16, 24, 2000, 100), (L2, 4, 3, 500, 30), (IP, 6, 10, 800, 40), (L2, 40, 20, 1500, 90)]
+
+
+@pytest.mark.parametrize("metric,M,dim,n,efc", CONFIGS)
+def test_search_equals_oracle(cuda, oracle, metric, M, dim, n, efc):
+    from sqlite_muninn_b200.builder import build_graph
+    base = uniform(n + dim, n, dim)
+    if metric == IP:
+        base /= np.linalg.norm(base, axis=1, keepdims=True)
+    q = uniform(n + dim + 1, 300, dim)
+    g = build_graph(base, metric, M, efc)
+    g.ids[:] = np.arange(n, dtype=np.int64) * 5 + 11  # rowids are not slots
+    og = oracle.graph(g)
+    with cuda.HnswIndexCuda.from_graph(g) as idx:
+        for k, ef in ((1, 1), (10, 10), (10, 20), (10, 64), (10, 256), (100, 100), (7, 500)):
+            ids, dist, cnt, st = idx.search(q, k, ef, want_stats=True)
+            o_ids, o_dist, o_cnt, o_st, _ = og.search(q, k, ef, canonical=True)
+            assert np.array_equal(cnt, o_cnt) and np.array_equal(dist, o_dist) and np.array_equal(ids, o_ids), (k, ef)
+            for f in ("n_dist", "n_dist_upper", "n_expand", "n_greedy_steps", "entry0"):
+                assert np.array_equal(st[f], o_st[f]), (f, k, ef)
+            assert np.array_equal(st["term"] == 2, o_st["term"] == 2)
+            r_ids, r_dist, r_cnt, _, _ = og.search(q, k, ef)  # the reference's two-heap order
+            assert_results_match(ids, dist, cnt, r_ids, r_dist, r_cnt, "vs reference order")
+
+
+def test_search_tie_heavy_data_follows_canonical_order(cuda, oracle):
+    """Integer-valued rows: many bit-equal distances. The kernel must follow the documented
+    (distance, slot) rule exactly, and stay a valid search (same distance multiset quality)."""
+    from sqlite_muninn_b200.builder import build_graph
+    base = np.round(uniform(5, 3000, 16) * 3).astype(np.float32)
+    q = np.round(uniform(6, 200, 16) * 3).astype(np.float32)
+    g = build_graph(base, L2, 8, 60)
+    og = oracle.graph(g)
+    with cuda.HnswIndexCuda.from_graph(g) as idx:
+        for ef in (10, 64, 200):
+            ids, dist, cnt, st = idx.search(q, 10, ef, want_stats=True)
+            o_ids, o_dist, o_cnt, o_st, _ = og.search(q, 10, ef, canonical=True)
+            assert np.array_equal(ids, o_ids) and np.array_equal(dist, o_dist) and np.array_equal(cnt, o_cnt)
+            assert np.array_equal(st["n_dist"], o_st["n_dist"])
+
+
+def test_edge_cases(cuda, oracle):
+    """test/test_hnsw_algo.c:72-94,147-180 and pytests/test_hnsw_vtab.py:93-119."""
+    from sqlite_muninn_b200.builder import build_graph
+    from sqlite_muninn_b200.graph import FlatGraph
+    # three points, nearest of (0.1, 0.1) is id 0, returns 3
+    pts = np.float32([[0, 0], [10, 0], [0, 10]])
+    g = build_graph(pts, L2, 16, 200)
+    with cuda.HnswIndexCuda.from_graph(g) as idx:
+        ids, dist, cnt = idx.search(np.float32([[0.1, 0.1]]), 3, 10)
+        assert cnt[0] == 3 and ids[0, 0] == 0 and dist[0, 0] < 1.0
+        ids, dist, cnt = idx.search(np.float32([[0.1, 0.1]]), 5)  # k > n, default ef = 2k
+        assert cnt[0] == 3 and list(ids[0, 3:]) == [-1, -1]
+        with pytest.raises(ValueError, match="expected 2-dim"):
+            idx.search(np.float32([[1, 2, 3]]), 1)
+        with pytest.raises(cuda.MuninnCudaError):
+            idx.search(np.float32([[1, 2]]), 0)
+    # empty index → 0 results
+    e = FlatGraph(4, 0, 8, 50, np.empty(0, np.int64), np.empty(0, np.int32), np.empty(0, np.uint8),
+                  np.empty((0, 4), np.float32), np.zeros(1, np.int64), np.empty(0, np.int32), -1, -1)
+    with cuda.HnswIndexCuda.from_graph(e) as idx:
+        ids, dist, cnt = idx.search(np.zeros((3, 4), np.float32), 2, 10)
+        assert (cnt == 0).all() and (ids == -1).all()
+    # search before upload is an error, not a silent empty result
+    with cuda.HnswIndexCuda(4, 0, 8) as idx:
+        with pytest.raises(cuda.MuninnCudaError):
+            idx.search(np.zeros((1, 4), np.float32), 1)
+    # deleted entry point / all deleted
+    g = build_graph(uniform(1, 50, 4), L2, 4, 20)
+    g.deleted[:] = 1
+    with cuda.HnswIndexCuda.from_graph(g) as idx:
+        ids, dist, cnt = idx.search(uniform(2, 4, 4), 3, 10)
+        assert (cnt == 0).all()
+    # re-upload replaces the graph (the vtab's dirty-flag path)
+    g1, g2 = build_graph(uniform(3, 200, 8), L2, 8, 40), build_graph(uniform(4, 300, 8), L2, 8, 40)
+    q = uniform(5, 16, 8)
+    with cuda.HnswIndexCuda.from_graph(g1) as idx:
+        a = idx.search(q, 5, 40)
+        idx.upload(g2)
+        b = idx.search(q, 5, 40)
+        o = oracle.graph(g2).search(q, 5, 40, canonical=True)
+        assert np.array_equal(b[0], o[0]) and not np.array_equal(a[0], b[0])
+
+
+def test_visited_table_overflow_retries_are_exact(cuda, oracle):
+    """A query whose visited set outgrows its level-0 table is redone in a larger one: force it
+    with ef small relative to the graph walk (huge patience via duplicates is not needed: use
+    a dense small-M0 table by searching with ef=k=1 on a graph where the walk is long)."""
+    from sqlite_muninn_b200.builder import build_graph
+    base = uniform(77, 20000, 8)
+    g = build_graph(base, L2, 4, 30, batch=512, warm=1024)
+    q = uniform(78, 500, 8)
+    with cuda.HnswIndexCuda.from_graph(g) as idx:
+        for ef in (1, 2, 40, 1000):
+            ids, dist, cnt, st = idx.search(q, 1, ef, want_stats=True)
+            o = oracle.graph(g).search(q, 1, ef, canonical=True)
+            assert np.array_equal(ids, o[0]) and np.array_equal(dist, o[1]) and np.array_equal(st["n_dist"], o[3]["n_dist"])
+
+
+def test_full_size_properties(cuda, oracle):
+    """BASELINE config-1 shape (10k×128, M=16) at batch 2k: idempotence, sortedness, counts, and
+    agreement with exact k-NN as recall; oracle equality on a 200-query sample."""
+    from sqlite_muninn_b200.builder import build_graph
+    base, q = uniform(1, 10000, 128), uniform(2, 2000, 128)
+    g = build_graph(base, L2, 16, 200, batch=256, warm=2048)
+    with cuda.HnswIndexCuda.from_graph(g) as idx:
+        ids, dist, cnt, st = idx.search(q, 10, 256, want_stats=True)
+        ids2, dist2, cnt2 = idx.search(q, 10, 256)
+        assert np.array_equal(ids, ids2) and np.array_equal(dist, dist2)
+        assert (cnt == 10).all() and (np.diff(dist, axis=1) >= 0).all()
+        assert all(len(set(r)) == 10 for r in ids)
+        t_idx, t_dist, t_cnt = idx.exact_knn(q, 10)
+        recall = np.mean([len(set(a) & set(b)) / 10 for a, b in zip(ids, t_idx)])
+        assert recall > 0.9, recall
+        o = oracle.graph(g).search(q[:200], 10, 256, canonical=True)
+        assert np.array_equal(ids[:200], o[0]) and np.array_equal(dist[:200], o[1])
+        assert np.array_equal(st["n_dist"][:200], o[3]["n_dist"])
+
+
+# ── exact k-NN: bit-exact ids and distances, ties to the lower index ──
+@pytest.mark.parametrize("metric,dim,n,k", [(L2, 128, 5000, 100), (COS, 24, 3000, 10), (IP, 10, 2000, 7), (L2, 3, 300, 300),
+                                            (L2, 6, 4000, 50)])
+def test_exact_knn_bit_exact(cuda, oracle, metric, dim, n, k):
+    from sqlite_muninn_b200.graph import FlatGraph
+    base = uniform(n, n, dim)
+    if dim == 6:
+        base = np.round(base * 2).astype(np.float32)  # ties
+    q = uniform(n + 1, 130, dim)
+    if dim == 6:
+        q = np.round(q * 2).astype(np.float32)
+    deleted = np.zeros(n, np.uint8)
+    deleted[::17] = 1
+    g = FlatGraph(dim, metric, 8, 10, np.arange(n, dtype=np.int64), np.zeros(n, np.int32), deleted, base,
+                  np.zeros(n + 1, np.int64), np.empty(0, np.int32), 0, 0)
+    with cuda.HnswIndexCuda.from_graph(g) as idx:
+        i_g, d_g, c_g = idx.exact_knn(q, k, index_base=1000)
+    i_o, d_o, c_o, _ = oracle.exact_knn(base, q, k, metric, deleted=deleted)
+    assert np.array_equal(c_g, c_o) and np.array_equal(d_g, d_o)
+    assert np.array_equal(i_g, np.where(i_o >= 0, i_o + 1000, -1))

@@ -1,0 +1,119 @@
+"""Host-side logic that needs no GPU: the graph builder against the real reference, the
+shadow-table reader/writer, and the C-ABI surface of libmuninn_cuda."""
+import ctypes
+import os
+import re
+import sqlite3
+
+import numpy as np
+import pytest
+
+from sqlite_muninn_b200 import cuda
+from sqlite_muninn_b200.builder import build_graph
+from sqlite_muninn_b200.shadow import load_from_shadow, write_shadow
+from tests.conftest import ROOT, uniform
+from tests.helpers import load_golden
+
+
+@pytest.mark.parametrize("metric,M,dim,n,efc", [(0, 8, 16, 1500, 60), (1, 16, 24, 700, 100), (2, 6, 10, 600, 40),
+                                                (0, 4, 128, 900, 40)])
+def test_builder_exact_mode_equals_reference(reference, metric, M, dim, n, efc):
+    """csrc/hnsw_build.c (batch=0) builds the graph hnsw_insert builds: entry point, levels and
+    ordered neighbour lists (src/hnsw_algo.c:520-666)."""
+    base = uniform(n + 7, n, dim)
+    if metric == 2:
+        base /= np.linalg.norm(base, axis=1, keepdims=True)
+    ri = reference.build(base, metric=metric, M=M, efc=efc)
+    assert build_graph(base, metric, M, efc, sort_lists=False).same_structure(ri.export())
+    ri.sort_lists()
+    assert build_graph(base, metric, M, efc, sort_lists=True).same_structure(ri.export())
+
+
+def test_builder_batch_mode_is_deterministic_and_searchable(oracle):
+    base = uniform(11, 6000, 32)
+    g1 = build_graph(base, 0, 8, 40, batch=256, warm=512, threads=4)
+    g2 = build_graph(base, 0, 8, 40, batch=256, warm=512, threads=2)
+    assert g1.same_structure(g2)
+    q = uniform(12, 50, 32)
+    ids, _, _, _, _ = oracle.graph(g1).search(q, 10, 200)
+    truth, _, _, _ = oracle.exact_knn(base, q, 10, 0)
+    recall = np.mean([len(set(a) & set(b)) / 10 for a, b in zip(ids, truth)])
+    assert recall > 0.8
+
+
+def test_shadow_roundtrip(tmp_path):
+    g, _, _, _ = load_golden("vtab_cosine_300x24")
+    conn = sqlite3.connect(str(tmp_path / "x.db"))
+    write_shadow(conn, "t", g)
+    g2 = load_from_shadow(conn, "t")
+    assert g.same_structure(g2) and np.array_equal(g.vectors, g2.vectors) and np.array_equal(g.deleted, g2.deleted)
+    assert (g2.dim, g2.metric, g2.M, g2.ef_construction) == (g.dim, g.metric, g.M, g.ef_construction)
+
+
+def test_reference_vtab_opens_our_shadow_tables(tmp_path, oracle):
+    """A graph built and written here is a valid hnsw_index for the UNMODIFIED reference
+    extension, and its MATCH results equal the oracle's on that graph."""
+    from oracle.bindings import REF_EXT_SO
+    if not os.path.exists(REF_EXT_SO):
+        pytest.skip("reference extension not built")
+    base = uniform(21, 500, 16)
+    g = build_graph(base, 0, 8, 64)
+    g.ids[:] = np.arange(500) * 3 + 1
+    path = str(tmp_path / "ours.db")
+    conn = sqlite3.connect(path)
+    write_shadow(conn, "t", g)
+    conn.close()
+    conn = sqlite3.connect(path)
+    conn.enable_load_extension(True)
+    conn.load_extension(REF_EXT_SO, entrypoint="sqlite3_muninn_init")
+    # the module table in sqlite_master is what makes the shadow tables a vtab
+    conn.execute("PRAGMA writable_schema=ON")
+    conn.execute("INSERT INTO sqlite_master(type,name,tbl_name,rootpage,sql) VALUES('table','t','t',0,"
+                 "'CREATE VIRTUAL TABLE t USING hnsw_index(dimensions=16, metric=''l2'', m=8, ef_construction=64)')")
+    conn.commit()
+    conn.close()
+    conn = sqlite3.connect(path)
+    conn.enable_load_extension(True)
+    conn.load_extension(REF_EXT_SO, entrypoint="sqlite3_muninn_init")
+    q = uniform(22, 20, 16)
+    og = oracle.graph(g)
+    ids, dist, cnt, _, _ = og.search(q, 5, 30)
+    for i in range(20):
+        rows = conn.execute("SELECT rowid, distance FROM t WHERE vector MATCH ? AND k = 5 AND ef_search = 30",
+                            (q[i].tobytes(),)).fetchall()
+        assert [r[0] for r in rows] == list(ids[i, :cnt[i]])
+        assert [r[1] for r in rows] == [float(x) for x in dist[i, :cnt[i]]]
+
+
+def test_abi_exports_every_declared_symbol():
+    header = open(os.path.join(ROOT, "include", "muninn_cuda.h")).read()
+    declared = set(re.findall(r"\b(muninn_cuda_[a-z0-9_]+)\s*\(", header))
+    assert declared == set(cuda.ABI_SYMBOLS)
+    L = ctypes.CDLL(cuda.CUDA_SO)
+    for sym in declared:
+        assert hasattr(L, sym), sym
+
+
+def test_abi_host_only_calls():
+    L = cuda.lib()
+    assert L.muninn_cuda_version().startswith(b"muninn-b200")
+    assert cuda.parse_metric("l2") == 0 and cuda.parse_metric("cosine") == 1
+    assert cuda.parse_metric("inner_product") == 2 and cuda.parse_metric("hamming") == -1
+    assert L.muninn_cuda_strerror(-2) == b"no CUDA device"
+
+
+def test_no_cpu_fallback_without_device():
+    if cuda.device_count() > 0:
+        pytest.skip("a device is present")
+    with pytest.raises(cuda.MuninnCudaError) as e:
+        cuda.HnswIndexCuda(8, 0, 8)
+    assert e.value.code == -2
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "sqlite_muninn_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".c", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in src.replace("the CPU oracle", "").replace("CPU oracle's", ""), f
