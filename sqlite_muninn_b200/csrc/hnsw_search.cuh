@@ -60,7 +60,7 @@ struct TeamSmem {
 };
 
 __host__ __device__ inline size_t search_smem_bytes(int ef, int ld) {
-    size_t b = (size_t)ef * 8 + (size_t)MAX_M0 * 8 + 32 * 8;
+    size_t b = (((size_t)ef * 8 + 15) & ~(size_t)15) + (size_t)MAX_M0 * 8 + 32 * 8;
     b += ((size_t)ld * 4 + 15) / 16 * 16;
     b += (size_t)DB * PSTRIDE * 4;
     b += (size_t)MAX_M0 * 4;
@@ -163,7 +163,7 @@ __global__ void __launch_bounds__(32) hnsw_search_kernel(const SearchParams p, c
     TeamSmem sm;
     {
         unsigned char *b = smem_raw;
-        sm.R = reinterpret_cast<unsigned long long *>(b); b += (size_t)p.ef * 8;
+        sm.R = reinterpret_cast<unsigned long long *>(b); b += ((size_t)p.ef * 8 + 15) & ~(size_t)15;
         sm.Fk = reinterpret_cast<unsigned long long *>(b); b += (size_t)MAX_M0 * 8;
         sm.S = reinterpret_cast<unsigned long long *>(b); b += 32 * 8;
         sm.q = reinterpret_cast<float *>(b); b += ((size_t)p.ld * 4 + 15) / 16 * 16;
