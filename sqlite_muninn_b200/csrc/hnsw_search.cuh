@@ -31,8 +31,15 @@
 
 namespace muninn {
 
-constexpr int DB = 8;             /* neighbour rows per distance batch */
-constexpr int PSTRIDE = 128 + 4;  /* floats per staged row: 32 chunks + 4 pad → conflict-free transposed reads */
+#ifndef MUNINN_SEARCH_MIN_BLOCKS
+#define MUNINN_SEARCH_MIN_BLOCKS 24 /* resident query teams per SM the register budget is sized for */
+#endif
+#ifndef MUNINN_PREFETCH
+#define MUNINN_PREFETCH 1
+#endif
+constexpr int DB = 8;             /* rows per distance batch in the greedy descent (4 lanes per row) */
+constexpr int RB = 16;            /* rows per distance batch in the layer-0 beam (2 lanes per row) */
+constexpr int PSTRIDE = 128 + 4;  /* floats per staged row: 32 chunks + 4 pad → conflict-free per-row reads */
 constexpr int MAX_M0 = 128;       /* layer-0 list capacity supported (M ≤ 64) */
 
 struct SearchParams {
@@ -55,66 +62,123 @@ struct TeamSmem {
     unsigned long long *Fk;  /* [MAX_M0] keys of this expansion's fresh neighbours */
     unsigned long long *S;   /* [32] survivors being merged */
     float *q;                /* [ld] */
-    float *P;                /* [DB * PSTRIDE] */
+    float *P;                /* [RB * PSTRIDE] row staging tile */
     int *Fs;                 /* [MAX_M0] fresh slots */
 };
 
 __host__ __device__ inline size_t search_smem_bytes(int ef, int ld) {
     size_t b = (((size_t)ef * 8 + 15) & ~(size_t)15) + (size_t)MAX_M0 * 8 + 32 * 8;
     b += ((size_t)ld * 4 + 15) / 16 * 16;
-    b += (size_t)DB * PSTRIDE * 4;
+    b += (size_t)RB * PSTRIDE * 4;
     b += (size_t)MAX_M0 * 4;
     return b;
 }
 
-/*
- * Distances from the staged query to up to DB rows. bs[0..nb) are slots (shared memory).
- * Every lane returns the distance of row (lane >> 2) (garbage if that row index ≥ nb).
- */
+/* 16-byte asynchronous global→shared copy (LDGSTS), L2-only caching: the gathered rows are
+ * streamed once and never reused by this SM */
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src) {
+    unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+}
+
 template <int METRIC>
-__device__ __forceinline__ float warp_dist_batch(const SearchParams &p, const TeamSmem &sm, const int *bs, int nb,
-                                                 float q_norm2, int lane) {
+__device__ __forceinline__ float prod1(float a, float b) {
+    if (METRIC == METRIC_L2) { float d = __fsub_rn(a, b); return __fmul_rn(d, d); }
+    return __fmul_rn(a, b);
+}
+
+/*
+ * Distances from the staged query to up to 32/L rows (L = lanes per row: 4 → ≤ 8 rows, 2 → ≤ 16).
+ * bs[0..nb) are slots (shared memory). The warp copies the rows into the staging tile with
+ * asynchronous 16-byte copies (lane c moves chunk c of every row: one fully coalesced row per
+ * instruction, all rows in flight at once, no registers held), then lane (row, h) walks ITS row
+ * in shared memory and accumulates chains h·4/L … of the reference's SSE loop in ascending
+ * element order (src/vec_math.c:82-86), followed by the fixed ((s0+s1)+s2)+s3 horizontal sum and
+ * the scalar tail (:88-94). Row stride PSTRIDE = 132 floats makes both mappings bank-conflict
+ * free. Every lane of a row group returns that row's distance.
+ */
+template <int METRIC, int L>
+__device__ __forceinline__ float warp_dist_rows(const SearchParams &p, const TeamSmem &sm, const int *bs, int nb,
+                                                float q_norm2, int lane) {
+    constexpr int CH = 4 / L;
     const int cpr = p.ld >> 2, cfull = p.dim >> 2, rem = p.dim & 3;
-    const int n_me = lane >> 2, j_me = lane & 3;
-    float s = 0.0f, tailv = 0.0f;
+    const int row = lane / L, h = lane % L, g = lane - h;
+    const bool mine = row < nb;
+    float nb2 = 1.0f;
+    if (METRIC == METRIC_COSINE && mine && h == 0) nb2 = p.norm2[bs[row]];
+    float s0 = 0.0f, s1 = 0.0f, tl0 = 0.0f, tl1 = 0.0f, tl2 = 0.0f;
     for (int t0 = 0; t0 < cpr; t0 += 32) {
-        const int c = t0 + lane;
-        float4 x[DB];
-        if (c < cpr) {
-#pragma unroll
-            for (int n = 0; n < DB; n++)
-                if (n < nb) x[n] = ldg_stream_f4(p.vec + (size_t)bs[n] * (size_t)p.ld + 4 * c);
-            const float4 qv = *reinterpret_cast<const float4 *>(sm.q + 4 * c);
-#pragma unroll
-            for (int n = 0; n < DB; n++)
-                if (n < nb) *reinterpret_cast<float4 *>(sm.P + n * PSTRIDE + 4 * lane) = prod4<METRIC>(qv, x[n]);
+        const int tc = cpr - t0 < 32 ? cpr - t0 : 32;
+        if (lane < tc) {
+            const float *src = p.vec + 4 * (t0 + lane);
+            float *dst = sm.P + 4 * lane;
+            for (int r = 0; r < nb; r++) cp_async16(dst + r * PSTRIDE, src + (size_t)bs[r] * (size_t)p.ld);
         }
+        cp_async_wait_all();
         __syncwarp();
-        int tfull = cfull - t0;
-        tfull = tfull > 32 ? 32 : tfull;
-        if (n_me < nb) {
-            const float *row = sm.P + n_me * PSTRIDE + j_me;
+        if (mine) {
+            int tfull = cfull - t0;
+            tfull = tfull > tc ? tc : tfull;
+            const float *xr = sm.P + row * PSTRIDE + CH * h;
+            const float *qr = sm.q + 4 * t0 + CH * h;
 #pragma unroll 8
-            for (int cc = 0; cc < tfull; cc++) s = __fadd_rn(s, row[4 * cc]);
-            if (rem && cfull >= t0 && cfull < t0 + 32 && j_me < rem) tailv = row[4 * (cfull - t0)];
+            for (int cc = 0; cc < tfull; cc++) {
+                if (CH == 2) {
+                    const float2 x = *reinterpret_cast<const float2 *>(xr + 4 * cc);
+                    const float2 q = *reinterpret_cast<const float2 *>(qr + 4 * cc);
+                    s0 = __fadd_rn(s0, prod1<METRIC>(q.x, x.x));
+                    s1 = __fadd_rn(s1, prod1<METRIC>(q.y, x.y));
+                } else {
+                    s0 = __fadd_rn(s0, prod1<METRIC>(qr[4 * cc], xr[4 * cc]));
+                }
+            }
+            if (rem && h == 0 && cfull >= t0 && cfull < t0 + 32) { /* the partial chunk: kept for after the horizontal sum */
+                const float *xt = sm.P + row * PSTRIDE + 4 * (cfull - t0), *qt = sm.q + 4 * cfull;
+                tl0 = prod1<METRIC>(qt[0], xt[0]);
+                if (rem > 1) tl1 = prod1<METRIC>(qt[1], xt[1]);
+                if (rem > 2) tl2 = prod1<METRIC>(qt[2], xt[2]);
+            }
         }
-        __syncwarp();
+        __syncwarp(); /* the tile is overwritten by the next column block */
     }
-    const int g = lane & ~3;
-    float s0 = __shfl_sync(FULL, s, g), s1 = __shfl_sync(FULL, s, g + 1), s2 = __shfl_sync(FULL, s, g + 2),
-          s3 = __shfl_sync(FULL, s, g + 3);
-    float sum = __fadd_rn(__fadd_rn(__fadd_rn(s0, s1), s2), s3);
+    float sum;
+    if (L == 4) {
+        float c0 = __shfl_sync(FULL, s0, g), c1 = __shfl_sync(FULL, s0, g + 1), c2 = __shfl_sync(FULL, s0, g + 2),
+              c3 = __shfl_sync(FULL, s0, g + 3);
+        sum = __fadd_rn(__fadd_rn(__fadd_rn(c0, c1), c2), c3);
+    } else {
+        float c2 = __shfl_sync(FULL, s0, g + 1), c3 = __shfl_sync(FULL, s1, g + 1);
+        sum = __fadd_rn(__fadd_rn(__fadd_rn(s0, s1), c2), c3); /* meaningful in lane g */
+    }
     if (rem) {
-        float t0v = __shfl_sync(FULL, tailv, g), t1v = __shfl_sync(FULL, tailv, g + 1),
-              t2v = __shfl_sync(FULL, tailv, g + 2);
-        sum = __fadd_rn(sum, t0v);
-        if (rem > 1) sum = __fadd_rn(sum, t1v);
-        if (rem > 2) sum = __fadd_rn(sum, t2v);
+        sum = __fadd_rn(sum, tl0);
+        if (rem > 1) sum = __fadd_rn(sum, tl1);
+        if (rem > 2) sum = __fadd_rn(sum, tl2);
     }
-    if (METRIC == METRIC_L2) return sum;
-    if (METRIC == METRIC_IP) return -sum;
-    float nb2 = (n_me < nb) ? p.norm2[bs[n_me]] : 1.0f;
-    return cosine_finish(sum, q_norm2, nb2);
+    float d;
+    if (METRIC == METRIC_L2) d = sum;
+    else if (METRIC == METRIC_IP) d = -sum;
+    else d = cosine_finish(sum, q_norm2, nb2);
+    return __shfl_sync(FULL, d, g);
+}
+
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
+/* Pull the rows of all `nf` fresh neighbours towards L2 in one go (4 lanes per row, one
+ * 128-byte line each per step) so that the 8-row distance batches that follow overlap their
+ * DRAM latency instead of paying it batch after batch. */
+__device__ __forceinline__ void prefetch_rows(const SearchParams &p, const int *slots, int nf, int lane) {
+    const int row_bytes = p.ld * 4;
+    for (int r0 = 0; r0 < nf; r0 += 8) {
+        int r = r0 + (lane >> 2);
+        if (r < nf) {
+            const char *base = reinterpret_cast<const char *>(p.vec + (size_t)slots[r] * (size_t)p.ld);
+            for (int off = (lane & 3) * 128; off < row_bytes; off += 512) prefetch_l2(base + off);
+        }
+    }
 }
 
 /* Σ q_i² in chain order: the `norm_a` accumulator of vec_cosine_distance (src/vec_math.c:104-118) */
@@ -157,7 +221,7 @@ __device__ __forceinline__ int visited_test_and_set(const SearchParams &p, unsig
 }
 
 template <int METRIC>
-__global__ void __launch_bounds__(32) hnsw_search_kernel(const SearchParams p, const int level) {
+__global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kernel(const SearchParams p, const int level) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x;
     TeamSmem sm;
@@ -167,7 +231,7 @@ __global__ void __launch_bounds__(32) hnsw_search_kernel(const SearchParams p, c
         sm.Fk = reinterpret_cast<unsigned long long *>(b); b += (size_t)MAX_M0 * 8;
         sm.S = reinterpret_cast<unsigned long long *>(b); b += 32 * 8;
         sm.q = reinterpret_cast<float *>(b); b += ((size_t)p.ld * 4 + 15) / 16 * 16;
-        sm.P = reinterpret_cast<float *>(b); b += (size_t)DB * PSTRIDE * 4;
+        sm.P = reinterpret_cast<float *>(b); b += (size_t)RB * PSTRIDE * 4;
         sm.Fs = reinterpret_cast<int *>(b);
     }
     unsigned long long *tab = p.vis + (size_t)blockIdx.x * (size_t)p.vis_cap;
@@ -200,7 +264,7 @@ __global__ void __launch_bounds__(32) hnsw_search_kernel(const SearchParams p, c
             int cur = p.entry_slot;
             if (lane == 0) sm.Fs[0] = cur;
             __syncwarp();
-            float cur_d = __shfl_sync(FULL, warp_dist_batch<METRIC>(p, sm, sm.Fs, 1, qn2, lane), 0);
+            float cur_d = __shfl_sync(FULL, warp_dist_rows<METRIC, 4>(p, sm, sm.Fs, 1, qn2, lane), 0);
             __syncwarp();
             for (int l = p.max_level; l > 0; l--) {
                 n_dist++; n_dist_upper++; /* the reference re-evaluates the entry at every level (:262) */
@@ -227,7 +291,7 @@ __global__ void __launch_bounds__(32) hnsw_search_kernel(const SearchParams p, c
                         __syncwarp();
                         if (nb == 0) break;
                         last_pos = sm.Fs[MAX_M0 / 2 + nb - 1];
-                        float d = warp_dist_batch<METRIC>(p, sm, sm.Fs, nb, qn2, lane);
+                        float d = warp_dist_rows<METRIC, 4>(p, sm, sm.Fs, nb, qn2, lane);
                         bool better = (lane & 3) == 0 && (lane >> 2) < nb && d < cur_d; /* strict, :274 */
                         unsigned bm = __ballot_sync(FULL, better);
                         if (bm) {
@@ -289,12 +353,21 @@ __global__ void __launch_bounds__(32) hnsw_search_kernel(const SearchParams p, c
                     n_ins += nf;
                     n_dist += nf;
                     __syncwarp();
+#if MUNINN_PREFETCH
+                    if (nf > RB) prefetch_rows(p, sm.Fs + RB, nf - RB, lane); /* the first batch is copied right away */
+#endif
                     /* distances */
-                    for (int b0 = 0; b0 < nf; b0 += DB) {
-                        int nb = nf - b0 < DB ? nf - b0 : DB;
-                        float d = warp_dist_batch<METRIC>(p, sm, sm.Fs + b0, nb, qn2, lane);
-                        if ((lane & 3) == 0 && (lane >> 2) < nb)
-                            sm.Fk[b0 + (lane >> 2)] = make_key(d, (unsigned)sm.Fs[b0 + (lane >> 2)] << 1);
+                    for (int b0 = 0; b0 < nf; b0 += RB) {
+                        const int nb = nf - b0 < RB ? nf - b0 : RB;
+                        if (nb > 8) {
+                            float d = warp_dist_rows<METRIC, 2>(p, sm, sm.Fs + b0, nb, qn2, lane);
+                            if ((lane & 1) == 0 && (lane >> 1) < nb)
+                                sm.Fk[b0 + (lane >> 1)] = make_key(d, (unsigned)sm.Fs[b0 + (lane >> 1)] << 1);
+                        } else {
+                            float d = warp_dist_rows<METRIC, 4>(p, sm, sm.Fs + b0, nb, qn2, lane);
+                            if ((lane & 3) == 0 && (lane >> 2) < nb)
+                                sm.Fk[b0 + (lane >> 2)] = make_key(d, (unsigned)sm.Fs[b0 + (lane >> 2)] << 1);
+                        }
                     }
                     __syncwarp();
                     /* R ← ef smallest of R ∪ F */

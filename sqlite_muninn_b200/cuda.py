@@ -16,7 +16,8 @@ import numpy as np
 from .graph import FlatGraph
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-CUDA_SO = os.path.join(_HERE, "csrc", "libmuninn_cuda.so")
+# MUNINN_CUDA_SO: alternative build of the same library (kernel A/B experiments)
+CUDA_SO = os.environ.get("MUNINN_CUDA_SO") or os.path.join(_HERE, "csrc", "libmuninn_cuda.so")
 
 STATS_DTYPE = np.dtype([("n_dist", np.int64), ("n_dist_upper", np.int64), ("n_expand", np.int32),
                         ("n_greedy_steps", np.int32), ("term", np.int32), ("entry0", np.int32)])
