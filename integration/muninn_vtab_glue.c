@@ -1,0 +1,167 @@
+/*
+ * muninn_vtab_glue.c — the host-side C a maintainer adds to sqlite-muninn to route the
+ * hnsw_index KNN plan through libmuninn_cuda. It is compiled INTO the reference's extension
+ * (see integration/build_patched_ext.sh and INTEGRATION.md); the vtab, its SQL surface, the
+ * shadow tables and muninn.c stay as they are.
+ *
+ * The reference's call site is one line, /root/reference/src/hnsw_vtab.c:604:
+ *     cur->result_count = hnsw_search(vtab->index, query, k, ef_search, cur->results);
+ * which becomes
+ *     cur->result_count = muninn_glue_search(vtab->index, query, k, ef_search, cur->results, &vtab->base.zErrMsg);
+ * plus a muninn_glue_mark_dirty(vtab->index) after each successful hnsw_insert / hnsw_delete
+ * in xUpdate (:698, :748) and a muninn_glue_release(vtab->index) before each hnsw_destroy in
+ * xDisconnect / xDestroy (:466, :474).
+ *
+ * The glue keeps one device handle per HnswIndex in a small side table, so the reference's
+ * structs need no new field. On the first search after a mutation it flattens the host index
+ * (every stored node, deleted ones included, neighbour lists in their live order) and
+ * re-uploads it: the dirty-flag rule of SURVEY.md §8b. There is no CPU fallback: a failure
+ * of the device path is reported through zErrMsg and the query fails.
+ */
+#include "hnsw_algo.h" /* the reference's header, -I<reference>/src */
+#include "muninn_cuda.h"
+#include "sqlite3ext.h"
+
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+SQLITE_EXTENSION_INIT3
+
+typedef struct {
+    const HnswIndex *index;
+    MuninnCudaIndex *handle;
+    int dirty;
+} GlueSlot;
+
+static GlueSlot *g_slots;
+static int g_nslots, g_capslots;
+
+static GlueSlot *slot_find(const HnswIndex *index, int create) {
+    for (int i = 0; i < g_nslots; i++)
+        if (g_slots[i].index == index) return &g_slots[i];
+    if (!create) return NULL;
+    if (g_nslots == g_capslots) {
+        int nc = g_capslots ? 2 * g_capslots : 8;
+        GlueSlot *ns = (GlueSlot *)realloc(g_slots, (size_t)nc * sizeof(GlueSlot));
+        if (!ns) return NULL;
+        g_slots = ns; g_capslots = nc;
+    }
+    g_slots[g_nslots] = (GlueSlot){index, NULL, 1};
+    return &g_slots[g_nslots++];
+}
+
+void muninn_glue_mark_dirty(const HnswIndex *index) {
+    GlueSlot *s = slot_find(index, 0);
+    if (s) s->dirty = 1;
+}
+
+void muninn_glue_release(const HnswIndex *index) {
+    GlueSlot *s = slot_find(index, 0);
+    if (!s) return;
+    muninn_cuda_index_destroy(s->handle);
+    *s = g_slots[--g_nslots];
+}
+
+static int cmp_i64(const void *a, const void *b) {
+    int64_t x = *(const int64_t *)a, y = *(const int64_t *)b;
+    return (x > y) - (x < y);
+}
+
+static int64_t slot_of(const int64_t *ids, int64_t n, int64_t id) {
+    int64_t lo = 0, hi = n - 1;
+    while (lo <= hi) {
+        int64_t mid = lo + (hi - lo) / 2;
+        if (ids[mid] == id) return mid;
+        if (ids[mid] < id) lo = mid + 1; else hi = mid - 1;
+    }
+    return -1;
+}
+
+/* host HnswIndex → the flat arrays of muninn_cuda_index_upload */
+static int glue_upload(GlueSlot *s, char **err) {
+    const HnswIndex *idx = s->index;
+    int64_t n = 0, n_lists = 0, n_edges = 0;
+    for (int i = 0; i < idx->node_capacity; i++) {
+        const HnswNode *nd = idx->nodes[i];
+        if (!nd) continue;
+        n++; n_lists += nd->level + 1;
+        for (int l = 0; l <= nd->level; l++) n_edges += nd->neighbor_count[l];
+    }
+    int64_t *ids = (int64_t *)malloc((size_t)(n + 1) * sizeof(int64_t));
+    int32_t *levels = (int32_t *)malloc((size_t)(n + 1) * sizeof(int32_t));
+    uint8_t *deleted = (uint8_t *)malloc((size_t)(n + 1));
+    float *vecs = (float *)malloc((size_t)(n + 1) * (size_t)idx->dim * sizeof(float));
+    int64_t *offs = (int64_t *)malloc((size_t)(n_lists + 1) * sizeof(int64_t));
+    int32_t *tg = (int32_t *)malloc((size_t)(n_edges + 1) * sizeof(int32_t));
+    int rc = MUNINN_CUDA_E_NOMEM;
+    if (ids && levels && deleted && vecs && offs && tg) {
+        int64_t k = 0;
+        for (int i = 0; i < idx->node_capacity; i++)
+            if (idx->nodes[i]) ids[k++] = idx->nodes[i]->id;
+        qsort(ids, (size_t)n, sizeof(int64_t), cmp_i64);
+        int64_t li = 0, e = 0;
+        offs[0] = 0;
+        for (int64_t sl = 0; sl < n; sl++) {
+            const HnswNode *nd = ht_find(idx->nodes, idx->node_capacity, ids[sl]);
+            levels[sl] = nd->level;
+            deleted[sl] = (uint8_t)(nd->deleted != 0);
+            memcpy(vecs + (size_t)sl * (size_t)idx->dim, nd->vector, (size_t)idx->dim * sizeof(float));
+            for (int l = 0; l <= nd->level; l++) {
+                /* the LIVE list order is kept: insertion order on a freshly built index, ascending
+                 * target id after xConnect reloaded it — so the device returns what the host
+                 * hnsw_search would return in either state (SURVEY.md finding 5) */
+                for (int j = 0; j < nd->neighbor_count[l]; j++)
+                    tg[e++] = (int32_t)slot_of(ids, n, nd->neighbors[l][j]);
+                offs[++li] = e;
+            }
+        }
+        int32_t entry = idx->entry_point == -1 ? -1 : (int32_t)slot_of(ids, n, idx->entry_point);
+        rc = muninn_cuda_index_upload(s->handle, n, ids, levels, deleted, vecs, offs, tg, entry, idx->max_level);
+        if (rc != MUNINN_CUDA_OK && err)
+            *err = sqlite3_mprintf("hnsw_index: GPU upload failed: %s", muninn_cuda_last_error(s->handle));
+    } else if (err) {
+        *err = sqlite3_mprintf("hnsw_index: out of memory flattening the index for upload");
+    }
+    free(ids); free(levels); free(deleted); free(vecs); free(offs); free(tg);
+    if (rc == MUNINN_CUDA_OK) s->dirty = 0;
+    return rc;
+}
+
+/* Drop-in for hnsw_search (src/hnsw_algo.h:73): same arguments and return value (number of
+ * results, 0 for an empty index); on a device failure returns 0 with *err set. */
+int muninn_glue_search(HnswIndex *index, const float *query, int k, int ef_search, HnswSearchResult *results,
+                       char **err) {
+    if (!index || index->entry_point == -1 || index->node_count == 0 || k < 1) return 0; /* hnsw_algo.c:671 */
+    GlueSlot *s = slot_find(index, 1);
+    if (!s) { if (err) *err = sqlite3_mprintf("hnsw_index: out of memory"); return 0; }
+    if (!s->handle) {
+        int dev = 0;
+        const char *env = getenv("MUNINN_CUDA_DEVICE");
+        if (env) dev = atoi(env);
+        int rc = muninn_cuda_index_create(dev, index->dim, (int)index->metric, index->M, &s->handle);
+        if (rc != MUNINN_CUDA_OK) {
+            if (err) *err = sqlite3_mprintf("hnsw_index: %s", muninn_cuda_last_error(NULL));
+            return 0;
+        }
+        s->dirty = 1;
+    }
+    if (s->dirty && glue_upload(s, err) != MUNINN_CUDA_OK) return 0;
+    int64_t *ids = (int64_t *)malloc((size_t)k * sizeof(int64_t));
+    float *dist = (float *)malloc((size_t)k * sizeof(float));
+    int32_t count = 0;
+    if (!ids || !dist) { free(ids); free(dist); if (err) *err = sqlite3_mprintf("hnsw_index: out of memory"); return 0; }
+    /* the blob pointer SQLite hands out may be unaligned (hnsw_vtab.c:588 casts it): copy */
+    float *q = (float *)malloc((size_t)index->dim * sizeof(float));
+    if (!q) { free(ids); free(dist); if (err) *err = sqlite3_mprintf("hnsw_index: out of memory"); return 0; }
+    memcpy(q, query, (size_t)index->dim * sizeof(float));
+    int rc = muninn_cuda_search_batch(s->handle, q, 1, k, ef_search, ids, dist, &count, NULL);
+    if (rc != MUNINN_CUDA_OK) {
+        if (err) *err = sqlite3_mprintf("hnsw_index: GPU search failed: %s", muninn_cuda_last_error(s->handle));
+        count = 0;
+    }
+    for (int i = 0; i < count; i++) { results[i].id = ids[i]; results[i].distance = dist[i]; }
+    free(ids); free(dist); free(q);
+    return count;
+}

@@ -1,0 +1,120 @@
+"""`-m gpu`: the drop-in boundary. The reference's extension with its KNN plan routed through
+libmuninn_cuda (integration/_build/muninn_cuda_ext.so: unchanged muninn.c, unchanged SQL
+surface, hnsw_vtab.c with the one-line call-site edit of INTEGRATION.md) must return what the
+UNMODIFIED reference extension returns for the same SQL, in every index state — freshly built,
+after deletes, after close/reopen — and reproduce the committed vtab fixtures.
+Mirrors /root/reference/pytests/test_hnsw_vtab.py."""
+import os
+import sqlite3
+
+import numpy as np
+import pytest
+
+from tests.conftest import ROOT, uniform
+from tests.helpers import load_golden
+
+pytestmark = pytest.mark.gpu
+CUDA_EXT = os.path.join(ROOT, "integration", "_build", "muninn_cuda_ext.so")
+METRIC_SQL = {0: "l2", 1: "cosine", 2: "inner_product"}
+
+
+def connect(path, ext):
+    conn = sqlite3.connect(path)
+    conn.enable_load_extension(True)
+    conn.load_extension(ext, entrypoint="sqlite3_muninn_init")
+    return conn
+
+
+@pytest.fixture(scope="module")
+def exts():
+    from oracle.bindings import REF_EXT_SO
+    if not os.path.exists(CUDA_EXT):
+        pytest.skip("integration/_build/muninn_cuda_ext.so not built (needs /root/reference at build time)")
+    return CUDA_EXT, (REF_EXT_SO if os.path.exists(REF_EXT_SO) else None)
+
+
+def knn(conn, q, k, ef=None):
+    if ef is None:
+        return conn.execute("SELECT rowid, distance FROM t WHERE vector MATCH ? AND k = ?", (q.tobytes(), k)).fetchall()
+    return conn.execute("SELECT rowid, distance FROM t WHERE vector MATCH ? AND k = ? AND ef_search = ?",
+                        (q.tobytes(), k, ef)).fetchall()
+
+
+@pytest.mark.parametrize("name", ["vtab_l2_400x16", "vtab_cosine_300x24", "vtab_ip_256x10", "vtab_l2_delete_200x8"])
+def test_vtab_reproduces_reference_fixture(exts, tmp_path, name):
+    """Rebuild the fixture's table with SQL INSERTs through the patched extension, reopen, query:
+    rowids and (double) distances equal those the unmodified reference returned."""
+    g, queries, k, cases = load_golden(name)
+    path = str(tmp_path / "g.db")
+    conn = connect(path, exts[0])
+    conn.execute(f"CREATE VIRTUAL TABLE t USING hnsw_index(dimensions={g.dim}, metric='{METRIC_SQL[g.metric]}', "
+                 f"m={g.M}, ef_construction={g.ef_construction})")
+    for i in range(g.n):
+        conn.execute("INSERT INTO t (rowid, vector) VALUES (?, ?)", (int(g.ids[i]), g.vectors[i].tobytes()))
+    for i in np.nonzero(g.deleted)[0]:
+        conn.execute("DELETE FROM t WHERE rowid = ?", (int(g.ids[i]),))
+    conn.commit()
+    conn.close()
+    conn = connect(path, exts[0])
+    efs = np.load(os.path.join(ROOT, "tests", "golden", name + ".npz"))["efs"]
+    for ef_raw, c in zip(efs, cases):
+        for qi, q in enumerate(queries):
+            rows = knn(conn, q, k, None if ef_raw < 0 else int(ef_raw))
+            n = int(c["cnt"][qi])
+            assert [r[0] for r in rows] == list(c["ids"][qi, :n]), (name, qi)
+            assert [r[1] for r in rows] == list(c["dist"][qi, :n]), (name, qi)
+    conn.close()
+
+
+def test_vtab_equals_unmodified_reference_in_every_state(exts, tmp_path):
+    if exts[1] is None:
+        pytest.skip("reference extension not built")
+    base, q = uniform(31, 600, 12), uniform(32, 40, 12)
+    conns = [connect(str(tmp_path / f"{i}.db"), e) for i, e in enumerate(exts)]
+    for c in conns:
+        c.execute("CREATE VIRTUAL TABLE t USING hnsw_index(dimensions=12, metric='l2', m=8, ef_construction=60)")
+        assert knn(c, q[0], 3) == []  # empty table
+        for i, v in enumerate(base[:400]):
+            c.execute("INSERT INTO t (rowid, vector) VALUES (?, ?)", (i * 2 + 1, v.tobytes()))
+
+    def same(tag):
+        for qi in range(40):
+            for k, ef in ((1, None), (5, None), (10, 64), (450, 500)):
+                a, b = knn(conns[0], q[qi], k, ef), knn(conns[1], q[qi], k, ef)
+                assert a == b, (tag, qi, k, ef)
+
+    same("fresh")  # list order = insertion order
+    for c in conns:
+        for i in range(0, 400, 7):
+            c.execute("DELETE FROM t WHERE rowid = ?", (i * 2 + 1,))
+    same("after delete")  # dirty flag → re-upload
+    for c in conns:
+        for i, v in enumerate(base[400:]):
+            c.execute("INSERT INTO t (rowid, vector) VALUES (?, ?)", (10_000 + i, v.tobytes()))
+    same("after more inserts")
+    for i, c in enumerate(conns):
+        c.commit()
+        c.close()
+    conns = [connect(str(tmp_path / f"{i}.db"), e) for i, e in enumerate(exts)]
+    same("reopened")  # xConnect → load_index_from_shadow → upload
+    # point lookup and vector column are served by the host copy, unchanged
+    for c in conns:
+        row = c.execute("SELECT vector FROM t WHERE rowid = 3").fetchone()
+        assert np.array_equal(np.frombuffer(row[0], np.float32), base[1])
+    for c in conns:
+        c.close()
+
+
+def test_vtab_errors_and_drop(exts, tmp_path):
+    conn = connect(str(tmp_path / "e.db"), exts[0])
+    conn.execute("CREATE VIRTUAL TABLE t USING hnsw_index(dimensions=3, metric='l2')")
+    conn.execute("INSERT INTO t (rowid, vector) VALUES (1, ?)", (np.float32([0, 0, 1]).tobytes(),))
+    with pytest.raises(sqlite3.OperationalError, match="expected 3-dim"):  # src/hnsw_vtab.c:595-597
+        knn(conn, np.float32([1, 2]), 1)
+    assert knn(conn, np.float32([0, 0, 0.9]), 5)[0][0] == 1  # k > n
+    with pytest.raises(sqlite3.OperationalError, match="unknown metric"):
+        conn.execute("CREATE VIRTUAL TABLE bad USING hnsw_index(dimensions=4, metric='hamming')")
+    conn.execute("DROP TABLE t")  # xDestroy releases the device handle
+    tables = {r[0] for r in conn.execute("SELECT name FROM sqlite_master").fetchall()}
+    assert not any(n.startswith("t_") for n in tables)
+    conn.close()
