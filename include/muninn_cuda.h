@@ -11,6 +11,7 @@
  *                                         (signature src/hnsw_algo.h:73), for nq queries at once
  *   muninn_cuda_search_batch_device       same, device-resident queries/results (benchmark `value`)
  *   muninn_cuda_exact_knn                 brute_force_knn test helper        test/test_hnsw_algo.c:10-34
+ *   muninn_cuda_set_exact_mode / _exact_stats / _exact_filter_probe   evaluation strategy of the same
  *   muninn_cuda_distance_batch            vec_get_distance_func(metric)(a,b) src/vec_math.c:180-190
  *   muninn_cuda_parse_metric              vec_parse_metric                   src/vec_math.c:192-204
  *
@@ -130,6 +131,35 @@ int muninn_cuda_exact_knn(MuninnCudaIndex *idx, const float *queries, int nq, in
                           int64_t *out_idx, float *out_dist, int32_t *out_count);
 int muninn_cuda_exact_knn_device(MuninnCudaIndex *idx, const float *d_queries, int nq, int k, int64_t index_base,
                                  int64_t *d_idx, float *d_dist, int32_t *d_count);
+/*
+ * How exact k-NN is evaluated. The OUTPUT is identical in every mode (bit-exact ids and distances,
+ * tests/test_gpu_exact_tc.py); the modes differ in how the n·nq distance evaluations are pruned.
+ *   MUNINN_EXACT_CUDA_CORE   every pair in the reference's fp32 chain order on the CUDA cores
+ *   MUNINN_EXACT_TC_3XTF32   (default) tiled Q·Xᵀ on the tensor cores as 3xTF32 (tcgen05 + TMA + TMEM)
+ *                            with a fused per-tile selection against each query's running k-th
+ *                            distance; only the survivors are evaluated in the reference's order
+ *   MUNINN_EXACT_TC_1XTF32   same with a single TF32 product and a correspondingly wider margin
+ * tile_rows = base rows per CTA tile (0 = default 256, or 128). In the tensor-core modes the
+ * device entry point synchronises once with the host before it returns.
+ */
+enum { MUNINN_EXACT_CUDA_CORE = 0, MUNINN_EXACT_TC_3XTF32 = 1, MUNINN_EXACT_TC_1XTF32 = 2 };
+int muninn_cuda_set_exact_mode(MuninnCudaIndex *idx, int mode, int tile_rows);
+
+/* Counters of the handle's most recent exact k-NN call. */
+typedef struct {
+    int32_t mode;             /* MUNINN_EXACT_* that ran */
+    int32_t chunks;           /* row chunks (split → filter → re-rank rounds) */
+    int64_t candidates;       /* (query, row) pairs that survived the filter and were re-ranked exactly */
+    int32_t overflow_queries; /* queries whose survivor list overflowed; recomputed on the CUDA cores */
+    float filter_ms;          /* Σ device time of the tensor-core filter launches (CUDA events) */
+    float c_eps;              /* error constant of the filter: |d~ - d_ref| <= c_eps·(|q|² + |x|²), or c_eps for cosine */
+} MuninnExactStats;
+int muninn_cuda_exact_stats(MuninnCudaIndex *idx, MuninnExactStats *out);
+
+/* Error probe for the tests: the filter's approximate distance d~ of every (query, row) pair of
+ * rows [0, rows) → out_approx [nq × rows] (host buffers). Needs a tensor-core exact mode. */
+int muninn_cuda_exact_filter_probe(MuninnCudaIndex *idx, const float *queries, int nq, int64_t rows, float *out_approx);
+
 /* Merge `parts` per-shard result lists ([parts × nq × k], as gathered by ncclAllGather) into
  * the global top-k under the same (distance, index) order. Device buffers. */
 int muninn_cuda_topk_merge_device(MuninnCudaIndex *idx, int parts, int nq, int k, const int64_t *d_idx_parts,

@@ -187,19 +187,22 @@ exact_select(const float *__restrict__ panel, int panel_ld, int rows, unsigned r
     if (lane == 0) topk_size[q] = size;
 }
 
-/* keys → (index + base, distance, count) */
+/* keys → (index + base, distance, count); list q goes to output row qmap[q] when qmap is given */
 __global__ void exact_emit(const unsigned long long *__restrict__ topk, const int *__restrict__ topk_size, int nq, int k,
-                           long long index_base, int64_t *out_idx, float *out_dist, int32_t *out_count) {
+                           long long index_base, const int *__restrict__ qmap, int64_t *out_idx, float *out_dist,
+                           int32_t *out_count) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nq * k) return;
     int q = i / k, j = i % k;
     int sz = topk_size[q];
+    const int qo = qmap ? qmap[q] : q;
+    const size_t o = (size_t)qo * k + j;
     if (j < sz) {
         unsigned long long e = topk[i];
-        out_idx[i] = index_base + (long long)(unsigned)e;
-        out_dist[i] = okey_inv((unsigned)(e >> 32));
-    } else { out_idx[i] = -1; out_dist[i] = 0.0f; }
-    if (j == 0) out_count[q] = sz;
+        out_idx[o] = index_base + (long long)(unsigned)e;
+        out_dist[o] = okey_inv((unsigned)(e >> 32));
+    } else { out_idx[o] = -1; out_dist[o] = 0.0f; }
+    if (j == 0) out_count[qo] = sz;
 }
 
 /* merge `parts` gathered lists per query under (distance, index); one warp per query */

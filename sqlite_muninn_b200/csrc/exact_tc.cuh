@@ -1,0 +1,452 @@
+/*
+ * exact_tc.cuh — exact k-NN, tensor-core path (sm_100a: TMA → tcgen05.mma kind::tf32 → TMEM).
+ *
+ * Output contract is unchanged: the brute_force_knn helper of the reference's tests
+ * (test/test_hnsw_algo.c:10-34) with the reference's distance arithmetic (src/vec_math.c:78-143),
+ * ascending by (distance, row index), bit-exact against the CPU oracle. Bit-exact fp32 chains
+ * cannot be produced by the tensor pipe, so the tensor pipe is used as a PROVABLE FILTER and the
+ * few survivors are re-evaluated with the reference's arithmetic:
+ *
+ *   1. split      x = hi + lo with hi = x & 0xffffe000 (a TF32 value, so the tensor core sees it
+ *                 unchanged whatever its input rounding), lo = x − hi (exact in fp32), lo cut the
+ *                 same way. Rows of a chunk and the queries are split once into K-padded slabs.
+ *   2. filter     tiled Q·Xᵀ as 3xTF32 (lo·hi + hi·lo + hi·hi; NPASS = 1 keeps hi·hi only):
+ *                 128 queries × BN rows per CTA tile, operands staged by TMA into 128B-swizzled
+ *                 shared memory, tcgen05.mma issued by one thread, fp32 accumulators in TMEM,
+ *                 double-buffered so the epilogue of tile i overlaps the MMAs of tile i+1.
+ *                 Fused per-tile selection in the epilogue: thread = one query (one TMEM lane);
+ *                 a row survives unless its approximate distance provably exceeds the query's
+ *                 current k-th exact distance τ_q:   d̃ > τ_q + ε(q, x).
+ *   3. re-rank    one warp per query: reference-order fp32 distance of every survivor, merged into
+ *                 the query's sorted (distance, row) list; τ_q ← its k-th entry.
+ *
+ * The base is processed in chunks whose size doubles (first chunk = the candidate capacity, every
+ * row of which survives because τ = +inf), so each chunk yields ≈ k survivors per query.
+ *
+ * Soundness: a row of the true top-k has d_ref ≤ τ_q at all times; with |d̃ − d_ref| ≤ ε it can
+ * never satisfy d̃ > τ_q + ε. ε = c·(‖q‖² + ‖x‖²) (L2, inner product) or c (cosine) with
+ * c = 2·(3·2⁻²⁰ + 3K·2⁻²³) + 4(K/4 + 8)·2⁻²⁴ for 3xTF32 — twice the worst-case split + fp32
+ * accumulation error of the K-term contraction plus the rounding of the reference's own chain and
+ * of the norms; tests/test_gpu_exact_tc.py measures the actual error against this bound. The test
+ * is written `!(d̃ > thr)` so a NaN anywhere keeps the row. A query whose survivors overflow its
+ * candidate list (massive ties, e.g. duplicated rows) is flagged and recomputed by the CUDA-core
+ * path (exact_knn.cuh) — still exact, only slower.
+ */
+#pragma once
+#include "muninn_dev.cuh"
+#include <cuda.h> /* CUtensorMap and its enums only; cuTensorMapEncodeTiled is looked up at run time */
+
+namespace muninn {
+namespace tc {
+
+constexpr int BM = 128;          /* queries per tile = TMEM lanes */
+constexpr int BK = 32;           /* fp32 per k-block: one 128-byte swizzle row */
+constexpr int UK = 8;            /* K of one tcgen05.mma.kind::tf32 */
+constexpr int THREADS = 192;     /* warp 0 TMA producer, warp 1 MMA issuer, warps 2-5 epilogue */
+constexpr unsigned TF32_MASK = 0xffffe000u;
+
+/* ───────────── PTX wrappers ───────────── */
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t done;
+    const uint32_t a = smem_u32(bar);
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done)
+                     : "r"(a), "r"(parity)
+                     : "memory");
+    } while (!done);
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, uint64_t *bar, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+                 : "memory");
+}
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap *map) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t *dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+/* arrives on the mbarrier once every tcgen05.mma issued so far by this thread has completed */
+__device__ __forceinline__ void tc_commit(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+/* D[tmem] (+)= A[smem] · B[smem]ᵀ, both operands K-major, TF32 inputs, fp32 accumulate */
+__device__ __forceinline__ void mma_tf32_ss(uint32_t d_tmem, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\t"
+                 "setp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+                 : "memory");
+}
+/* 32 lanes × 32 consecutive columns → 32 registers per thread (thread = lane) */
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                   "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                   "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                 : "r"(taddr)
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+/* shared-memory matrix descriptor of a K-major tile whose rows are 128 bytes, 128B-swizzled (what
+ * TMA writes with CU_TENSOR_MAP_SWIZZLE_128B): 8-row groups 1024 bytes apart, sm_100 descriptor
+ * version 1. The tile base must be 1024-byte aligned; a K step of UK elements inside the swizzle
+ * row is an address advance of UK*4 bytes. */
+__device__ __forceinline__ uint64_t make_desc_k128(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3ffffu) >> 4);
+    d |= (uint64_t)1 << 16;             /* leading byte offset: unused with a swizzled K-major tile */
+    d |= (uint64_t)(1024 >> 4) << 32;   /* stride byte offset between 8-row groups */
+    d |= (uint64_t)1 << 46;             /* descriptor version (Blackwell) */
+    d |= (uint64_t)2 << 61;             /* SWIZZLE_128B */
+    return d;
+}
+/* instruction descriptor: D fp32, A and B TF32, both K-major, M = 128, N = bn */
+__host__ __device__ constexpr uint32_t make_idesc_tf32(int bn) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(bn >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+}
+
+/* ───────────── filter kernel ───────────── */
+
+struct FilterParams {
+    const float *xnorm2; /* [n] Σx² per row of the handle, reference chain order */
+    const float *qaux;   /* [nq] Σq² (L2, inner product) or 1/√Σq² (cosine; NaN when Σq² < 1e-18) */
+    const float *tau;    /* [nq] current k-th exact distance (+inf while fewer than k rows were seen) */
+    int *cand;           /* [nq × cand_cap] surviving row indices of this chunk */
+    int *cand_count;     /* [nq] */
+    int cand_cap;
+    long long row0;      /* first row of the chunk (the x tensor maps start there) */
+    int rows, nq, kblocks;
+    float c_eps;
+    float *dbg_panel;    /* optional [nq × dbg_ld]: d̃ of every pair of the chunk (error probe) */
+    int dbg_ld;
+};
+
+template <int NPASS, int BN>
+struct FilterCfg {
+    static constexpr int SLABS = NPASS == 3 ? 2 : 1;
+    static constexpr int A_BYTES = BM * BK * 4, B_BYTES = BN * BK * 4;
+    static constexpr int STAGE_BYTES = SLABS * (A_BYTES + B_BYTES);
+    static constexpr int NSTAGES = (200 * 1024) / STAGE_BYTES > 8 ? 8 : (200 * 1024) / STAGE_BYTES;
+    static constexpr int TMEM_COLS = 2 * BN;
+    /* stages | xaux[2][BN] | barriers (2·NSTAGES + 4) | tmem pointer ; + 1024 alignment slack */
+    static constexpr size_t SMEM_BYTES = 1024 + (size_t)NSTAGES * STAGE_BYTES + 2 * BN * 4 + (2 * NSTAGES + 4) * 8 + 16;
+};
+
+template <int METRIC, int NPASS, int BN>
+__global__ void __launch_bounds__(THREADS, 1)
+exact_tc_filter(const __grid_constant__ CUtensorMap tm_qhi, const __grid_constant__ CUtensorMap tm_qlo,
+                const __grid_constant__ CUtensorMap tm_xhi, const __grid_constant__ CUtensorMap tm_xlo,
+                const FilterParams p) {
+    using Cfg = FilterCfg<NPASS, BN>;
+    constexpr int NST = Cfg::NSTAGES;
+    extern __shared__ unsigned char smem_dyn[];
+    unsigned char *base = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~(uintptr_t)1023);
+    unsigned char *stages = base;
+    float *xaux = reinterpret_cast<float *>(base + (size_t)NST * Cfg::STAGE_BYTES);
+    uint64_t *full = reinterpret_cast<uint64_t *>(xaux + 2 * BN);
+    uint64_t *empty = full + NST;
+    uint64_t *tmem_full = empty + NST;
+    uint64_t *tmem_empty = tmem_full + 2;
+    uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_qt = (p.nq + BM - 1) / BM, n_xt = (p.rows + BN - 1) / BN;
+    const long long n_tiles = (long long)n_qt * n_xt;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tm_qhi); prefetch_tmap(&tm_xhi);
+        if (NPASS == 3) { prefetch_tmap(&tm_qlo); prefetch_tmap(&tm_xlo); }
+        for (int s = 0; s < NST; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (int a = 0; a < 2; a++) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], 4); }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_ptr, Cfg::TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp == 0) {
+        /* ── TMA producer: one thread streams the k-blocks of every tile through the stage ring ── */
+        if (lane == 0) {
+            int s = 0; uint32_t ph = 0;
+            for (long long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+                const int xt = (int)(t / n_qt), qt = (int)(t % n_qt);
+                for (int kb = 0; kb < p.kblocks; kb++) {
+                    mbar_wait(&empty[s], ph ^ 1);
+                    unsigned char *st = stages + (size_t)s * Cfg::STAGE_BYTES;
+                    mbar_expect_tx(&full[s], Cfg::STAGE_BYTES);
+                    tma_load_2d(st, &tm_qhi, &full[s], kb * BK, qt * BM);
+                    tma_load_2d(st + Cfg::A_BYTES, &tm_xhi, &full[s], kb * BK, xt * BN);
+                    if (NPASS == 3) {
+                        tma_load_2d(st + Cfg::A_BYTES + Cfg::B_BYTES, &tm_qlo, &full[s], kb * BK, qt * BM);
+                        tma_load_2d(st + 2 * Cfg::A_BYTES + Cfg::B_BYTES, &tm_xlo, &full[s], kb * BK, xt * BN);
+                    }
+                    if (++s == NST) { s = 0; ph ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        /* ── MMA issuer: one thread; accumulator stage a = tile parity ── */
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc_tf32(BN);
+            int s = 0; uint32_t ph = 0; int a = 0; uint32_t aph = 0;
+            for (long long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+                mbar_wait(&tmem_empty[a], aph ^ 1); /* the epilogue has drained this accumulator */
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(a * BN);
+                for (int kb = 0; kb < p.kblocks; kb++) {
+                    mbar_wait(&full[s], ph);
+                    tc_fence_after();
+                    const uint32_t st = smem_u32(stages + (size_t)s * Cfg::STAGE_BYTES);
+                    const uint64_t a_hi = make_desc_k128(st), b_hi = make_desc_k128(st + Cfg::A_BYTES);
+                    uint32_t acc = kb > 0 ? 1u : 0u;
+                    if (NPASS == 3) { /* small terms first: lo·hi, hi·lo, then hi·hi */
+                        const uint64_t a_lo = make_desc_k128(st + Cfg::A_BYTES + Cfg::B_BYTES),
+                                       b_lo = make_desc_k128(st + 2 * Cfg::A_BYTES + Cfg::B_BYTES);
+#pragma unroll
+                        for (int k4 = 0; k4 < BK / UK; k4++) { mma_tf32_ss(d_tmem, a_lo + 2 * k4, b_hi + 2 * k4, idesc, acc); acc = 1u; }
+#pragma unroll
+                        for (int k4 = 0; k4 < BK / UK; k4++) mma_tf32_ss(d_tmem, a_hi + 2 * k4, b_lo + 2 * k4, idesc, 1u);
+                    }
+#pragma unroll
+                    for (int k4 = 0; k4 < BK / UK; k4++) { mma_tf32_ss(d_tmem, a_hi + 2 * k4, b_hi + 2 * k4, idesc, acc); acc = 1u; }
+                    tc_commit(&empty[s]); /* frees the stage once these MMAs have read it */
+                    if (kb == p.kblocks - 1) tc_commit(&tmem_full[a]);
+                    if (++s == NST) { s = 0; ph ^= 1; }
+                }
+                if (++a == 2) { a = 0; aph ^= 1; }
+            }
+        }
+    } else {
+        /* ── epilogue: 4 warps, warp w reads TMEM lanes 32·(w mod 4)…, thread = one query ── */
+        const int quarter = warp & 3, et = (warp - 2) * 32 + lane;
+        const int qrow = quarter * 32 + lane;
+        int a = 0; uint32_t aph = 0;
+        for (long long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+            const int xt = (int)(t / n_qt), qt = (int)(t % n_qt);
+            const int q = qt * BM + qrow;
+            const bool qvalid = q < p.nq;
+            const int ncols = p.rows - xt * BN < BN ? p.rows - xt * BN : BN;
+            const long long xrow0 = p.row0 + (long long)xt * BN;
+            float qa = 0.0f, tq = 0.0f;
+            if (qvalid) { qa = p.qaux[q]; tq = __ldcg(p.tau + q) + 1e-30f; }
+            if (METRIC == METRIC_COSINE) tq += p.c_eps;
+            float *xa = xaux + a * BN;
+            for (int j = et; j < BN; j += 128) {
+                float v = 0.0f;
+                if (j < ncols) {
+                    v = p.xnorm2[xrow0 + j];
+                    if (METRIC == METRIC_COSINE) v = v < 1e-18f ? __int_as_float(0x7fc00000) : rsqrtf(v);
+                }
+                xa[j] = v;
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            mbar_wait(&tmem_full[a], aph);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(a * BN);
+            for (int c0 = 0; c0 < ncols; c0 += 32) {
+                uint32_t v[32];
+                tmem_ld32(taddr + (uint32_t)c0, v);
+                tmem_ld_wait();
+                if (qvalid) {
+#pragma unroll
+                    for (int j = 0; j < 32; j++) {
+                        const float s = __uint_as_float(v[j]);
+                        const float x = xa[c0 + j];
+                        float d, thr;
+                        if (METRIC == METRIC_L2) { const float u = qa + x; d = fmaf(-2.0f, s, u); thr = fmaf(p.c_eps, u, tq); }
+                        else if (METRIC == METRIC_IP) { const float u = qa + x; d = -s; thr = fmaf(p.c_eps, u, tq); }
+                        else { d = fmaf(-(s * x), qa, 1.0f); thr = tq; }
+                        if (p.dbg_panel && c0 + j < ncols)
+                            p.dbg_panel[(size_t)q * p.dbg_ld + (size_t)(xrow0 - p.row0) + c0 + j] = d;
+                        if (!(d > thr) && c0 + j < ncols) {
+                            const int pos = atomicAdd(p.cand_count + q, 1);
+                            if (pos < p.cand_cap) p.cand[(size_t)q * p.cand_cap + pos] = (int)(xrow0 + c0 + j);
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[a]);
+            if (++a == 2) { a = 0; aph ^= 1; }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, Cfg::TMEM_COLS); }
+}
+
+/* ───────────── split / prepare ───────────── */
+
+__device__ __forceinline__ void split_tf32(float x, float &hi, float &lo) {
+    hi = __uint_as_float(__float_as_uint(x) & TF32_MASK);
+    lo = __uint_as_float(__float_as_uint(__fsub_rn(x, hi)) & TF32_MASK); /* x − hi is exact */
+}
+
+/* rows [0, rows) of src (row stride ld_src floats, `dim` valid) → hi / lo slabs [rows × kp], zero padded */
+__global__ void tc_split_rows(const float *__restrict__ src, int ld_src, int dim, long long rows, int kp,
+                              float *__restrict__ hi, float *__restrict__ lo) {
+    const long long total = rows * (long long)(kp >> 2);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long r = i / (kp >> 2);
+        const int c = (int)(i % (kp >> 2)) * 4;
+        float v[4], h[4], l[4];
+        if ((ld_src & 3) == 0 && c + 4 <= ld_src) {
+            const float4 t = *reinterpret_cast<const float4 *>(src + r * ld_src + c);
+            v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+#pragma unroll
+            for (int j = 0; j < 4; j++) if (c + j >= dim) v[j] = 0.0f;
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; j++) v[j] = c + j < dim ? src[r * ld_src + c + j] : 0.0f;
+        }
+#pragma unroll
+        for (int j = 0; j < 4; j++) split_tf32(v[j], h[j], l[j]);
+        *reinterpret_cast<float4 *>(hi + r * kp + c) = make_float4(h[0], h[1], h[2], h[3]);
+        if (lo) *reinterpret_cast<float4 *>(lo + r * kp + c) = make_float4(l[0], l[1], l[2], l[3]);
+    }
+}
+
+/* per query: Σq² in chain order → qaux; τ = +inf; empty candidate list, empty top-k, no overflow */
+template <int METRIC>
+__global__ void tc_prep_queries(const float *__restrict__ queries, int dim, int nq, float *__restrict__ qaux,
+                                float *__restrict__ tau, int *__restrict__ cand_count, int *__restrict__ topk_size,
+                                int *__restrict__ overflow) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nq) return;
+    const float n2 = chained_sum_serial<METRIC_IP>(queries + (size_t)q * dim, queries + (size_t)q * dim, dim);
+    float a = n2;
+    if (METRIC == METRIC_COSINE) a = n2 < 1e-18f ? __int_as_float(0x7fc00000) : rsqrtf(n2);
+    qaux[q] = a;
+    tau[q] = __int_as_float(0x7f800000);
+    cand_count[q] = 0; topk_size[q] = 0; overflow[q] = 0;
+}
+
+/* ───────────── re-rank ───────────── */
+
+/* chained sum of the reference's loop for one (query, row) pair, computed by 4 adjacent lanes:
+ * lane h owns SSE lane h (elements i ≡ h mod 4, ascending), then ((s0+s1)+s2)+s3 and the scalar
+ * tail (src/vec_math.c:82-94). All 4 lanes return the sum. */
+template <int METRIC>
+__device__ __forceinline__ float quad_chain(const float *__restrict__ q, const float *__restrict__ x, int dim, int lane, bool have) {
+    const int h = lane & 3, g = lane & ~3, cfull = dim >> 2;
+    float s = 0.0f;
+    if (have)
+        for (int c = 0; c < cfull; c++) {
+            const float a = q[4 * c + h], b = x[4 * c + h];
+            float pr;
+            if (METRIC == METRIC_L2) { const float d = __fsub_rn(a, b); pr = __fmul_rn(d, d); } else pr = __fmul_rn(a, b);
+            s = __fadd_rn(s, pr);
+        }
+    const float c0 = __shfl_sync(FULL, s, g), c1 = __shfl_sync(FULL, s, g + 1), c2 = __shfl_sync(FULL, s, g + 2),
+                c3 = __shfl_sync(FULL, s, g + 3);
+    float sum = __fadd_rn(__fadd_rn(__fadd_rn(c0, c1), c2), c3);
+    if (have)
+        for (int i = cfull * 4; i < dim; i++) {
+            const float a = q[i], b = x[i];
+            float pr;
+            if (METRIC == METRIC_L2) { const float d = __fsub_rn(a, b); pr = __fmul_rn(d, d); } else pr = __fmul_rn(a, b);
+            sum = __fadd_rn(sum, pr);
+        }
+    return sum;
+}
+
+/* one warp per query: exact distances of the chunk's survivors → sorted top-k → τ */
+template <int METRIC>
+__global__ void __launch_bounds__(128)
+exact_tc_rerank(const float *__restrict__ vec, const float *__restrict__ norm2, const uint8_t *__restrict__ deleted, int ld,
+                int dim, const float *__restrict__ queries, int nq, int k, const int *__restrict__ cand,
+                int *__restrict__ cand_count, int cap, unsigned long long *__restrict__ topk, int *__restrict__ topk_size,
+                float *__restrict__ tau, int *__restrict__ overflow, unsigned long long *__restrict__ n_cand_total) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int q = blockIdx.x * 4 + wib;
+    unsigned long long *R = reinterpret_cast<unsigned long long *>(smem_raw) + (size_t)wib * (k + 32);
+    unsigned long long *S = R + k;
+    if (q >= nq) return;
+    int cnt = cand_count[q];
+    if (cnt > cap) { if (lane == 0) overflow[q] = 1; cnt = cap; }
+    int size = topk_size[q];
+    if (cnt > 0) {
+        for (int i = lane; i < size; i += 32) R[i] = topk[(size_t)q * k + i];
+        __syncwarp();
+        const float *qv = queries + (size_t)q * dim;
+        float qn2 = 0.0f;
+        if (METRIC == METRIC_COSINE) qn2 = quad_chain<METRIC_IP>(qv, qv, dim, lane, true);
+        int ev = 0, mp;
+        for (int c0 = 0; c0 < cnt; c0 += 8) {
+            const int ci = c0 + (lane >> 2);
+            const bool have = ci < cnt;
+            const int row = have ? cand[(size_t)q * cap + ci] : 0;
+            const float sum = quad_chain<METRIC>(qv, vec + (size_t)row * ld, dim, lane, have);
+            float d;
+            if (METRIC == METRIC_L2) d = sum;
+            else if (METRIC == METRIC_IP) d = -sum;
+            else d = cosine_finish(sum, qn2, have ? norm2[row] : 1.0f);
+            const bool live = have && (lane & 3) == 0 && !(deleted && deleted[row]);
+            const unsigned long long worst = size >= k ? R[k - 1] : KEY_NONE;
+            const unsigned long long f = live ? make_key(d, (unsigned)row) : KEY_NONE;
+            const bool keep = f < worst;
+            const unsigned km = __ballot_sync(FULL, keep);
+            const int ns = __popc(km);
+            if (ns == 0) continue;
+            if (keep) S[__popc(km & ((1u << lane) - 1))] = f;
+            __syncwarp();
+            size = warp_merge_sorted(R, size, k, S, ns, lane, &mp, &ev);
+        }
+        __syncwarp();
+        for (int i = lane; i < size; i += 32) topk[(size_t)q * k + i] = R[i];
+        if (lane == 0) {
+            topk_size[q] = size;
+            if (size >= k) tau[q] = okey_inv((unsigned)(R[k - 1] >> 32));
+            cand_count[q] = 0;
+            atomicAdd(n_cand_total, (unsigned long long)cnt);
+        }
+    }
+}
+
+/* flagged queries → dense list (order irrelevant) */
+__global__ void tc_compact_overflow(const int *__restrict__ overflow, int nq, int *__restrict__ qmap, int *__restrict__ n_flag) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q < nq && overflow[q]) qmap[atomicAdd(n_flag, 1)] = q;
+}
+__global__ void tc_gather_queries(const float *__restrict__ queries, int dim, const int *__restrict__ qmap, int n,
+                                  float *__restrict__ out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < (long long)n * dim) out[i] = queries[(size_t)qmap[i / dim] * dim + i % dim];
+}
+
+} // namespace tc
+} // namespace muninn

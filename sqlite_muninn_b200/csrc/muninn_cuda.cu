@@ -13,6 +13,7 @@
  */
 #include "../../include/muninn_cuda.h"
 #include "exact_knn.cuh"
+#include "exact_tc.cuh"
 #include "hnsw_search.cuh"
 
 #include <algorithm>
@@ -51,6 +52,18 @@ struct MuninnCudaIndex {
     /* exact k-NN scratch */
     float *d_panel = nullptr; size_t panel_floats = 0;
     unsigned long long *d_topk = nullptr; int *d_topk_size = nullptr; size_t topk_cap = 0, topk_q = 0;
+    /* exact k-NN, tensor-core filter (exact_tc.cuh) */
+    int exact_mode = MUNINN_EXACT_TC_3XTF32, tc_tile_rows = 256;
+    float *d_qsplit = nullptr; size_t qsplit_floats = 0;   /* q_hi | q_lo, [nq × kp] each */
+    float *d_xsplit = nullptr; size_t xsplit_floats = 0;   /* x_hi | x_lo of one chunk */
+    float *d_qaux = nullptr, *d_tau = nullptr; int *d_cand_count = nullptr, *d_overflow = nullptr, *d_qmap = nullptr;
+    size_t tcq_cap = 0;
+    int *d_cand = nullptr; size_t cand_entries = 0;
+    float *d_qgather = nullptr; size_t qgather_floats = 0;
+    float *d_dbg = nullptr; size_t dbg_floats = 0;
+    unsigned long long *d_tc_ctr = nullptr;                /* [0] survivors re-ranked, [1] flagged queries (int) */
+    std::vector<cudaEvent_t> tc_ev;
+    MuninnExactStats exact_stats = {};
     std::string err;
 };
 
@@ -150,6 +163,10 @@ extern "C" void muninn_cuda_index_destroy(MuninnCudaIndex *h) {
     free_graph(h);
     cudaFree(h->d_vis); cudaFree(h->d_ctl); cudaFree(h->d_retry); cudaFree(h->d_stage);
     cudaFree(h->d_panel); cudaFree(h->d_topk); cudaFree(h->d_topk_size);
+    cudaFree(h->d_qsplit); cudaFree(h->d_xsplit); cudaFree(h->d_qaux); cudaFree(h->d_tau); cudaFree(h->d_cand_count);
+    cudaFree(h->d_overflow); cudaFree(h->d_qmap); cudaFree(h->d_cand); cudaFree(h->d_qgather); cudaFree(h->d_dbg);
+    cudaFree(h->d_tc_ctr);
+    for (cudaEvent_t e : h->tc_ev) cudaEventDestroy(e);
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
@@ -423,14 +440,22 @@ static void launch_dist_tile(MuninnCudaIndex *h, long long row0, int rows, const
                                                          nq, h->d_panel, panel_ld);
 }
 
-extern "C" int muninn_cuda_exact_knn_device(MuninnCudaIndex *h, const float *d_queries, int nq, int k,
-                                            int64_t index_base, int64_t *d_idx, float *d_dist, int32_t *d_count) {
-    if (!h) return MUNINN_CUDA_E_ARG;
-    if (!h->uploaded) return fail(h, MUNINN_CUDA_E_STATE, "exact k-NN before muninn_cuda_index_upload");
-    if (nq < 0 || k < 1 || k > 2048) return fail(h, MUNINN_CUDA_E_ARG, "need nq >= 0 and 1 <= k <= 2048 (nq=%d k=%d)", nq, k);
-    if (nq == 0) return MUNINN_CUDA_OK;
-    if (!d_queries || !d_idx || !d_dist || !d_count) return fail(h, MUNINN_CUDA_E_ARG, "NULL buffer");
-    CK(h, cudaSetDevice(h->device));
+static int ensure_topk(MuninnCudaIndex *h, int nq, int k) {
+    if ((size_t)nq * k > h->topk_cap || (size_t)nq > h->topk_q) {
+        CK(h, cudaStreamSynchronize(h->stream));
+        cudaFree(h->d_topk); cudaFree(h->d_topk_size); h->d_topk = nullptr; h->d_topk_size = nullptr;
+        h->topk_cap = h->topk_q = 0;
+        CK(h, cudaMalloc((void **)&h->d_topk, (size_t)nq * k * 8));
+        CK(h, cudaMalloc((void **)&h->d_topk_size, (size_t)nq * 4));
+        h->topk_cap = (size_t)nq * k; h->topk_q = (size_t)nq;
+    }
+    return MUNINN_CUDA_OK;
+}
+
+/* CUDA-core path: reference-order chains for every (query, row) pair. List q is written to
+ * output row d_qmap[q] when d_qmap is given (the tensor path's overflow fallback). */
+static int exact_knn_cudacore(MuninnCudaIndex *h, const float *d_queries, int nq, int k, int64_t index_base,
+                              const int *d_qmap, int64_t *d_idx, float *d_dist, int32_t *d_count) {
     /* distance panel: at most 1 GiB, whole 64-row tiles */
     long long chunk = (long long)((1ull << 28) / (unsigned long long)nq);
     chunk = std::max<long long>(XT, chunk / XT * XT);
@@ -442,18 +467,12 @@ extern "C" int muninn_cuda_exact_knn_device(MuninnCudaIndex *h, const float *d_q
         CK(h, cudaMalloc((void **)&h->d_panel, need * 4));
         h->panel_floats = need;
     }
-    if ((size_t)nq * k > h->topk_cap || (size_t)nq > h->topk_q) {
-        CK(h, cudaStreamSynchronize(h->stream));
-        cudaFree(h->d_topk); cudaFree(h->d_topk_size); h->d_topk = nullptr; h->d_topk_size = nullptr;
-        CK(h, cudaMalloc((void **)&h->d_topk, (size_t)nq * k * 8));
-        CK(h, cudaMalloc((void **)&h->d_topk_size, (size_t)nq * 4));
-        h->topk_cap = (size_t)nq * k; h->topk_q = (size_t)nq;
-    }
+    int rc = ensure_topk(h, nq, k);
+    if (rc) return rc;
     CK(h, cudaMemsetAsync(h->d_topk_size, 0, (size_t)nq * 4, h->stream));
     const size_t sel_smem = (size_t)4 * (k + 32) * 8;
     if (sel_smem > 48 * 1024)
         CK(h, cudaFuncSetAttribute(exact_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sel_smem));
-    CK(h, cudaEventRecord(h->ev0, h->stream));
     for (long long row0 = 0; row0 < h->n; row0 += chunk) {
         const int rows = (int)std::min<long long>(chunk, h->n - row0);
         if (h->metric == MUNINN_METRIC_L2) launch_dist_tile<METRIC_L2>(h, row0, rows, d_queries, nq, (int)chunk);
@@ -465,11 +484,266 @@ extern "C" int muninn_cuda_exact_knn_device(MuninnCudaIndex *h, const float *d_q
         CK(h, cudaGetLastError());
     }
     exact_emit<<<(unsigned)(((size_t)nq * k + 255) / 256), 256, 0, h->stream>>>(h->d_topk, h->d_topk_size, nq, k, index_base,
-                                                                               d_idx, d_dist, d_count);
+                                                                               d_qmap, d_idx, d_dist, d_count);
     h->launches++;
     CK(h, cudaGetLastError());
+    return MUNINN_CUDA_OK;
+}
+
+/* ── tensor-core filter path (exact_tc.cuh) ── */
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn tensor_map_encoder() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *sym = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)sym;
+    }
+    return fn;
+}
+
+/* [rows × kp] fp32, row-major; box = 32 floats (one 128-byte swizzle row) × box_rows */
+static int make_slab_map(MuninnCudaIndex *h, CUtensorMap *map, const float *ptr, int kp, long long rows, int box_rows) {
+    EncodeTiledFn enc = tensor_map_encoder();
+    if (!enc) return fail(h, MUNINN_CUDA_E_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+    cuuint64_t dims[2] = {(cuuint64_t)kp, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)kp * 4};
+    cuuint32_t box[2] = {(cuuint32_t)tc::BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(h, MUNINN_CUDA_E_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return MUNINN_CUDA_OK;
+}
+
+template <typename T>
+static cudaError_t grow(T **ptr, size_t *have, size_t need, cudaStream_t st) {
+    if (need <= *have) return cudaSuccess;
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) return e;
+    cudaFree(*ptr); *ptr = nullptr; *have = 0;
+    e = cudaMalloc((void **)ptr, need * sizeof(T));
+    if (e == cudaSuccess) *have = need;
+    return e;
+}
+
+/* error constant of the filter (exact_tc.cuh header): c such that |d̃ − d_ref| ≤ c·(‖q‖² + ‖x‖²) */
+static float tc_eps(int mode, int kp) {
+    const double split = mode == MUNINN_EXACT_TC_3XTF32 ? 3.0 * ldexp(1.0, -20) : ldexp(1.0, -9);
+    const double terms = mode == MUNINN_EXACT_TC_3XTF32 ? 3.0 * kp : 1.0 * kp;
+    return (float)(2.0 * (split + terms * ldexp(1.0, -23)) + 4.0 * (kp / 4.0 + 8.0) * ldexp(1.0, -24));
+}
+
+template <int METRIC, int NPASS, int BN>
+static cudaError_t launch_filter(MuninnCudaIndex *h, const CUtensorMap maps[4], const tc::FilterParams &fp) {
+    using Cfg = tc::FilterCfg<NPASS, BN>;
+    auto kern = tc::exact_tc_filter<METRIC, NPASS, BN>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    const long long tiles = (long long)((fp.nq + tc::BM - 1) / tc::BM) * ((fp.rows + BN - 1) / BN);
+    const int grid = (int)std::min<long long>(tiles, h->num_sms);
+    kern<<<grid, tc::THREADS, Cfg::SMEM_BYTES, h->stream>>>(maps[0], maps[1], maps[2], maps[3], fp);
+    return cudaGetLastError();
+}
+
+template <int METRIC>
+static cudaError_t launch_filter_m(MuninnCudaIndex *h, const CUtensorMap maps[4], const tc::FilterParams &fp) {
+    const bool three = h->exact_mode == MUNINN_EXACT_TC_3XTF32;
+    if (h->tc_tile_rows == 128)
+        return three ? launch_filter<METRIC, 3, 128>(h, maps, fp) : launch_filter<METRIC, 1, 128>(h, maps, fp);
+    return three ? launch_filter<METRIC, 3, 256>(h, maps, fp) : launch_filter<METRIC, 1, 256>(h, maps, fp);
+}
+
+/* Runs split → filter → re-rank over doubling chunks of rows [0, n_rows). With d_dbg set only the
+ * first chunk (all n_rows rows, τ = +inf) is filtered and its d̃ panel kept (error probe). */
+static int exact_knn_tc(MuninnCudaIndex *h, const float *d_queries, int nq, int k, int64_t index_base, int64_t *d_idx,
+                        float *d_dist, int32_t *d_count, float *d_dbg, long long dbg_rows) {
+    const int kp = (h->dim + tc::BK - 1) / tc::BK * tc::BK, bn = h->tc_tile_rows;
+    const bool three = h->exact_mode == MUNINN_EXACT_TC_3XTF32;
+    const int cap = d_dbg ? 256 : std::max(1024, (4 * k + 255) / 256 * 256);
+    const long long n = d_dbg ? dbg_rows : h->n;
+    /* row scratch: ≤ 1 GiB of split slabs per chunk, whole tiles */
+    long long chunk_max = (long long)((1ull << 30) / ((size_t)kp * 4 * (three ? 2 : 1)));
+    chunk_max = std::max<long long>(cap, chunk_max / 256 * 256);
+    if (d_dbg) chunk_max = std::max<long long>(chunk_max, n);
+    const long long xrows = std::min<long long>(chunk_max, std::max<long long>(n, 1));
+    cudaStream_t st = h->stream;
+    CK(h, grow(&h->d_qsplit, &h->qsplit_floats, (size_t)2 * nq * kp, st));
+    CK(h, grow(&h->d_xsplit, &h->xsplit_floats, (size_t)2 * xrows * kp, st));
+    if ((size_t)nq > h->tcq_cap) {
+        CK(h, cudaStreamSynchronize(st));
+        cudaFree(h->d_qaux); cudaFree(h->d_tau); cudaFree(h->d_cand_count); cudaFree(h->d_overflow); cudaFree(h->d_qmap);
+        h->d_qaux = h->d_tau = nullptr; h->d_cand_count = h->d_overflow = h->d_qmap = nullptr; h->tcq_cap = 0;
+        CK(h, cudaMalloc((void **)&h->d_qaux, (size_t)nq * 4)); CK(h, cudaMalloc((void **)&h->d_tau, (size_t)nq * 4));
+        CK(h, cudaMalloc((void **)&h->d_cand_count, (size_t)nq * 4)); CK(h, cudaMalloc((void **)&h->d_overflow, (size_t)nq * 4));
+        CK(h, cudaMalloc((void **)&h->d_qmap, (size_t)nq * 4));
+        h->tcq_cap = (size_t)nq;
+    }
+    CK(h, grow(&h->d_cand, &h->cand_entries, (size_t)nq * cap, st));
+    if (!h->d_tc_ctr) CK(h, cudaMalloc((void **)&h->d_tc_ctr, 16));
+    int rc = ensure_topk(h, nq, k);
+    if (rc) return rc;
+    CK(h, cudaMemsetAsync(h->d_tc_ctr, 0, 16, st));
+
+    float *q_hi = h->d_qsplit, *q_lo = h->d_qsplit + (size_t)nq * kp;
+    float *x_hi = h->d_xsplit, *x_lo = h->d_xsplit + (size_t)xrows * kp;
+    const int pq_grid = (nq + 127) / 128;
+    if (h->metric == MUNINN_METRIC_L2) tc::tc_prep_queries<METRIC_L2><<<pq_grid, 128, 0, st>>>(d_queries, h->dim, nq, h->d_qaux, h->d_tau, h->d_cand_count, h->d_topk_size, h->d_overflow);
+    else if (h->metric == MUNINN_METRIC_COSINE) tc::tc_prep_queries<METRIC_COSINE><<<pq_grid, 128, 0, st>>>(d_queries, h->dim, nq, h->d_qaux, h->d_tau, h->d_cand_count, h->d_topk_size, h->d_overflow);
+    else tc::tc_prep_queries<METRIC_IP><<<pq_grid, 128, 0, st>>>(d_queries, h->dim, nq, h->d_qaux, h->d_tau, h->d_cand_count, h->d_topk_size, h->d_overflow);
+    tc::tc_split_rows<<<h->num_sms * 8, 256, 0, st>>>(d_queries, h->dim, h->dim, nq, kp, q_hi, three ? q_lo : nullptr);
+    h->launches += 2;
+    CK(h, cudaGetLastError());
+
+    CUtensorMap maps[4];
+    rc = make_slab_map(h, &maps[0], q_hi, kp, nq, tc::BM);
+    if (!rc) rc = make_slab_map(h, &maps[1], three ? q_lo : q_hi, kp, nq, tc::BM);
+    if (rc) return rc;
+
+    const size_t rr_smem = (size_t)4 * (k + 32) * 8;
+    if (rr_smem > 48 * 1024) {
+        CK(h, cudaFuncSetAttribute(tc::exact_tc_rerank<METRIC_L2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rr_smem));
+        CK(h, cudaFuncSetAttribute(tc::exact_tc_rerank<METRIC_COSINE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rr_smem));
+        CK(h, cudaFuncSetAttribute(tc::exact_tc_rerank<METRIC_IP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rr_smem));
+    }
+    tc::FilterParams fp;
+    memset(&fp, 0, sizeof fp);
+    fp.xnorm2 = h->d_norm2; fp.qaux = h->d_qaux; fp.tau = h->d_tau; fp.cand = h->d_cand; fp.cand_count = h->d_cand_count;
+    fp.cand_cap = cap; fp.nq = nq; fp.kblocks = kp / tc::BK; fp.c_eps = tc_eps(h->exact_mode, kp);
+    fp.dbg_panel = d_dbg; fp.dbg_ld = (int)n;
+
+    int chunks = 0;
+    size_t ev_used = 0;
+    for (long long done = 0; done < n;) {
+        long long chunk = done == 0 ? std::min<long long>(cap, n) : std::min<long long>(std::min(done, chunk_max), n - done);
+        if (d_dbg) chunk = n;
+        tc::tc_split_rows<<<h->num_sms * 8, 256, 0, st>>>(h->d_vec + (size_t)done * h->ld, h->ld, h->dim, chunk, kp, x_hi,
+                                                          three ? x_lo : nullptr);
+        rc = make_slab_map(h, &maps[2], x_hi, kp, chunk, bn);
+        if (!rc) rc = make_slab_map(h, &maps[3], three ? x_lo : x_hi, kp, chunk, bn);
+        if (rc) return rc;
+        fp.row0 = done; fp.rows = (int)chunk;
+        while (h->tc_ev.size() < ev_used + 2) {
+            cudaEvent_t e;
+            CK(h, cudaEventCreate(&e));
+            h->tc_ev.push_back(e);
+        }
+        CK(h, cudaEventRecord(h->tc_ev[ev_used], st));
+        cudaError_t e = h->metric == MUNINN_METRIC_L2       ? launch_filter_m<METRIC_L2>(h, maps, fp)
+                        : h->metric == MUNINN_METRIC_COSINE ? launch_filter_m<METRIC_COSINE>(h, maps, fp)
+                                                            : launch_filter_m<METRIC_IP>(h, maps, fp);
+        CK(h, e);
+        CK(h, cudaEventRecord(h->tc_ev[ev_used + 1], st));
+        ev_used += 2;
+        h->launches += 2;
+        if (d_dbg) { chunks = 1; break; }
+        const int rr_grid = (nq + 3) / 4;
+        if (h->metric == MUNINN_METRIC_L2)
+            tc::exact_tc_rerank<METRIC_L2><<<rr_grid, 128, rr_smem, st>>>(h->d_vec, h->d_norm2, h->d_deleted, h->ld, h->dim, d_queries, nq, k, h->d_cand, h->d_cand_count, cap, h->d_topk, h->d_topk_size, h->d_tau, h->d_overflow, h->d_tc_ctr);
+        else if (h->metric == MUNINN_METRIC_COSINE)
+            tc::exact_tc_rerank<METRIC_COSINE><<<rr_grid, 128, rr_smem, st>>>(h->d_vec, h->d_norm2, h->d_deleted, h->ld, h->dim, d_queries, nq, k, h->d_cand, h->d_cand_count, cap, h->d_topk, h->d_topk_size, h->d_tau, h->d_overflow, h->d_tc_ctr);
+        else
+            tc::exact_tc_rerank<METRIC_IP><<<rr_grid, 128, rr_smem, st>>>(h->d_vec, h->d_norm2, h->d_deleted, h->ld, h->dim, d_queries, nq, k, h->d_cand, h->d_cand_count, cap, h->d_topk, h->d_topk_size, h->d_tau, h->d_overflow, h->d_tc_ctr);
+        h->launches++;
+        CK(h, cudaGetLastError());
+        done += chunk;
+        chunks++;
+    }
+    h->exact_stats.mode = h->exact_mode; h->exact_stats.chunks = chunks; h->exact_stats.c_eps = fp.c_eps;
+    h->exact_stats.candidates = 0; h->exact_stats.overflow_queries = 0;
+    if (d_dbg) {
+        CK(h, cudaStreamSynchronize(st));
+        float ms = 0.0f;
+        cudaEventElapsedTime(&ms, h->tc_ev[0], h->tc_ev[1]);
+        h->exact_stats.filter_ms = ms;
+        return MUNINN_CUDA_OK;
+    }
+    exact_emit<<<(unsigned)(((size_t)nq * k + 255) / 256), 256, 0, st>>>(h->d_topk, h->d_topk_size, nq, k, index_base, nullptr,
+                                                                        d_idx, d_dist, d_count);
+    int *d_nflag = reinterpret_cast<int *>(h->d_tc_ctr + 1);
+    tc::tc_compact_overflow<<<(nq + 255) / 256, 256, 0, st>>>(h->d_overflow, nq, h->d_qmap, d_nflag);
+    h->launches += 2;
+    CK(h, cudaGetLastError());
+    unsigned long long ctr[2] = {0, 0};
+    CK(h, cudaMemcpyAsync(ctr, h->d_tc_ctr, 16, cudaMemcpyDeviceToHost, st));
+    CK(h, cudaStreamSynchronize(st)); /* the one host round trip of this path: how many queries overflowed */
+    float fms = 0.0f;
+    for (size_t i = 0; i + 1 < ev_used; i += 2) {
+        float ms = 0.0f;
+        cudaEventElapsedTime(&ms, h->tc_ev[i], h->tc_ev[i + 1]);
+        fms += ms;
+    }
+    const int nflag = (int)(unsigned)ctr[1];
+    h->exact_stats.filter_ms = fms; h->exact_stats.candidates = (int64_t)ctr[0]; h->exact_stats.overflow_queries = nflag;
+    if (nflag > 0) {
+        CK(h, grow(&h->d_qgather, &h->qgather_floats, (size_t)nflag * h->dim, st));
+        tc::tc_gather_queries<<<(unsigned)(((size_t)nflag * h->dim + 255) / 256), 256, 0, st>>>(d_queries, h->dim, h->d_qmap, nflag,
+                                                                                             h->d_qgather);
+        h->launches++;
+        CK(h, cudaGetLastError());
+        rc = exact_knn_cudacore(h, h->d_qgather, nflag, k, index_base, h->d_qmap, d_idx, d_dist, d_count);
+        if (rc) return rc;
+    }
+    return MUNINN_CUDA_OK;
+}
+
+extern "C" int muninn_cuda_exact_knn_device(MuninnCudaIndex *h, const float *d_queries, int nq, int k, int64_t index_base,
+                                            int64_t *d_idx, float *d_dist, int32_t *d_count) {
+    if (!h) return MUNINN_CUDA_E_ARG;
+    if (!h->uploaded) return fail(h, MUNINN_CUDA_E_STATE, "exact k-NN before muninn_cuda_index_upload");
+    if (nq < 0 || k < 1 || k > 2048) return fail(h, MUNINN_CUDA_E_ARG, "need nq >= 0 and 1 <= k <= 2048 (nq=%d k=%d)", nq, k);
+    if (nq == 0) return MUNINN_CUDA_OK;
+    if (!d_queries || !d_idx || !d_dist || !d_count) return fail(h, MUNINN_CUDA_E_ARG, "NULL buffer");
+    CK(h, cudaSetDevice(h->device));
+    CK(h, cudaEventRecord(h->ev0, h->stream));
+    int rc;
+    if (h->exact_mode == MUNINN_EXACT_CUDA_CORE || h->n == 0) {
+        h->exact_stats = MuninnExactStats{};
+        rc = exact_knn_cudacore(h, d_queries, nq, k, index_base, nullptr, d_idx, d_dist, d_count);
+    } else {
+        rc = exact_knn_tc(h, d_queries, nq, k, index_base, d_idx, d_dist, d_count, nullptr, 0);
+    }
+    if (rc) return rc;
     CK(h, cudaEventRecord(h->ev1, h->stream));
     h->have_timing = true;
+    return MUNINN_CUDA_OK;
+}
+
+extern "C" int muninn_cuda_set_exact_mode(MuninnCudaIndex *h, int mode, int tile_rows) {
+    if (!h) return MUNINN_CUDA_E_ARG;
+    if (mode < MUNINN_EXACT_CUDA_CORE || mode > MUNINN_EXACT_TC_1XTF32) return fail(h, MUNINN_CUDA_E_ARG, "unknown exact mode %d", mode);
+    if (tile_rows != 0 && tile_rows != 128 && tile_rows != 256) return fail(h, MUNINN_CUDA_E_ARG, "tile_rows must be 0, 128 or 256");
+    h->exact_mode = mode;
+    h->tc_tile_rows = tile_rows ? tile_rows : 256;
+    return MUNINN_CUDA_OK;
+}
+
+extern "C" int muninn_cuda_exact_stats(MuninnCudaIndex *h, MuninnExactStats *out) {
+    if (!h || !out) return MUNINN_CUDA_E_ARG;
+    *out = h->exact_stats;
+    return MUNINN_CUDA_OK;
+}
+
+/* Error probe: d̃ of the filter for every (query, row) pair of rows [0, rows) → out_approx [nq × rows] (host). */
+extern "C" int muninn_cuda_exact_filter_probe(MuninnCudaIndex *h, const float *queries, int nq, int64_t rows, float *out_approx) {
+    if (!h) return MUNINN_CUDA_E_ARG;
+    if (!h->uploaded) return fail(h, MUNINN_CUDA_E_STATE, "probe before muninn_cuda_index_upload");
+    if (h->exact_mode == MUNINN_EXACT_CUDA_CORE) return fail(h, MUNINN_CUDA_E_STATE, "probe needs a tensor-core exact mode");
+    if (nq < 1 || rows < 1 || rows > h->n || !queries || !out_approx || (size_t)nq * (size_t)rows > (1ull << 28))
+        return fail(h, MUNINN_CUDA_E_ARG, "bad probe arguments");
+    CK(h, cudaSetDevice(h->device));
+    CK(h, grow(&h->d_dbg, &h->dbg_floats, (size_t)nq * rows, h->stream));
+    CK(h, grow(&h->d_qgather, &h->qgather_floats, (size_t)nq * h->dim, h->stream));
+    CK(h, cudaMemcpyAsync(h->d_qgather, queries, (size_t)nq * h->dim * 4, cudaMemcpyHostToDevice, h->stream));
+    int rc = exact_knn_tc(h, h->d_qgather, nq, 1, 0, nullptr, nullptr, nullptr, h->d_dbg, rows);
+    if (rc) return rc;
+    CK(h, cudaMemcpy(out_approx, h->d_dbg, (size_t)nq * rows * 4, cudaMemcpyDeviceToHost));
     return MUNINN_CUDA_OK;
 }
 

@@ -29,7 +29,16 @@ ABI_SYMBOLS = (
     "muninn_cuda_search_batch", "muninn_cuda_search_batch_device", "muninn_cuda_set_stream",
     "muninn_cuda_last_kernel_ms", "muninn_cuda_launch_count", "muninn_cuda_set_tuning", "muninn_cuda_exact_knn",
     "muninn_cuda_exact_knn_device", "muninn_cuda_topk_merge_device", "muninn_cuda_distance_batch",
+    "muninn_cuda_set_exact_mode", "muninn_cuda_exact_stats", "muninn_cuda_exact_filter_probe",
 )
+
+EXACT_CUDA_CORE, EXACT_TC_3XTF32, EXACT_TC_1XTF32 = 0, 1, 2
+
+
+class ExactStats(C.Structure):
+    """MuninnExactStats (include/muninn_cuda.h)."""
+    _fields_ = [("mode", C.c_int32), ("chunks", C.c_int32), ("candidates", C.c_int64), ("overflow_queries", C.c_int32),
+                ("filter_ms", C.c_float), ("c_eps", C.c_float)]
 
 _p = np.ctypeslib.ndpointer
 _f32 = _p(np.float32, flags="C_CONTIGUOUS")
@@ -76,6 +85,9 @@ def lib():
         L.muninn_cuda_exact_knn_device.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_int64, _vp, _vp, _vp]
         L.muninn_cuda_topk_merge_device.argtypes = [_vp, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp]
         L.muninn_cuda_distance_batch.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int64, _f32, _f32, _f32]
+        L.muninn_cuda_set_exact_mode.argtypes = [_vp, C.c_int, C.c_int]
+        L.muninn_cuda_exact_stats.argtypes = [_vp, C.POINTER(ExactStats)]
+        L.muninn_cuda_exact_filter_probe.argtypes = [_vp, _vp, C.c_int, C.c_int64, _vp]
         _lib = L
     return _lib
 
@@ -195,6 +207,22 @@ class HnswIndexCuda:
 
     def exact_knn_device(self, q_ptr: int, nq: int, k: int, index_base: int, idx_ptr: int, dist_ptr: int, cnt_ptr: int):
         self._check(self.L.muninn_cuda_exact_knn_device(self.h, q_ptr, nq, k, index_base, idx_ptr, dist_ptr, cnt_ptr))
+
+    def set_exact_mode(self, mode: int = EXACT_TC_3XTF32, tile_rows: int = 0):
+        """How exact k-NN prunes its n·nq distance evaluations (results are identical in every mode)."""
+        self._check(self.L.muninn_cuda_set_exact_mode(self.h, mode, tile_rows))
+
+    def exact_stats(self) -> dict:
+        st = ExactStats()
+        self._check(self.L.muninn_cuda_exact_stats(self.h, C.byref(st)))
+        return {f: getattr(st, f) for f, _ in ExactStats._fields_}
+
+    def exact_filter_probe(self, queries, rows: int) -> np.ndarray:
+        """The tensor-core filter's approximate distances for rows [0, rows) (error-bound tests)."""
+        q = np.ascontiguousarray(np.atleast_2d(queries), np.float32)
+        out = np.empty((q.shape[0], rows), np.float32)
+        self._check(self.L.muninn_cuda_exact_filter_probe(self.h, _ptr(q), q.shape[0], rows, _ptr(out)))
+        return out
 
     def topk_merge_device(self, parts: int, nq: int, k: int, idx_parts: int, dist_parts: int, cnt_parts: int,
                           idx_ptr: int, dist_ptr: int, cnt_ptr: int):

@@ -1,0 +1,150 @@
+"""`-m gpu`: exact k-NN through the tensor-core filter (tcgen05 3xTF32 / 1xTF32, exact_tc.cuh) is
+bit-identical to the CPU oracle and to the CUDA-core path — ids, distances and counts — including
+deleted rows, ragged sizes, dims that are not multiples of 4 or 32, tie-heavy data that overflows the
+survivor lists, and zero vectors; and the filter's error stays well inside the margin its soundness
+argument assumes (test/test_hnsw_algo.c:10-34 of the reference)."""
+import numpy as np
+import pytest
+
+from tests.conftest import uniform
+
+pytestmark = pytest.mark.gpu
+L2, COS, IP = 0, 1, 2
+
+
+@pytest.fixture(scope="module")
+def cuda():
+    from sqlite_muninn_b200 import cuda as c
+    assert c.device_count() > 0, "no CUDA device: the product has no CPU path"
+    return c
+
+
+def flat(base, metric, deleted=None):
+    from sqlite_muninn_b200.graph import FlatGraph
+    n, dim = base.shape
+    deleted = np.zeros(n, np.uint8) if deleted is None else deleted
+    return FlatGraph(dim, metric, 8, 10, np.arange(n, dtype=np.int64), np.zeros(n, np.int32), deleted, base,
+                     np.zeros(n + 1, np.int64), np.empty(0, np.int32), 0 if n else -1, 0 if n else -1)
+
+
+def latent(seed, n, dim, rank=8):
+    """low intrinsic dimension: distances spread out, so the filter has something to prune"""
+    rng = np.random.default_rng(seed)
+    A = rng.standard_normal((rank, dim)).astype(np.float32) / np.float32(np.sqrt(rank))
+    return (rng.standard_normal((n, rank)).astype(np.float32) @ A
+            + np.float32(0.05) * rng.standard_normal((n, dim)).astype(np.float32)).astype(np.float32)
+
+
+CASES = [  # metric, dim, n, nq, k
+    (L2, 128, 20000, 300, 10), (L2, 128, 9000, 130, 100), (COS, 768, 6000, 129, 10), (IP, 96, 12000, 257, 10),
+    (COS, 24, 5000, 64, 7), (L2, 3, 3000, 33, 5), (IP, 10, 2500, 1, 3), (L2, 131, 4100, 200, 20),
+    (L2, 100, 1500, 128, 300), (COS, 33, 1024, 5, 1), (L2, 16, 700, 40, 10)]
+
+
+@pytest.mark.parametrize("metric,dim,n,nq,k", CASES)
+def test_tensor_modes_equal_oracle(cuda, oracle, metric, dim, n, nq, k):
+    base = latent(n + dim, n, dim) if dim >= 16 else uniform(n + dim, n, dim)
+    q = latent(n + dim, nq + n, dim)[n:] if dim >= 16 else uniform(n + dim + 1, nq, dim)
+    if metric == IP:
+        base /= np.linalg.norm(base, axis=1, keepdims=True)
+    deleted = np.zeros(n, np.uint8)
+    deleted[::13] = 1
+    i_o, d_o, c_o, _ = oracle.exact_knn(base, q, k, metric, deleted=deleted, threads=8)
+    with cuda.HnswIndexCuda.from_graph(flat(base, metric, deleted)) as idx:
+        for mode, tile in ((cuda.EXACT_TC_3XTF32, 256), (cuda.EXACT_TC_3XTF32, 128), (cuda.EXACT_TC_1XTF32, 256),
+                           (cuda.EXACT_TC_1XTF32, 128), (cuda.EXACT_CUDA_CORE, 0)):
+            idx.set_exact_mode(mode, tile)
+            i_g, d_g, c_g = idx.exact_knn(q, k, index_base=7)
+            st = idx.exact_stats()
+            assert np.array_equal(c_g, c_o), (mode, tile)
+            assert d_g.tobytes() == d_o.tobytes(), (mode, tile)
+            assert np.array_equal(i_g, np.where(i_o >= 0, i_o + 7, -1)), (mode, tile)
+            assert st["mode"] == mode
+            if mode != cuda.EXACT_CUDA_CORE:
+                assert st["chunks"] >= 1 and st["candidates"] >= min(n, 1024) * nq * 0  # counters are live
+                assert st["filter_ms"] > 0.0
+
+
+def test_filter_prunes(cuda, oracle):
+    """On spread-out data the 3xTF32 filter leaves ≈ k survivors per doubling chunk, not n."""
+    n, dim, nq, k = 60000, 128, 256, 10
+    base, q = latent(1, n, dim), latent(2, nq, dim)
+    with cuda.HnswIndexCuda.from_graph(flat(base, L2)) as idx:
+        idx.set_exact_mode(cuda.EXACT_TC_3XTF32, 256)
+        i_g, d_g, c_g = idx.exact_knn(q, k)
+        st = idx.exact_stats()
+    i_o, d_o, c_o, _ = oracle.exact_knn(base, q, k, L2, threads=8)
+    assert np.array_equal(i_g, i_o) and d_g.tobytes() == d_o.tobytes()
+    assert st["overflow_queries"] == 0
+    per_query = st["candidates"] / nq
+    assert per_query < 1024 + 40 * k * st["chunks"], per_query  # first chunk (1024 rows) passes whole
+    assert per_query < 0.05 * n
+
+
+def test_tie_heavy_data_overflows_and_stays_exact(cuda, oracle):
+    """Duplicated rows: every copy of a top-k row ties with τ and must survive; the survivor lists
+    overflow, the flagged queries are recomputed on the CUDA cores, ties still go to the lower index."""
+    rng = np.random.default_rng(5)
+    proto = np.round(rng.uniform(-2, 2, (6, 8))).astype(np.float32)
+    base = proto[rng.integers(0, 6, 30000)]
+    q = np.concatenate([proto[:3] + np.float32(0.25), latent(9, 20, 8)]).astype(np.float32)
+    i_o, d_o, c_o, _ = oracle.exact_knn(base, q, 10, L2, threads=8)
+    with cuda.HnswIndexCuda.from_graph(flat(base, L2)) as idx:
+        for mode in (cuda.EXACT_TC_3XTF32, cuda.EXACT_TC_1XTF32):
+            idx.set_exact_mode(mode, 256)
+            i_g, d_g, c_g = idx.exact_knn(q, 10)
+            st = idx.exact_stats()
+            assert st["overflow_queries"] > 0
+            assert np.array_equal(c_g, c_o) and d_g.tobytes() == d_o.tobytes() and np.array_equal(i_g, i_o), mode
+
+
+def test_zero_vectors_cosine(cuda, oracle):
+    n, dim = 3000, 20
+    base = uniform(3, n, dim)
+    base[::7] = 0.0
+    q = uniform(4, 50, dim)
+    q[3] = 0.0
+    i_o, d_o, c_o, _ = oracle.exact_knn(base, q, 10, COS, threads=4)
+    with cuda.HnswIndexCuda.from_graph(flat(base, COS)) as idx:
+        idx.set_exact_mode(cuda.EXACT_TC_3XTF32, 256)
+        i_g, d_g, c_g = idx.exact_knn(q, 10)
+    assert np.array_equal(c_g, c_o) and d_g.tobytes() == d_o.tobytes() and np.array_equal(i_g, i_o)
+
+
+def test_fewer_rows_than_k_and_empty(cuda, oracle):
+    base, q = uniform(1, 5, 12), uniform(2, 9, 12)
+    i_o, d_o, c_o, _ = oracle.exact_knn(base, q, 8, L2)
+    with cuda.HnswIndexCuda.from_graph(flat(base, L2)) as idx:
+        i_g, d_g, c_g = idx.exact_knn(q, 8)
+    assert np.array_equal(c_g, c_o) and np.array_equal(i_g, i_o) and d_g.tobytes() == d_o.tobytes()
+    with cuda.HnswIndexCuda.from_graph(flat(np.empty((0, 12), np.float32), L2)) as idx:
+        i_g, d_g, c_g = idx.exact_knn(q, 8)
+    assert (c_g == 0).all() and (i_g == -1).all()
+
+
+@pytest.mark.parametrize("metric,dim", [(L2, 128), (L2, 768), (COS, 768), (IP, 96), (COS, 100), (L2, 5)])
+@pytest.mark.parametrize("mode", [1, 2])
+def test_filter_error_is_inside_the_margin(cuda, metric, dim, mode):
+    """|d̃ − d| of the tensor-core contraction against float64, as a fraction of the margin ε the
+    filter adds to τ (the soundness argument needs < 1). ε carries a factor 2 over the worst case by
+    construction, so 1/2 is the ceiling; 3xTF32 is dominated by the (pessimistic) accumulation term
+    and must stay below 1/10, 1xTF32 by the input truncation itself and may approach 1/2."""
+    n, nq = 2048, 200
+    base = uniform(dim, n, dim) * np.float32(3.0)
+    q = uniform(dim + 1, nq, dim) * np.float32(3.0)
+    with cuda.HnswIndexCuda.from_graph(flat(base, metric)) as idx:
+        idx.set_exact_mode(mode, 256)
+        approx = idx.exact_filter_probe(q, n).astype(np.float64)
+        c_eps = idx.exact_stats()["c_eps"]
+    b64, q64 = base.astype(np.float64), q.astype(np.float64)
+    dot = q64 @ b64.T
+    qn, xn = (q64 * q64).sum(1)[:, None], (b64 * b64).sum(1)[None, :]
+    if metric == L2:
+        true, eps = qn + xn - 2 * dot, c_eps * (qn + xn)
+    elif metric == IP:
+        true, eps = -dot, c_eps * (qn + xn)
+    else:
+        true, eps = 1.0 - dot / np.sqrt(qn * xn), c_eps * np.ones_like(dot)
+    ratio = float((np.abs(approx - true) / eps).max())
+    print(f"metric={metric} dim={dim} mode={mode}: max |err|/eps = {ratio:.4f} (c_eps={c_eps:.3e})")
+    assert ratio < (0.1 if mode == 1 else 0.5)
