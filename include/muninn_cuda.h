@@ -152,12 +152,13 @@ typedef struct {
     int64_t candidates;       /* (query, row) pairs that survived the filter and were re-ranked exactly */
     int32_t overflow_queries; /* queries whose survivor list overflowed; recomputed on the CUDA cores */
     float filter_ms;          /* Σ device time of the tensor-core filter launches (CUDA events) */
-    float c_eps;              /* error constant of the filter: |d~ - d_ref| <= c_eps·(|q|² + |x|²), or c_eps for cosine */
+    float c_eps;              /* error constant of the filter: |d~ - d_ref| <= c_eps·(|q|² + |x|²), or c_eps for cosine;
+                                 in terms of the contraction: |sum~ - sum(q·x)| <= c_eps/2 · (|q|² + |x|²) */
 } MuninnExactStats;
 int muninn_cuda_exact_stats(MuninnCudaIndex *idx, MuninnExactStats *out);
 
-/* Error probe for the tests: the filter's approximate distance d~ of every (query, row) pair of
- * rows [0, rows) → out_approx [nq × rows] (host buffers). Needs a tensor-core exact mode. */
+/* Error probe for the tests: the filter's tensor-core contraction sum(q·x) of every (query, row)
+ * pair of rows [0, rows) → out_approx [nq × rows] (host buffers). Needs a tensor-core exact mode. */
 int muninn_cuda_exact_filter_probe(MuninnCudaIndex *idx, const float *queries, int nq, int64_t rows, float *out_approx);
 
 /* Merge `parts` per-shard result lists ([parts × nq × k], as gathered by ncclAllGather) into
@@ -169,6 +170,11 @@ int muninn_cuda_topk_merge_device(MuninnCudaIndex *idx, int parts, int nq, int k
 /* n distances metric(a[i], b[i]) with the reference's summation order (src/vec_math.c:78-143).
  * Host buffers [n × dim]; used by the known-answer tests of test/test_vec_math.c. */
 int muninn_cuda_distance_batch(int device, int metric, int dim, int64_t n, const float *a, const float *b, float *out);
+
+/* Diagnostic for the roofline report (no reference counterpart): GB/s this device delivers for
+ * independent random gathers of row_bytes-byte rows out of a slab_bytes slab (slab >> L2) — the
+ * access pattern of hnsw_search's neighbour-vector reads with nothing dependent in the way. */
+int muninn_cuda_gather_ceiling(int device, int row_bytes, int64_t slab_bytes, float *out_gbps);
 
 #ifdef __cplusplus
 }

@@ -20,8 +20,8 @@
  *   3. re-rank    one warp per query: reference-order fp32 distance of every survivor, merged into
  *                 the query's sorted (distance, row) list; τ_q ← its k-th entry.
  *
- * The base is processed in chunks whose size doubles (first chunk = the candidate capacity, every
- * row of which survives because τ = +inf), so each chunk yields ≈ k survivors per query.
+ * The base is processed in chunks whose size doubles (the first chunk is small — max(256, 2k) rows —
+ * because every row of it survives, τ being +inf), so each later chunk yields ≈ k survivors per query.
  *
  * Soundness: a row of the true top-k has d_ref ≤ τ_q at all times; with |d̃ − d_ref| ≤ ε it can
  * never satisfy d̃ > τ_q + ε. ε = c·(‖q‖² + ‖x‖²) (L2, inner product) or c (cosine) with
@@ -139,7 +139,7 @@ __host__ __device__ constexpr uint32_t make_idesc_tf32(int bn) {
 
 struct FilterParams {
     const float *xnorm2; /* [n] Σx² per row of the handle, reference chain order */
-    const float *qaux;   /* [nq] Σq² (L2, inner product) or 1/√Σq² (cosine; NaN when Σq² < 1e-18) */
+    const float *qaux;   /* [nq] Σq², reference chain order */
     const float *tau;    /* [nq] current k-th exact distance (+inf while fewer than k rows were seen) */
     int *cand;           /* [nq × cand_cap] surviving row indices of this chunk */
     int *cand_count;     /* [nq] */
@@ -147,7 +147,7 @@ struct FilterParams {
     long long row0;      /* first row of the chunk (the x tensor maps start there) */
     int rows, nq, kblocks;
     float c_eps;
-    float *dbg_panel;    /* optional [nq × dbg_ld]: d̃ of every pair of the chunk (error probe) */
+    float *dbg_panel;    /* DBG instantiation only, [nq × dbg_ld]: the contraction Σq·x of every pair (error probe) */
     int dbg_ld;
 };
 
@@ -162,7 +162,7 @@ struct FilterCfg {
     static constexpr size_t SMEM_BYTES = 1024 + (size_t)NSTAGES * STAGE_BYTES + 2 * BN * 4 + (2 * NSTAGES + 4) * 8 + 16;
 };
 
-template <int METRIC, int NPASS, int BN>
+template <int METRIC, int NPASS, int BN, bool DBG>
 __global__ void __launch_bounds__(THREADS, 1)
 exact_tc_filter(const __grid_constant__ CUtensorMap tm_qhi, const __grid_constant__ CUtensorMap tm_qlo,
                 const __grid_constant__ CUtensorMap tm_xhi, const __grid_constant__ CUtensorMap tm_xlo,
@@ -170,7 +170,8 @@ exact_tc_filter(const __grid_constant__ CUtensorMap tm_qhi, const __grid_constan
     using Cfg = FilterCfg<NPASS, BN>;
     constexpr int NST = Cfg::NSTAGES;
     extern __shared__ unsigned char smem_dyn[];
-    unsigned char *base = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~(uintptr_t)1023);
+    /* 1024-byte aligned base (128B swizzle atom); plain offset arithmetic keeps the shared address space */
+    unsigned char *base = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
     unsigned char *stages = base;
     float *xaux = reinterpret_cast<float *>(base + (size_t)NST * Cfg::STAGE_BYTES);
     uint64_t *full = reinterpret_cast<uint64_t *>(xaux + 2 * BN);
@@ -249,9 +250,17 @@ exact_tc_filter(const __grid_constant__ CUtensorMap tm_qhi, const __grid_constan
             }
         }
     } else {
-        /* ── epilogue: 4 warps, warp w reads TMEM lanes 32·(w mod 4)…, thread = one query ── */
+        /* ── epilogue: 4 warps, warp w reads TMEM lanes 32·(w mod 4)…, thread = one query ──
+         * With s = Σ q·x from TMEM, "d̃ > τ + ε" is rearranged so that one add (or multiply) and one
+         * compare per pair remain, everything else being per query or per row:
+         *   L2      (qn+xn) − 2s > τ + c(qn+xn)   ⇔  s < [h·qn − τ/2] + [h·xn],  h = (1−c)/2
+         *   IP      −s > τ + c(qn+xn)             ⇔  s < [−τ − c·qn] + [−c·xn]
+         *   cosine  1 − s/(√qn√xn) > τ + c        ⇔  s·(1/√xn) < (1 − τ − c)·√qn
+         * (the few extra roundings are ~2⁻²³ relative, far inside the factor-2 slack of c). A pair is
+         * pruned only when the compare is TRUE, so NaN/inf anywhere keeps the row. */
         const int quarter = warp & 3, et = (warp - 2) * 32 + lane;
         const int qrow = quarter * 32 + lane;
+        const float c = p.c_eps, hh = 0.5f * (1.0f - c);
         int a = 0; uint32_t aph = 0;
         for (long long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
             const int xt = (int)(t / n_qt), qt = (int)(t % n_qt);
@@ -259,15 +268,21 @@ exact_tc_filter(const __grid_constant__ CUtensorMap tm_qhi, const __grid_constan
             const bool qvalid = q < p.nq;
             const int ncols = p.rows - xt * BN < BN ? p.rows - xt * BN : BN;
             const long long xrow0 = p.row0 + (long long)xt * BN;
-            float qa = 0.0f, tq = 0.0f;
-            if (qvalid) { qa = p.qaux[q]; tq = __ldcg(p.tau + q) + 1e-30f; }
-            if (METRIC == METRIC_COSINE) tq += p.c_eps;
+            float qa = 0.0f;
+            if (qvalid) {
+                const float qn = p.qaux[q], tq = __ldcg(p.tau + q) + 1e-30f;
+                if (METRIC == METRIC_L2) qa = fmaf(hh, qn, -0.5f * tq);
+                else if (METRIC == METRIC_IP) qa = fmaf(-c, qn, -tq);
+                else qa = qn < 1e-18f ? __int_as_float(0x7fc00000) : (1.0f - tq - c) * sqrtf(qn);
+            }
             float *xa = xaux + a * BN;
             for (int j = et; j < BN; j += 128) {
                 float v = 0.0f;
                 if (j < ncols) {
-                    v = p.xnorm2[xrow0 + j];
-                    if (METRIC == METRIC_COSINE) v = v < 1e-18f ? __int_as_float(0x7fc00000) : rsqrtf(v);
+                    const float xn = p.xnorm2[xrow0 + j];
+                    if (METRIC == METRIC_L2) v = hh * xn;
+                    else if (METRIC == METRIC_IP) v = -c * xn;
+                    else v = xn < 1e-18f ? __int_as_float(0x7fc00000) : rsqrtf(xn);
                 }
                 xa[j] = v;
             }
@@ -279,22 +294,31 @@ exact_tc_filter(const __grid_constant__ CUtensorMap tm_qhi, const __grid_constan
                 uint32_t v[32];
                 tmem_ld32(taddr + (uint32_t)c0, v);
                 tmem_ld_wait();
-                if (qvalid) {
+                if (DBG) {
+                    if (qvalid)
+                        for (int j = 0; j < 32 && c0 + j < ncols; j++)
+                            p.dbg_panel[(size_t)q * p.dbg_ld + (size_t)(xrow0 - p.row0) + c0 + j] = __uint_as_float(v[j]);
+                    continue;
+                }
+                uint32_t keep = 0;
 #pragma unroll
-                    for (int j = 0; j < 32; j++) {
-                        const float s = __uint_as_float(v[j]);
-                        const float x = xa[c0 + j];
-                        float d, thr;
-                        if (METRIC == METRIC_L2) { const float u = qa + x; d = fmaf(-2.0f, s, u); thr = fmaf(p.c_eps, u, tq); }
-                        else if (METRIC == METRIC_IP) { const float u = qa + x; d = -s; thr = fmaf(p.c_eps, u, tq); }
-                        else { d = fmaf(-(s * x), qa, 1.0f); thr = tq; }
-                        if (p.dbg_panel && c0 + j < ncols)
-                            p.dbg_panel[(size_t)q * p.dbg_ld + (size_t)(xrow0 - p.row0) + c0 + j] = d;
-                        if (!(d > thr) && c0 + j < ncols) {
-                            const int pos = atomicAdd(p.cand_count + q, 1);
-                            if (pos < p.cand_cap) p.cand[(size_t)q * p.cand_cap + pos] = (int)(xrow0 + c0 + j);
-                        }
+                for (int j4 = 0; j4 < 32; j4 += 4) {
+                    const float4 x4 = *reinterpret_cast<const float4 *>(xa + c0 + j4);
+                    const float xs[4] = {x4.x, x4.y, x4.z, x4.w};
+#pragma unroll
+                    for (int jj = 0; jj < 4; jj++) {
+                        const float sdot = __uint_as_float(v[j4 + jj]);
+                        const bool prune = METRIC == METRIC_COSINE ? (sdot * xs[jj] < qa) : (sdot < qa + xs[jj]);
+                        keep |= prune ? 0u : (1u << (j4 + jj));
                     }
+                }
+                if (ncols - c0 < 32) keep &= (1u << (ncols - c0)) - 1u;
+                if (!qvalid) keep = 0;
+                while (keep) { /* rare: ≈ k survivors per query per chunk */
+                    const int j = __ffs(keep) - 1;
+                    keep &= keep - 1;
+                    const int pos = atomicAdd(p.cand_count + q, 1);
+                    if (pos < p.cand_cap) p.cand[(size_t)q * p.cand_cap + pos] = (int)(xrow0 + c0 + j);
                 }
             }
             tc_fence_before();
@@ -347,9 +371,7 @@ __global__ void tc_prep_queries(const float *__restrict__ queries, int dim, int 
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= nq) return;
     const float n2 = chained_sum_serial<METRIC_IP>(queries + (size_t)q * dim, queries + (size_t)q * dim, dim);
-    float a = n2;
-    if (METRIC == METRIC_COSINE) a = n2 < 1e-18f ? __int_as_float(0x7fc00000) : rsqrtf(n2);
-    qaux[q] = a;
+    qaux[q] = n2;
     tau[q] = __int_as_float(0x7f800000);
     cand_count[q] = 0; topk_size[q] = 0; overflow[q] = 0;
 }

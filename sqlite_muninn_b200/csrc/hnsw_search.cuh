@@ -10,9 +10,9 @@
  * pulls query indices from a global counter until the batch is drained, so long and short
  * searches balance across the 148 SMs. Per team, in shared memory: the query, the result list
  * R (ef entries, ascending (distance, slot) 64-bit keys, bit 0 = "expanded"), and a 4 KB
- * staging tile for the distance transposition. Per team, in HBM: an open-addressing visited
- * table of 64-bit (epoch, slot) entries; entries of older epochs read as empty, so the table
- * is never cleared between queries.
+ * staging tile for the distance transposition. Per team, in HBM (L2-resident in practice): an
+ * open-addressing visited table of 32-bit slot entries, cleared by the team at the start of each
+ * query (a few dozen 16-byte stores).
  *
  * Distances: for a batch of up to 8 neighbour rows the 32 lanes load one 16-byte chunk of
  * every row each (fully coalesced 512 B per row at dim 128, eight independent 128-bit loads
@@ -37,8 +37,21 @@ namespace muninn {
 #ifndef MUNINN_PREFETCH
 #define MUNINN_PREFETCH 1
 #endif
+#ifndef MUNINN_RB
+#define MUNINN_RB 0 /* 0 = by row width: 12 rows (24 teams/SM) for one-column-block rows, else 16 */
+#endif
+#ifndef MUNINN_ROW_EVICT_FIRST
+#define MUNINN_ROW_EVICT_FIRST 1 /* gathered rows are streamed: L2 evict-first keeps lists and visited tables resident */
+#endif
+#ifndef MUNINN_NEXT_PREFETCH
+#define MUNINN_NEXT_PREFETCH 0   /* fetch the next candidate's neighbour list while R is being merged (measured: no gain) */
+#endif
 constexpr int DB = 8;             /* rows per distance batch in the greedy descent (4 lanes per row) */
-constexpr int RB = 16;            /* rows per distance batch in the layer-0 beam (2 lanes per row) */
+/* Rows per beam batch. Rows of ≤ 512 bytes are staged in one go: 12-row batches shrink the tile so
+ * that 24 teams fit an SM (measured +2 % over 16 rows / 20 teams). Wider rows take several column
+ * blocks per batch, each a memory round trip: keep the batch as large as the lanes allow. */
+__host__ __device__ inline int beam_rows(int ld) { return MUNINN_RB ? (MUNINN_RB == 12 ? 12 : 16) : (ld <= 128 ? 12 : 16); }
+constexpr unsigned VIS_EMPTY = 0xffffffffu;
 constexpr int PSTRIDE = 128 + 4;  /* floats per staged row: 32 chunks + 4 pad → conflict-free per-row reads */
 constexpr int MAX_M0 = 128;       /* layer-0 list capacity supported (M ≤ 64) */
 
@@ -53,32 +66,44 @@ struct SearchParams {
     int64_t *out_ids; float *out_dist; int32_t *out_count; MuninnSearchStats *stats;
     /* work lists: level 0 processes queries 0..nq-1; level>0 processes in_list[0..*in_count) */
     const int *in_list; const int *in_count; int *out_list; int *out_count_retry; int *work_counter;
-    /* visited tables */
-    unsigned long long *vis; unsigned vis_shift; unsigned vis_cap; unsigned epoch_base;
+    /* visited tables: one per team, vis_cap 32-bit slots each (VIS_EMPTY = free), cleared per query */
+    unsigned *vis; unsigned vis_shift; unsigned vis_cap;
 };
 
 struct TeamSmem {
     unsigned long long *R;   /* [ef] */
-    unsigned long long *Fk;  /* [MAX_M0] keys of this expansion's fresh neighbours */
+    unsigned long long *Fk;  /* [M0] keys of this expansion's fresh neighbours */
     unsigned long long *S;   /* [32] survivors being merged */
     float *q;                /* [ld] */
-    float *P;                /* [RB * PSTRIDE] row staging tile */
-    int *Fs;                 /* [MAX_M0] fresh slots */
+    float *P;                /* [beam_rows * PSTRIDE] row staging tile */
+    int *Fs;                 /* [fs_len(M0)] fresh slots; the greedy descent keeps list positions at Fs[fs_pos(M0) + i] */
 };
 
-__host__ __device__ inline size_t search_smem_bytes(int ef, int ld) {
-    size_t b = (((size_t)ef * 8 + 15) & ~(size_t)15) + (size_t)MAX_M0 * 8 + 32 * 8;
+__host__ __device__ inline int fs_pos(int M0) { return M0 > DB ? M0 : DB; }
+__host__ __device__ inline int fs_len(int M0) { return fs_pos(M0) + DB; }
+
+__host__ __device__ inline size_t search_smem_bytes(int ef, int ld, int M0) {
+    size_t b = (((size_t)ef * 8 + 15) & ~(size_t)15) + (size_t)M0 * 8 + 32 * 8;
     b += ((size_t)ld * 4 + 15) / 16 * 16;
-    b += (size_t)RB * PSTRIDE * 4;
-    b += (size_t)MAX_M0 * 4;
+    b += (size_t)beam_rows(ld) * PSTRIDE * 4;
+    b += ((size_t)fs_len(M0) * 4 + 15) & ~(size_t)15;
     return b;
 }
 
 /* 16-byte asynchronous global→shared copy (LDGSTS), L2-only caching: the gathered rows are
  * streamed once and never reused by this SM */
-__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src) {
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src, unsigned long long policy) {
     unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+#if MUNINN_ROW_EVICT_FIRST
+    asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(d), "l"(gmem_src), "l"(policy) : "memory");
+#else
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src) : "memory");
+#endif
+}
+__device__ __forceinline__ unsigned long long l2_evict_first_policy() {
+    unsigned long long pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
 }
 __device__ __forceinline__ void cp_async_wait_all() {
     asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
@@ -102,7 +127,7 @@ __device__ __forceinline__ float prod1(float a, float b) {
  */
 template <int METRIC, int L>
 __device__ __forceinline__ float warp_dist_rows(const SearchParams &p, const TeamSmem &sm, const int *bs, int nb,
-                                                float q_norm2, int lane) {
+                                                float q_norm2, int lane, unsigned long long pol) {
     constexpr int CH = 4 / L;
     const int cpr = p.ld >> 2, cfull = p.dim >> 2, rem = p.dim & 3;
     const int row = lane / L, h = lane % L, g = lane - h;
@@ -115,7 +140,7 @@ __device__ __forceinline__ float warp_dist_rows(const SearchParams &p, const Tea
         if (lane < tc) {
             const float *src = p.vec + 4 * (t0 + lane);
             float *dst = sm.P + 4 * lane;
-            for (int r = 0; r < nb; r++) cp_async16(dst + r * PSTRIDE, src + (size_t)bs[r] * (size_t)p.ld);
+            for (int r = 0; r < nb; r++) cp_async16(dst + r * PSTRIDE, src + (size_t)bs[r] * (size_t)p.ld, pol);
         }
         cp_async_wait_all();
         __syncwarp();
@@ -170,13 +195,13 @@ __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefe
 /* Pull the rows of all `nf` fresh neighbours towards L2 in one go (4 lanes per row, one
  * 128-byte line each per step) so that the 8-row distance batches that follow overlap their
  * DRAM latency instead of paying it batch after batch. */
-__device__ __forceinline__ void prefetch_rows(const SearchParams &p, const int *slots, int nf, int lane) {
+__device__ __forceinline__ void prefetch_rows(const SearchParams &p, const int *slots, int nf, int lane, int from_byte = 0) {
     const int row_bytes = p.ld * 4;
     for (int r0 = 0; r0 < nf; r0 += 8) {
         int r = r0 + (lane >> 2);
         if (r < nf) {
             const char *base = reinterpret_cast<const char *>(p.vec + (size_t)slots[r] * (size_t)p.ld);
-            for (int off = (lane & 3) * 128; off < row_bytes; off += 512) prefetch_l2(base + off);
+            for (int off = from_byte + (lane & 3) * 128; off < row_bytes; off += 512) prefetch_l2(base + off);
         }
     }
 }
@@ -187,30 +212,27 @@ __device__ __forceinline__ float query_norm2(const float *q, int dim) {
 }
 
 /* visited test-and-set for one neighbour per lane; returns 1 if the slot was not yet visited.
- * The table is private to the team: plain L2-level loads/stores, intra-warp claim conflicts
- * resolved with match.any. */
-__device__ __forceinline__ int visited_test_and_set(const SearchParams &p, unsigned long long *tab, unsigned epoch,
-                                                    int t, bool valid, int lane) {
+ * The table is private to the team and cleared at the start of every query: 32-bit entries (eight
+ * per 32-byte sector, so a probe chain usually stays in one sector), plain L2-level loads/stores,
+ * intra-warp claim conflicts resolved with match.any. */
+__device__ __forceinline__ int visited_test_and_set(const SearchParams &p, unsigned *tab, int t, bool valid, int lane) {
     unsigned h = ((unsigned)t * 2654435761u) >> p.vis_shift;
     const unsigned mask = p.vis_cap - 1;
     bool active = valid;
     int fresh = 0;
-    const unsigned long long mine = ((unsigned long long)epoch << 32) | (unsigned)t;
     while (__any_sync(FULL, active)) {
-        unsigned long long e = active ? __ldcg(tab + h) : 0ull;
-        bool cur = (unsigned)(e >> 32) == epoch;
+        unsigned e = active ? __ldcg(tab + h) : 0u;
         bool claim = false;
         if (active) {
-            if (cur) {
-                if ((unsigned)e == (unsigned)t) active = false; /* already visited */
-                else h = (h + 1) & mask;
-            } else claim = true;
+            if (e == (unsigned)t) active = false; /* already visited */
+            else if (e != VIS_EMPTY) h = (h + 1) & mask;
+            else claim = true;
         }
         unsigned cm = __ballot_sync(FULL, claim);
         if (claim) {
             unsigned peers = __match_any_sync(cm, h);
             if ((__ffs(peers) - 1) == lane) {
-                __stcg(tab + h, mine);
+                __stcg(tab + h, (unsigned)t);
                 fresh = 1;
                 active = false;
             } else h = (h + 1) & mask;
@@ -220,7 +242,16 @@ __device__ __forceinline__ int visited_test_and_set(const SearchParams &p, unsig
     return fresh;
 }
 
-template <int METRIC>
+__device__ __forceinline__ void visited_clear(unsigned *tab, unsigned cap, int lane) {
+    uint4 *t4 = reinterpret_cast<uint4 *>(tab);
+    const uint4 e = make_uint4(VIS_EMPTY, VIS_EMPTY, VIS_EMPTY, VIS_EMPTY);
+    for (unsigned i = lane; i < (cap >> 2); i += 32) __stcg(t4 + i, e);
+    __syncwarp();
+}
+
+/* RB = beam_rows(p.ld), as a template parameter: with a run-time batch size the L2-hinted copy loop
+ * compiled (nvcc 12.9) to code that faults with "illegal instruction" on sm_100a. */
+template <int METRIC, int RB>
 __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kernel(const SearchParams p, const int level) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x;
@@ -228,15 +259,16 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
     {
         unsigned char *b = smem_raw;
         sm.R = reinterpret_cast<unsigned long long *>(b); b += ((size_t)p.ef * 8 + 15) & ~(size_t)15;
-        sm.Fk = reinterpret_cast<unsigned long long *>(b); b += (size_t)MAX_M0 * 8;
+        sm.Fk = reinterpret_cast<unsigned long long *>(b); b += (size_t)p.M0 * 8;
         sm.S = reinterpret_cast<unsigned long long *>(b); b += 32 * 8;
         sm.q = reinterpret_cast<float *>(b); b += ((size_t)p.ld * 4 + 15) / 16 * 16;
         sm.P = reinterpret_cast<float *>(b); b += (size_t)RB * PSTRIDE * 4;
         sm.Fs = reinterpret_cast<int *>(b);
     }
-    unsigned long long *tab = p.vis + (size_t)blockIdx.x * (size_t)p.vis_cap;
+    unsigned *tab = p.vis + (size_t)blockIdx.x * (size_t)p.vis_cap;
     const int nwork = level == 0 ? p.nq : *p.in_count;
-    const int ef = p.ef;
+    const int ef = p.ef, FP = fs_pos(p.M0);
+    const unsigned long long pol = l2_evict_first_policy();
 
     for (;;) {
         int w = 0;
@@ -244,9 +276,6 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
         w = __shfl_sync(FULL, w, 0);
         if (w >= nwork) break;
         const int qi = level == 0 ? w : p.in_list[w];
-        /* unique per (launch chain, retry level, query): a retry re-lays the arena out with a
-         * larger capacity, so it must not recognise entries its level-0 attempt wrote */
-        const unsigned epoch = p.epoch_base + (unsigned)level * (unsigned)p.nq + (unsigned)qi + 1u;
 
         /* stage the query (pad lanes to the 4-float row stride with zeros) */
         const float *qg = p.queries + (size_t)qi * (size_t)p.dim;
@@ -264,7 +293,7 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
             int cur = p.entry_slot;
             if (lane == 0) sm.Fs[0] = cur;
             __syncwarp();
-            float cur_d = __shfl_sync(FULL, warp_dist_rows<METRIC, 4>(p, sm, sm.Fs, 1, qn2, lane), 0);
+            float cur_d = __shfl_sync(FULL, warp_dist_rows<METRIC, 4>(p, sm, sm.Fs, 1, qn2, lane, pol), 0);
             __syncwarp();
             for (int l = p.max_level; l > 0; l--) {
                 n_dist++; n_dist_upper++; /* the reference re-evaluates the entry at every level (:262) */
@@ -284,14 +313,14 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
                             int t = pos < p.M ? lst[pos] : -1;
                             unsigned vm = __ballot_sync(FULL, t >= 0);
                             int r = __popc(vm & ((1u << lane) - 1));
-                            if (t >= 0 && nb + r < DB) { sm.Fs[nb + r] = t; sm.Fs[MAX_M0 / 2 + nb + r] = pos; }
+                            if (t >= 0 && nb + r < DB) { sm.Fs[nb + r] = t; sm.Fs[FP + nb + r] = pos; }
                             nb += __popc(vm);
                         }
                         if (nb > DB) nb = DB;
                         __syncwarp();
                         if (nb == 0) break;
-                        last_pos = sm.Fs[MAX_M0 / 2 + nb - 1];
-                        float d = warp_dist_rows<METRIC, 4>(p, sm, sm.Fs, nb, qn2, lane);
+                        last_pos = sm.Fs[FP + nb - 1];
+                        float d = warp_dist_rows<METRIC, 4>(p, sm, sm.Fs, nb, qn2, lane, pol);
                         bool better = (lane & 3) == 0 && (lane >> 2) < nb && d < cur_d; /* strict, :274 */
                         unsigned bm = __ballot_sync(FULL, better);
                         if (bm) {
@@ -299,7 +328,7 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
                             n_dist += j + 1; n_dist_upper += j + 1;
                             cur_d = __shfl_sync(FULL, d, src);
                             cur = sm.Fs[j];
-                            i0 = sm.Fs[MAX_M0 / 2 + j] + 1;
+                            i0 = sm.Fs[FP + j] + 1;
                             changed = true;
                             n_greedy++;
                         } else {
@@ -318,9 +347,11 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
                 n_dist++;
                 if (lane == 0) sm.R[0] = make_key(cur_d, (unsigned)cur << 1);
                 size = 1;
-                visited_test_and_set(p, tab, epoch, cur, lane == 0, lane);
+                visited_clear(tab, p.vis_cap, lane);
+                visited_test_and_set(p, tab, cur, lane == 0, lane);
                 __syncwarp();
                 int stale = 0, lb = 0, n_ins = 1, evicted_open = 0;
+                int pre_slot = -1, pre_t = -1; /* neighbour list fetched ahead for the expected next candidate */
                 for (;;) {
                     /* closest unexpanded entry of R */
                     int pos = -1;
@@ -344,8 +375,10 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
                     const int32_t *lst = p.nbr0 + (size_t)c * (size_t)p.M0;
                     for (int base = 0; base < p.M0; base += 32) {
                         int pos0 = base + lane;
-                        int t = pos0 < p.M0 ? lst[pos0] : -1;
-                        int fresh = visited_test_and_set(p, tab, epoch, t, t >= 0, lane);
+                        int t;
+                        if (MUNINN_NEXT_PREFETCH && base == 0 && c == pre_slot) t = pre_t;
+                        else t = pos0 < p.M0 ? lst[pos0] : -1;
+                        int fresh = visited_test_and_set(p, tab, t, t >= 0, lane);
                         unsigned fm = __ballot_sync(FULL, fresh);
                         if (fresh) sm.Fs[nf + __popc(fm & ((1u << lane) - 1))] = t;
                         nf += __popc(fm);
@@ -355,21 +388,49 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
                     __syncwarp();
 #if MUNINN_PREFETCH
                     if (nf > RB) prefetch_rows(p, sm.Fs + RB, nf - RB, lane); /* the first batch is copied right away */
+                    /* wide rows: the first batch's later column blocks would each pay a DRAM round trip */
+                    if (p.ld > 128) prefetch_rows(p, sm.Fs, nf < RB ? nf : RB, lane, 512);
 #endif
                     /* distances */
                     for (int b0 = 0; b0 < nf; b0 += RB) {
                         const int nb = nf - b0 < RB ? nf - b0 : RB;
                         if (nb > 8) {
-                            float d = warp_dist_rows<METRIC, 2>(p, sm, sm.Fs + b0, nb, qn2, lane);
+                            float d = warp_dist_rows<METRIC, 2>(p, sm, sm.Fs + b0, nb, qn2, lane, pol);
                             if ((lane & 1) == 0 && (lane >> 1) < nb)
                                 sm.Fk[b0 + (lane >> 1)] = make_key(d, (unsigned)sm.Fs[b0 + (lane >> 1)] << 1);
                         } else {
-                            float d = warp_dist_rows<METRIC, 4>(p, sm, sm.Fs + b0, nb, qn2, lane);
+                            float d = warp_dist_rows<METRIC, 4>(p, sm, sm.Fs + b0, nb, qn2, lane, pol);
                             if ((lane & 3) == 0 && (lane >> 2) < nb)
                                 sm.Fk[b0 + (lane >> 2)] = make_key(d, (unsigned)sm.Fs[b0 + (lane >> 2)] << 1);
                         }
                     }
                     __syncwarp();
+#if MUNINN_NEXT_PREFETCH
+                    {   /* the next pop is the smaller of (first open entry of R, best fresh key that will
+                         * enter R): start loading its neighbour list now, the merge below hides the latency */
+                        unsigned long long kmin = KEY_NONE;
+                        for (int base = lane; base < nf; base += 32) { unsigned long long f = sm.Fk[base]; kmin = f < kmin ? f : kmin; }
+#pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) { unsigned long long oth = __shfl_xor_sync(FULL, kmin, o); kmin = oth < kmin ? oth : kmin; }
+                        const unsigned long long worst0 = size >= ef ? sm.R[ef - 1] : KEY_NONE;
+                        if (!(kmin < worst0)) kmin = KEY_NONE;
+                        unsigned long long rnext = KEY_NONE;
+                        for (int base = lb & ~31; base < size; base += 32) {
+                            int idx = base + lane;
+                            bool open = idx < size && idx >= lb && !(sm.R[idx] & 1ull);
+                            unsigned om = __ballot_sync(FULL, open);
+                            if (om) { rnext = sm.R[base + __ffs(om) - 1]; break; }
+                        }
+                        const unsigned long long nk = kmin < rnext ? kmin : rnext;
+                        pre_slot = -1;
+                        if (nk != KEY_NONE) {
+                            pre_slot = (int)((unsigned)nk >> 1);
+                            const int32_t *nl = p.nbr0 + (size_t)pre_slot * (size_t)p.M0;
+                            pre_t = lane < p.M0 ? nl[lane] : -1;
+                            if (p.M0 > 32 && lane == 0) prefetch_l2(nl + 32);
+                        }
+                    }
+#endif
                     /* R ← ef smallest of R ∪ F */
                     bool improved = false;
                     for (int base = 0; base < nf; base += 32) {

@@ -42,8 +42,7 @@ struct MuninnCudaIndex {
     bool have_timing = false;
     int num_sms = 0, teams_per_sm = 0, warps_per_query = 1;
     int64_t launches = 0;
-    unsigned epoch_base = 0;
-    unsigned long long *d_vis = nullptr; size_t vis_entries = 0;
+    unsigned *d_vis = nullptr; size_t vis_entries = 0;  /* visited arena: teams × cap 32-bit slots */
     int *d_ctl = nullptr;        /* [8]: work counters ×3, retry counts ×2 */
     int *d_retry = nullptr; size_t retry_cap = 0; /* 2 × nq */
     /* staging for the host-buffer entry points */
@@ -291,10 +290,10 @@ static unsigned pow2_at_least(unsigned long long v) {
 }
 static unsigned log2u(unsigned v) { unsigned l = 0; while ((1u << l) < v) l++; return l; }
 
-template <int METRIC>
-static cudaError_t launch_levels(MuninnCudaIndex *h, SearchParams p, size_t smem, const int teams[3],
-                                 const unsigned caps[3], int nlevels, int nq) {
-    cudaError_t e = cudaFuncSetAttribute(hnsw_search_kernel<METRIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+template <int METRIC, int RB>
+static cudaError_t launch_levels_rb(MuninnCudaIndex *h, SearchParams p, size_t smem, const int teams[3],
+                                    const unsigned caps[3], int nlevels, int nq) {
+    cudaError_t e = cudaFuncSetAttribute(hnsw_search_kernel<METRIC, RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     for (int lv = 0; lv < nlevels; lv++) {
         p.vis_cap = caps[lv];
@@ -304,7 +303,7 @@ static cudaError_t launch_levels(MuninnCudaIndex *h, SearchParams p, size_t smem
         p.in_count = lv == 0 ? nullptr : h->d_ctl + 3 + (lv - 1);
         p.out_list = h->d_retry + (size_t)(lv < 2 ? lv : 0) * nq;
         p.out_count_retry = h->d_ctl + 3 + lv;
-        hnsw_search_kernel<METRIC><<<teams[lv], 32, smem, h->stream>>>(p, lv);
+        hnsw_search_kernel<METRIC, RB><<<teams[lv], 32, smem, h->stream>>>(p, lv);
         h->launches++;
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
@@ -313,10 +312,21 @@ static cudaError_t launch_levels(MuninnCudaIndex *h, SearchParams p, size_t smem
 }
 
 template <int METRIC>
-static cudaError_t occupancy_of(int *occ, size_t smem) {
-    cudaError_t e = cudaFuncSetAttribute(hnsw_search_kernel<METRIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+static cudaError_t launch_levels(MuninnCudaIndex *h, SearchParams p, size_t smem, const int teams[3],
+                                 const unsigned caps[3], int nlevels, int nq) {
+    return beam_rows(h->ld) == 12 ? launch_levels_rb<METRIC, 12>(h, p, smem, teams, caps, nlevels, nq)
+                                  : launch_levels_rb<METRIC, 16>(h, p, smem, teams, caps, nlevels, nq);
+}
+
+template <int METRIC, int RB>
+static cudaError_t occupancy_of_rb(int *occ, size_t smem) {
+    cudaError_t e = cudaFuncSetAttribute(hnsw_search_kernel<METRIC, RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, hnsw_search_kernel<METRIC>, 32, smem);
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, hnsw_search_kernel<METRIC, RB>, 32, smem);
+}
+template <int METRIC>
+static cudaError_t occupancy_of(int *occ, size_t smem, int ld) {
+    return beam_rows(ld) == 12 ? occupancy_of_rb<METRIC, 12>(occ, smem) : occupancy_of_rb<METRIC, 16>(occ, smem);
 }
 
 extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *d_queries, int nq, int k, int ef,
@@ -328,14 +338,14 @@ extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *
     if (nq == 0) return MUNINN_CUDA_OK;
     if (!d_queries || !d_ids || !d_dist || !d_count) return fail(h, MUNINN_CUDA_E_ARG, "NULL buffer");
     if (ef < k) ef = k; /* src/hnsw_algo.c:673 */
-    const size_t smem = search_smem_bytes(ef, h->ld);
+    const size_t smem = search_smem_bytes(ef, h->ld, h->M0);
     if (smem > 200 * 1024) return fail(h, MUNINN_CUDA_E_ARG, "ef=%d with dim=%d needs %zu B of shared memory per query (limit 200 KiB)", ef, h->dim, smem);
     CK(h, cudaSetDevice(h->device));
 
     int occ = 0;
-    cudaError_t oe = h->metric == MUNINN_METRIC_L2       ? occupancy_of<METRIC_L2>(&occ, smem)
-                     : h->metric == MUNINN_METRIC_COSINE ? occupancy_of<METRIC_COSINE>(&occ, smem)
-                                                         : occupancy_of<METRIC_IP>(&occ, smem);
+    cudaError_t oe = h->metric == MUNINN_METRIC_L2       ? occupancy_of<METRIC_L2>(&occ, smem, h->ld)
+                     : h->metric == MUNINN_METRIC_COSINE ? occupancy_of<METRIC_COSINE>(&occ, smem, h->ld)
+                                                         : occupancy_of<METRIC_IP>(&occ, smem, h->ld);
     CK(h, oe);
     if (occ < 1) return fail(h, MUNINN_CUDA_E_CUDA, "search kernel does not fit on an SM");
     int tps = h->teams_per_sm > 0 ? std::min(h->teams_per_sm, occ) : occ;
@@ -350,16 +360,11 @@ extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *
     const size_t arena = std::max<size_t>((size_t)teams[0] * caps[0], cap_all);
     for (int lv = 1; lv < 3; lv++) teams[lv] = (int)std::max<size_t>(1, std::min<size_t>(arena / caps[lv], (size_t)teams[0]));
 
-    if (arena > h->vis_entries) {
+    if (arena > h->vis_entries) { /* no initialisation needed: every query clears its team's table */
         CK(h, cudaStreamSynchronize(h->stream));
         cudaFree(h->d_vis); h->d_vis = nullptr; h->vis_entries = 0;
-        CK(h, cudaMalloc((void **)&h->d_vis, arena * 8));
-        CK(h, cudaMemsetAsync(h->d_vis, 0, arena * 8, h->stream));
-        h->vis_entries = arena; h->epoch_base = 0;
-    }
-    if ((unsigned long long)h->epoch_base + 3ull * (unsigned)nq + 2ull >= 0xffffffffull) {
-        CK(h, cudaMemsetAsync(h->d_vis, 0, h->vis_entries * 8, h->stream));
-        h->epoch_base = 0;
+        CK(h, cudaMalloc((void **)&h->d_vis, arena * 4));
+        h->vis_entries = arena;
     }
     if ((size_t)2 * nq > h->retry_cap) {
         CK(h, cudaStreamSynchronize(h->stream));
@@ -378,8 +383,7 @@ extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *
     p.queries = d_queries; p.nq = nq; p.k = k; p.ef = ef;
     p.patience_max = std::max(ef / 4, 10); /* src/hnsw_algo.c:372-374 */
     p.out_ids = d_ids; p.out_dist = d_dist; p.out_count = d_count; p.stats = d_stats;
-    p.vis = h->d_vis; p.epoch_base = h->epoch_base;
-    h->epoch_base += 3u * (unsigned)nq;
+    p.vis = h->d_vis;
 
     CK(h, cudaEventRecord(h->ev0, h->stream));
     cudaError_t e = h->metric == MUNINN_METRIC_L2       ? launch_levels<METRIC_L2>(h, p, smem, teams, caps, nlevels, nq)
@@ -540,10 +544,10 @@ static float tc_eps(int mode, int kp) {
     return (float)(2.0 * (split + terms * ldexp(1.0, -23)) + 4.0 * (kp / 4.0 + 8.0) * ldexp(1.0, -24));
 }
 
-template <int METRIC, int NPASS, int BN>
+template <int METRIC, int NPASS, int BN, bool DBG = false>
 static cudaError_t launch_filter(MuninnCudaIndex *h, const CUtensorMap maps[4], const tc::FilterParams &fp) {
     using Cfg = tc::FilterCfg<NPASS, BN>;
-    auto kern = tc::exact_tc_filter<METRIC, NPASS, BN>;
+    auto kern = tc::exact_tc_filter<METRIC, NPASS, BN, DBG>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES);
     if (e != cudaSuccess) return e;
     const long long tiles = (long long)((fp.nq + tc::BM - 1) / tc::BM) * ((fp.rows + BN - 1) / BN);
@@ -555,6 +559,7 @@ static cudaError_t launch_filter(MuninnCudaIndex *h, const CUtensorMap maps[4], 
 template <int METRIC>
 static cudaError_t launch_filter_m(MuninnCudaIndex *h, const CUtensorMap maps[4], const tc::FilterParams &fp) {
     const bool three = h->exact_mode == MUNINN_EXACT_TC_3XTF32;
+    if (fp.dbg_panel) return three ? launch_filter<METRIC, 3, 256, true>(h, maps, fp) : launch_filter<METRIC, 1, 256, true>(h, maps, fp);
     if (h->tc_tile_rows == 128)
         return three ? launch_filter<METRIC, 3, 128>(h, maps, fp) : launch_filter<METRIC, 1, 128>(h, maps, fp);
     return three ? launch_filter<METRIC, 3, 256>(h, maps, fp) : launch_filter<METRIC, 1, 256>(h, maps, fp);
@@ -621,7 +626,9 @@ static int exact_knn_tc(MuninnCudaIndex *h, const float *d_queries, int nq, int 
     int chunks = 0;
     size_t ev_used = 0;
     for (long long done = 0; done < n;) {
-        long long chunk = done == 0 ? std::min<long long>(cap, n) : std::min<long long>(std::min(done, chunk_max), n - done);
+        /* first chunk: every row survives (τ = +inf), so keep it small but ≥ 2k rows; then double */
+        long long chunk = done == 0 ? std::min<long long>(std::min(cap, std::max(256, (2 * k + 255) / 256 * 256)), n)
+                                    : std::min<long long>(std::min(done, chunk_max), n - done);
         if (d_dbg) chunk = n;
         tc::tc_split_rows<<<h->num_sms * 8, 256, 0, st>>>(h->d_vec + (size_t)done * h->ld, h->ld, h->dim, chunk, kp, x_hi,
                                                           three ? x_lo : nullptr);
@@ -730,7 +737,7 @@ extern "C" int muninn_cuda_exact_stats(MuninnCudaIndex *h, MuninnExactStats *out
     return MUNINN_CUDA_OK;
 }
 
-/* Error probe: d̃ of the filter for every (query, row) pair of rows [0, rows) → out_approx [nq × rows] (host). */
+/* Error probe: the filter's contraction Σq·x for every (query, row) pair of rows [0, rows) → out_approx [nq × rows] (host). */
 extern "C" int muninn_cuda_exact_filter_probe(MuninnCudaIndex *h, const float *queries, int nq, int64_t rows, float *out_approx) {
     if (!h) return MUNINN_CUDA_E_ARG;
     if (!h->uploaded) return fail(h, MUNINN_CUDA_E_STATE, "probe before muninn_cuda_index_upload");
@@ -812,5 +819,66 @@ extern "C" int muninn_cuda_distance_batch(int device, int metric, int dim, int64
             rc = MUNINN_CUDA_E_CUDA;
     }
     cudaFree(da); cudaFree(db); cudaFree(dout);
+    return rc;
+}
+
+/* ───────────────────────── access-pattern ceiling (diagnostic) ───────────────────────── */
+
+/* Independent random gathers of whole rows (16-byte chunk per lane, one coalesced request per 512
+ * bytes), two rows in flight per warp, 64 warps per SM, no dependent work: what the memory system
+ * delivers for the search kernel's access pattern when nothing else is in the way. */
+__global__ void __launch_bounds__(256) gather_ceiling_kernel(const float4 *__restrict__ slab, unsigned long long row_mask,
+                                                             int chunks_per_row, int iters, float *out) {
+    const int lane = threadIdx.x & 31;
+    unsigned long long s = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 0x9E3779B97F4A7C15ull + 12345;
+    float acc = 0.f;
+    for (int it = 0; it < iters; it++) {
+        float4 v[2];
+#pragma unroll
+        for (int r = 0; r < 2; r++) {
+            s = s * 6364136223846793005ull + 1442695040888963407ull;
+            const float4 *p = slab + ((s >> 24) & row_mask) * (unsigned long long)chunks_per_row;
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int c = lane; c < chunks_per_row; c += 32) {
+                const float4 t = ldg_stream_f4(reinterpret_cast<const float *>(p + c));
+                a.x += t.x; a.y += t.y; a.z += t.z; a.w += t.w;
+            }
+            v[r] = a;
+        }
+        acc += v[0].x + v[0].y + v[0].z + v[0].w + v[1].x + v[1].y + v[1].z + v[1].w;
+    }
+    if (acc == 123.456f) out[0] = acc;
+}
+
+extern "C" int muninn_cuda_gather_ceiling(int device, int row_bytes, int64_t slab_bytes, float *out_gbps) {
+    if (!out_gbps || row_bytes < 16 || (row_bytes & 15) || slab_bytes < (int64_t)row_bytes * 1024) return MUNINN_CUDA_E_ARG;
+    if (muninn_cuda_device_count() <= 0) return MUNINN_CUDA_E_NODEVICE;
+    if (cudaSetDevice(device) != cudaSuccess) return MUNINN_CUDA_E_ARG;
+    unsigned long long rows = 1;
+    while (2 * rows * (unsigned long long)row_bytes <= (unsigned long long)slab_bytes) rows *= 2;
+    float4 *slab = nullptr; float *out = nullptr;
+    int sms = 0, rc = MUNINN_CUDA_OK;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (cudaMalloc((void **)&slab, rows * row_bytes) != cudaSuccess || cudaMalloc((void **)&out, 4) != cudaSuccess) rc = MUNINN_CUDA_E_NOMEM;
+    if (!rc && (cudaMemset(slab, 0, rows * row_bytes) != cudaSuccess || cudaEventCreate(&e0) != cudaSuccess ||
+                cudaEventCreate(&e1) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess))
+        rc = MUNINN_CUDA_E_CUDA;
+    if (!rc) {
+        const int grid = sms * 8, iters = (int)std::max<long long>(50, (1ll << 34) / ((long long)grid * 8 * 2 * row_bytes));
+        gather_ceiling_kernel<<<grid, 256>>>(slab, rows - 1, row_bytes / 16, 20, out);
+        float best = 1e30f;
+        for (int rep = 0; rep < 3 && !rc; rep++) {
+            cudaEventRecord(e0);
+            gather_ceiling_kernel<<<grid, 256>>>(slab, rows - 1, row_bytes / 16, iters, out);
+            cudaEventRecord(e1);
+            float ms = 0.f;
+            if (cudaEventSynchronize(e1) != cudaSuccess || cudaEventElapsedTime(&ms, e0, e1) != cudaSuccess) rc = MUNINN_CUDA_E_CUDA;
+            best = std::min(best, ms);
+        }
+        if (!rc) *out_gbps = (float)((double)grid * 8 * iters * 2 * row_bytes / best / 1e6);
+    }
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    cudaFree(slab); cudaFree(out);
     return rc;
 }

@@ -30,6 +30,7 @@ ABI_SYMBOLS = (
     "muninn_cuda_last_kernel_ms", "muninn_cuda_launch_count", "muninn_cuda_set_tuning", "muninn_cuda_exact_knn",
     "muninn_cuda_exact_knn_device", "muninn_cuda_topk_merge_device", "muninn_cuda_distance_batch",
     "muninn_cuda_set_exact_mode", "muninn_cuda_exact_stats", "muninn_cuda_exact_filter_probe",
+    "muninn_cuda_gather_ceiling",
 )
 
 EXACT_CUDA_CORE, EXACT_TC_3XTF32, EXACT_TC_1XTF32 = 0, 1, 2
@@ -88,6 +89,7 @@ def lib():
         L.muninn_cuda_set_exact_mode.argtypes = [_vp, C.c_int, C.c_int]
         L.muninn_cuda_exact_stats.argtypes = [_vp, C.POINTER(ExactStats)]
         L.muninn_cuda_exact_filter_probe.argtypes = [_vp, _vp, C.c_int, C.c_int64, _vp]
+        L.muninn_cuda_gather_ceiling.argtypes = [C.c_int, C.c_int, C.c_int64, C.POINTER(C.c_float)]
         _lib = L
     return _lib
 
@@ -110,6 +112,15 @@ def distance_batch(metric: int, a, b, device: int = 0) -> np.ndarray:
     if rc != 0:
         raise MuninnCudaError(rc, lib().muninn_cuda_strerror(rc).decode())
     return out
+
+
+def gather_ceiling(row_bytes: int, slab_bytes: int = 1 << 30, device: int = 0) -> float:
+    """GB/s of independent random row gathers on this device (roofline diagnostic)."""
+    out = C.c_float(0.0)
+    rc = lib().muninn_cuda_gather_ceiling(device, row_bytes, slab_bytes, C.byref(out))
+    if rc != 0:
+        raise MuninnCudaError(rc, lib().muninn_cuda_strerror(rc).decode())
+    return float(out.value)
 
 
 def _ptr(a: np.ndarray | None):

@@ -134,17 +134,17 @@ def test_filter_error_is_inside_the_margin(cuda, metric, dim, mode):
     q = uniform(dim + 1, nq, dim) * np.float32(3.0)
     with cuda.HnswIndexCuda.from_graph(flat(base, metric)) as idx:
         idx.set_exact_mode(mode, 256)
-        approx = idx.exact_filter_probe(q, n).astype(np.float64)
+        s_tc = idx.exact_filter_probe(q, n).astype(np.float64)  # the tensor-core contraction Σ q·x
         c_eps = idx.exact_stats()["c_eps"]
     b64, q64 = base.astype(np.float64), q.astype(np.float64)
     dot = q64 @ b64.T
     qn, xn = (q64 * q64).sum(1)[:, None], (b64 * b64).sum(1)[None, :]
-    if metric == L2:
-        true, eps = qn + xn - 2 * dot, c_eps * (qn + xn)
-    elif metric == IP:
-        true, eps = -dot, c_eps * (qn + xn)
-    else:
-        true, eps = 1.0 - dot / np.sqrt(qn * xn), c_eps * np.ones_like(dot)
-    ratio = float((np.abs(approx - true) / eps).max())
+    if metric == L2:  # d̃ = qn + xn − 2s
+        err, eps = 2 * np.abs(s_tc - dot), c_eps * (qn + xn)
+    elif metric == IP:  # d̃ = −s
+        err, eps = np.abs(s_tc - dot), c_eps * (qn + xn)
+    else:  # d̃ = 1 − s/(|q||x|)
+        err, eps = np.abs(s_tc - dot) / np.sqrt(qn * xn), c_eps * np.ones_like(dot)
+    ratio = float((err / eps).max())
     print(f"metric={metric} dim={dim} mode={mode}: max |err|/eps = {ratio:.4f} (c_eps={c_eps:.3e})")
     assert ratio < (0.1 if mode == 1 else 0.5)
