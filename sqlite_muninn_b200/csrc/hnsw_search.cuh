@@ -43,6 +43,12 @@ namespace muninn {
 #ifndef MUNINN_ROW_EVICT_FIRST
 #define MUNINN_ROW_EVICT_FIRST 1 /* gathered rows are streamed: L2 evict-first keeps lists and visited tables resident */
 #endif
+#ifndef MUNINN_BULK_ROWS
+#define MUNINN_BULK_ROWS 1       /* rows staged by one TMA bulk copy each (lane r issues row r) instead of 16-byte LDGSTS */
+#endif
+#ifndef MUNINN_F32X2
+#define MUNINN_F32X2 1           /* the two chains a lane owns are kept as one packed f32x2 register pair */
+#endif
 #ifndef MUNINN_NEXT_PREFETCH
 #define MUNINN_NEXT_PREFETCH 0   /* fetch the next candidate's neighbour list while R is being merged (measured: no gain) */
 #endif
@@ -77,6 +83,8 @@ struct TeamSmem {
     float *q;                /* [ld] */
     float *P;                /* [beam_rows * PSTRIDE] row staging tile */
     int *Fs;                 /* [fs_len(M0)] fresh slots; the greedy descent keeps list positions at Fs[fs_pos(M0) + i] */
+    unsigned long long *bar; /* mbarrier the bulk row copies complete on */
+    unsigned phase;          /* its current parity */
 };
 
 __host__ __device__ inline int fs_pos(int M0) { return M0 > DB ? M0 : DB; }
@@ -87,6 +95,7 @@ __host__ __device__ inline size_t search_smem_bytes(int ef, int ld, int M0) {
     b += ((size_t)ld * 4 + 15) / 16 * 16;
     b += (size_t)beam_rows(ld) * PSTRIDE * 4;
     b += ((size_t)fs_len(M0) * 4 + 15) & ~(size_t)15;
+    b += 16; /* mbarrier */
     return b;
 }
 
@@ -109,6 +118,53 @@ __device__ __forceinline__ void cp_async_wait_all() {
     asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
 }
 
+/* TMA bulk copy global → shared of `bytes` (multiple of 16), completion counted on an mbarrier */
+__device__ __forceinline__ void bulk_row_copy(void *smem_dst, const void *gmem_src, unsigned bytes, unsigned long long *bar,
+                                              unsigned long long policy) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst), b = (unsigned)__cvta_generic_to_shared(bar);
+#if MUNINN_ROW_EVICT_FIRST
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 ::"r"(d), "l"(gmem_src), "r"(bytes), "r"(b), "l"(policy) : "memory");
+#else
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(d), "l"(gmem_src), "r"(bytes), "r"(b) : "memory");
+#endif
+}
+__device__ __forceinline__ void bar_init(unsigned long long *bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void bar_expect_tx(unsigned long long *bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bar_wait(unsigned long long *bar, unsigned parity) {
+    const unsigned a = (unsigned)__cvta_generic_to_shared(bar);
+    unsigned done;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(a), "r"(parity) : "memory");
+    } while (!done);
+}
+
+/* packed pair of fp32 (sm_100 FADD2): both halves are IEEE round-to-nearest, i.e. bit-identical to two
+ * scalar operations. The products stay scalar FMULs on purpose: ptxas contracts mul.rn.f32x2 +
+ * add.rn.f32x2 into one FFMA2, which would not be the reference's two roundings. */
+__device__ __forceinline__ unsigned long long f2_pack(float lo, float hi) {
+    return ((unsigned long long)__float_as_uint(hi) << 32) | __float_as_uint(lo);
+}
+__device__ __forceinline__ float f2_lo(unsigned long long v) { return __uint_as_float((unsigned)v); }
+__device__ __forceinline__ float f2_hi(unsigned long long v) { return __uint_as_float((unsigned)(v >> 32)); }
+__device__ __forceinline__ unsigned long long f2_sub(unsigned long long a, unsigned long long b) {
+    unsigned long long d;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ unsigned long long f2_add(unsigned long long a, unsigned long long b) {
+    unsigned long long d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+
 template <int METRIC>
 __device__ __forceinline__ float prod1(float a, float b) {
     if (METRIC == METRIC_L2) { float d = __fsub_rn(a, b); return __fmul_rn(d, d); }
@@ -126,7 +182,7 @@ __device__ __forceinline__ float prod1(float a, float b) {
  * free. Every lane of a row group returns that row's distance.
  */
 template <int METRIC, int L>
-__device__ __forceinline__ float warp_dist_rows(const SearchParams &p, const TeamSmem &sm, const int *bs, int nb,
+__device__ __forceinline__ float warp_dist_rows(const SearchParams &p, TeamSmem &sm, const int *bs, int nb,
                                                 float q_norm2, int lane, unsigned long long pol) {
     constexpr int CH = 4 / L;
     const int cpr = p.ld >> 2, cfull = p.dim >> 2, rem = p.dim & 3;
@@ -135,8 +191,16 @@ __device__ __forceinline__ float warp_dist_rows(const SearchParams &p, const Tea
     float nb2 = 1.0f;
     if (METRIC == METRIC_COSINE && mine && h == 0) nb2 = p.norm2[bs[row]];
     float s0 = 0.0f, s1 = 0.0f, tl0 = 0.0f, tl1 = 0.0f, tl2 = 0.0f;
+    unsigned long long s01 = 0ull; /* (s0, s1) packed, CH == 2 */
     for (int t0 = 0; t0 < cpr; t0 += 32) {
         const int tc = cpr - t0 < 32 ? cpr - t0 : 32;
+#if MUNINN_BULK_ROWS
+        if (lane == 0) bar_expect_tx(sm.bar, (unsigned)(nb * tc * 16));
+        __syncwarp();
+        if (lane < nb) bulk_row_copy(sm.P + lane * PSTRIDE, p.vec + (size_t)bs[lane] * (size_t)p.ld + 4 * t0, (unsigned)(tc * 16), sm.bar, pol);
+        bar_wait(sm.bar, sm.phase);
+        sm.phase ^= 1u;
+#else
         if (lane < tc) {
             const float *src = p.vec + 4 * (t0 + lane);
             float *dst = sm.P + 4 * lane;
@@ -144,6 +208,7 @@ __device__ __forceinline__ float warp_dist_rows(const SearchParams &p, const Tea
         }
         cp_async_wait_all();
         __syncwarp();
+#endif
         if (mine) {
             int tfull = cfull - t0;
             tfull = tfull > tc ? tc : tfull;
@@ -151,7 +216,16 @@ __device__ __forceinline__ float warp_dist_rows(const SearchParams &p, const Tea
             const float *qr = sm.q + 4 * t0 + CH * h;
 #pragma unroll 8
             for (int cc = 0; cc < tfull; cc++) {
-                if (CH == 2) {
+                if (CH == 2 && MUNINN_F32X2) {
+                    const unsigned long long x = *reinterpret_cast<const unsigned long long *>(xr + 4 * cc);
+                    const unsigned long long q = *reinterpret_cast<const unsigned long long *>(qr + 4 * cc);
+                    unsigned long long pr;
+                    if (METRIC == METRIC_L2) {
+                        const unsigned long long d = f2_sub(q, x);
+                        pr = f2_pack(__fmul_rn(f2_lo(d), f2_lo(d)), __fmul_rn(f2_hi(d), f2_hi(d)));
+                    } else pr = f2_pack(__fmul_rn(f2_lo(q), f2_lo(x)), __fmul_rn(f2_hi(q), f2_hi(x)));
+                    s01 = f2_add(s01, pr);
+                } else if (CH == 2) {
                     const float2 x = *reinterpret_cast<const float2 *>(xr + 4 * cc);
                     const float2 q = *reinterpret_cast<const float2 *>(qr + 4 * cc);
                     s0 = __fadd_rn(s0, prod1<METRIC>(q.x, x.x));
@@ -169,6 +243,7 @@ __device__ __forceinline__ float warp_dist_rows(const SearchParams &p, const Tea
         }
         __syncwarp(); /* the tile is overwritten by the next column block */
     }
+    if (CH == 2 && MUNINN_F32X2) { s0 = f2_lo(s01); s1 = f2_hi(s01); }
     float sum;
     if (L == 4) {
         float c0 = __shfl_sync(FULL, s0, g), c1 = __shfl_sync(FULL, s0, g + 1), c2 = __shfl_sync(FULL, s0, g + 2),
@@ -263,8 +338,14 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
         sm.S = reinterpret_cast<unsigned long long *>(b); b += 32 * 8;
         sm.q = reinterpret_cast<float *>(b); b += ((size_t)p.ld * 4 + 15) / 16 * 16;
         sm.P = reinterpret_cast<float *>(b); b += (size_t)RB * PSTRIDE * 4;
-        sm.Fs = reinterpret_cast<int *>(b);
+        sm.Fs = reinterpret_cast<int *>(b); b += ((size_t)fs_len(p.M0) * 4 + 15) & ~(size_t)15;
+        sm.bar = reinterpret_cast<unsigned long long *>(b);
+        sm.phase = 0u;
     }
+#if MUNINN_BULK_ROWS
+    if (lane == 0) bar_init(sm.bar, 1);
+    __syncwarp();
+#endif
     unsigned *tab = p.vis + (size_t)blockIdx.x * (size_t)p.vis_cap;
     const int nwork = level == 0 ? p.nq : *p.in_count;
     const int ef = p.ef, FP = fs_pos(p.M0);
