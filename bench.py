@@ -435,6 +435,13 @@ def run_gpu_arm(args, rank: int, local_rank: int, world: int) -> None:
         cpu_desc = {"value": n_s / secs, "unit": "queries/s", "cores": cpu.threads, "kind": cpu.kind,
                     "sample": f"first {n_s} of the {nq} queries, ef={ef}, k={k}, {secs:.1f}s on {cpu.threads} host threads",
                     "id_exact_fraction_vs_gpu": same}
+        # the same search with only the linear visited scan swapped for O(1) stamps
+        # (oracle/hnsw_oracle.c, results bit-identical to the reference's) — the stronger CPU comparison
+        from oracle.bindings import Oracle
+        o_ids, _, _, _, o_secs = Oracle().graph(g).search(queries[:n_s], k, ef, threads=cpu.threads, want_stats=False)
+        cpu_desc["modified_reference_o1_visited"] = {
+            "value": n_s / max(o_secs, 1e-9), "unit": "queries/s", "cores": cpu.threads, "kind": "port",
+            "ids_identical_to_reference": bool(np.array_equal(o_ids, c_ids))}
     if rank == 0:
         peak, which = measured_peak_gbs()
         k_ms = float(np.mean(kernel_ms))

@@ -135,14 +135,17 @@ int muninn_cuda_exact_knn_device(MuninnCudaIndex *idx, const float *d_queries, i
  * How exact k-NN is evaluated. The OUTPUT is identical in every mode (bit-exact ids and distances,
  * tests/test_gpu_exact_tc.py); the modes differ in how the n·nq distance evaluations are pruned.
  *   MUNINN_EXACT_CUDA_CORE   every pair in the reference's fp32 chain order on the CUDA cores
- *   MUNINN_EXACT_TC_3XTF32   (default) tiled Q·Xᵀ on the tensor cores as 3xTF32 (tcgen05 + TMA + TMEM)
+ *   MUNINN_EXACT_TC_3XTF32   tiled Q·Xᵀ on the tensor cores as 3xTF32 (tcgen05 + TMA + TMEM)
  *                            with a fused per-tile selection against each query's running k-th
  *                            distance; only the survivors are evaluated in the reference's order
- *   MUNINN_EXACT_TC_1XTF32   same with a single TF32 product and a correspondingly wider margin
+ *   MUNINN_EXACT_TC_1XTF32   same with a single TF32 product and a correspondingly wider margin; the
+ *                            MMA reads the fp32 rows as stored (no split pass: the base is read once)
+ *   MUNINN_EXACT_TC_AUTO     (default) 3xTF32 for batches of >= 1024 queries (tensor-bound), 1xTF32 below
+ *                            (HBM-bound); muninn_cuda_exact_stats reports which one ran
  * tile_rows = base rows per CTA tile (0 = default 256, or 128). In the tensor-core modes the
  * device entry point synchronises once with the host before it returns.
  */
-enum { MUNINN_EXACT_CUDA_CORE = 0, MUNINN_EXACT_TC_3XTF32 = 1, MUNINN_EXACT_TC_1XTF32 = 2 };
+enum { MUNINN_EXACT_CUDA_CORE = 0, MUNINN_EXACT_TC_3XTF32 = 1, MUNINN_EXACT_TC_1XTF32 = 2, MUNINN_EXACT_TC_AUTO = 3 };
 int muninn_cuda_set_exact_mode(MuninnCudaIndex *idx, int mode, int tile_rows);
 
 /* Counters of the handle's most recent exact k-NN call. */

@@ -52,7 +52,8 @@ struct MuninnCudaIndex {
     float *d_panel = nullptr; size_t panel_floats = 0;
     unsigned long long *d_topk = nullptr; int *d_topk_size = nullptr; size_t topk_cap = 0, topk_q = 0;
     /* exact k-NN, tensor-core filter (exact_tc.cuh) */
-    int exact_mode = MUNINN_EXACT_TC_3XTF32, tc_tile_rows = 256;
+    int exact_mode = MUNINN_EXACT_TC_AUTO, tc_tile_rows = 256;
+    int exact_mode_run = MUNINN_EXACT_TC_3XTF32; /* what AUTO resolved to for the current call */
     float *d_qsplit = nullptr; size_t qsplit_floats = 0;   /* q_hi | q_lo, [nq × kp] each */
     float *d_xsplit = nullptr; size_t xsplit_floats = 0;   /* x_hi | x_lo of one chunk */
     float *d_qaux = nullptr, *d_tau = nullptr; int *d_cand_count = nullptr, *d_overflow = nullptr, *d_qmap = nullptr;
@@ -514,6 +515,8 @@ static EncodeTiledFn tensor_map_encoder() {
 
 /* [rows × kp] fp32, row-major; box = 32 floats (one 128-byte swizzle row) × box_rows */
 static int make_slab_map(MuninnCudaIndex *h, CUtensorMap *map, const float *ptr, int kp, long long rows, int box_rows) {
+    /* kp = floats per row = row stride; columns past kp (the last k-block of a raw slab whose width is
+     * not a multiple of 32) are out of bounds for TMA and arrive as zeros */
     EncodeTiledFn enc = tensor_map_encoder();
     if (!enc) return fail(h, MUNINN_CUDA_E_CUDA, "cuTensorMapEncodeTiled not available from the driver");
     cuuint64_t dims[2] = {(cuuint64_t)kp, (cuuint64_t)rows};
@@ -558,7 +561,7 @@ static cudaError_t launch_filter(MuninnCudaIndex *h, const CUtensorMap maps[4], 
 
 template <int METRIC>
 static cudaError_t launch_filter_m(MuninnCudaIndex *h, const CUtensorMap maps[4], const tc::FilterParams &fp) {
-    const bool three = h->exact_mode == MUNINN_EXACT_TC_3XTF32;
+    const bool three = h->exact_mode_run == MUNINN_EXACT_TC_3XTF32;
     if (fp.dbg_panel) return three ? launch_filter<METRIC, 3, 256, true>(h, maps, fp) : launch_filter<METRIC, 1, 256, true>(h, maps, fp);
     if (h->tc_tile_rows == 128)
         return three ? launch_filter<METRIC, 3, 128>(h, maps, fp) : launch_filter<METRIC, 1, 128>(h, maps, fp);
@@ -570,14 +573,19 @@ static cudaError_t launch_filter_m(MuninnCudaIndex *h, const CUtensorMap maps[4]
 static int exact_knn_tc(MuninnCudaIndex *h, const float *d_queries, int nq, int k, int64_t index_base, int64_t *d_idx,
                         float *d_dist, int32_t *d_count, float *d_dbg, long long dbg_rows) {
     const int kp = (h->dim + tc::BK - 1) / tc::BK * tc::BK, bn = h->tc_tile_rows;
-    const bool three = h->exact_mode == MUNINN_EXACT_TC_3XTF32;
+    /* AUTO: large batches are tensor-bound → 3xTF32 (tight margin, split slabs); small batches are
+     * HBM-bound → one TF32 product straight off the fp32 slab (no split pass: the base is read once) */
+    h->exact_mode_run = h->exact_mode == MUNINN_EXACT_TC_AUTO ? (nq >= 1024 || d_dbg ? MUNINN_EXACT_TC_3XTF32 : MUNINN_EXACT_TC_1XTF32)
+                                                              : h->exact_mode;
+    const bool three = h->exact_mode_run == MUNINN_EXACT_TC_3XTF32;
+    const bool raw_x = !three; /* 1xTF32: the MMA reads the fp32 rows as they are (it drops the low 13 bits) */
     const int cap = d_dbg ? 256 : std::max(1024, (4 * k + 255) / 256 * 256);
     const long long n = d_dbg ? dbg_rows : h->n;
-    /* row scratch: ≤ 1 GiB of split slabs per chunk, whole tiles */
-    long long chunk_max = (long long)((1ull << 30) / ((size_t)kp * 4 * (three ? 2 : 1)));
+    /* row scratch: ≤ 1 GiB of split slabs per chunk, whole tiles (none when the slab is read raw) */
+    long long chunk_max = raw_x ? (1ll << 40) : (long long)((1ull << 30) / ((size_t)kp * 4 * (three ? 2 : 1)));
     chunk_max = std::max<long long>(cap, chunk_max / 256 * 256);
     if (d_dbg) chunk_max = std::max<long long>(chunk_max, n);
-    const long long xrows = std::min<long long>(chunk_max, std::max<long long>(n, 1));
+    const long long xrows = raw_x ? 1 : std::min<long long>(chunk_max, std::max<long long>(n, 1));
     cudaStream_t st = h->stream;
     CK(h, grow(&h->d_qsplit, &h->qsplit_floats, (size_t)2 * nq * kp, st));
     CK(h, grow(&h->d_xsplit, &h->xsplit_floats, (size_t)2 * xrows * kp, st));
@@ -620,7 +628,7 @@ static int exact_knn_tc(MuninnCudaIndex *h, const float *d_queries, int nq, int 
     tc::FilterParams fp;
     memset(&fp, 0, sizeof fp);
     fp.xnorm2 = h->d_norm2; fp.qaux = h->d_qaux; fp.tau = h->d_tau; fp.cand = h->d_cand; fp.cand_count = h->d_cand_count;
-    fp.cand_cap = cap; fp.nq = nq; fp.kblocks = kp / tc::BK; fp.c_eps = tc_eps(h->exact_mode, kp);
+    fp.cand_cap = cap; fp.nq = nq; fp.kblocks = kp / tc::BK; fp.c_eps = tc_eps(h->exact_mode_run, kp);
     fp.dbg_panel = d_dbg; fp.dbg_ld = (int)n;
 
     int chunks = 0;
@@ -628,12 +636,18 @@ static int exact_knn_tc(MuninnCudaIndex *h, const float *d_queries, int nq, int 
     for (long long done = 0; done < n;) {
         /* first chunk: every row survives (τ = +inf), so keep it small but ≥ 2k rows; then double */
         long long chunk = done == 0 ? std::min<long long>(std::min(cap, std::max(256, (2 * k + 255) / 256 * 256)), n)
-                                    : std::min<long long>(std::min(done, chunk_max), n - done);
+                                    : std::min<long long>(std::min(3 * done, chunk_max), n - done); /* ×4 per round: ≈ 3k survivors */
         if (d_dbg) chunk = n;
-        tc::tc_split_rows<<<h->num_sms * 8, 256, 0, st>>>(h->d_vec + (size_t)done * h->ld, h->ld, h->dim, chunk, kp, x_hi,
-                                                          three ? x_lo : nullptr);
-        rc = make_slab_map(h, &maps[2], x_hi, kp, chunk, bn);
-        if (!rc) rc = make_slab_map(h, &maps[3], three ? x_lo : x_hi, kp, chunk, bn);
+        if (raw_x) {
+            rc = make_slab_map(h, &maps[2], h->d_vec + (size_t)done * h->ld, h->ld, chunk, bn);
+            maps[3] = maps[2];
+        } else {
+            tc::tc_split_rows<<<h->num_sms * 8, 256, 0, st>>>(h->d_vec + (size_t)done * h->ld, h->ld, h->dim, chunk, kp, x_hi,
+                                                              three ? x_lo : nullptr);
+            h->launches++;
+            rc = make_slab_map(h, &maps[2], x_hi, kp, chunk, bn);
+            if (!rc) rc = make_slab_map(h, &maps[3], three ? x_lo : x_hi, kp, chunk, bn);
+        }
         if (rc) return rc;
         fp.row0 = done; fp.rows = (int)chunk;
         while (h->tc_ev.size() < ev_used + 2) {
@@ -648,7 +662,7 @@ static int exact_knn_tc(MuninnCudaIndex *h, const float *d_queries, int nq, int 
         CK(h, e);
         CK(h, cudaEventRecord(h->tc_ev[ev_used + 1], st));
         ev_used += 2;
-        h->launches += 2;
+        h->launches++;
         if (d_dbg) { chunks = 1; break; }
         const int rr_grid = (nq + 3) / 4;
         if (h->metric == MUNINN_METRIC_L2)
@@ -662,7 +676,7 @@ static int exact_knn_tc(MuninnCudaIndex *h, const float *d_queries, int nq, int 
         done += chunk;
         chunks++;
     }
-    h->exact_stats.mode = h->exact_mode; h->exact_stats.chunks = chunks; h->exact_stats.c_eps = fp.c_eps;
+    h->exact_stats.mode = h->exact_mode_run; h->exact_stats.chunks = chunks; h->exact_stats.c_eps = fp.c_eps;
     h->exact_stats.candidates = 0; h->exact_stats.overflow_queries = 0;
     if (d_dbg) {
         CK(h, cudaStreamSynchronize(st));
@@ -724,7 +738,7 @@ extern "C" int muninn_cuda_exact_knn_device(MuninnCudaIndex *h, const float *d_q
 
 extern "C" int muninn_cuda_set_exact_mode(MuninnCudaIndex *h, int mode, int tile_rows) {
     if (!h) return MUNINN_CUDA_E_ARG;
-    if (mode < MUNINN_EXACT_CUDA_CORE || mode > MUNINN_EXACT_TC_1XTF32) return fail(h, MUNINN_CUDA_E_ARG, "unknown exact mode %d", mode);
+    if (mode < MUNINN_EXACT_CUDA_CORE || mode > MUNINN_EXACT_TC_AUTO) return fail(h, MUNINN_CUDA_E_ARG, "unknown exact mode %d", mode);
     if (tile_rows != 0 && tile_rows != 128 && tile_rows != 256) return fail(h, MUNINN_CUDA_E_ARG, "tile_rows must be 0, 128 or 256");
     h->exact_mode = mode;
     h->tc_tile_rows = tile_rows ? tile_rows : 256;

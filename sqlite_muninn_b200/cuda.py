@@ -33,7 +33,7 @@ ABI_SYMBOLS = (
     "muninn_cuda_gather_ceiling",
 )
 
-EXACT_CUDA_CORE, EXACT_TC_3XTF32, EXACT_TC_1XTF32 = 0, 1, 2
+EXACT_CUDA_CORE, EXACT_TC_3XTF32, EXACT_TC_1XTF32, EXACT_TC_AUTO = 0, 1, 2, 3
 
 
 class ExactStats(C.Structure):
@@ -219,7 +219,7 @@ class HnswIndexCuda:
     def exact_knn_device(self, q_ptr: int, nq: int, k: int, index_base: int, idx_ptr: int, dist_ptr: int, cnt_ptr: int):
         self._check(self.L.muninn_cuda_exact_knn_device(self.h, q_ptr, nq, k, index_base, idx_ptr, dist_ptr, cnt_ptr))
 
-    def set_exact_mode(self, mode: int = EXACT_TC_3XTF32, tile_rows: int = 0):
+    def set_exact_mode(self, mode: int = EXACT_TC_AUTO, tile_rows: int = 0):
         """How exact k-NN prunes its n·nq distance evaluations (results are identical in every mode)."""
         self._check(self.L.muninn_cuda_set_exact_mode(self.h, mode, tile_rows))
 

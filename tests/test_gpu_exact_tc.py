@@ -38,7 +38,7 @@ def latent(seed, n, dim, rank=8):
 CASES = [  # metric, dim, n, nq, k
     (L2, 128, 20000, 300, 10), (L2, 128, 9000, 130, 100), (COS, 768, 6000, 129, 10), (IP, 96, 12000, 257, 10),
     (COS, 24, 5000, 64, 7), (L2, 3, 3000, 33, 5), (IP, 10, 2500, 1, 3), (L2, 131, 4100, 200, 20),
-    (L2, 100, 1500, 128, 300), (COS, 33, 1024, 5, 1), (L2, 16, 700, 40, 10)]
+    (L2, 100, 1500, 128, 300), (COS, 33, 1024, 5, 1), (L2, 16, 700, 40, 10), (L2, 64, 30000, 1100, 10)]
 
 
 @pytest.mark.parametrize("metric,dim,n,nq,k", CASES)
@@ -52,14 +52,16 @@ def test_tensor_modes_equal_oracle(cuda, oracle, metric, dim, n, nq, k):
     i_o, d_o, c_o, _ = oracle.exact_knn(base, q, k, metric, deleted=deleted, threads=8)
     with cuda.HnswIndexCuda.from_graph(flat(base, metric, deleted)) as idx:
         for mode, tile in ((cuda.EXACT_TC_3XTF32, 256), (cuda.EXACT_TC_3XTF32, 128), (cuda.EXACT_TC_1XTF32, 256),
-                           (cuda.EXACT_TC_1XTF32, 128), (cuda.EXACT_CUDA_CORE, 0)):
+                           (cuda.EXACT_TC_1XTF32, 128), (cuda.EXACT_TC_AUTO, 0), (cuda.EXACT_CUDA_CORE, 0)):
             idx.set_exact_mode(mode, tile)
             i_g, d_g, c_g = idx.exact_knn(q, k, index_base=7)
             st = idx.exact_stats()
             assert np.array_equal(c_g, c_o), (mode, tile)
             assert d_g.tobytes() == d_o.tobytes(), (mode, tile)
             assert np.array_equal(i_g, np.where(i_o >= 0, i_o + 7, -1)), (mode, tile)
-            assert st["mode"] == mode
+            # AUTO resolves by batch size: tensor-bound batches → 3xTF32, HBM-bound ones → 1xTF32 off the raw slab
+            want_mode = mode if mode != cuda.EXACT_TC_AUTO else (cuda.EXACT_TC_3XTF32 if nq >= 1024 else cuda.EXACT_TC_1XTF32)
+            assert st["mode"] == want_mode
             if mode != cuda.EXACT_CUDA_CORE:
                 assert st["chunks"] >= 1 and st["candidates"] >= min(n, 1024) * nq * 0  # counters are live
                 assert st["filter_ms"] > 0.0
