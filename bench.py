@@ -282,7 +282,12 @@ def exact_summary(args, nq: int, total_ms: float, st: dict, n_rows: int | None =
            "filter_ms": round(st["filter_ms"], 3), "chunks": st["chunks"],
            "survivors_per_query": round(st["candidates"] / max(nq, 1), 1), "overflow_queries": st["overflow_queries"],
            "algorithmic_TFLOPs": round(flops / max(total_ms, 1e-9) / 1e9, 1)}
-    if st["mode"] != 0 and st["filter_ms"] > 0:
+    if st["mode"] == 2 and st["filter_ms"] > 0:  # small batches: one TF32 product off the raw slab, HBM-bound
+        hbm, hw = measured_peak_gbs()
+        ach = n_rows * args.dim * 4.0 / st["filter_ms"] / 1e6
+        out["roofline"] = {"bound": "hbm", "achieved": round(ach, 1), "peak": hbm, "unit": "GB/s", "frac": round(ach / hbm, 4),
+                           "peak_source": hw, "kernel": "exact_tc_filter (base rows read once / its CUDA-event time)"}
+    elif st["mode"] != 0 and st["filter_ms"] > 0:
         ach = issued / st["filter_ms"] / 1e9
         out["roofline"] = {"bound": "tensor", "achieved": round(ach, 1), "peak": round(peak, 1), "unit": "TFLOP/s",
                            "frac": round(ach / peak, 4), "peak_source": which, "kernel": "exact_tc_filter",

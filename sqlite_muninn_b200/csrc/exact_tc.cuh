@@ -405,6 +405,41 @@ __device__ __forceinline__ float quad_chain(const float *__restrict__ q, const f
     return sum;
 }
 
+/* the same for RU rows at once per lane quad: RU independent chains per lane, RU rows' loads in flight
+ * (the survivors are random rows of the slab: latency, not arithmetic, is what this kernel waits on) */
+template <int METRIC, int RU>
+__device__ __forceinline__ void quad_chain_multi(const float *__restrict__ q, const float *const (&x)[RU], const bool (&have)[RU],
+                                                 int dim, int lane, float (&sum)[RU]) {
+    const int h = lane & 3, g = lane & ~3, cfull = dim >> 2;
+    float s[RU];
+#pragma unroll
+    for (int u = 0; u < RU; u++) s[u] = 0.0f;
+    for (int c = 0; c < cfull; c++) {
+        const float a = q[4 * c + h];
+#pragma unroll
+        for (int u = 0; u < RU; u++) {
+            const float b = have[u] ? x[u][4 * c + h] : 0.0f;
+            float pr;
+            if (METRIC == METRIC_L2) { const float d = __fsub_rn(a, b); pr = __fmul_rn(d, d); } else pr = __fmul_rn(a, b);
+            s[u] = __fadd_rn(s[u], pr);
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < RU; u++) {
+        const float c0 = __shfl_sync(FULL, s[u], g), c1 = __shfl_sync(FULL, s[u], g + 1), c2 = __shfl_sync(FULL, s[u], g + 2),
+                    c3 = __shfl_sync(FULL, s[u], g + 3);
+        float t = __fadd_rn(__fadd_rn(__fadd_rn(c0, c1), c2), c3);
+        if (have[u])
+            for (int i = cfull * 4; i < dim; i++) {
+                const float a = q[i], b = x[u][i];
+                float pr;
+                if (METRIC == METRIC_L2) { const float d = __fsub_rn(a, b); pr = __fmul_rn(d, d); } else pr = __fmul_rn(a, b);
+                t = __fadd_rn(t, pr);
+            }
+        sum[u] = t;
+    }
+}
+
 /* one warp per query: exact distances of the chunk's survivors → sorted top-k → τ */
 template <int METRIC>
 __global__ void __launch_bounds__(128)
@@ -412,6 +447,7 @@ exact_tc_rerank(const float *__restrict__ vec, const float *__restrict__ norm2, 
                 int dim, const float *__restrict__ queries, int nq, int k, const int *__restrict__ cand,
                 int *__restrict__ cand_count, int cap, unsigned long long *__restrict__ topk, int *__restrict__ topk_size,
                 float *__restrict__ tau, int *__restrict__ overflow, unsigned long long *__restrict__ n_cand_total) {
+    constexpr int RU = 4; /* rows per lane quad per round: 32 survivors in flight per warp */
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int q = blockIdx.x * 4 + wib;
@@ -428,25 +464,37 @@ exact_tc_rerank(const float *__restrict__ vec, const float *__restrict__ norm2, 
         float qn2 = 0.0f;
         if (METRIC == METRIC_COSINE) qn2 = quad_chain<METRIC_IP>(qv, qv, dim, lane, true);
         int ev = 0, mp;
-        for (int c0 = 0; c0 < cnt; c0 += 8) {
-            const int ci = c0 + (lane >> 2);
-            const bool have = ci < cnt;
-            const int row = have ? cand[(size_t)q * cap + ci] : 0;
-            const float sum = quad_chain<METRIC>(qv, vec + (size_t)row * ld, dim, lane, have);
-            float d;
-            if (METRIC == METRIC_L2) d = sum;
-            else if (METRIC == METRIC_IP) d = -sum;
-            else d = cosine_finish(sum, qn2, have ? norm2[row] : 1.0f);
-            const bool live = have && (lane & 3) == 0 && !(deleted && deleted[row]);
-            const unsigned long long worst = size >= k ? R[k - 1] : KEY_NONE;
-            const unsigned long long f = live ? make_key(d, (unsigned)row) : KEY_NONE;
-            const bool keep = f < worst;
-            const unsigned km = __ballot_sync(FULL, keep);
-            const int ns = __popc(km);
-            if (ns == 0) continue;
-            if (keep) S[__popc(km & ((1u << lane) - 1))] = f;
-            __syncwarp();
-            size = warp_merge_sorted(R, size, k, S, ns, lane, &mp, &ev);
+        for (int c0 = 0; c0 < cnt; c0 += 8 * RU) {
+            const float *xr[RU];
+            bool have[RU];
+            int row[RU];
+            float sum[RU];
+#pragma unroll
+            for (int u = 0; u < RU; u++) {
+                const int ci = c0 + u * 8 + (lane >> 2);
+                have[u] = ci < cnt;
+                row[u] = have[u] ? cand[(size_t)q * cap + ci] : 0;
+                xr[u] = vec + (size_t)row[u] * ld;
+            }
+            quad_chain_multi<METRIC, RU>(qv, xr, have, dim, lane, sum);
+#pragma unroll
+            for (int u = 0; u < RU; u++) {
+                if (c0 + u * 8 >= cnt) break; /* warp-uniform */
+                float d;
+                if (METRIC == METRIC_L2) d = sum[u];
+                else if (METRIC == METRIC_IP) d = -sum[u];
+                else d = cosine_finish(sum[u], qn2, have[u] ? norm2[row[u]] : 1.0f);
+                const bool live = have[u] && (lane & 3) == 0 && !(deleted && deleted[row[u]]);
+                const unsigned long long worst = size >= k ? R[k - 1] : KEY_NONE;
+                const unsigned long long f = live ? make_key(d, (unsigned)row[u]) : KEY_NONE;
+                const bool keep = f < worst;
+                const unsigned km = __ballot_sync(FULL, keep);
+                const int ns = __popc(km);
+                if (ns == 0) continue;
+                if (keep) S[__popc(km & ((1u << lane) - 1))] = f;
+                __syncwarp();
+                size = warp_merge_sorted(R, size, k, S, ns, lane, &mp, &ev);
+            }
         }
         __syncwarp();
         for (int i = lane; i < size; i += 32) topk[(size_t)q * k + i] = R[i];

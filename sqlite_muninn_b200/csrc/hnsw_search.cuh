@@ -53,10 +53,14 @@ namespace muninn {
 #define MUNINN_NEXT_PREFETCH 0   /* fetch the next candidate's neighbour list while R is being merged (measured: no gain) */
 #endif
 constexpr int DB = 8;             /* rows per distance batch in the greedy descent (4 lanes per row) */
-/* Rows per beam batch. Rows of ≤ 512 bytes are staged in one go: 12-row batches shrink the tile so
- * that 24 teams fit an SM (measured +2 % over 16 rows / 20 teams). Wider rows take several column
+/* Rows per beam batch. Rows of ≤ 512 bytes are staged in one go: 13-row batches shrink the tile so
+ * that 24 teams fit an SM (measured +5 % over 16 rows / 20 teams, +3 % over 12 rows). Wider rows take several column
  * blocks per batch, each a memory round trip: keep the batch as large as the lanes allow. */
-__host__ __device__ inline int beam_rows(int ld) { return MUNINN_RB ? (MUNINN_RB == 12 ? 12 : 16) : (ld <= 128 ? 12 : 16); }
+#ifndef MUNINN_RB_NARROW
+#define MUNINN_RB_NARROW 13 /* batch rows for rows of ≤ 512 bytes: the largest tile that still lets 24 teams share an SM */
+#endif
+constexpr int RB_NARROW = MUNINN_RB_NARROW, RB_WIDE = 16;
+__host__ __device__ inline int beam_rows(int ld) { return MUNINN_RB ? (MUNINN_RB < 16 ? RB_NARROW : RB_WIDE) : (ld <= 128 ? RB_NARROW : RB_WIDE); }
 constexpr unsigned VIS_EMPTY = 0xffffffffu;
 constexpr int PSTRIDE = 128 + 4;  /* floats per staged row: 32 chunks + 4 pad → conflict-free per-row reads */
 constexpr int MAX_M0 = 128;       /* layer-0 list capacity supported (M ≤ 64) */

@@ -315,8 +315,8 @@ static cudaError_t launch_levels_rb(MuninnCudaIndex *h, SearchParams p, size_t s
 template <int METRIC>
 static cudaError_t launch_levels(MuninnCudaIndex *h, SearchParams p, size_t smem, const int teams[3],
                                  const unsigned caps[3], int nlevels, int nq) {
-    return beam_rows(h->ld) == 12 ? launch_levels_rb<METRIC, 12>(h, p, smem, teams, caps, nlevels, nq)
-                                  : launch_levels_rb<METRIC, 16>(h, p, smem, teams, caps, nlevels, nq);
+    return beam_rows(h->ld) == RB_NARROW ? launch_levels_rb<METRIC, RB_NARROW>(h, p, smem, teams, caps, nlevels, nq)
+                                         : launch_levels_rb<METRIC, RB_WIDE>(h, p, smem, teams, caps, nlevels, nq);
 }
 
 template <int METRIC, int RB>
@@ -327,7 +327,7 @@ static cudaError_t occupancy_of_rb(int *occ, size_t smem) {
 }
 template <int METRIC>
 static cudaError_t occupancy_of(int *occ, size_t smem, int ld) {
-    return beam_rows(ld) == 12 ? occupancy_of_rb<METRIC, 12>(occ, smem) : occupancy_of_rb<METRIC, 16>(occ, smem);
+    return beam_rows(ld) == RB_NARROW ? occupancy_of_rb<METRIC, RB_NARROW>(occ, smem) : occupancy_of_rb<METRIC, RB_WIDE>(occ, smem);
 }
 
 extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *d_queries, int nq, int k, int ef,

@@ -72,8 +72,9 @@ def main():
                 "tile_rows": tile, "ms": round(best, 3), "filter_ms": round(fbest, 3), "chunks": st["chunks"],
                 "survivors_per_query": round(st["candidates"] / args.nq, 1), "overflow_queries": st["overflow_queries"],
                 "algorithmic_TFLOPs": round(flops / best / 1e9, 1)}
-        if mode != 0:
-            issued = flops * (3 if mode == 1 else 1)
+        if st["mode"] != 0:
+            issued = flops * (3 if st["mode"] == 1 else 1)
+            line["mode_run"] = st["mode"]
             line["roofline"] = {"bound": "tensor", "achieved": round(issued / fbest / 1e9, 1), "peak": peak, "unit": "TFLOP/s",
                                 "frac": round(issued / fbest / 1e9 / peak, 4), "peak_source": src,
                                 "note": "issued TF32 MMA flops of the filter kernel / its CUDA-event time"}
