@@ -295,6 +295,15 @@ def exact_summary(args, nq: int, total_ms: float, st: dict, n_rows: int | None =
     return out
 
 
+def ncu_traffic(args, ef):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE level-0 search launch, from the `ncu --set full` capture
+    of this command summarised in profiles/r1_search_kernel_v5_ncu_full.txt (7.818 GB + 0.661 GB; algorithmic bytes
+    of the same launch: 8.472 GB). Only the captured configuration has a number."""
+    if (args.config, args.n, args.nq, ef) == (2, 1_000_000, 10_000, 64):
+        return 8.479e9
+    return None
+
+
 def measured_peak_gbs():
     try:
         return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "measured"
@@ -462,7 +471,7 @@ def run_gpu_arm(args, rank: int, local_rank: int, world: int) -> None:
                     "h2d_bytes_per_step": nq * dim * 4, "d2h_bytes_per_step": nq * k * 12 + nq * 4},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                         "frac": round(achieved / peak, 4), "traffic": None, "peak_source": which,
+                         "frac": round(achieved / peak, 4), "traffic": ncu_traffic(args, ef), "peak_source": which,
                          "kernel": f"hnsw_search_kernel<{METRIC_TEXT[args.metric]}>", "kernel_ms": round(k_ms, 3),
                          "of_nominal_8TBps": round(achieved / 8000.0, 4),
                          "random_row_gather_peak": {"GBps": round(gather_peak, 1), "frac": round(achieved / gather_peak, 4),
@@ -605,7 +614,7 @@ def run_exact_arm(args, rank: int, local_rank: int, world: int) -> None:
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--steps", type=int, default=300)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", type=int, default=2, choices=sorted(CONFIGS),

@@ -49,6 +49,9 @@ namespace muninn {
 #ifndef MUNINN_F32X2
 #define MUNINN_F32X2 1           /* the two chains a lane owns are kept as one packed f32x2 register pair */
 #endif
+#ifndef MUNINN_VIS_EVICT_LAST
+#define MUNINN_VIS_EVICT_LAST 0  /* L2 evict-last hint on visited-table probes and claims */
+#endif
 #ifndef MUNINN_NEXT_PREFETCH
 #define MUNINN_NEXT_PREFETCH 0   /* fetch the next candidate's neighbour list while R is being merged (measured: no gain) */
 #endif
@@ -294,13 +297,35 @@ __device__ __forceinline__ float query_norm2(const float *q, int dim) {
  * The table is private to the team and cleared at the start of every query: 32-bit entries (eight
  * per 32-byte sector, so a probe chain usually stays in one sector), plain L2-level loads/stores,
  * intra-warp claim conflicts resolved with match.any. */
-__device__ __forceinline__ int visited_test_and_set(const SearchParams &p, unsigned *tab, int t, bool valid, int lane) {
+__device__ __forceinline__ unsigned vis_load(const unsigned *a, unsigned long long pol) {
+#if MUNINN_VIS_EVICT_LAST
+    unsigned v;
+    asm volatile("ld.global.cg.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(a), "l"(pol) : "memory");
+    return v;
+#else
+    return __ldcg(a);
+#endif
+}
+__device__ __forceinline__ void vis_store(unsigned *a, unsigned v, unsigned long long pol) {
+#if MUNINN_VIS_EVICT_LAST
+    asm volatile("st.global.cg.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(a), "r"(v), "l"(pol) : "memory");
+#else
+    __stcg(a, v);
+#endif
+}
+__device__ __forceinline__ unsigned long long l2_evict_last_policy() {
+    unsigned long long pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ int visited_test_and_set(const SearchParams &p, unsigned *tab, int t, bool valid, int lane,
+                                                    unsigned long long vpol = 0ull) {
     unsigned h = ((unsigned)t * 2654435761u) >> p.vis_shift;
     const unsigned mask = p.vis_cap - 1;
     bool active = valid;
     int fresh = 0;
     while (__any_sync(FULL, active)) {
-        unsigned e = active ? __ldcg(tab + h) : 0u;
+        unsigned e = active ? vis_load(tab + h, vpol) : 0u;
         bool claim = false;
         if (active) {
             if (e == (unsigned)t) active = false; /* already visited */
@@ -311,7 +336,7 @@ __device__ __forceinline__ int visited_test_and_set(const SearchParams &p, unsig
         if (claim) {
             unsigned peers = __match_any_sync(cm, h);
             if ((__ffs(peers) - 1) == lane) {
-                __stcg(tab + h, (unsigned)t);
+                vis_store(tab + h, (unsigned)t, vpol);
                 fresh = 1;
                 active = false;
             } else h = (h + 1) & mask;
@@ -354,6 +379,7 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
     const int nwork = level == 0 ? p.nq : *p.in_count;
     const int ef = p.ef, FP = fs_pos(p.M0);
     const unsigned long long pol = l2_evict_first_policy();
+    const unsigned long long vpol = MUNINN_VIS_EVICT_LAST ? l2_evict_last_policy() : 0ull;
 
     for (;;) {
         int w = 0;
@@ -433,7 +459,7 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
                 if (lane == 0) sm.R[0] = make_key(cur_d, (unsigned)cur << 1);
                 size = 1;
                 visited_clear(tab, p.vis_cap, lane);
-                visited_test_and_set(p, tab, cur, lane == 0, lane);
+                visited_test_and_set(p, tab, cur, lane == 0, lane, vpol);
                 __syncwarp();
                 int stale = 0, lb = 0, n_ins = 1, evicted_open = 0;
                 int pre_slot = -1, pre_t = -1; /* neighbour list fetched ahead for the expected next candidate */
@@ -453,7 +479,7 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
                     if (lane == 0) sm.R[pos] |= 1ull;
                     lb = pos + 1;
                     n_expand++;
-                    if ((unsigned)(n_ins + p.M0) > (p.vis_cap >> 1)) { overflow = true; break; }
+                    if ((unsigned)(n_ins + p.M0) > p.vis_cap - (p.vis_cap >> 2)) { overflow = true; break; } /* keep the load ≤ 3/4 */
 
                     /* neighbour list → visited filter → fresh slots */
                     int nf = 0;
@@ -463,7 +489,7 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
                         int t;
                         if (MUNINN_NEXT_PREFETCH && base == 0 && c == pre_slot) t = pre_t;
                         else t = pos0 < p.M0 ? lst[pos0] : -1;
-                        int fresh = visited_test_and_set(p, tab, t, t >= 0, lane);
+                        int fresh = visited_test_and_set(p, tab, t, t >= 0, lane, vpol);
                         unsigned fm = __ballot_sync(FULL, fresh);
                         if (fresh) sm.Fs[nf + __popc(fm & ((1u << lane) - 1))] = t;
                         nf += __popc(fm);

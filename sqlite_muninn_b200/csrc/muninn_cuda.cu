@@ -16,6 +16,10 @@
 #include "exact_tc.cuh"
 #include "hnsw_search.cuh"
 
+#ifndef MUNINN_VIS_FACTOR
+#define MUNINN_VIS_FACTOR 2
+#endif
+
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
@@ -354,7 +358,10 @@ extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *
     unsigned caps[3];
     teams[0] = (int)std::min<long long>((long long)h->num_sms * tps, nq);
     const unsigned cap_all = pow2_at_least(2ull * (unsigned long long)(h->n + h->M0 + 1));
-    caps[0] = std::min(pow2_at_least(4ull * (unsigned long long)ef * h->M0), cap_all);
+    /* first-level table: 2·ef·2M slots. A search visits ≈ 0.8·ef·2M nodes on the bench graphs, so the table
+     * runs at ≈ 40 % load at the end of a typical query and the whole arena (teams × cap × 4 B = 58 MB at
+     * config 2) stays L2-resident; the rare query that would pass 3/4 load is redone at the next level. */
+    caps[0] = std::min(pow2_at_least((unsigned long long)MUNINN_VIS_FACTOR * (unsigned long long)ef * h->M0), cap_all);
     caps[1] = (unsigned)std::min<unsigned long long>(16ull * caps[0], cap_all);
     caps[2] = cap_all;
     int nlevels = caps[0] == cap_all ? 1 : (caps[1] == cap_all ? 2 : 3);
