@@ -16,6 +16,9 @@
 #include "exact_tc.cuh"
 #include "hnsw_search.cuh"
 
+#ifndef MUNINN_D128
+#define MUNINN_D128 1 /* constant-trip-count instances of the search kernel for dim 96 / 128 / 768 */
+#endif
 #ifndef MUNINN_VIS_FACTOR
 #define MUNINN_VIS_FACTOR 2
 #endif
@@ -295,10 +298,10 @@ static unsigned pow2_at_least(unsigned long long v) {
 }
 static unsigned log2u(unsigned v) { unsigned l = 0; while ((1u << l) < v) l++; return l; }
 
-template <int METRIC, int RB>
+template <int METRIC, int RB, int CD>
 static cudaError_t launch_levels_rb(MuninnCudaIndex *h, SearchParams p, size_t smem, const int teams[3],
                                     const unsigned caps[3], int nlevels, int nq) {
-    cudaError_t e = cudaFuncSetAttribute(hnsw_search_kernel<METRIC, RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(hnsw_search_kernel<METRIC, RB, CD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     for (int lv = 0; lv < nlevels; lv++) {
         p.vis_cap = caps[lv];
@@ -308,7 +311,7 @@ static cudaError_t launch_levels_rb(MuninnCudaIndex *h, SearchParams p, size_t s
         p.in_count = lv == 0 ? nullptr : h->d_ctl + 3 + (lv - 1);
         p.out_list = h->d_retry + (size_t)(lv < 2 ? lv : 0) * nq;
         p.out_count_retry = h->d_ctl + 3 + lv;
-        hnsw_search_kernel<METRIC, RB><<<teams[lv], 32, smem, h->stream>>>(p, lv);
+        hnsw_search_kernel<METRIC, RB, CD><<<teams[lv], 32, smem, h->stream>>>(p, lv);
         h->launches++;
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
@@ -319,19 +322,26 @@ static cudaError_t launch_levels_rb(MuninnCudaIndex *h, SearchParams p, size_t s
 template <int METRIC>
 static cudaError_t launch_levels(MuninnCudaIndex *h, SearchParams p, size_t smem, const int teams[3],
                                  const unsigned caps[3], int nlevels, int nq) {
-    return beam_rows(h->ld) == RB_NARROW ? launch_levels_rb<METRIC, RB_NARROW>(h, p, smem, teams, caps, nlevels, nq)
-                                         : launch_levels_rb<METRIC, RB_WIDE>(h, p, smem, teams, caps, nlevels, nq);
+    /* constant-dimension instances for the shapes BASELINE.json names; any other dim runs the generic ones */
+    if (MUNINN_D128 && h->dim == 128) return launch_levels_rb<METRIC, RB_NARROW, 128>(h, p, smem, teams, caps, nlevels, nq);
+    if (MUNINN_D128 && h->dim == 96) return launch_levels_rb<METRIC, RB_NARROW, 96>(h, p, smem, teams, caps, nlevels, nq);
+    if (MUNINN_D128 && h->dim == 768) return launch_levels_rb<METRIC, RB_WIDE, 768>(h, p, smem, teams, caps, nlevels, nq);
+    return beam_rows(h->ld) == RB_NARROW ? launch_levels_rb<METRIC, RB_NARROW, 0>(h, p, smem, teams, caps, nlevels, nq)
+                                         : launch_levels_rb<METRIC, RB_WIDE, 0>(h, p, smem, teams, caps, nlevels, nq);
 }
 
-template <int METRIC, int RB>
+template <int METRIC, int RB, int CD>
 static cudaError_t occupancy_of_rb(int *occ, size_t smem) {
-    cudaError_t e = cudaFuncSetAttribute(hnsw_search_kernel<METRIC, RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(hnsw_search_kernel<METRIC, RB, CD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, hnsw_search_kernel<METRIC, RB>, 32, smem);
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, hnsw_search_kernel<METRIC, RB, CD>, 32, smem);
 }
 template <int METRIC>
-static cudaError_t occupancy_of(int *occ, size_t smem, int ld) {
-    return beam_rows(ld) == RB_NARROW ? occupancy_of_rb<METRIC, RB_NARROW>(occ, smem) : occupancy_of_rb<METRIC, RB_WIDE>(occ, smem);
+static cudaError_t occupancy_of(int *occ, size_t smem, int ld, int dim) {
+    if (MUNINN_D128 && dim == 128) return occupancy_of_rb<METRIC, RB_NARROW, 128>(occ, smem);
+    if (MUNINN_D128 && dim == 96) return occupancy_of_rb<METRIC, RB_NARROW, 96>(occ, smem);
+    if (MUNINN_D128 && dim == 768) return occupancy_of_rb<METRIC, RB_WIDE, 768>(occ, smem);
+    return beam_rows(ld) == RB_NARROW ? occupancy_of_rb<METRIC, RB_NARROW, 0>(occ, smem) : occupancy_of_rb<METRIC, RB_WIDE, 0>(occ, smem);
 }
 
 extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *d_queries, int nq, int k, int ef,
@@ -348,9 +358,9 @@ extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *
     CK(h, cudaSetDevice(h->device));
 
     int occ = 0;
-    cudaError_t oe = h->metric == MUNINN_METRIC_L2       ? occupancy_of<METRIC_L2>(&occ, smem, h->ld)
-                     : h->metric == MUNINN_METRIC_COSINE ? occupancy_of<METRIC_COSINE>(&occ, smem, h->ld)
-                                                         : occupancy_of<METRIC_IP>(&occ, smem, h->ld);
+    cudaError_t oe = h->metric == MUNINN_METRIC_L2       ? occupancy_of<METRIC_L2>(&occ, smem, h->ld, h->dim)
+                     : h->metric == MUNINN_METRIC_COSINE ? occupancy_of<METRIC_COSINE>(&occ, smem, h->ld, h->dim)
+                                                         : occupancy_of<METRIC_IP>(&occ, smem, h->ld, h->dim);
     CK(h, oe);
     if (occ < 1) return fail(h, MUNINN_CUDA_E_CUDA, "search kernel does not fit on an SM");
     int tps = h->teams_per_sm > 0 ? std::min(h->teams_per_sm, occ) : occ;
