@@ -7,6 +7,8 @@
  *
  *   muninn_cuda_index_create / _destroy   hnsw_create / hnsw_destroy         src/hnsw_algo.h:56-59
  *   muninn_cuda_index_upload              load_index_from_shadow             src/hnsw_vtab.c:286-341
+ *   muninn_cuda_index_patch               the effect of hnsw_insert / hnsw_delete on the stored graph
+ *                                                                            src/hnsw_algo.c:520-666, :717-805
  *   muninn_cuda_search_batch              hnsw_search, called at             src/hnsw_vtab.c:604
  *                                         (signature src/hnsw_algo.h:73), for nq queries at once
  *   muninn_cuda_search_batch_device       same, device-resident queries/results (benchmark `value`)
@@ -90,6 +92,26 @@ const char *muninn_cuda_last_error(const MuninnCudaIndex *idx);
 int muninn_cuda_index_upload(MuninnCudaIndex *idx, int64_t n, const int64_t *ids, const int32_t *levels,
                              const uint8_t *deleted, const float *vectors, const int64_t *list_offsets,
                              const int32_t *targets, int32_t entry_slot, int32_t max_level);
+
+/*
+ * Incremental form of muninn_cuda_index_upload for the vtab's xUpdate path, so that an INSERT or DELETE does not
+ * re-send the whole index. The reference mutates little per call: hnsw_insert (src/hnsw_algo.c:520-666) creates
+ * one node and rewrites only the lists of the nodes it links it to; hnsw_delete (:717-805) flags one node and
+ * rewrites only the lists of its former neighbours (the node stays stored). The caller sends the records of
+ * exactly those nodes, in the upload's format:
+ *   n_total        stored rows after the change; new rows must carry ids above every stored id, so that they take
+ *                  slots n_old..n_total-1 (otherwise slots shift: re-upload instead)
+ *   n_patch        nodes whose record follows; every new node must be among them
+ *   slots[n_patch] their slots; ids / levels / deleted / vectors [n_patch × dim]: their records (levels of stored
+ *                  nodes cannot change, a deleted node cannot come back)
+ *   list_offsets, targets   their neighbour lists, node-major level-minor, as in muninn_cuda_index_upload
+ *   entry_slot, max_level   the index's after the change
+ * References to a newly deleted slot become holes in every list of the device copy, as upload stores them.
+ * Synchronous. A search after the patch returns exactly what it would after a full upload of the new state.
+ */
+int muninn_cuda_index_patch(MuninnCudaIndex *idx, int64_t n_total, int32_t n_patch, const int32_t *slots, const int64_t *ids,
+                            const int32_t *levels, const uint8_t *deleted, const float *vectors, const int64_t *list_offsets,
+                            const int32_t *targets, int32_t entry_slot, int32_t max_level);
 
 /*
  * Batched hnsw_search. Host buffers; the call copies queries to the device, runs the

@@ -185,6 +185,12 @@ class RefIndex:
     def delete(self, rowid: int) -> int:
         return self.ref.L.ref_delete(self.h, rowid)
 
+    def insert(self, ids, vectors) -> int:
+        """hnsw_insert for each (id, vector), in order."""
+        v = np.ascontiguousarray(np.atleast_2d(vectors), np.float32)
+        ids = np.ascontiguousarray(ids, np.int64)
+        return self.ref.L.ref_insert_many(self.h, v.shape[0], ids, v)
+
     def sort_lists(self):
         """Bring neighbour lists into shadow-table (reloaded) order."""
         self.ref.L.ref_sort_lists(self.h)

@@ -38,6 +38,11 @@ struct MuninnCudaIndex {
     long long n = 0, n_live = 0;
     int entry_slot = -1, max_level = -1;
     bool uploaded = false;
+    /* host mirrors muninn_cuda_index_patch needs, and the device capacities it grows */
+    std::vector<int32_t> h_levels, h_upper_base;
+    std::vector<uint8_t> h_deleted;
+    long long n_upper = 0, cap_n = 0, cap_upper = 0;
+    int64_t last_id = 0;
     /* device graph */
     float *d_vec = nullptr, *d_norm2 = nullptr;
     int32_t *d_nbr0 = nullptr, *d_upper_base = nullptr, *d_nbrU = nullptr;
@@ -285,7 +290,160 @@ extern "C" int muninn_cuda_index_upload(MuninnCudaIndex *h, int64_t n, const int
     }
     CK(h, cudaStreamSynchronize(st)); /* host vectors above go out of scope */
     h->n = n; h->n_live = n_live; h->entry_slot = entry_slot; h->max_level = max_level;
+    h->h_levels.assign(levels, levels + n); h->h_upper_base = upper_base; h->h_deleted = del;
+    h->n_upper = n_upper; h->cap_n = std::max<long long>(n, 1); h->cap_upper = std::max<long long>(n_upper, 1);
+    h->last_id = n ? ids[n - 1] : 0;
     h->uploaded = true;
+    return MUNINN_CUDA_OK;
+}
+
+/* ───────────────────────── incremental update ───────────────────────── */
+
+/* every reference to a slot that has just been flagged deleted becomes a hole (-1), as upload stores it */
+__global__ void purge_slots_kernel(int32_t *__restrict__ lists, long long count, const int32_t *__restrict__ dead, int ndead) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x) {
+        const int32_t t = lists[i];
+        if (t < 0) continue;
+        for (int j = 0; j < ndead; j++)
+            if (t == dead[j]) { lists[i] = -1; break; }
+    }
+}
+
+template <typename T>
+static cudaError_t regrow(T **ptr, size_t keep, size_t newcount, cudaStream_t st) {
+    T *np = nullptr;
+    cudaError_t e = cudaMalloc((void **)&np, std::max<size_t>(newcount, 1) * sizeof(T));
+    if (e != cudaSuccess) return e;
+    if (keep) e = cudaMemcpyAsync(np, *ptr, keep * sizeof(T), cudaMemcpyDeviceToDevice, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    cudaFree(*ptr);
+    *ptr = np;
+    return e;
+}
+
+extern "C" int muninn_cuda_index_patch(MuninnCudaIndex *h, int64_t n_total, int32_t n_patch, const int32_t *slots,
+                                       const int64_t *ids, const int32_t *levels, const uint8_t *deleted, const float *vectors,
+                                       const int64_t *list_offsets, const int32_t *targets, int32_t entry_slot,
+                                       int32_t max_level) {
+    if (!h) return MUNINN_CUDA_E_ARG;
+    if (!h->uploaded) return fail(h, MUNINN_CUDA_E_STATE, "patch before muninn_cuda_index_upload");
+    if (n_total < h->n || n_total > 0x7ffffff0LL || n_patch < 0) return fail(h, MUNINN_CUDA_E_ARG, "bad n_total / n_patch");
+    if (n_patch > 0 && (!slots || !ids || !levels || !vectors || !list_offsets)) return fail(h, MUNINN_CUDA_E_ARG, "NULL array");
+    if (entry_slot < -1 || entry_slot >= n_total) return fail(h, MUNINN_CUDA_E_ARG, "entry_slot %d out of range", entry_slot);
+    CK(h, cudaSetDevice(h->device));
+    cudaStream_t st = h->stream;
+    const int M = h->M, M0 = h->M0;
+    const long long n_old = h->n;
+    /* validate; new slots must be exactly n_old..n_total-1, each present once, ids ascending past the old maximum */
+    std::vector<int32_t> order(n_patch);
+    for (int i = 0; i < n_patch; i++) order[i] = i;
+    std::sort(order.begin(), order.end(), [&](int a, int b) { return slots[a] < slots[b]; });
+    long long expect_new = n_old, add_upper = 0;
+    int64_t prev_id = h->last_id;
+    for (int oi = 0; oi < n_patch; oi++) {
+        const int i = order[oi];
+        const long long sl = slots[i];
+        if (sl < 0 || sl >= n_total || (oi > 0 && slots[order[oi - 1]] == sl)) return fail(h, MUNINN_CUDA_E_ARG, "bad or duplicate slot %lld", sl);
+        if (levels[i] < 0 || levels[i] >= 32) return fail(h, MUNINN_CUDA_E_ARG, "level out of range");
+        if (sl >= n_old) {
+            if (sl != expect_new++) return fail(h, MUNINN_CUDA_E_ARG, "new nodes must fill slots %lld..%lld", n_old, (long long)n_total - 1);
+            if (n_old + (sl - n_old) > 0 && ids[i] <= prev_id) return fail(h, MUNINN_CUDA_E_ARG, "new ids must ascend past the stored ones");
+            prev_id = ids[i];
+            add_upper += levels[i];
+        } else if (levels[i] != h->h_levels[sl]) return fail(h, MUNINN_CUDA_E_ARG, "level of slot %lld changed", sl);
+    }
+    if (expect_new != n_total) return fail(h, MUNINN_CUDA_E_ARG, "patch does not contain every new node");
+    /* grow */
+    if (n_total > h->cap_n) {
+        const long long nc = n_total + n_total / 2 + 1024;
+        CK(h, regrow(&h->d_vec, (size_t)n_old * h->ld, (size_t)nc * h->ld, st));
+        CK(h, regrow(&h->d_nbr0, (size_t)n_old * M0, (size_t)nc * M0, st));
+        CK(h, regrow(&h->d_upper_base, (size_t)n_old, (size_t)nc, st));
+        CK(h, regrow(&h->d_norm2, (size_t)n_old, (size_t)nc, st));
+        CK(h, regrow(&h->d_deleted, (size_t)n_old, (size_t)nc, st));
+        CK(h, regrow(&h->d_ids, (size_t)n_old, (size_t)nc, st));
+        h->cap_n = nc;
+    }
+    if (h->n_upper + add_upper > h->cap_upper) {
+        const long long nc = (h->n_upper + add_upper) * 3 / 2 + 1024;
+        CK(h, regrow(&h->d_nbrU, (size_t)h->n_upper * M, (size_t)nc * M, st));
+        h->cap_upper = nc;
+    }
+    h->h_levels.resize(n_total); h->h_upper_base.resize(n_total, -1); h->h_deleted.resize(n_total, 0);
+    /* records: new nodes first get their slots' bookkeeping, newly deleted slots are collected */
+    std::vector<int32_t> dead;
+    for (int oi = 0; oi < n_patch; oi++) {
+        const int i = order[oi];
+        const long long sl = slots[i];
+        const uint8_t d = deleted ? (deleted[i] != 0) : 0;
+        if (sl >= n_old) {
+            h->h_levels[sl] = levels[i];
+            h->h_upper_base[sl] = levels[i] > 0 ? (int32_t)h->n_upper : -1;
+            h->n_upper += levels[i];
+            h->h_deleted[sl] = d;
+            if (!d) h->n_live++;
+        } else if (d != h->h_deleted[sl]) {
+            if (!d) return fail(h, MUNINN_CUDA_E_ARG, "slot %lld cannot be undeleted", sl);
+            h->h_deleted[sl] = 1; h->n_live--;
+            dead.push_back((int32_t)sl);
+        }
+    }
+    /* staging: rows of the patched lists with deleted targets as holes */
+    std::vector<int32_t> rows0((size_t)n_patch * M0, -1);
+    std::vector<std::vector<int32_t>> rowsU;
+    std::vector<long long> rowsU_at;
+    int64_t li = 0;
+    for (int i = 0; i < n_patch; i++) {
+        const long long sl = slots[i];
+        for (int l = 0; l <= levels[i]; l++, li++) {
+            const int64_t b = list_offsets[li], e = list_offsets[li + 1];
+            const int capl = l == 0 ? M0 : M;
+            if (e < b || e - b > capl) return fail(h, MUNINN_CUDA_E_ARG, "list (slot %lld, level %d) has %lld entries, capacity %d", sl, l, (long long)(e - b), capl);
+            std::vector<int32_t> up;
+            int32_t *dst = &rows0[(size_t)i * M0];
+            if (l > 0) { up.assign(M, -1); dst = up.data(); }
+            for (int64_t j = b; j < e; j++) {
+                const int32_t t = targets[j];
+                if (t < -1 || t >= n_total) return fail(h, MUNINN_CUDA_E_ARG, "target %d out of range", t);
+                if (t >= 0 && h->h_levels[t] < l) return fail(h, MUNINN_CUDA_E_ARG, "edge to slot %d at level %d above its level", t, l);
+                dst[j - b] = (t >= 0 && !h->h_deleted[t]) ? t : -1;
+            }
+            if (l > 0) { rowsU.push_back(std::move(up)); rowsU_at.push_back(((long long)h->h_upper_base[sl] + (l - 1)) * M); }
+        }
+    }
+    for (int i = 0; i < n_patch; i++) {
+        const long long sl = slots[i];
+        CK(h, cudaMemcpyAsync(h->d_nbr0 + (size_t)sl * M0, &rows0[(size_t)i * M0], (size_t)M0 * 4, cudaMemcpyHostToDevice, st));
+        CK(h, cudaMemcpyAsync(h->d_deleted + sl, &h->h_deleted[sl], 1, cudaMemcpyHostToDevice, st));
+        if (sl >= n_old) {
+            if (h->ld != h->dim) CK(h, cudaMemsetAsync(h->d_vec + (size_t)sl * h->ld, 0, (size_t)h->ld * 4, st));
+            CK(h, cudaMemcpyAsync(h->d_vec + (size_t)sl * h->ld, vectors + (size_t)i * h->dim, (size_t)h->dim * 4, cudaMemcpyHostToDevice, st));
+            CK(h, cudaMemcpyAsync(h->d_ids + sl, ids + i, 8, cudaMemcpyHostToDevice, st));
+            CK(h, cudaMemcpyAsync(h->d_upper_base + sl, &h->h_upper_base[sl], 4, cudaMemcpyHostToDevice, st));
+        }
+    }
+    for (size_t u = 0; u < rowsU.size(); u++)
+        CK(h, cudaMemcpyAsync(h->d_nbrU + rowsU_at[u], rowsU[u].data(), (size_t)M * 4, cudaMemcpyHostToDevice, st));
+    if (n_total > n_old) {
+        row_norm2_kernel<<<(unsigned)((n_total - n_old + 255) / 256), 256, 0, st>>>(h->d_vec + (size_t)n_old * h->ld, h->ld, h->dim,
+                                                                                 n_total - n_old, h->d_norm2 + n_old);
+        h->launches++;
+    }
+    int32_t *d_dead = nullptr;
+    if (!dead.empty()) {
+        CK(h, cudaMalloc((void **)&d_dead, dead.size() * 4));
+        CK(h, cudaMemcpyAsync(d_dead, dead.data(), dead.size() * 4, cudaMemcpyHostToDevice, st));
+        purge_slots_kernel<<<h->num_sms * 8, 256, 0, st>>>(h->d_nbr0, (long long)n_total * M0, d_dead, (int)dead.size());
+        if (h->n_upper) purge_slots_kernel<<<h->num_sms * 2, 256, 0, st>>>(h->d_nbrU, h->n_upper * M, d_dead, (int)dead.size());
+        h->launches += 2;
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st); /* the staging vectors above go out of scope */
+    cudaFree(d_dead);
+    CK(h, e);
+    h->n = n_total; h->entry_slot = entry_slot; h->max_level = max_level;
+    if (n_total > n_old) h->last_id = prev_id;
+    if (entry_slot >= 0 && h->h_levels[entry_slot] < max_level) return fail(h, MUNINN_CUDA_E_ARG, "entry node level < max_level");
     return MUNINN_CUDA_OK;
 }
 

@@ -30,7 +30,7 @@ ABI_SYMBOLS = (
     "muninn_cuda_last_kernel_ms", "muninn_cuda_launch_count", "muninn_cuda_set_tuning", "muninn_cuda_exact_knn",
     "muninn_cuda_exact_knn_device", "muninn_cuda_topk_merge_device", "muninn_cuda_distance_batch",
     "muninn_cuda_set_exact_mode", "muninn_cuda_exact_stats", "muninn_cuda_exact_filter_probe",
-    "muninn_cuda_gather_ceiling",
+    "muninn_cuda_gather_ceiling", "muninn_cuda_index_patch",
 )
 
 EXACT_CUDA_CORE, EXACT_TC_3XTF32, EXACT_TC_1XTF32, EXACT_TC_AUTO = 0, 1, 2, 3
@@ -89,6 +89,7 @@ def lib():
         L.muninn_cuda_set_exact_mode.argtypes = [_vp, C.c_int, C.c_int]
         L.muninn_cuda_exact_stats.argtypes = [_vp, C.POINTER(ExactStats)]
         L.muninn_cuda_exact_filter_probe.argtypes = [_vp, _vp, C.c_int, C.c_int64, _vp]
+        L.muninn_cuda_index_patch.argtypes = [_vp, C.c_int64, C.c_int32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int32, C.c_int32]
         L.muninn_cuda_gather_ceiling.argtypes = [C.c_int, C.c_int, C.c_int64, C.POINTER(C.c_float)]
         _lib = L
     return _lib
@@ -174,6 +175,26 @@ class HnswIndexCuda:
         self._check(self.L.muninn_cuda_index_upload(self.h, g.n, _ptr(g.ids), _ptr(g.levels), _ptr(g.deleted),
                                                     _ptr(g.vectors), _ptr(g.list_offsets), _ptr(g.targets),
                                                     g.entry_slot, g.max_level))
+        self.n = g.n
+
+    def patch(self, g: FlatGraph, slots):
+        """Send only the records of `slots` (every new node included) of the new state `g`: what hnsw_insert /
+        hnsw_delete changed (/root/reference/src/hnsw_algo.c:520-666, :717-805)."""
+        g.validate()
+        slots = np.ascontiguousarray(slots, np.int32)
+        first = g.first_list()
+        offs, tg = [0], []
+        for s_ in slots:
+            for l in range(int(g.levels[s_]) + 1):
+                li = int(first[s_]) + l
+                tg.append(g.targets[g.list_offsets[li]:g.list_offsets[li + 1]])
+                offs.append(offs[-1] + len(tg[-1]))
+        offs = np.asarray(offs, np.int64)
+        tg = np.ascontiguousarray(np.concatenate(tg) if tg else np.empty(0), np.int32)
+        ids = np.ascontiguousarray(g.ids[slots]); lv = np.ascontiguousarray(g.levels[slots])
+        dl = np.ascontiguousarray(g.deleted[slots]); vec = np.ascontiguousarray(g.vectors[slots])
+        self._check(self.L.muninn_cuda_index_patch(self.h, g.n, len(slots), _ptr(slots), _ptr(ids), _ptr(lv), _ptr(dl),
+                                                   _ptr(vec), _ptr(offs), _ptr(tg), g.entry_slot, g.max_level))
         self.n = g.n
 
     # -- search ------------------------------------------------------------------------
