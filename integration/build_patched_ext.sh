@@ -22,12 +22,12 @@ fi
 TMP=$(mktemp -d)
 trap 'rm -rf "$TMP"' EXIT
 sed -e 's|cur->result_count = hnsw_search(vtab->index, query, k, ef_search, cur->results);|cur->result_count = muninn_glue_search(vtab->index, query, k, ef_search, cur->results, \&vtab->base.zErrMsg); if (vtab->base.zErrMsg) return SQLITE_ERROR;|' \
-    -e 's|rc = hnsw_delete(vtab->index, id);|rc = hnsw_delete(vtab->index, id); muninn_glue_mark_dirty(vtab->index);|' \
-    -e 's|rc = hnsw_insert(vtab->index, id, vec);|rc = hnsw_insert(vtab->index, id, vec); muninn_glue_mark_dirty(vtab->index);|' \
+    -e 's|rc = hnsw_delete(vtab->index, id);|rc = hnsw_delete(vtab->index, id); if (rc == 0) muninn_glue_note_delete(vtab->index, id);|' \
+    -e 's|rc = hnsw_insert(vtab->index, id, vec);|rc = hnsw_insert(vtab->index, id, vec); if (rc == 0) muninn_glue_note_insert(vtab->index, id);|' \
     -e 's|^\( *\)hnsw_destroy(vtab->index);|\1muninn_glue_release(vtab->index); hnsw_destroy(vtab->index);|' \
     "$REF/src/hnsw_vtab.c" > "$TMP/hnsw_vtab.c"
 grep -q muninn_glue_search "$TMP/hnsw_vtab.c" || { echo "integration: call site not found in hnsw_vtab.c" >&2; exit 1; }
-[ "$(grep -c muninn_glue_mark_dirty "$TMP/hnsw_vtab.c")" = 2 ] || { echo "integration: xUpdate anchors not found" >&2; exit 1; }
+[ "$(grep -c "muninn_glue_note_" "$TMP/hnsw_vtab.c")" = 2 ] || { echo "integration: xUpdate anchors not found" >&2; exit 1; }
 [ "$(grep -c muninn_glue_release "$TMP/hnsw_vtab.c")" -ge 1 ] || { echo "integration: hnsw_destroy anchors not found" >&2; exit 1; }
 SRCS=""
 for f in "$REF"/src/*.c; do
@@ -38,7 +38,7 @@ for f in "$REF"/src/*.c; do
 done
 mkdir -p "$HERE/_build"
 CSRC="$ROOT/sqlite_muninn_b200/csrc"
-$CC -O2 -std=c11 -fPIC -D_POSIX_C_SOURCE=200809L -DMUNINN_NO_LLAMA -shared \
+$CC -O2 -std=c11 -fPIC -D_POSIX_C_SOURCE=200809L -DMUNINN_NO_LLAMA -shared -Wl,-Bsymbolic \
     -I"$REF/src" -I"$REF/vendor/yyjson" -I"$ROOT/include" -I"$HERE" \
     -include "$HERE/muninn_vtab_glue.h" \
     -o "$HERE/_build/muninn_cuda_ext.so" \

@@ -8,15 +8,19 @@
  *     cur->result_count = hnsw_search(vtab->index, query, k, ef_search, cur->results);
  * which becomes
  *     cur->result_count = muninn_glue_search(vtab->index, query, k, ef_search, cur->results, &vtab->base.zErrMsg);
- * plus a muninn_glue_mark_dirty(vtab->index) after each successful hnsw_insert / hnsw_delete
- * in xUpdate (:698, :748) and a muninn_glue_release(vtab->index) before each hnsw_destroy in
+ * plus a muninn_glue_note_insert / muninn_glue_note_delete(vtab->index, id) after each hnsw_insert /
+ * hnsw_delete in xUpdate (:698, :748) and a muninn_glue_release(vtab->index) before each hnsw_destroy in
  * xDisconnect / xDestroy (:466, :474).
  *
  * The glue keeps one device handle per HnswIndex in a small side table, so the reference's
- * structs need no new field. On the first search after a mutation it flattens the host index
- * (every stored node, deleted ones included, neighbour lists in their live order) and
- * re-uploads it: the dirty-flag rule of SURVEY.md §8b. There is no CPU fallback: a failure
- * of the device path is reported through zErrMsg and the query fails.
+ * structs need no new field. The first search flattens the host index (every stored node, deleted
+ * ones included, neighbour lists in their live order) and uploads it. Later mutations are NOT
+ * re-uploaded wholesale: hnsw_insert changes the new node and the nodes it linked it to, hnsw_delete
+ * the deleted node and its former neighbours (src/hnsw_algo.c:520-666, :717-805), so the glue
+ * remembers those ids and, on the next search, sends just their records with muninn_cuda_index_patch
+ * (SURVEY.md §8f N4). It falls back to a full upload when an inserted rowid is not above every stored
+ * one (slots would shift) or when the pending set has grown past a quarter of the index. There is no
+ * CPU fallback: a failure of the device path is reported through zErrMsg and the query fails.
  */
 #include "hnsw_algo.h" /* the reference's header, -I<reference>/src */
 #include "muninn_cuda.h"
@@ -32,7 +36,13 @@ SQLITE_EXTENSION_INIT3
 typedef struct {
     const HnswIndex *index;
     MuninnCudaIndex *handle;
-    int dirty;
+    int dirty;          /* full upload needed */
+    int64_t *ids;       /* sorted rowids of the device copy: slot = rank */
+    int64_t n, cap;
+    int64_t *pend;      /* rowids whose record changed since the device copy was made */
+    int64_t npend, cappend;
+    int64_t max_id;     /* highest rowid on the device or pending */
+    int64_t n_patches, n_uploads; /* counters for the tests */
 } GlueSlot;
 
 static GlueSlot *g_slots;
@@ -48,20 +58,8 @@ static GlueSlot *slot_find(const HnswIndex *index, int create) {
         if (!ns) return NULL;
         g_slots = ns; g_capslots = nc;
     }
-    g_slots[g_nslots] = (GlueSlot){index, NULL, 1};
+    g_slots[g_nslots] = (GlueSlot){index, NULL, 1, NULL, 0, 0, NULL, 0, 0, 0, 0, 0};
     return &g_slots[g_nslots++];
-}
-
-void muninn_glue_mark_dirty(const HnswIndex *index) {
-    GlueSlot *s = slot_find(index, 0);
-    if (s) s->dirty = 1;
-}
-
-void muninn_glue_release(const HnswIndex *index) {
-    GlueSlot *s = slot_find(index, 0);
-    if (!s) return;
-    muninn_cuda_index_destroy(s->handle);
-    *s = g_slots[--g_nslots];
 }
 
 static int cmp_i64(const void *a, const void *b) {
@@ -77,6 +75,58 @@ static int64_t slot_of(const int64_t *ids, int64_t n, int64_t id) {
         if (ids[mid] < id) lo = mid + 1; else hi = mid - 1;
     }
     return -1;
+}
+
+void muninn_glue_mark_dirty(const HnswIndex *index) {
+    GlueSlot *s = slot_find(index, 0);
+    if (s) s->dirty = 1;
+}
+
+static void pend_add(GlueSlot *s, int64_t id) {
+    if (s->dirty) return;
+    if (s->npend == s->cappend) {
+        int64_t nc = s->cappend ? 2 * s->cappend : 256;
+        int64_t *np = (int64_t *)realloc(s->pend, (size_t)nc * sizeof(int64_t));
+        if (!np) { s->dirty = 1; return; }
+        s->pend = np; s->cappend = nc;
+    }
+    s->pend[s->npend++] = id;
+    if (s->npend > 64 && s->npend > s->n) s->dirty = 1; /* more change records than nodes: start over */
+}
+
+/* the node `id` and every node in its lists: all that hnsw_insert(id) or hnsw_delete(id) modified */
+static void note_node_and_neighbours(const HnswIndex *index, int64_t id) {
+    GlueSlot *s = slot_find(index, 0);
+    if (!s || !s->handle || s->dirty) return; /* nothing on the device yet, or a full upload is due anyway */
+    const HnswNode *nd = ht_find(index->nodes, index->node_capacity, id);
+    if (!nd) { s->dirty = 1; return; }
+    pend_add(s, id);
+    for (int l = 0; l <= nd->level; l++)
+        for (int j = 0; j < nd->neighbor_count[l]; j++) pend_add(s, nd->neighbors[l][j]);
+}
+
+void muninn_glue_note_insert(const HnswIndex *index, int64_t id) {
+    GlueSlot *s = slot_find(index, 0);
+    if (s && s->handle && !s->dirty) {
+        if (s->n > 0 && id <= s->max_id) s->dirty = 1; /* not above every stored rowid: slots would shift */
+        else s->max_id = id;
+    }
+    note_node_and_neighbours(index, id);
+}
+
+void muninn_glue_note_delete(const HnswIndex *index, int64_t id) { note_node_and_neighbours(index, id); }
+
+/* process-wide counters (the tests read them through the loaded extension with ctypes) */
+static int64_t g_total_patches, g_total_uploads;
+int64_t muninn_glue_total_patches(void) { return g_total_patches; }
+int64_t muninn_glue_total_uploads(void) { return g_total_uploads; }
+
+void muninn_glue_release(const HnswIndex *index) {
+    GlueSlot *s = slot_find(index, 0);
+    if (!s) return;
+    muninn_cuda_index_destroy(s->handle);
+    free(s->ids); free(s->pend);
+    *s = g_slots[--g_nslots];
 }
 
 /* host HnswIndex → the flat arrays of muninn_cuda_index_upload */
@@ -124,8 +174,75 @@ static int glue_upload(GlueSlot *s, char **err) {
     } else if (err) {
         *err = sqlite3_mprintf("hnsw_index: out of memory flattening the index for upload");
     }
-    free(ids); free(levels); free(deleted); free(vecs); free(offs); free(tg);
-    if (rc == MUNINN_CUDA_OK) s->dirty = 0;
+    free(levels); free(deleted); free(vecs); free(offs); free(tg);
+    if (rc == MUNINN_CUDA_OK) {
+        free(s->ids);
+        s->ids = ids; s->n = n; s->cap = n + 1; s->max_id = n ? ids[n - 1] : 0;
+        s->dirty = 0; s->npend = 0; s->n_uploads++; g_total_uploads++;
+    } else free(ids);
+    return rc;
+}
+
+/* pending change records → muninn_cuda_index_patch. Returns MUNINN_CUDA_OK, or an error after which the
+ * caller falls back to a full upload. */
+static int glue_patch(GlueSlot *s) {
+    const HnswIndex *idx = s->index;
+    qsort(s->pend, (size_t)s->npend, sizeof(int64_t), cmp_i64);
+    int64_t np = 0;
+    for (int64_t i = 0; i < s->npend; i++)
+        if (np == 0 || s->pend[i] != s->pend[np - 1]) s->pend[np++] = s->pend[i];
+    /* new rowids (absent from the device copy) are above every stored one and come out of the sort ascending */
+    int64_t n_new = 0;
+    for (int64_t i = 0; i < np; i++)
+        if (slot_of(s->ids, s->n, s->pend[i]) < 0) n_new++;
+    const int64_t n_total = s->n + n_new;
+    if (n_total + 1 > s->cap) {
+        int64_t nc = n_total + n_total / 2 + 64;
+        int64_t *ni = (int64_t *)realloc(s->ids, (size_t)nc * sizeof(int64_t));
+        if (!ni) return MUNINN_CUDA_E_NOMEM;
+        s->ids = ni; s->cap = nc;
+    }
+    int64_t k = s->n;
+    for (int64_t i = 0; i < np; i++)
+        if (slot_of(s->ids, s->n, s->pend[i]) < 0) {
+            if (k > 0 && s->pend[i] <= s->ids[k - 1]) return MUNINN_CUDA_E_ARG;
+            s->ids[k++] = s->pend[i];
+        }
+    int64_t n_lists = 0, n_edges = 0;
+    for (int64_t i = 0; i < np; i++) {
+        const HnswNode *nd = ht_find(idx->nodes, idx->node_capacity, s->pend[i]);
+        if (!nd) return MUNINN_CUDA_E_ARG;
+        n_lists += nd->level + 1;
+        for (int l = 0; l <= nd->level; l++) n_edges += nd->neighbor_count[l];
+    }
+    int32_t *slots = (int32_t *)malloc((size_t)(np + 1) * sizeof(int32_t));
+    int32_t *levels = (int32_t *)malloc((size_t)(np + 1) * sizeof(int32_t));
+    uint8_t *deleted = (uint8_t *)malloc((size_t)(np + 1));
+    float *vecs = (float *)malloc((size_t)(np + 1) * (size_t)idx->dim * sizeof(float));
+    int64_t *offs = (int64_t *)malloc((size_t)(n_lists + 1) * sizeof(int64_t));
+    int32_t *tg = (int32_t *)malloc((size_t)(n_edges + 1) * sizeof(int32_t));
+    int rc = MUNINN_CUDA_E_NOMEM;
+    if (slots && levels && deleted && vecs && offs && tg) {
+        int64_t li = 0, e = 0;
+        offs[0] = 0;
+        for (int64_t i = 0; i < np; i++) {
+            const HnswNode *nd = ht_find(idx->nodes, idx->node_capacity, s->pend[i]);
+            slots[i] = (int32_t)slot_of(s->ids, n_total, s->pend[i]);
+            levels[i] = nd->level;
+            deleted[i] = (uint8_t)(nd->deleted != 0);
+            memcpy(vecs + (size_t)i * (size_t)idx->dim, nd->vector, (size_t)idx->dim * sizeof(float));
+            for (int l = 0; l <= nd->level; l++) {
+                for (int j = 0; j < nd->neighbor_count[l]; j++) tg[e++] = (int32_t)slot_of(s->ids, n_total, nd->neighbors[l][j]);
+                offs[++li] = e;
+            }
+        }
+        int32_t entry = idx->entry_point == -1 ? -1 : (int32_t)slot_of(s->ids, n_total, idx->entry_point);
+        rc = muninn_cuda_index_patch(s->handle, n_total, (int32_t)np, slots, s->pend, levels, deleted, vecs, offs, tg, entry,
+                                     idx->max_level);
+    }
+    free(slots); free(levels); free(deleted); free(vecs); free(offs); free(tg);
+    if (getenv("MUNINN_GLUE_TRACE")) fprintf(stderr, "muninn_glue: patch of %lld records (%lld new) -> rc %d\n", (long long)np, (long long)n_new, rc);
+    if (rc == MUNINN_CUDA_OK) { s->n = n_total; s->npend = 0; s->n_patches++; g_total_patches++; }
     return rc;
 }
 
@@ -147,6 +264,7 @@ int muninn_glue_search(HnswIndex *index, const float *query, int k, int ef_searc
         }
         s->dirty = 1;
     }
+    if (!s->dirty && s->npend > 0 && glue_patch(s) != MUNINN_CUDA_OK) s->dirty = 1; /* anything a patch cannot express */
     if (s->dirty && glue_upload(s, err) != MUNINN_CUDA_OK) return 0;
     int64_t *ids = (int64_t *)malloc((size_t)k * sizeof(int64_t));
     float *dist = (float *)malloc((size_t)k * sizeof(float));

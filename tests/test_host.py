@@ -117,3 +117,32 @@ def test_product_never_imports_the_oracle():
             if f.endswith((".py", ".c", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in src.replace("the CPU oracle", "").replace("CPU oracle's", ""), f
+
+
+def test_patched_and_reference_extensions_stay_distinct_in_one_process(tmp_path):
+    """SQLite dlopens extensions RTLD_GLOBAL, so two builds of the same sources would interpose on
+    each other (the second one's init registering the first one's module): both are linked
+    -Bsymbolic. Proof, without a GPU: the patched extension's KNN plan fails loudly (no device, no
+    CPU path) while the unmodified reference, loaded after it, still answers on the CPU."""
+    from oracle.bindings import REF_EXT_SO
+    cuda_ext = os.path.join(ROOT, "integration", "_build", "muninn_cuda_ext.so")
+    if not (os.path.exists(cuda_ext) and os.path.exists(REF_EXT_SO)):
+        pytest.skip("extensions not built")
+    assert b"muninn_glue_search" in open(cuda_ext, "rb").read()
+    assert b"muninn_glue_search" not in open(REF_EXT_SO, "rb").read()
+    if cuda.device_count() > 0:
+        pytest.skip("a device is present: covered by tests/test_gpu_vtab.py")
+    conns = []
+    for i, ext in enumerate((cuda_ext, REF_EXT_SO)):
+        c = sqlite3.connect(str(tmp_path / f"{i}.db"))
+        c.enable_load_extension(True)
+        c.load_extension(ext, entrypoint="sqlite3_muninn_init")
+        c.execute("CREATE VIRTUAL TABLE t USING hnsw_index(dimensions=4, metric='l2')")
+        for r in range(1, 20):
+            c.execute("INSERT INTO t (rowid, vector) VALUES (?, ?)", (r, np.float32([r, 0, 0, 1]).tobytes()))
+        conns.append(c)
+    q = np.float32([3.2, 0, 0, 1]).tobytes()
+    sql = "SELECT rowid FROM t WHERE vector MATCH ? AND k = 2"
+    assert [r[0] for r in conns[1].execute(sql, (q,)).fetchall()] == [3, 4]
+    with pytest.raises(sqlite3.OperationalError, match="no CUDA device"):
+        conns[0].execute(sql, (q,)).fetchall()
