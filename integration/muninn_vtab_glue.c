@@ -248,11 +248,10 @@ static int glue_patch(GlueSlot *s) {
 
 /* Drop-in for hnsw_search (src/hnsw_algo.h:73): same arguments and return value (number of
  * results, 0 for an empty index); on a device failure returns 0 with *err set. */
-int muninn_glue_search(HnswIndex *index, const float *query, int k, int ef_search, HnswSearchResult *results,
-                       char **err) {
-    if (!index || index->entry_point == -1 || index->node_count == 0 || k < 1) return 0; /* hnsw_algo.c:671 */
+/* handle of `index`, created on first use and brought up to date (patch, else full upload); NULL with *err set */
+static GlueSlot *glue_sync(HnswIndex *index, char **err) {
     GlueSlot *s = slot_find(index, 1);
-    if (!s) { if (err) *err = sqlite3_mprintf("hnsw_index: out of memory"); return 0; }
+    if (!s) { if (err) *err = sqlite3_mprintf("hnsw_index: out of memory"); return NULL; }
     if (!s->handle) {
         int dev = 0;
         const char *env = getenv("MUNINN_CUDA_DEVICE");
@@ -260,12 +259,39 @@ int muninn_glue_search(HnswIndex *index, const float *query, int k, int ef_searc
         int rc = muninn_cuda_index_create(dev, index->dim, (int)index->metric, index->M, &s->handle);
         if (rc != MUNINN_CUDA_OK) {
             if (err) *err = sqlite3_mprintf("hnsw_index: %s", muninn_cuda_last_error(NULL));
-            return 0;
+            return NULL;
         }
         s->dirty = 1;
     }
     if (!s->dirty && s->npend > 0 && glue_patch(s) != MUNINN_CUDA_OK) s->dirty = 1; /* anything a patch cannot express */
-    if (s->dirty && glue_upload(s, err) != MUNINN_CUDA_OK) return 0;
+    if (s->dirty && glue_upload(s, err) != MUNINN_CUDA_OK) return NULL;
+    return s;
+}
+
+/* Batched form (the per-entity KNN loop of src/llama_er.c:237-284 as ONE launch): nq queries
+ * [nq × dim] → ids [nq × k] (rowids, -1 padded), dist [nq × k], counts [nq]. Returns 0, or -1 with *err set. */
+int muninn_glue_search_batch(HnswIndex *index, const float *queries, int nq, int k, int ef_search, int64_t *ids,
+                             float *dist, int32_t *counts, char **err) {
+    if (nq < 1 || k < 1) return 0;
+    if (!index || index->entry_point == -1 || index->node_count == 0) { /* hnsw_algo.c:671 */
+        for (int i = 0; i < nq; i++) counts[i] = 0;
+        return 0;
+    }
+    GlueSlot *s = glue_sync(index, err);
+    if (!s) return -1;
+    int rc = muninn_cuda_search_batch(s->handle, queries, nq, k, ef_search, ids, dist, counts, NULL);
+    if (rc != MUNINN_CUDA_OK) {
+        if (err) *err = sqlite3_mprintf("hnsw_index: GPU search failed: %s", muninn_cuda_last_error(s->handle));
+        return -1;
+    }
+    return 0;
+}
+
+int muninn_glue_search(HnswIndex *index, const float *query, int k, int ef_search, HnswSearchResult *results,
+                       char **err) {
+    if (!index || index->entry_point == -1 || index->node_count == 0 || k < 1) return 0; /* hnsw_algo.c:671 */
+    GlueSlot *s = glue_sync(index, err);
+    if (!s) return 0;
     int64_t *ids = (int64_t *)malloc((size_t)k * sizeof(int64_t));
     float *dist = (float *)malloc((size_t)k * sizeof(float));
     int32_t count = 0;

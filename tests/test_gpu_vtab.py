@@ -171,6 +171,92 @@ def test_vtab_interleaved_writes_use_incremental_patches(exts, tmp_path):
         c.close()
 
 
+def batch_rows(conn, queries, k, ef=None):
+    """hnsw_knn_batch → per-query lists of (rowid, distance), the shape knn() returns"""
+    if ef is None:
+        rows = conn.execute("SELECT query, id, distance, rank FROM hnsw_knn_batch('t', ?, ?)", (queries.tobytes(), k)).fetchall()
+    else:
+        rows = conn.execute("SELECT query, id, distance, rank FROM hnsw_knn_batch('t', ?, ?, ?)",
+                            (queries.tobytes(), k, ef)).fetchall()
+    out = [[] for _ in range(len(queries))]
+    for qi, rid, d, rank in rows:
+        assert rank == len(out[qi])  # rows arrive grouped by query, in rank order
+        out[qi].append((rid, d))
+    return out
+
+
+@pytest.mark.parametrize("metric,dim", [("l2", 16), ("cosine", 24), ("inner_product", 10)])
+def test_batch_tvf_equals_per_query_sql_of_the_unmodified_reference(exts, tmp_path, metric, dim):
+    """hnsw_knn_batch('t', <nq vectors>, k[, ef]) answers in one launch what the
+    reference answers with one `vector MATCH ?` statement per query (src/llama_er.c:237-284)."""
+    if exts[1] is None:
+        pytest.skip("reference extension not built")
+    base, q = uniform(51, 700, dim), uniform(52, 64, dim)
+    conns = [connect(str(tmp_path / f"b{i}.db"), e) for i, e in enumerate(exts)]
+    for c in conns:
+        c.execute(f"CREATE VIRTUAL TABLE t USING hnsw_index(dimensions={dim}, metric='{metric}', m=8, ef_construction=50)")
+    assert batch_rows(conns[0], q, 5) == [[] for _ in q]  # empty index: no rows
+    for c in conns:
+        for i, v in enumerate(base[:600]):
+            c.execute("INSERT INTO t (rowid, vector) VALUES (?, ?)", (3 * i + 2, v.tobytes()))
+        for i in range(0, 600, 11):
+            c.execute("DELETE FROM t WHERE rowid = ?", (3 * i + 2,))
+
+    def same(tag):
+        for k, ef in ((1, None), (10, None), (10, 100), (40, 30), (700, 800)):
+            got = batch_rows(conns[0], q, k, ef)
+            for qi in range(len(q)):
+                assert same_rows(got[qi], knn(conns[1], q[qi], k, ef)), (tag, qi, k, ef)
+            assert got[5] == knn(conns[0], q[5], k, ef)  # and exactly the patched vtab's own single-query answer
+
+    same("built")
+    for c in conns:  # writes between batches reach the device as a patch
+        for i, v in enumerate(base[600:]):
+            c.execute("INSERT INTO t (rowid, vector) VALUES (?, ?)", (5000 + i, v.tobytes()))
+        c.execute("DELETE FROM t WHERE rowid = ?", (5003,))
+    same("after writes")
+    # one query, and a blob SQLite hands over unaligned (sliced out of a larger one)
+    assert same_rows(batch_rows(conns[0], q[:1], 7)[0], knn(conns[1], q[0], 7))
+    odd = conns[0].execute("SELECT id FROM hnsw_knn_batch('t', substr(?, 2), 3)", (b"\x00" + q[:3].tobytes(),)).fetchall()
+    assert [r[0] for r in odd] == [r[0] for qi in range(3) for r in knn(conns[0], q[qi], 3)]
+    with pytest.raises(sqlite3.OperationalError, match="whole number of"):
+        conns[0].execute("SELECT * FROM hnsw_knn_batch('t', ?, 3)", (q.tobytes()[:-4],)).fetchall()
+    for c in conns:
+        c.close()
+
+
+def test_er_blocking_stage_through_the_batch_tvf(exts, tmp_path):
+    """The ER blocking loop of src/llama_er.c:237-284 (per entity: KNN, drop self, distance threshold,
+    de-duplicated (lo, hi) pairs keeping the smaller distance) written once with the reference's
+    per-entity statement on the unmodified extension and once as ONE SQL statement over
+    hnsw_knn_batch: the candidate pairs and their distances are identical."""
+    if exts[1] is None:
+        pytest.skip("reference extension not built")
+    rng = np.random.default_rng(9)
+    proto = uniform(61, 80, 32)
+    ent = (proto[rng.integers(0, 80, 400)] + np.float32(0.15) * uniform(62, 400, 32)).astype(np.float32)
+    conns = [connect(str(tmp_path / f"er{i}.db"), e) for i, e in enumerate(exts)]
+    for c in conns:
+        c.execute("CREATE VIRTUAL TABLE t USING hnsw_index(dimensions=32, metric='cosine', m=16, ef_construction=100)")
+        for i, v in enumerate(ent):
+            c.execute("INSERT INTO t (rowid, vector) VALUES (?, ?)", (i + 1, v.tobytes()))
+    k, thr = 10, 0.05
+    want = {}
+    for i in range(len(ent)):  # the reference's loop
+        for nid, dist in knn(conns[1], ent[i], k):
+            if nid == i + 1 or dist > thr:
+                continue
+            key = (min(i + 1, nid), max(i + 1, nid))
+            want[key] = min(dist, want.get(key, np.inf))
+    got = conns[0].execute(
+        "SELECT min(query + 1, id), max(query + 1, id), min(distance) FROM hnsw_knn_batch('t', ?, ?) "
+        "WHERE id <> query + 1 AND distance <= ? GROUP BY 1, 2", (ent.tobytes(), k, thr)).fetchall()
+    assert len(want) > 300
+    assert {(a, b): d for a, b, d in got} == want
+    for c in conns:
+        c.close()
+
+
 def test_vtab_errors_and_drop(exts, tmp_path):
     conn = connect(str(tmp_path / "e.db"), exts[0])
     conn.execute("CREATE VIRTUAL TABLE t USING hnsw_index(dimensions=3, metric='l2')")

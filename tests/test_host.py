@@ -146,3 +146,31 @@ def test_patched_and_reference_extensions_stay_distinct_in_one_process(tmp_path)
     assert [r[0] for r in conns[1].execute(sql, (q,)).fetchall()] == [3, 4]
     with pytest.raises(sqlite3.OperationalError, match="no CUDA device"):
         conns[0].execute(sql, (q,)).fetchall()
+
+
+def test_batch_tvf_argument_errors_need_no_device(tmp_path):
+    """hnsw_knn_batch (integration/muninn_batch_tvf.c): argument checking and the empty-index case run on
+    the host; a non-empty index without a device fails loudly."""
+    cuda_ext = os.path.join(ROOT, "integration", "_build", "muninn_cuda_ext.so")
+    if not os.path.exists(cuda_ext):
+        pytest.skip("integration/_build/muninn_cuda_ext.so not built")
+    c = sqlite3.connect(str(tmp_path / "b.db"))
+    c.enable_load_extension(True)
+    c.load_extension(cuda_ext, entrypoint="sqlite3_muninn_init")
+    c.execute("CREATE VIRTUAL TABLE t USING hnsw_index(dimensions=4, metric='l2')")
+    q = np.float32([[1, 0, 0, 1], [2, 0, 0, 1]]).tobytes()
+    assert c.execute("SELECT * FROM hnsw_knn_batch('t', ?, 3)", (q,)).fetchall() == []  # src/hnsw_algo.c:671
+    assert c.execute("SELECT * FROM hnsw_knn_batch('t', ?, 3, 50)", (b"",)).fetchall() == []
+    c.execute("INSERT INTO t (rowid, vector) VALUES (1, ?)", (np.float32([1, 0, 0, 1]).tobytes(),))
+    c.execute("CREATE TABLE plain(vector, k, ef_search)")
+    for sql, args, msg in (("SELECT * FROM hnsw_knn_batch('t', ?, 3)", (q[:-4],), "whole number of 4-dim vectors"),
+                           ("SELECT * FROM hnsw_knn_batch('nope', ?, 3)", (q,), "no such table"),
+                           ("SELECT * FROM hnsw_knn_batch('plain', ?, 3)", (q,), "not an hnsw_index table"),
+                           ("SELECT * FROM hnsw_knn_batch('t', ?)", (q,), "missing argument"),
+                           ("SELECT * FROM hnsw_knn_batch('t', ?, 0)", (q,), "k >= 1"),
+                           ("SELECT rowid FROM t WHERE vector MATCH ? AND k = 2", (None,), "expected 4-dim vector")):
+        with pytest.raises(sqlite3.OperationalError, match=msg):
+            c.execute(sql, args).fetchall()
+    if cuda.device_count() == 0:
+        with pytest.raises(sqlite3.OperationalError, match="no CUDA device"):
+            c.execute("SELECT * FROM hnsw_knn_batch('t', ?, 3)", (q,)).fetchall()
