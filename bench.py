@@ -297,10 +297,11 @@ def exact_summary(args, nq: int, total_ms: float, st: dict, n_rows: int | None =
 
 def ncu_traffic(args, ef):
     """dram__bytes_read.sum + dram__bytes_write.sum of ONE level-0 search launch, from the `ncu --set full` capture
-    of this command summarised in profiles/r1_search_kernel_v5_ncu_full.txt (7.818 GB + 0.661 GB; algorithmic bytes
-    of the same launch: 8.472 GB). Only the captured configuration has a number."""
+    of this command summarised in profiles/r1_search_kernel_v6_ncu_full.txt (6.818 GB + 0.281 GB; algorithmic bytes
+    of the same launch: 8.472 GB — the 58 MB visited arena leaves the rest of the 126 MB L2 to the hot rows and lists,
+    so DRAM moves 0.84x of the algorithmic bytes). Only the captured configuration has a number."""
     if (args.config, args.n, args.nq, ef) == (2, 1_000_000, 10_000, 64):
-        return 8.479e9
+        return 7.099e9
     return None
 
 
