@@ -67,6 +67,16 @@ __host__ __device__ inline int beam_rows(int ld) { return MUNINN_RB ? (MUNINN_RB
 constexpr unsigned VIS_EMPTY = 0xffffffffu;
 constexpr int PSTRIDE = 128 + 4;  /* floats per staged row: 32 chunks + 4 pad → conflict-free per-row reads */
 constexpr int MAX_M0 = 128;       /* layer-0 list capacity supported (M ≤ 64) */
+/* dim 96 (config 4): rows are 384 bytes, so a 16-row tile at stride 100 floats (≡ 4 mod 32: conflict-free like 132)
+ * is SMALLER than the 13-row tile at stride 132 — the full 16-row batch at the same 24 teams/SM */
+#ifndef MUNINN_D96_WIDE
+#define MUNINN_D96_WIDE 1
+#endif
+template <int CD> struct TileOf { static constexpr int stride = (MUNINN_D96_WIDE && CD == 96) ? 100 : PSTRIDE; };
+constexpr int RB_D96 = MUNINN_D96_WIDE ? 16 : MUNINN_RB_NARROW;
+__host__ __device__ inline bool tile_d96(int ld, int dim) { return MUNINN_D96_WIDE && ld == 96 && dim == 96; }
+__host__ __device__ inline int tile_rows(int ld, int dim) { return tile_d96(ld, dim) ? RB_D96 : beam_rows(ld); }
+__host__ __device__ inline int tile_stride(int ld, int dim) { return tile_d96(ld, dim) ? 100 : PSTRIDE; }
 
 struct SearchParams {
     /* graph */
@@ -97,10 +107,10 @@ struct TeamSmem {
 __host__ __device__ inline int fs_pos(int M0) { return M0 > DB ? M0 : DB; }
 __host__ __device__ inline int fs_len(int M0) { return fs_pos(M0) + DB; }
 
-__host__ __device__ inline size_t search_smem_bytes(int ef, int ld, int M0) {
+__host__ __device__ inline size_t search_smem_bytes(int ef, int ld, int M0, int dim) {
     size_t b = (((size_t)ef * 8 + 15) & ~(size_t)15) + (size_t)M0 * 8 + 32 * 8;
     b += ((size_t)ld * 4 + 15) / 16 * 16;
-    b += (size_t)beam_rows(ld) * PSTRIDE * 4;
+    b += (size_t)tile_rows(ld, dim) * tile_stride(ld, dim) * 4;
     b += ((size_t)fs_len(M0) * 4 + 15) & ~(size_t)15;
     b += 16; /* mbarrier */
     return b;
@@ -192,6 +202,7 @@ template <int METRIC, int L, int CD>
 __device__ __forceinline__ float warp_dist_rows(const SearchParams &p, TeamSmem &sm, const int *bs, int nb,
                                                 float q_norm2, int lane, unsigned long long pol) {
     constexpr int CH = 4 / L;
+    constexpr int PS = TileOf<CD>::stride;
     /* CD != 0: dim == ld == CD (a multiple of 4, no tail) is a compile-time constant, so every trip count below
      * is one too — the unrolled chain loop sheds its counter/branch overhead (−9 % kernel time at dim 128) */
     const int cpr = CD ? CD / 4 : p.ld >> 2, cfull = CD ? CD / 4 : p.dim >> 2, rem = CD ? 0 : p.dim & 3;
@@ -206,14 +217,14 @@ __device__ __forceinline__ float warp_dist_rows(const SearchParams &p, TeamSmem 
 #if MUNINN_BULK_ROWS
         if (lane == 0) bar_expect_tx(sm.bar, (unsigned)(nb * tc * 16));
         __syncwarp();
-        if (lane < nb) bulk_row_copy(sm.P + lane * PSTRIDE, p.vec + (size_t)bs[lane] * (size_t)p.ld + 4 * t0, (unsigned)(tc * 16), sm.bar, pol);
+        if (lane < nb) bulk_row_copy(sm.P + lane * PS, p.vec + (size_t)bs[lane] * (size_t)p.ld + 4 * t0, (unsigned)(tc * 16), sm.bar, pol);
         bar_wait(sm.bar, sm.phase);
         sm.phase ^= 1u;
 #else
         if (lane < tc) {
             const float *src = p.vec + 4 * (t0 + lane);
             float *dst = sm.P + 4 * lane;
-            for (int r = 0; r < nb; r++) cp_async16(dst + r * PSTRIDE, src + (size_t)bs[r] * (size_t)p.ld, pol);
+            for (int r = 0; r < nb; r++) cp_async16(dst + r * PS, src + (size_t)bs[r] * (size_t)p.ld, pol);
         }
         cp_async_wait_all();
         __syncwarp();
@@ -221,7 +232,7 @@ __device__ __forceinline__ float warp_dist_rows(const SearchParams &p, TeamSmem 
         if (mine) {
             int tfull = cfull - t0;
             tfull = tfull > tc ? tc : tfull;
-            const float *xr = sm.P + row * PSTRIDE + CH * h;
+            const float *xr = sm.P + row * PS + CH * h;
             const float *qr = sm.q + 4 * t0 + CH * h;
 #pragma unroll (CD ? (CD / 4 < 32 ? CD / 4 : 32) : 8)
             for (int cc = 0; cc < tfull; cc++) {
@@ -244,7 +255,7 @@ __device__ __forceinline__ float warp_dist_rows(const SearchParams &p, TeamSmem 
                 }
             }
             if (rem && h == 0 && cfull >= t0 && cfull < t0 + 32) { /* the partial chunk: kept for after the horizontal sum */
-                const float *xt = sm.P + row * PSTRIDE + 4 * (cfull - t0), *qt = sm.q + 4 * cfull;
+                const float *xt = sm.P + row * PS + 4 * (cfull - t0), *qt = sm.q + 4 * cfull;
                 tl0 = prod1<METRIC>(qt[0], xt[0]);
                 if (rem > 1) tl1 = prod1<METRIC>(qt[1], xt[1]);
                 if (rem > 2) tl2 = prod1<METRIC>(qt[2], xt[2]);
@@ -368,7 +379,7 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
         sm.Fk = reinterpret_cast<unsigned long long *>(b); b += (size_t)p.M0 * 8;
         sm.S = reinterpret_cast<unsigned long long *>(b); b += 32 * 8;
         sm.q = reinterpret_cast<float *>(b); b += ((size_t)p.ld * 4 + 15) / 16 * 16;
-        sm.P = reinterpret_cast<float *>(b); b += (size_t)RB * PSTRIDE * 4;
+        sm.P = reinterpret_cast<float *>(b); b += (size_t)RB * TileOf<CD>::stride * 4;
         sm.Fs = reinterpret_cast<int *>(b); b += ((size_t)fs_len(p.M0) * 4 + 15) & ~(size_t)15;
         sm.bar = reinterpret_cast<unsigned long long *>(b);
         sm.phase = 0u;

@@ -299,14 +299,26 @@ extern "C" int muninn_cuda_index_upload(MuninnCudaIndex *h, int64_t n, const int
 
 /* ───────────────────────── incremental update ───────────────────────── */
 
-/* every reference to a slot that has just been flagged deleted becomes a hole (-1), as upload stores it */
-__global__ void purge_slots_kernel(int32_t *__restrict__ lists, long long count, const int32_t *__restrict__ dead, int ndead) {
+/* every reference to a slot flagged deleted becomes a hole (-1), as upload stores it: one pass over the lists,
+ * one L2-resident flag lookup per live entry, independent of how many slots were deleted */
+__global__ void purge_slots_kernel(int32_t *__restrict__ lists, long long count, const uint8_t *__restrict__ deleted) {
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x) {
         const int32_t t = lists[i];
-        if (t < 0) continue;
-        for (int j = 0; j < ndead; j++)
-            if (t == dead[j]) { lists[i] = -1; break; }
+        if (t >= 0 && deleted[t]) lists[i] = -1;
     }
+}
+
+/* staged patch records → their places: `width` ints of record r go to lists[at[r] .. at[r] + width) */
+__global__ void patch_scatter_rows_kernel(int n, const long long *__restrict__ at, const int32_t *__restrict__ rows, int width,
+                                          int32_t *__restrict__ lists) {
+    const long long total = (long long)n * width;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x)
+        lists[at[i / width] + i % width] = rows[i];
+}
+__global__ void patch_scatter_flags_kernel(int n, const int32_t *__restrict__ slots, const uint8_t *__restrict__ flags,
+                                           uint8_t *__restrict__ deleted) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) deleted[slots[i]] = flags[i];
 }
 
 template <typename T>
@@ -321,6 +333,9 @@ static cudaError_t regrow(T **ptr, size_t keep, size_t newcount, cudaStream_t st
     return e;
 }
 
+static int ensure_stage(MuninnCudaIndex *h, size_t bytes);
+static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
 extern "C" int muninn_cuda_index_patch(MuninnCudaIndex *h, int64_t n_total, int32_t n_patch, const int32_t *slots,
                                        const int64_t *ids, const int32_t *levels, const uint8_t *deleted, const float *vectors,
                                        const int64_t *list_offsets, const int32_t *targets, int32_t entry_slot,
@@ -333,27 +348,79 @@ extern "C" int muninn_cuda_index_patch(MuninnCudaIndex *h, int64_t n_total, int3
     CK(h, cudaSetDevice(h->device));
     cudaStream_t st = h->stream;
     const int M = h->M, M0 = h->M0;
-    const long long n_old = h->n;
-    /* validate; new slots must be exactly n_old..n_total-1, each present once, ids ascending past the old maximum */
+    const long long n_old = h->n, n_new = n_total - n_old;
+
+    /* ── phase 1: validate everything; the handle is not touched until the whole patch is known to be sound ── */
     std::vector<int32_t> order(n_patch);
     for (int i = 0; i < n_patch; i++) order[i] = i;
     std::sort(order.begin(), order.end(), [&](int a, int b) { return slots[a] < slots[b]; });
-    long long expect_new = n_old, add_upper = 0;
+    std::vector<int32_t> new_levels((size_t)n_new);
+    std::vector<uint8_t> new_deleted((size_t)n_new);
+    std::vector<int32_t> new_rec((size_t)n_new); /* record index of new slot n_old + j */
+    long long expect_new = n_old, add_upper = 0, n_upper_rows = 0;
     int64_t prev_id = h->last_id;
     for (int oi = 0; oi < n_patch; oi++) {
         const int i = order[oi];
         const long long sl = slots[i];
         if (sl < 0 || sl >= n_total || (oi > 0 && slots[order[oi - 1]] == sl)) return fail(h, MUNINN_CUDA_E_ARG, "bad or duplicate slot %lld", sl);
         if (levels[i] < 0 || levels[i] >= 32) return fail(h, MUNINN_CUDA_E_ARG, "level out of range");
-        if (sl >= n_old) {
+        const uint8_t d = deleted ? (deleted[i] != 0) : 0;
+        if (sl >= n_old) { /* new slots must be exactly n_old..n_total-1, ids ascending past the stored maximum */
             if (sl != expect_new++) return fail(h, MUNINN_CUDA_E_ARG, "new nodes must fill slots %lld..%lld", n_old, (long long)n_total - 1);
-            if (n_old + (sl - n_old) > 0 && ids[i] <= prev_id) return fail(h, MUNINN_CUDA_E_ARG, "new ids must ascend past the stored ones");
+            if (sl > 0 && ids[i] <= prev_id) return fail(h, MUNINN_CUDA_E_ARG, "new ids must ascend past the stored ones");
             prev_id = ids[i];
             add_upper += levels[i];
-        } else if (levels[i] != h->h_levels[sl]) return fail(h, MUNINN_CUDA_E_ARG, "level of slot %lld changed", sl);
+            new_levels[sl - n_old] = levels[i]; new_deleted[sl - n_old] = d; new_rec[sl - n_old] = i;
+        } else {
+            if (levels[i] != h->h_levels[sl]) return fail(h, MUNINN_CUDA_E_ARG, "level of slot %lld changed", sl);
+            if (!d && h->h_deleted[sl]) return fail(h, MUNINN_CUDA_E_ARG, "slot %lld cannot be undeleted", sl);
+        }
+        n_upper_rows += levels[i];
     }
     if (expect_new != n_total) return fail(h, MUNINN_CUDA_E_ARG, "patch does not contain every new node");
-    /* grow */
+    auto level_of = [&](int32_t t) { return t < n_old ? h->h_levels[t] : new_levels[t - n_old]; };
+    if (entry_slot >= 0 && level_of(entry_slot) < max_level) return fail(h, MUNINN_CUDA_E_ARG, "entry node level < max_level");
+    /* deleted flags as they will stand after the patch, for the hole rule below */
+    std::vector<std::pair<int32_t, uint8_t>> newly_dead; /* (slot, 1) of old slots that turn deleted */
+    for (int i = 0; i < n_patch; i++)
+        if (slots[i] < n_old && deleted && deleted[i] && !h->h_deleted[slots[i]]) newly_dead.push_back({slots[i], 1});
+    std::sort(newly_dead.begin(), newly_dead.end());
+    auto dead_after = [&](int32_t t) -> bool {
+        if (t >= n_old) return new_deleted[t - n_old] != 0;
+        if (h->h_deleted[t]) return true;
+        return std::binary_search(newly_dead.begin(), newly_dead.end(), std::make_pair(t, (uint8_t)1));
+    };
+    /* staging: level-0 rows [n_patch × M0], upper rows [n_upper_rows × M] with their destinations */
+    std::vector<int32_t> rows0((size_t)n_patch * M0, -1), rowsU((size_t)n_upper_rows * M, -1);
+    std::vector<long long> at0((size_t)n_patch), atU((size_t)n_upper_rows);
+    std::vector<int32_t> ub_new((size_t)n_new, -1);
+    {
+        long long nu = h->n_upper;
+        for (long long j = 0; j < n_new; j++) { if (new_levels[j] > 0) { ub_new[j] = (int32_t)nu; nu += new_levels[j]; } }
+    }
+    int64_t li = 0;
+    long long ur = 0;
+    for (int i = 0; i < n_patch; i++) {
+        const int32_t sl = slots[i];
+        at0[i] = (long long)sl * M0;
+        const long long ub = sl < n_old ? h->h_upper_base[sl] : ub_new[sl - n_old];
+        for (int l = 0; l <= levels[i]; l++, li++) {
+            const int64_t b = list_offsets[li], e = list_offsets[li + 1];
+            const int capl = l == 0 ? M0 : M;
+            if (e < b || e - b > capl) return fail(h, MUNINN_CUDA_E_ARG, "list (slot %d, level %d) has %lld entries, capacity %d", sl, l, (long long)(e - b), capl);
+            if (e > b && !targets) return fail(h, MUNINN_CUDA_E_ARG, "NULL array");
+            int32_t *dst = l == 0 ? &rows0[(size_t)i * M0] : &rowsU[(size_t)ur * M];
+            for (int64_t j = b; j < e; j++) {
+                const int32_t t = targets[j];
+                if (t < -1 || t >= n_total) return fail(h, MUNINN_CUDA_E_ARG, "target %d out of range", t);
+                if (t >= 0 && level_of(t) < l) return fail(h, MUNINN_CUDA_E_ARG, "edge to slot %d at level %d above its level", t, l);
+                dst[j - b] = (t >= 0 && !dead_after(t)) ? t : -1;
+            }
+            if (l > 0) atU[ur++] = (ub + (l - 1)) * M;
+        }
+    }
+
+    /* ── phase 2: grow, then move the records (a handful of bulk copies + scatter kernels) ── */
     if (n_total > h->cap_n) {
         const long long nc = n_total + n_total / 2 + 1024;
         CK(h, regrow(&h->d_vec, (size_t)n_old * h->ld, (size_t)nc * h->ld, st));
@@ -369,81 +436,76 @@ extern "C" int muninn_cuda_index_patch(MuninnCudaIndex *h, int64_t n_total, int3
         CK(h, regrow(&h->d_nbrU, (size_t)h->n_upper * M, (size_t)nc * M, st));
         h->cap_upper = nc;
     }
-    h->h_levels.resize(n_total); h->h_upper_base.resize(n_total, -1); h->h_deleted.resize(n_total, 0);
-    /* records: new nodes first get their slots' bookkeeping, newly deleted slots are collected */
-    std::vector<int32_t> dead;
-    for (int oi = 0; oi < n_patch; oi++) {
-        const int i = order[oi];
-        const long long sl = slots[i];
-        const uint8_t d = deleted ? (deleted[i] != 0) : 0;
-        if (sl >= n_old) {
-            h->h_levels[sl] = levels[i];
-            h->h_upper_base[sl] = levels[i] > 0 ? (int32_t)h->n_upper : -1;
-            h->n_upper += levels[i];
-            h->h_deleted[sl] = d;
-            if (!d) h->n_live++;
-        } else if (d != h->h_deleted[sl]) {
-            if (!d) return fail(h, MUNINN_CUDA_E_ARG, "slot %lld cannot be undeleted", sl);
-            h->h_deleted[sl] = 1; h->n_live--;
-            dead.push_back((int32_t)sl);
-        }
+    std::vector<uint8_t> flags((size_t)n_patch);
+    for (int i = 0; i < n_patch; i++) flags[i] = deleted ? (deleted[i] != 0) : 0;
+    const size_t b_at0 = align256((size_t)n_patch * 8), b_rows0 = align256((size_t)n_patch * M0 * 4),
+                 b_atU = align256((size_t)n_upper_rows * 8), b_rowsU = align256((size_t)n_upper_rows * M * 4),
+                 b_slots = align256((size_t)n_patch * 4), b_flags = align256((size_t)n_patch);
+    int rc = ensure_stage(h, b_at0 + b_rows0 + b_atU + b_rowsU + b_slots + b_flags + 256);
+    if (rc) return rc;
+    char *sb = (char *)h->d_stage;
+    long long *d_at0 = (long long *)sb; sb += b_at0;
+    int32_t *d_rows0 = (int32_t *)sb; sb += b_rows0;
+    long long *d_atU = (long long *)sb; sb += b_atU;
+    int32_t *d_rowsU = (int32_t *)sb; sb += b_rowsU;
+    int32_t *d_slots = (int32_t *)sb; sb += b_slots;
+    uint8_t *d_flags = (uint8_t *)sb;
+    std::vector<float> vec_new;
+    std::vector<int64_t> ids_new((size_t)n_new);
+    if (n_patch > 0) {
+        CK(h, cudaMemcpyAsync(d_at0, at0.data(), (size_t)n_patch * 8, cudaMemcpyHostToDevice, st));
+        CK(h, cudaMemcpyAsync(d_rows0, rows0.data(), (size_t)n_patch * M0 * 4, cudaMemcpyHostToDevice, st));
+        CK(h, cudaMemcpyAsync(d_slots, slots, (size_t)n_patch * 4, cudaMemcpyHostToDevice, st));
+        CK(h, cudaMemcpyAsync(d_flags, flags.data(), (size_t)n_patch, cudaMemcpyHostToDevice, st));
+        const long long tot = (long long)n_patch * M0;
+        patch_scatter_rows_kernel<<<(unsigned)std::min<long long>((tot + 255) / 256, 4096), 256, 0, st>>>(n_patch, d_at0, d_rows0, M0, h->d_nbr0);
+        patch_scatter_flags_kernel<<<(unsigned)((n_patch + 255) / 256), 256, 0, st>>>(n_patch, d_slots, d_flags, h->d_deleted);
+        h->launches += 2;
     }
-    /* staging: rows of the patched lists with deleted targets as holes */
-    std::vector<int32_t> rows0((size_t)n_patch * M0, -1);
-    std::vector<std::vector<int32_t>> rowsU;
-    std::vector<long long> rowsU_at;
-    int64_t li = 0;
-    for (int i = 0; i < n_patch; i++) {
-        const long long sl = slots[i];
-        for (int l = 0; l <= levels[i]; l++, li++) {
-            const int64_t b = list_offsets[li], e = list_offsets[li + 1];
-            const int capl = l == 0 ? M0 : M;
-            if (e < b || e - b > capl) return fail(h, MUNINN_CUDA_E_ARG, "list (slot %lld, level %d) has %lld entries, capacity %d", sl, l, (long long)(e - b), capl);
-            std::vector<int32_t> up;
-            int32_t *dst = &rows0[(size_t)i * M0];
-            if (l > 0) { up.assign(M, -1); dst = up.data(); }
-            for (int64_t j = b; j < e; j++) {
-                const int32_t t = targets[j];
-                if (t < -1 || t >= n_total) return fail(h, MUNINN_CUDA_E_ARG, "target %d out of range", t);
-                if (t >= 0 && h->h_levels[t] < l) return fail(h, MUNINN_CUDA_E_ARG, "edge to slot %d at level %d above its level", t, l);
-                dst[j - b] = (t >= 0 && !h->h_deleted[t]) ? t : -1;
-            }
-            if (l > 0) { rowsU.push_back(std::move(up)); rowsU_at.push_back(((long long)h->h_upper_base[sl] + (l - 1)) * M); }
-        }
-    }
-    for (int i = 0; i < n_patch; i++) {
-        const long long sl = slots[i];
-        CK(h, cudaMemcpyAsync(h->d_nbr0 + (size_t)sl * M0, &rows0[(size_t)i * M0], (size_t)M0 * 4, cudaMemcpyHostToDevice, st));
-        CK(h, cudaMemcpyAsync(h->d_deleted + sl, &h->h_deleted[sl], 1, cudaMemcpyHostToDevice, st));
-        if (sl >= n_old) {
-            if (h->ld != h->dim) CK(h, cudaMemsetAsync(h->d_vec + (size_t)sl * h->ld, 0, (size_t)h->ld * 4, st));
-            CK(h, cudaMemcpyAsync(h->d_vec + (size_t)sl * h->ld, vectors + (size_t)i * h->dim, (size_t)h->dim * 4, cudaMemcpyHostToDevice, st));
-            CK(h, cudaMemcpyAsync(h->d_ids + sl, ids + i, 8, cudaMemcpyHostToDevice, st));
-            CK(h, cudaMemcpyAsync(h->d_upper_base + sl, &h->h_upper_base[sl], 4, cudaMemcpyHostToDevice, st));
-        }
-    }
-    for (size_t u = 0; u < rowsU.size(); u++)
-        CK(h, cudaMemcpyAsync(h->d_nbrU + rowsU_at[u], rowsU[u].data(), (size_t)M * 4, cudaMemcpyHostToDevice, st));
-    if (n_total > n_old) {
-        row_norm2_kernel<<<(unsigned)((n_total - n_old + 255) / 256), 256, 0, st>>>(h->d_vec + (size_t)n_old * h->ld, h->ld, h->dim,
-                                                                                 n_total - n_old, h->d_norm2 + n_old);
+    if (n_upper_rows > 0) {
+        CK(h, cudaMemcpyAsync(d_atU, atU.data(), (size_t)n_upper_rows * 8, cudaMemcpyHostToDevice, st));
+        CK(h, cudaMemcpyAsync(d_rowsU, rowsU.data(), (size_t)n_upper_rows * M * 4, cudaMemcpyHostToDevice, st));
+        const long long tot = n_upper_rows * M;
+        patch_scatter_rows_kernel<<<(unsigned)std::min<long long>((tot + 255) / 256, 4096), 256, 0, st>>>((int)n_upper_rows, d_atU, d_rowsU, M, h->d_nbrU);
         h->launches++;
     }
-    int32_t *d_dead = nullptr;
-    if (!dead.empty()) {
-        CK(h, cudaMalloc((void **)&d_dead, dead.size() * 4));
-        CK(h, cudaMemcpyAsync(d_dead, dead.data(), dead.size() * 4, cudaMemcpyHostToDevice, st));
-        purge_slots_kernel<<<h->num_sms * 8, 256, 0, st>>>(h->d_nbr0, (long long)n_total * M0, d_dead, (int)dead.size());
-        if (h->n_upper) purge_slots_kernel<<<h->num_sms * 2, 256, 0, st>>>(h->d_nbrU, h->n_upper * M, d_dead, (int)dead.size());
-        h->launches += 2;
+    if (n_new > 0) { /* new slots are contiguous: rows (zero-padded to ld), ids and upper_base go out as three plain copies */
+        vec_new.assign((size_t)n_new * h->ld, 0.0f);
+        for (long long j = 0; j < n_new; j++) {
+            memcpy(&vec_new[(size_t)j * h->ld], vectors + (size_t)new_rec[j] * h->dim, (size_t)h->dim * 4);
+            ids_new[j] = ids[new_rec[j]];
+        }
+        CK(h, cudaMemcpyAsync(h->d_vec + (size_t)n_old * h->ld, vec_new.data(), vec_new.size() * 4, cudaMemcpyHostToDevice, st));
+        CK(h, cudaMemcpyAsync(h->d_ids + n_old, ids_new.data(), (size_t)n_new * 8, cudaMemcpyHostToDevice, st));
+        CK(h, cudaMemcpyAsync(h->d_upper_base + n_old, ub_new.data(), (size_t)n_new * 4, cudaMemcpyHostToDevice, st));
+        row_norm2_kernel<<<(unsigned)((n_new + 255) / 256), 256, 0, st>>>(h->d_vec + (size_t)n_old * h->ld, h->ld, h->dim, n_new,
+                                                                        h->d_norm2 + n_old);
+        h->launches++;
+    }
+    if (!newly_dead.empty()) { /* after the flags above, in stream order */
+        purge_slots_kernel<<<h->num_sms * 8, 256, 0, st>>>(h->d_nbr0, (long long)n_total * M0, h->d_deleted);
+        const long long nu = h->n_upper + add_upper;
+        if (nu) purge_slots_kernel<<<h->num_sms * 2, 256, 0, st>>>(h->d_nbrU, nu * M, h->d_deleted);
+        h->launches += nu ? 2 : 1;
     }
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaStreamSynchronize(st); /* the staging vectors above go out of scope */
-    cudaFree(d_dead);
-    CK(h, e);
+    if (e != cudaSuccess) { /* the device copy is in an unknown state: only a fresh upload makes the handle usable again */
+        h->uploaded = false;
+        CK(h, e);
+    }
+    /* ── phase 3: commit the host mirrors ── */
+    h->h_levels.resize(n_total); h->h_upper_base.resize(n_total, -1); h->h_deleted.resize(n_total, 0);
+    for (long long j = 0; j < n_new; j++) {
+        h->h_levels[n_old + j] = new_levels[j];
+        h->h_upper_base[n_old + j] = ub_new[j];
+        h->h_deleted[n_old + j] = new_deleted[j];
+        if (!new_deleted[j]) h->n_live++;
+    }
+    for (auto &nd : newly_dead) { h->h_deleted[nd.first] = 1; h->n_live--; }
+    h->n_upper += add_upper;
     h->n = n_total; h->entry_slot = entry_slot; h->max_level = max_level;
-    if (n_total > n_old) h->last_id = prev_id;
-    if (entry_slot >= 0 && h->h_levels[entry_slot] < max_level) return fail(h, MUNINN_CUDA_E_ARG, "entry node level < max_level");
+    if (n_new > 0) h->last_id = prev_id;
     return MUNINN_CUDA_OK;
 }
 
@@ -482,7 +544,7 @@ static cudaError_t launch_levels(MuninnCudaIndex *h, SearchParams p, size_t smem
                                  const unsigned caps[3], int nlevels, int nq) {
     /* constant-dimension instances for the shapes BASELINE.json names; any other dim runs the generic ones */
     if (MUNINN_D128 && h->dim == 128) return launch_levels_rb<METRIC, RB_NARROW, 128>(h, p, smem, teams, caps, nlevels, nq);
-    if (MUNINN_D128 && h->dim == 96) return launch_levels_rb<METRIC, RB_NARROW, 96>(h, p, smem, teams, caps, nlevels, nq);
+    if (MUNINN_D128 && h->dim == 96) return launch_levels_rb<METRIC, RB_D96, 96>(h, p, smem, teams, caps, nlevels, nq);
     if (MUNINN_D128 && h->dim == 768) return launch_levels_rb<METRIC, RB_WIDE, 768>(h, p, smem, teams, caps, nlevels, nq);
     return beam_rows(h->ld) == RB_NARROW ? launch_levels_rb<METRIC, RB_NARROW, 0>(h, p, smem, teams, caps, nlevels, nq)
                                          : launch_levels_rb<METRIC, RB_WIDE, 0>(h, p, smem, teams, caps, nlevels, nq);
@@ -497,7 +559,7 @@ static cudaError_t occupancy_of_rb(int *occ, size_t smem) {
 template <int METRIC>
 static cudaError_t occupancy_of(int *occ, size_t smem, int ld, int dim) {
     if (MUNINN_D128 && dim == 128) return occupancy_of_rb<METRIC, RB_NARROW, 128>(occ, smem);
-    if (MUNINN_D128 && dim == 96) return occupancy_of_rb<METRIC, RB_NARROW, 96>(occ, smem);
+    if (MUNINN_D128 && dim == 96) return occupancy_of_rb<METRIC, RB_D96, 96>(occ, smem);
     if (MUNINN_D128 && dim == 768) return occupancy_of_rb<METRIC, RB_WIDE, 768>(occ, smem);
     return beam_rows(ld) == RB_NARROW ? occupancy_of_rb<METRIC, RB_NARROW, 0>(occ, smem) : occupancy_of_rb<METRIC, RB_WIDE, 0>(occ, smem);
 }
@@ -511,7 +573,7 @@ extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *
     if (nq == 0) return MUNINN_CUDA_OK;
     if (!d_queries || !d_ids || !d_dist || !d_count) return fail(h, MUNINN_CUDA_E_ARG, "NULL buffer");
     if (ef < k) ef = k; /* src/hnsw_algo.c:673 */
-    const size_t smem = search_smem_bytes(ef, h->ld, h->M0);
+    const size_t smem = search_smem_bytes(ef, h->ld, h->M0, MUNINN_D128 ? h->dim : -1);
     if (smem > 200 * 1024) return fail(h, MUNINN_CUDA_E_ARG, "ef=%d with dim=%d needs %zu B of shared memory per query (limit 200 KiB)", ef, h->dim, smem);
     CK(h, cudaSetDevice(h->device));
 
@@ -570,8 +632,6 @@ extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *
     h->have_timing = true;
     return MUNINN_CUDA_OK;
 }
-
-static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 static int ensure_stage(MuninnCudaIndex *h, size_t bytes) {
     if (bytes <= h->stage_bytes) return MUNINN_CUDA_OK;

@@ -181,6 +181,10 @@ class HnswIndexCuda:
         """Send only the records of `slots` (every new node included) of the new state `g`: what hnsw_insert /
         hnsw_delete changed (/root/reference/src/hnsw_algo.c:520-666, :717-805)."""
         g.validate()
+        self.patch_unchecked(g, slots)
+
+    def patch_unchecked(self, g: FlatGraph, slots):
+        """patch() without the host-side FlatGraph.validate(): the library's own checks are the only gate (tests)."""
         slots = np.ascontiguousarray(slots, np.int32)
         first = g.first_list()
         offs, tg = [0], []

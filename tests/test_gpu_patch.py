@@ -79,3 +79,36 @@ def test_patch_rejects_what_it_cannot_express(reference):
             idx.patch(g2, [0])
         with pytest.raises(MuninnCudaError):
             idx.patch(g, [0, 0])  # duplicate slot
+
+
+def test_rejected_patch_leaves_the_handle_untouched(reference):
+    """Validation comes before any mutation: after a patch the library refuses (a list over capacity found in
+    the LAST record), searches answer as before and a sound patch of the same
+    burst still applies — the device copy then equals a fresh upload."""
+    import copy
+    from sqlite_muninn_b200.cuda import HnswIndexCuda, MuninnCudaError
+    base, q = uniform(6, 330, 12), uniform(7, 64, 12)
+    ref = reference.build(base[:300], ids=np.arange(300, dtype=np.int64) + 1, metric=0, M=4, efc=30)
+    g = ref.export()
+    with HnswIndexCuda.from_graph(g) as idx:
+        before = idx.search(q, 10, 50, want_stats=True)
+        assert ref.insert(np.arange(301, 331, dtype=np.int64), base[300:]) == 0
+        assert ref.delete(17) == 0
+        g2 = ref.export()
+        touched = changed_slots(g, g2)
+        bad = copy.deepcopy(g2)
+        assert touched[-1] == bad.n - 1  # the newest node: its record is the last one the library looks at
+        # stretch the very last list (the newest node's top level) past any capacity (2M = 8)
+        bad.targets = np.concatenate([bad.targets, np.zeros(9, np.int32)])
+        bad.list_offsets = bad.list_offsets.copy()
+        bad.list_offsets[-1] += 9
+        with pytest.raises(MuninnCudaError, match="capacity"):
+            idx.patch_unchecked(bad, touched)
+        after = idx.search(q, 10, 50, want_stats=True)
+        for x, y in zip(before[:3], after[:3]):
+            assert np.array_equal(x, y)
+        assert np.array_equal(before[3]["n_dist"], after[3]["n_dist"])
+        idx.patch(g2, touched)
+        with HnswIndexCuda.from_graph(g2) as fresh:
+            a, b = idx.search(q, 10, 50), fresh.search(q, 10, 50)
+            assert all(np.array_equal(x, y) for x, y in zip(a, b))
