@@ -34,6 +34,7 @@
  */
 #pragma once
 #include "muninn_dev.cuh"
+#include "hnsw_search.cuh" /* warp_dist_rows: TMA-staged rows, the reference's chain order */
 #include <cuda.h> /* CUtensorMap and its enums only; cuTensorMapEncodeTiled is looked up at run time */
 
 namespace muninn {
@@ -262,43 +263,67 @@ exact_tc_filter(const __grid_constant__ CUtensorMap tm_qhi, const __grid_constan
         const int qrow = quarter * 32 + lane;
         const float c = p.c_eps, hh = 0.5f * (1.0f - c);
         int a = 0; uint32_t aph = 0;
+        /* the epilogue is the critical role when the batch is small (one MMA per 128 KB of rows): nothing in it may
+         * wait on global memory. The per-row terms of the NEXT tile are fetched while this one is processed, the
+         * per-query term is recomputed only when the query tile changes, and each 32-column TMEM read is issued
+         * before the previous one is consumed. */
+        constexpr int XPT = BN / 128;
+        float xn_pre[XPT];
+        auto fetch_xn = [&](long long t2) {
+#pragma unroll
+            for (int u = 0; u < XPT; u++) {
+                xn_pre[u] = 0.0f;
+                if (t2 < n_tiles) {
+                    const int xt2 = (int)(t2 / n_qt), j = et + 128 * u;
+                    if (xt2 * BN + j < p.rows) xn_pre[u] = __ldg(p.xnorm2 + p.row0 + (long long)xt2 * BN + j);
+                }
+            }
+        };
+        fetch_xn(blockIdx.x);
+        int qt_have = -1;
+        float qa = 0.0f;
+        bool qvalid = false;
+        int q = 0;
         for (long long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
             const int xt = (int)(t / n_qt), qt = (int)(t % n_qt);
-            const int q = qt * BM + qrow;
-            const bool qvalid = q < p.nq;
             const int ncols = p.rows - xt * BN < BN ? p.rows - xt * BN : BN;
             const long long xrow0 = p.row0 + (long long)xt * BN;
-            float qa = 0.0f;
-            if (qvalid) {
-                const float qn = p.qaux[q], tq = __ldcg(p.tau + q) + 1e-30f;
-                if (METRIC == METRIC_L2) qa = fmaf(hh, qn, -0.5f * tq);
-                else if (METRIC == METRIC_IP) qa = fmaf(-c, qn, -tq);
-                else qa = qn < 1e-18f ? __int_as_float(0x7fc00000) : (1.0f - tq - c) * sqrtf(qn);
+            if (qt != qt_have) {
+                qt_have = qt;
+                q = qt * BM + qrow;
+                qvalid = q < p.nq;
+                qa = 0.0f;
+                if (qvalid) {
+                    const float qn = p.qaux[q], tq = __ldcg(p.tau + q) + 1e-30f;
+                    if (METRIC == METRIC_L2) qa = fmaf(hh, qn, -0.5f * tq);
+                    else if (METRIC == METRIC_IP) qa = fmaf(-c, qn, -tq);
+                    else qa = qn < 1e-18f ? __int_as_float(0x7fc00000) : (1.0f - tq - c) * sqrtf(qn);
+                }
             }
             float *xa = xaux + a * BN;
-            for (int j = et; j < BN; j += 128) {
+#pragma unroll
+            for (int u = 0; u < XPT; u++) {
+                const int j = et + 128 * u;
                 float v = 0.0f;
                 if (j < ncols) {
-                    const float xn = p.xnorm2[xrow0 + j];
+                    const float xn = xn_pre[u];
                     if (METRIC == METRIC_L2) v = hh * xn;
                     else if (METRIC == METRIC_IP) v = -c * xn;
                     else v = xn < 1e-18f ? __int_as_float(0x7fc00000) : rsqrtf(xn);
                 }
                 xa[j] = v;
             }
+            fetch_xn(t + gridDim.x); /* in flight during this tile's columns */
             asm volatile("bar.sync 1, 128;" ::: "memory");
             mbar_wait(&tmem_full[a], aph);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(a * BN);
-            for (int c0 = 0; c0 < ncols; c0 += 32) {
-                uint32_t v[32];
-                tmem_ld32(taddr + (uint32_t)c0, v);
-                tmem_ld_wait();
+            auto consume = [&](const uint32_t (&v)[32], int c0) {
                 if (DBG) {
                     if (qvalid)
                         for (int j = 0; j < 32 && c0 + j < ncols; j++)
                             p.dbg_panel[(size_t)q * p.dbg_ld + (size_t)(xrow0 - p.row0) + c0 + j] = __uint_as_float(v[j]);
-                    continue;
+                    return;
                 }
                 uint32_t keep = 0;
 #pragma unroll
@@ -319,6 +344,19 @@ exact_tc_filter(const __grid_constant__ CUtensorMap tm_qhi, const __grid_constan
                     keep &= keep - 1;
                     const int pos = atomicAdd(p.cand_count + q, 1);
                     if (pos < p.cand_cap) p.cand[(size_t)q * p.cand_cap + pos] = (int)(xrow0 + c0 + j);
+                }
+            };
+            uint32_t va[32], vb[32];
+            tmem_ld32(taddr, va);
+            for (int c0 = 0; c0 < ncols; c0 += 64) {
+                tmem_ld_wait();
+                const bool more = c0 + 32 < ncols;
+                if (more) tmem_ld32(taddr + (uint32_t)(c0 + 32), vb);
+                consume(va, c0);
+                if (more) {
+                    tmem_ld_wait();
+                    if (c0 + 64 < ncols) tmem_ld32(taddr + (uint32_t)(c0 + 64), va);
+                    consume(vb, c0 + 32);
                 }
             }
             tc_fence_before();
@@ -413,7 +451,13 @@ __device__ __forceinline__ void quad_chain_multi(const float *__restrict__ q, co
     const int h = lane & 3, g = lane & ~3, cfull = dim >> 2;
     float s[RU];
 #pragma unroll
-    for (int u = 0; u < RU; u++) s[u] = 0.0f;
+    for (int u = 0; u < RU; u++) {
+        s[u] = 0.0f;
+        /* every 128-byte line of the row towards L2 now: the chain loop below would otherwise discover them one
+         * DRAM round trip after the other */
+        if (have[u])
+            for (int off = 32 * h; off < dim; off += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(x[u] + off));
+    }
     for (int c = 0; c < cfull; c++) {
         const float a = q[4 * c + h];
 #pragma unroll
@@ -504,6 +548,158 @@ exact_tc_rerank(const float *__restrict__ vec, const float *__restrict__ norm2, 
             cand_count[q] = 0;
             atomicAdd(n_cand_total, (unsigned long long)cnt);
         }
+    }
+}
+
+/* Small batches (the HBM-bound regime, nq < 1024): ONE CTA of 8 warps per query instead of one warp. The
+ * survivors' exact distances are computed by all warps at once (256 rows in flight per query), the keys that
+ * beat the current k-th best are appended to the query's sorted list in shared memory and the union is put in
+ * order: a radix select finds the k-th smallest distance, the keys up to it are sorted bitonically — the k smallest
+ * keys of R ∪ survivors, the same set in the same (distance, row) order as the warp kernel's sequence of merges.
+ * smem: A[P_alloc] | B[P_alloc], P_alloc = pow2 ≥ k + cap. */
+template <int METRIC>
+__global__ void __launch_bounds__(256)
+exact_tc_rerank_cta(const float *__restrict__ vec, const float *__restrict__ norm2, const uint8_t *__restrict__ deleted, int ld,
+                    int dim, const float *__restrict__ queries, int nq, int k, const int *__restrict__ cand,
+                    int *__restrict__ cand_count, int cap, unsigned long long *__restrict__ topk, int *__restrict__ topk_size,
+                    float *__restrict__ tau, int *__restrict__ overflow, unsigned long long *__restrict__ n_cand_total, int P_alloc) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    unsigned long long *A = reinterpret_cast<unsigned long long *>(smem_raw);
+    __shared__ int s_fill, s_hist[256], s_sel[2];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, q = blockIdx.x;
+    if (q >= nq) return;
+    int cnt = cand_count[q];
+    if (cnt > cap) { if (threadIdx.x == 0) overflow[q] = 1; cnt = cap; }
+    if (cnt <= 0) return; /* block-uniform */
+    const int size = topk_size[q];
+    for (int i = threadIdx.x; i < size; i += 256) A[i] = topk[(size_t)q * k + i];
+    if (threadIdx.x == 0) s_fill = size;
+    __syncthreads();
+    const unsigned long long worst = size >= k ? A[k - 1] : KEY_NONE;
+    /* distances: the search kernel's row path — 16 survivors per warp per round, each row one TMA bulk copy into
+     * the warp's shared-memory tile, two lanes per row walking the reference's chains (hnsw_search.cuh) */
+    SearchParams sp;
+    sp.vec = vec; sp.norm2 = norm2; sp.ld = ld; sp.dim = dim;
+    TeamSmem sm;
+    {
+        unsigned char *b = smem_raw + (size_t)2 * P_alloc * 8;
+        sm.q = reinterpret_cast<float *>(b); b += ((size_t)ld * 4 + 15) / 16 * 16;
+        sm.P = reinterpret_cast<float *>(b) + (size_t)wib * 16 * PSTRIDE; b += (size_t)8 * 16 * PSTRIDE * 4;
+        sm.Fs = reinterpret_cast<int *>(b) + wib * 16; b += 8 * 16 * 4;
+        sm.bar = reinterpret_cast<unsigned long long *>(b) + wib;
+        sm.phase = 0u;
+        sm.R = sm.Fk = sm.S = nullptr;
+    }
+    for (int i = threadIdx.x; i < ld; i += 256) sm.q[i] = i < dim ? queries[(size_t)q * dim + i] : 0.0f;
+    if (lane == 0) bar_init(sm.bar, 1);
+    __syncthreads();
+    float qn2 = 0.0f;
+    if (METRIC == METRIC_COSINE) qn2 = query_norm2(sm.q, dim);
+    const unsigned long long pol = l2_evict_first_policy();
+    for (int c0 = wib * 16; c0 < cnt; c0 += 8 * 16) {
+        const int nb = cnt - c0 < 16 ? cnt - c0 : 16;
+        if (lane < nb) sm.Fs[lane] = cand[(size_t)q * cap + c0 + lane];
+        __syncwarp();
+        const float d = warp_dist_rows<METRIC, 2, 0>(sp, sm, sm.Fs, nb, qn2, lane, pol);
+        const int r = lane >> 1;
+        const int row = r < nb ? sm.Fs[r] : 0;
+        const bool live = (lane & 1) == 0 && r < nb && !(deleted && deleted[row]);
+        const unsigned long long f = live ? make_key(d, (unsigned)row) : KEY_NONE;
+        const bool keep = f < worst;
+        const unsigned km = __ballot_sync(FULL, keep);
+        if (km) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(&s_fill, __popc(km));
+            base = __shfl_sync(FULL, base, 0);
+            if (keep) A[base + __popc(km & ((1u << lane) - 1))] = f;
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    const int total = s_fill;
+    unsigned long long *srt = A;
+    if (total > size) { /* something entered: the k smallest of the union, in order */
+        int m = total;
+        if (total > 512) {
+            /* radix select on the distance half of the keys: thr = the k-th smallest distance (k ≤ 512 < total), then
+             * only the keys with distance ≤ thr (k of them, plus ties of the k-th) are sorted */
+            unsigned prefix = 0;
+            int want = k;
+            for (int pass = 3; pass >= 0; pass--) {
+                const int shift = 8 * pass;
+                s_hist[threadIdx.x] = 0;
+                __syncthreads();
+                for (int i0 = 0; i0 < total; i0 += 256) {
+                    const int i = i0 + threadIdx.x;
+                    unsigned hi = 0;
+                    bool in = i < total;
+                    if (in) {
+                        hi = (unsigned)(A[i] >> 32);
+                        in = pass == 3 || (hi >> (shift + 8)) == (prefix >> (shift + 8));
+                    }
+                    const unsigned pm = __ballot_sync(FULL, in);
+                    if (in) {
+                        const unsigned bin = (hi >> shift) & 255u;
+                        const unsigned peers = __match_any_sync(pm, bin);
+                        if ((__ffs(peers) - 1) == lane) atomicAdd(&s_hist[bin], __popc(peers));
+                    }
+                }
+                __syncthreads();
+                if (wib == 0) {
+                    int part = 0;
+#pragma unroll
+                    for (int b8 = 0; b8 < 8; b8++) part += s_hist[8 * lane + b8];
+                    int incl = part;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) { const int up = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += up; }
+                    const unsigned hit = __ballot_sync(FULL, incl >= want);
+                    const int L = __ffs(hit) - 1; /* total ≥ want: some lane hits */
+                    if (lane == L) {
+                        int before = incl - part, b8 = 0;
+                        while (before + s_hist[8 * lane + b8] < want) { before += s_hist[8 * lane + b8]; b8++; }
+                        s_sel[0] = (int)(prefix | ((unsigned)(8 * lane + b8) << shift));
+                        s_sel[1] = want - before;
+                    }
+                }
+                __syncthreads();
+                prefix = (unsigned)s_sel[0];
+                want = s_sel[1];
+            }
+            if (threadIdx.x == 0) s_fill = 0;
+            __syncthreads();
+            unsigned long long *B = A + P_alloc;
+            for (int i = threadIdx.x; i < total; i += 256) {
+                const unsigned long long e = A[i];
+                if ((unsigned)(e >> 32) <= prefix) B[atomicAdd(&s_fill, 1)] = e;
+            }
+            __syncthreads();
+            m = s_fill;
+            srt = B;
+        }
+        int P = 64;
+        while (P < m) P <<= 1;
+        for (int i = m + threadIdx.x; i < P; i += 256) srt[i] = KEY_NONE;
+        __syncthreads();
+        for (int kk = 2; kk <= P; kk <<= 1)
+            for (int j = kk >> 1; j > 0; j >>= 1) {
+                for (int i = threadIdx.x; i < P; i += 256) {
+                    const int ixj = i ^ j;
+                    if (ixj > i) {
+                        const unsigned long long x = srt[i], y = srt[ixj];
+                        const bool up = (i & kk) == 0;
+                        if ((x > y) == up) { srt[i] = y; srt[ixj] = x; }
+                    }
+                }
+                __syncthreads();
+            }
+    }
+    const int nsize = total < k ? total : k;
+    for (int i = threadIdx.x; i < nsize; i += 256) topk[(size_t)q * k + i] = srt[i];
+    if (threadIdx.x == 0) {
+        topk_size[q] = nsize;
+        if (nsize >= k) tau[q] = okey_inv((unsigned)(srt[k - 1] >> 32));
+        cand_count[q] = 0;
+        atomicAdd(n_cand_total, (unsigned long long)cnt);
     }
 }
 

@@ -814,7 +814,11 @@ static int exact_knn_tc(MuninnCudaIndex *h, const float *d_queries, int nq, int 
                                                               : h->exact_mode;
     const bool three = h->exact_mode_run == MUNINN_EXACT_TC_3XTF32;
     const bool raw_x = !three; /* 1xTF32: the MMA reads the fp32 rows as they are (it drops the low 13 bits) */
-    const int cap = d_dbg ? 256 : std::max(1024, (4 * k + 255) / 256 * 256);
+    /* small batches are HBM- and launch-bound: larger survivor lists (re-ranked by a CTA per query) allow ×17..32
+     * chunk growth, i.e. 4-5 chunks instead of 9 over millions of rows */
+    const bool small = !d_dbg && nq < 1024 && k <= 512 && h->ld <= 4096; /* the CTA re-rank's shared memory: 128 KB of keys + 68 KB of row tiles + the query */
+    const int cap = d_dbg ? 256 : small ? 4096 : std::max(1024, (4 * k + 255) / 256 * 256);
+    const int grow_c = small ? std::min(31, std::max(3, 2 * cap / (5 * k))) : 3; /* expected survivors per chunk ≈ grow_c·k */
     const long long n = d_dbg ? dbg_rows : h->n;
     /* row scratch: ≤ 1 GiB of split slabs per chunk, whole tiles (none when the slab is read raw) */
     long long chunk_max = raw_x ? (1ll << 40) : (long long)((1ull << 30) / ((size_t)kp * 4 * (three ? 2 : 1)));
@@ -854,8 +858,17 @@ static int exact_knn_tc(MuninnCudaIndex *h, const float *d_queries, int nq, int 
     if (!rc) rc = make_slab_map(h, &maps[1], three ? q_lo : q_hi, kp, nq, tc::BM);
     if (rc) return rc;
 
-    const size_t rr_smem = (size_t)4 * (k + 32) * 8;
-    if (rr_smem > 48 * 1024) {
+    size_t rr_smem = (size_t)4 * (k + 32) * 8;
+    int rr_P = 0;
+    if (small) {
+        size_t P = 64;
+        while (P < (size_t)k + cap) P <<= 1;
+        rr_smem = 2 * P * 8 + ((size_t)h->ld * 4 + 15) / 16 * 16 + (size_t)8 * 16 * PSTRIDE * 4 + 8 * 16 * 4 + 8 * 8;
+        rr_P = (int)P;
+        CK(h, cudaFuncSetAttribute(tc::exact_tc_rerank_cta<METRIC_L2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rr_smem));
+        CK(h, cudaFuncSetAttribute(tc::exact_tc_rerank_cta<METRIC_COSINE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rr_smem));
+        CK(h, cudaFuncSetAttribute(tc::exact_tc_rerank_cta<METRIC_IP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rr_smem));
+    } else if (rr_smem > 48 * 1024) {
         CK(h, cudaFuncSetAttribute(tc::exact_tc_rerank<METRIC_L2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rr_smem));
         CK(h, cudaFuncSetAttribute(tc::exact_tc_rerank<METRIC_COSINE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rr_smem));
         CK(h, cudaFuncSetAttribute(tc::exact_tc_rerank<METRIC_IP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rr_smem));
@@ -870,8 +883,8 @@ static int exact_knn_tc(MuninnCudaIndex *h, const float *d_queries, int nq, int 
     size_t ev_used = 0;
     for (long long done = 0; done < n;) {
         /* first chunk: every row survives (τ = +inf), so keep it small but ≥ 2k rows; then double */
-        long long chunk = done == 0 ? std::min<long long>(std::min(cap, std::max(256, (2 * k + 255) / 256 * 256)), n)
-                                    : std::min<long long>(std::min(3 * done, chunk_max), n - done); /* ×4 per round: ≈ 3k survivors */
+        long long chunk = done == 0 ? std::min<long long>(small ? cap / 2 : std::min(cap, std::max(256, (2 * k + 255) / 256 * 256)), n)
+                                    : std::min<long long>(std::min((long long)grow_c * done, chunk_max), n - done); /* ×(1+grow_c) per round */
         if (d_dbg) chunk = n;
         if (raw_x) {
             rc = make_slab_map(h, &maps[2], h->d_vec + (size_t)done * h->ld, h->ld, chunk, bn);
@@ -900,7 +913,14 @@ static int exact_knn_tc(MuninnCudaIndex *h, const float *d_queries, int nq, int 
         h->launches++;
         if (d_dbg) { chunks = 1; break; }
         const int rr_grid = (nq + 3) / 4;
-        if (h->metric == MUNINN_METRIC_L2)
+        if (small) {
+            if (h->metric == MUNINN_METRIC_L2)
+                tc::exact_tc_rerank_cta<METRIC_L2><<<nq, 256, rr_smem, st>>>(h->d_vec, h->d_norm2, h->d_deleted, h->ld, h->dim, d_queries, nq, k, h->d_cand, h->d_cand_count, cap, h->d_topk, h->d_topk_size, h->d_tau, h->d_overflow, h->d_tc_ctr, rr_P);
+            else if (h->metric == MUNINN_METRIC_COSINE)
+                tc::exact_tc_rerank_cta<METRIC_COSINE><<<nq, 256, rr_smem, st>>>(h->d_vec, h->d_norm2, h->d_deleted, h->ld, h->dim, d_queries, nq, k, h->d_cand, h->d_cand_count, cap, h->d_topk, h->d_topk_size, h->d_tau, h->d_overflow, h->d_tc_ctr, rr_P);
+            else
+                tc::exact_tc_rerank_cta<METRIC_IP><<<nq, 256, rr_smem, st>>>(h->d_vec, h->d_norm2, h->d_deleted, h->ld, h->dim, d_queries, nq, k, h->d_cand, h->d_cand_count, cap, h->d_topk, h->d_topk_size, h->d_tau, h->d_overflow, h->d_tc_ctr, rr_P);
+        } else if (h->metric == MUNINN_METRIC_L2)
             tc::exact_tc_rerank<METRIC_L2><<<rr_grid, 128, rr_smem, st>>>(h->d_vec, h->d_norm2, h->d_deleted, h->ld, h->dim, d_queries, nq, k, h->d_cand, h->d_cand_count, cap, h->d_topk, h->d_topk_size, h->d_tau, h->d_overflow, h->d_tc_ctr);
         else if (h->metric == MUNINN_METRIC_COSINE)
             tc::exact_tc_rerank<METRIC_COSINE><<<rr_grid, 128, rr_smem, st>>>(h->d_vec, h->d_norm2, h->d_deleted, h->ld, h->dim, d_queries, nq, k, h->d_cand, h->d_cand_count, cap, h->d_topk, h->d_topk_size, h->d_tau, h->d_overflow, h->d_tc_ctr);

@@ -68,7 +68,8 @@ def test_tensor_modes_equal_oracle(cuda, oracle, metric, dim, n, nq, k):
 
 
 def test_filter_prunes(cuda, oracle):
-    """On spread-out data the 3xTF32 filter leaves ≈ k survivors per doubling chunk, not n."""
+    """On spread-out data the 3xTF32 filter leaves ≈ (growth factor)·k survivors per chunk, not n. A batch of
+    256 queries runs the small-batch policy: 2048-row first chunk (all survive), ×32 growth."""
     n, dim, nq, k = 60000, 128, 256, 10
     base, q = latent(1, n, dim), latent(2, nq, dim)
     with cuda.HnswIndexCuda.from_graph(flat(base, L2)) as idx:
@@ -79,7 +80,7 @@ def test_filter_prunes(cuda, oracle):
     assert np.array_equal(i_g, i_o) and d_g.tobytes() == d_o.tobytes()
     assert st["overflow_queries"] == 0
     per_query = st["candidates"] / nq
-    assert per_query < 1024 + 40 * k * st["chunks"], per_query  # first chunk (1024 rows) passes whole
+    assert per_query < 2048 + 60 * k * st["chunks"], per_query  # the first chunk passes whole
     assert per_query < 0.05 * n
 
 
