@@ -69,6 +69,14 @@ constexpr int PSTRIDE = 128 + 4;  /* floats per staged row: 32 chunks + 4 pad â†
 constexpr int MAX_M0 = 128;       /* layer-0 list capacity supported (M â‰¤ 64) */
 /* dim 96 (config 4): rows are 384 bytes, so a 16-row tile at stride 100 floats (â‰¡ 4 mod 32: conflict-free like 132)
  * is SMALLER than the 13-row tile at stride 132 â€” the full 16-row batch at the same 24 teams/SM */
+/* Pull the neighbour list of the LIKELY next candidate towards L2 while the current one is still being worked on:
+ * at pop time the second-closest open entry of R, and after the distances every fresh node that beats it. The
+ * list read at the top of the next expansion is then an L2 hit instead of a DRAM round trip on the critical path
+ * (prefetches only: no registers held, no effect on results). Measured at config 2 (two interleaved A/B pairs):
+ * 1.687 / 1.621 ms with, 1.611 / 1.671 ms without â€” inside the run-to-run noise, so it stays off. */
+#ifndef MUNINN_LIST_PREFETCH
+#define MUNINN_LIST_PREFETCH 0
+#endif
 #ifndef MUNINN_D96_WIDE
 #define MUNINN_D96_WIDE 1
 #endif
@@ -479,11 +487,26 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
                 for (;;) {
                     /* closest unexpanded entry of R */
                     int pos = -1;
+                    unsigned long long next_open = KEY_NONE; /* lower bound of the keys behind the popped entry */
+                    (void)next_open;
                     for (int base = lb & ~31; base < size; base += 32) {
                         int idx = base + lane;
                         bool open = idx < size && idx >= lb && !(sm.R[idx] & 1ull);
                         unsigned om = __ballot_sync(FULL, open);
-                        if (om) { pos = base + __ffs(om) - 1; break; }
+                        if (om) {
+                            pos = base + __ffs(om) - 1;
+#if MUNINN_LIST_PREFETCH
+                            /* every entry behind pos is â‰¥ R[pos + 1]: a fresh node below that key is popped before any of them */
+                            next_open = pos + 1 < size ? sm.R[pos + 1] : KEY_NONE;
+                            const unsigned om2 = om & (om - 1);
+                            if (om2) {
+                                const unsigned long long second = sm.R[base + __ffs(om2) - 1];
+                                const char *nl = reinterpret_cast<const char *>(p.nbr0 + (size_t)((unsigned)second >> 1) * (size_t)p.M0);
+                                if (lane * 128 < p.M0 * 4) prefetch_l2(nl + lane * 128);
+                            }
+#endif
+                            break;
+                        }
                     }
                     if (pos < 0) { term = (size >= ef && evicted_open) ? 1 : 0; break; }
                     if (stale >= p.patience_max && size >= ef) { term = 2; break; } /* :391-392 */
@@ -529,6 +552,17 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
                         }
                     }
                     __syncwarp();
+#if MUNINN_LIST_PREFETCH
+                    for (int base = 0; base < nf; base += 32) { /* fresh nodes that will be popped before next_open */
+                        if (base + lane < nf) {
+                            const unsigned long long f = sm.Fk[base + lane];
+                            if (f < next_open) {
+                                const char *nl = reinterpret_cast<const char *>(p.nbr0 + (size_t)((unsigned)f >> 1) * (size_t)p.M0);
+                                for (int off = 0; off < p.M0 * 4; off += 128) prefetch_l2(nl + off);
+                            }
+                        }
+                    }
+#endif
 #if MUNINN_NEXT_PREFETCH
                     {   /* the next pop is the smaller of (first open entry of R, best fresh key that will
                          * enter R): start loading its neighbour list now, the merge below hides the latency */

@@ -60,6 +60,7 @@ struct MuninnCudaIndex {
     /* staging for the host-buffer entry points */
     void *d_stage = nullptr; size_t stage_bytes = 0;
     void *h_pinned = nullptr; size_t pinned_bytes = 0;
+    size_t occ_smem = 0; int occ_val = 0; /* cached occupancy of the search kernel for the last shared-memory size */
     /* exact k-NN scratch */
     float *d_panel = nullptr; size_t panel_floats = 0;
     unsigned long long *d_topk = nullptr; int *d_topk_size = nullptr; size_t topk_cap = 0, topk_q = 0;
@@ -577,11 +578,14 @@ extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *
     if (smem > 200 * 1024) return fail(h, MUNINN_CUDA_E_ARG, "ef=%d with dim=%d needs %zu B of shared memory per query (limit 200 KiB)", ef, h->dim, smem);
     CK(h, cudaSetDevice(h->device));
 
-    int occ = 0;
-    cudaError_t oe = h->metric == MUNINN_METRIC_L2       ? occupancy_of<METRIC_L2>(&occ, smem, h->ld, h->dim)
-                     : h->metric == MUNINN_METRIC_COSINE ? occupancy_of<METRIC_COSINE>(&occ, smem, h->ld, h->dim)
-                                                         : occupancy_of<METRIC_IP>(&occ, smem, h->ld, h->dim);
-    CK(h, oe);
+    int occ = h->occ_val;
+    if (smem != h->occ_smem) { /* the occupancy query costs microseconds: once per (ef, index shape) */
+        cudaError_t oe = h->metric == MUNINN_METRIC_L2       ? occupancy_of<METRIC_L2>(&occ, smem, h->ld, h->dim)
+                         : h->metric == MUNINN_METRIC_COSINE ? occupancy_of<METRIC_COSINE>(&occ, smem, h->ld, h->dim)
+                                                             : occupancy_of<METRIC_IP>(&occ, smem, h->ld, h->dim);
+        CK(h, oe);
+        h->occ_smem = smem; h->occ_val = occ;
+    }
     if (occ < 1) return fail(h, MUNINN_CUDA_E_CUDA, "search kernel does not fit on an SM");
     int tps = h->teams_per_sm > 0 ? std::min(h->teams_per_sm, occ) : occ;
     int teams[3];
@@ -660,6 +664,29 @@ extern "C" int muninn_cuda_search_batch(MuninnCudaIndex *h, const float *queries
     float *dq = (float *)b; int64_t *di = (int64_t *)(b + bq); float *dd = (float *)(b + bq + bi);
     int32_t *dc = (int32_t *)(b + bq + bi + bd);
     MuninnSearchStats *ds = out_stats ? (MuninnSearchStats *)(b + bq + bi + bd + bc) : nullptr;
+    /* small batches (the vtab's one query per statement): the call is latency, not bandwidth — stage through one
+     * pinned buffer so that the results come back with ONE device→host copy instead of three pageable ones */
+    const size_t out_bytes = bi + bd + bc, in_bytes = (size_t)nq * h->dim * 4;
+    const bool tiny = !out_stats && in_bytes + out_bytes <= 64 * 1024;
+    if (tiny && h->pinned_bytes < 128 * 1024) {
+        if (h->h_pinned) { cudaFreeHost(h->h_pinned); h->h_pinned = nullptr; h->pinned_bytes = 0; }
+        if (cudaMallocHost(&h->h_pinned, 128 * 1024) == cudaSuccess) h->pinned_bytes = 128 * 1024;
+        else cudaGetLastError();
+    }
+    if (tiny && h->pinned_bytes >= 128 * 1024) {
+        char *pin = (char *)h->h_pinned;
+        memcpy(pin, queries, in_bytes);
+        CK(h, cudaMemcpyAsync(dq, pin, in_bytes, cudaMemcpyHostToDevice, h->stream));
+        rc = muninn_cuda_search_batch_device(h, dq, nq, k, ef, di, dd, dc, nullptr);
+        if (rc) return rc;
+        char *res = pin + 64 * 1024;
+        CK(h, cudaMemcpyAsync(res, b + bq, out_bytes, cudaMemcpyDeviceToHost, h->stream));
+        CK(h, cudaStreamSynchronize(h->stream));
+        memcpy(out_ids, res, (size_t)nq * k * 8);
+        memcpy(out_dist, res + bi, (size_t)nq * k * 4);
+        memcpy(out_count, res + bi + bd, (size_t)nq * 4);
+        return MUNINN_CUDA_OK;
+    }
     CK(h, cudaMemcpyAsync(dq, queries, (size_t)nq * h->dim * 4, cudaMemcpyHostToDevice, h->stream));
     rc = muninn_cuda_search_batch_device(h, dq, nq, k, ef, di, dd, dc, ds);
     if (rc) return rc;
