@@ -152,6 +152,7 @@ struct FilterParams {
     int dbg_ld;
 };
 
+constexpr int SBUF = 16; /* survivors an epilogue thread parks in shared memory before one atomic appends them */
 template <int NPASS, int BN>
 struct FilterCfg {
     static constexpr int SLABS = NPASS == 3 ? 2 : 1;
@@ -159,8 +160,8 @@ struct FilterCfg {
     static constexpr int STAGE_BYTES = SLABS * (A_BYTES + B_BYTES);
     static constexpr int NSTAGES = (200 * 1024) / STAGE_BYTES > 8 ? 8 : (200 * 1024) / STAGE_BYTES;
     static constexpr int TMEM_COLS = 2 * BN;
-    /* stages | xaux[2][BN] | barriers (2·NSTAGES + 4) | tmem pointer ; + 1024 alignment slack */
-    static constexpr size_t SMEM_BYTES = 1024 + (size_t)NSTAGES * STAGE_BYTES + 2 * BN * 4 + (2 * NSTAGES + 4) * 8 + 16;
+    /* stages | xaux[2][BN] | barriers (2·NSTAGES + 4) | tmem pointer | sbuf[128][SBUF] ; + 1024 alignment slack */
+    static constexpr size_t SMEM_BYTES = 1024 + (size_t)NSTAGES * STAGE_BYTES + 2 * BN * 4 + (2 * NSTAGES + 4) * 8 + 16 + 128 * SBUF * 4;
 };
 
 template <int METRIC, int NPASS, int BN, bool DBG>
@@ -180,6 +181,7 @@ exact_tc_filter(const __grid_constant__ CUtensorMap tm_qhi, const __grid_constan
     uint64_t *tmem_full = empty + NST;
     uint64_t *tmem_empty = tmem_full + 2;
     uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(tmem_empty + 2);
+    int *sbuf = reinterpret_cast<int *>(tmem_ptr + 4); /* [128 epilogue threads × SBUF] parked survivors */
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_qt = (p.nq + BM - 1) / BM, n_xt = (p.rows + BN - 1) / BN;
@@ -284,11 +286,21 @@ exact_tc_filter(const __grid_constant__ CUtensorMap tm_qhi, const __grid_constan
         float qa = 0.0f;
         bool qvalid = false;
         int q = 0;
+        int *mybuf = sbuf + et * SBUF;
+        int nbuf = 0;
+        auto flush = [&]() { /* this thread's parked survivors → the list of query q */
+            if (nbuf == 0) return;
+            const int pos = atomicAdd(p.cand_count + q, nbuf);
+            for (int i = 0; i < nbuf; i++)
+                if (pos + i < p.cand_cap) p.cand[(size_t)q * p.cand_cap + pos + i] = mybuf[i];
+            nbuf = 0;
+        };
         for (long long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
             const int xt = (int)(t / n_qt), qt = (int)(t % n_qt);
             const int ncols = p.rows - xt * BN < BN ? p.rows - xt * BN : BN;
             const long long xrow0 = p.row0 + (long long)xt * BN;
             if (qt != qt_have) {
+                flush(); /* the list belongs to the query this thread served so far */
                 qt_have = qt;
                 q = qt * BM + qrow;
                 qvalid = q < p.nq;
@@ -339,11 +351,15 @@ exact_tc_filter(const __grid_constant__ CUtensorMap tm_qhi, const __grid_constan
                 }
                 if (ncols - c0 < 32) keep &= (1u << (ncols - c0)) - 1u;
                 if (!qvalid) keep = 0;
-                while (keep) { /* rare: ≈ k survivors per query per chunk */
+                /* Survivors are rare per pair (≈ 0.1 %) but not per warp-step (32 queries × 32 rows): appending each
+                 * with its own atomic made most steps wait for an L2 round trip — that, not the compares, was the whole
+                 * cost of this epilogue (0.27 of 0.76 ms at 6.25M×128, nq=100). They are parked in a per-thread
+                 * shared-memory list instead and appended SBUF at a time with one atomic. */
+                while (keep) {
                     const int j = __ffs(keep) - 1;
                     keep &= keep - 1;
-                    const int pos = atomicAdd(p.cand_count + q, 1);
-                    if (pos < p.cand_cap) p.cand[(size_t)q * p.cand_cap + pos] = (int)(xrow0 + c0 + j);
+                    mybuf[nbuf++] = (int)(xrow0 + c0 + j);
+                    if (nbuf == SBUF) flush();
                 }
             };
             uint32_t va[32], vb[32];
@@ -364,6 +380,7 @@ exact_tc_filter(const __grid_constant__ CUtensorMap tm_qhi, const __grid_constan
             if (lane == 0) mbar_arrive(&tmem_empty[a]);
             if (++a == 2) { a = 0; aph ^= 1; }
         }
+        flush();
     }
     tc_fence_before();
     __syncthreads();
