@@ -297,11 +297,11 @@ def exact_summary(args, nq: int, total_ms: float, st: dict, n_rows: int | None =
 
 def ncu_traffic(args, ef):
     """dram__bytes_read.sum + dram__bytes_write.sum of ONE level-0 search launch, from the `ncu --set full` capture
-    of this command summarised in profiles/r1_search_kernel_v6_ncu_full.txt (6.818 GB + 0.281 GB; algorithmic bytes
+    of this command summarised in profiles/r1_search_kernel_v7_ncu_full.txt (6.812 GB + 0.284 GB; algorithmic bytes
     of the same launch: 8.472 GB — the 58 MB visited arena leaves the rest of the 126 MB L2 to the hot rows and lists,
     so DRAM moves 0.84x of the algorithmic bytes). Only the captured configuration has a number."""
     if (args.config, args.n, args.nq, ef) == (2, 1_000_000, 10_000, 64):
-        return 7.099e9
+        return 7.096e9
     return None
 
 
@@ -406,22 +406,22 @@ def run_gpu_arm(args, rank: int, local_rank: int, world: int) -> None:
     clocks.start()
     launches0 = idx.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    kernel_ms = []
+    # the search kernel's own launch duration, live, inside the timed region: one event pair per step on the
+    # launching stream (recording is asynchronous; the pairs are read after the final synchronize). A pair spans the
+    # level-0 launch and the two retry-level launches that exit at once.
+    step_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     torch.cuda.synchronize()
     e0.record(stream)
-    for _ in range(args.steps):
+    for a, b in step_ev:
+        a.record(stream)
         search_dev(ef)
-        if args.per_step_kernel_time:
-            kernel_ms.append(idx.last_kernel_ms())
+        b.record(stream)
     e1.record(stream)
     torch.cuda.synchronize()
     barrier()
     total_ms = e0.elapsed_time(e1)
     launches = idx.launch_count() - launches0
-    if not kernel_ms:  # one extra untimed step measures the kernel's own duration live
-        for _ in range(3):
-            search_dev(ef)
-            kernel_ms.append(idx.last_kernel_ms())
+    kernel_ms = [a.elapsed_time(b) for a, b in step_ev]
     # ── end-to-end: host (pinned) buffers through muninn_cuda_search_batch ──
     h_ids = torch.empty((nq, k), dtype=torch.int64).pin_memory()
     h_dist = torch.empty((nq, k), dtype=torch.float32).pin_memory()
@@ -631,7 +631,7 @@ def main():
     ap.add_argument("--teams-per-sm", type=int, default=0)
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--per-step-kernel-time", action="store_true")
+    ap.add_argument("--per-step-kernel-time", action="store_true", help="kept for compatibility: per-step event pairs are always recorded")
     ap.add_argument("--exact-mode", type=int, default=None, help="config 5: 0 cuda-core, 1 3xTF32 (default), 2 1xTF32")
     args = ap.parse_args()
     cfg = CONFIGS[args.config]

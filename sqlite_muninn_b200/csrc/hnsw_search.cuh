@@ -339,6 +339,63 @@ __device__ __forceinline__ unsigned long long l2_evict_last_policy() {
     asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
     return pol;
 }
+/* 0 = one entry per probe (linear probing), 4 / 8 = entries per bucket. Measured at config 2 (kernel ms at ef 64 / 128 /
+ * 256): linear 1.625 / 3.23 / 7.07, 8-entry 1.616 / 3.42 / 7.55 (fewer round trips but twice the loads and compares: a
+ * loss once the merge makes the kernel issue-bound), 4-entry 1.532 / 3.06 / 6.74 — one 16-byte load, the best everywhere. */
+#ifndef MUNINN_VIS_BUCKET
+#define MUNINN_VIS_BUCKET 4
+#endif
+#if MUNINN_VIS_BUCKET
+/* Bucketised table: a key hashes to a BUCKET of VB (4 or 8) 32-bit entries inside one 32-byte sector, fetched with
+ * 16-byte loads in one L2 round trip. Entries fill a bucket from the front and are never removed, so "found / first
+ * empty slot / full" are all decided from that one fetch; only a full bucket (rare below 3/4 load: a search ends
+ * near 40 %) sends the lane on to the next one. With one entry per probe every call paid ≈ 3.5 dependent round trips
+ * (32 lanes: some lane always collides); this pays ≈ 1. Lanes claiming in the same bucket take consecutive empty
+ * slots in lane order (match.any), no atomics. */
+__device__ __forceinline__ int visited_test_and_set(const SearchParams &p, unsigned *tab, int t, bool valid, int lane,
+                                                    unsigned long long vpol = 0ull) {
+    (void)vpol;
+    constexpr int VB = MUNINN_VIS_BUCKET == 4 ? 4 : 8, VBL = VB == 4 ? 2 : 3;
+    const unsigned bmask = (p.vis_cap >> VBL) - 1;
+    unsigned b = (((unsigned)t * 2654435761u) >> p.vis_shift) >> VBL;
+    bool active = valid;
+    int fresh = 0;
+    while (__any_sync(FULL, active)) {
+        bool claim = false;
+        int first_empty = VB;
+        if (active) {
+            const uint4 *bp = reinterpret_cast<const uint4 *>(tab + ((size_t)b << VBL));
+            unsigned e[VB];
+            {
+                const uint4 e0 = __ldcg(bp);
+                e[0] = e0.x; e[1] = e0.y; e[2] = e0.z; e[3] = e0.w;
+                if (VB == 8) { const uint4 e1 = __ldcg(bp + 1); e[VB - 4] = e1.x; e[VB - 3] = e1.y; e[VB - 2] = e1.z; e[VB - 1] = e1.w; }
+            }
+            bool found = false;
+#pragma unroll
+            for (int i = VB - 1; i >= 0; i--) {
+                found |= e[i] == (unsigned)t;
+                if (e[i] == VIS_EMPTY) first_empty = i;
+            }
+            if (found) active = false;            /* already visited */
+            else if (first_empty == VB) b = (b + 1) & bmask; /* full: the key, if present, lives further on */
+            else claim = true;
+        }
+        const unsigned cm = __ballot_sync(FULL, claim);
+        if (claim) {
+            const unsigned peers = __match_any_sync(cm, b);
+            const int slot = first_empty + __popc(peers & ((1u << lane) - 1));
+            if (slot < VB) {
+                __stcg(tab + ((size_t)b << VBL) + slot, (unsigned)t);
+                fresh = 1;
+                active = false;
+            } else b = (b + 1) & bmask; /* the bucket filled up under this very call */
+        }
+        __syncwarp();
+    }
+    return fresh;
+}
+#else
 __device__ __forceinline__ int visited_test_and_set(const SearchParams &p, unsigned *tab, int t, bool valid, int lane,
                                                     unsigned long long vpol = 0ull) {
     unsigned h = ((unsigned)t * 2654435761u) >> p.vis_shift;
@@ -366,6 +423,8 @@ __device__ __forceinline__ int visited_test_and_set(const SearchParams &p, unsig
     }
     return fresh;
 }
+
+#endif
 
 __device__ __forceinline__ void visited_clear(unsigned *tab, unsigned cap, int lane) {
     uint4 *t4 = reinterpret_cast<uint4 *>(tab);
