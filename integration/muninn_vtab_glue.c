@@ -26,6 +26,7 @@
 #include "muninn_cuda.h"
 #include "sqlite3ext.h"
 
+#include <pthread.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -45,21 +46,32 @@ typedef struct {
     int64_t n_patches, n_uploads; /* counters for the tests */
 } GlueSlot;
 
-static GlueSlot *g_slots;
+/* One heap-allocated slot per HnswIndex, found by pointer. The table itself is guarded by a mutex: connections on
+ * different threads create and drop their indexes concurrently. A slot is only ever used by the connection that owns
+ * its index (SQLite serialises the calls into one vtab), so the slot's fields need no lock of their own. */
+static GlueSlot **g_slots;
 static int g_nslots, g_capslots;
+static pthread_mutex_t g_lock = PTHREAD_MUTEX_INITIALIZER;
 
 static GlueSlot *slot_find(const HnswIndex *index, int create) {
+    GlueSlot *s = NULL;
+    pthread_mutex_lock(&g_lock);
     for (int i = 0; i < g_nslots; i++)
-        if (g_slots[i].index == index) return &g_slots[i];
-    if (!create) return NULL;
-    if (g_nslots == g_capslots) {
-        int nc = g_capslots ? 2 * g_capslots : 8;
-        GlueSlot *ns = (GlueSlot *)realloc(g_slots, (size_t)nc * sizeof(GlueSlot));
-        if (!ns) return NULL;
-        g_slots = ns; g_capslots = nc;
+        if (g_slots[i]->index == index) { s = g_slots[i]; break; }
+    if (!s && create) {
+        if (g_nslots == g_capslots) {
+            int nc = g_capslots ? 2 * g_capslots : 8;
+            GlueSlot **ns = (GlueSlot **)realloc(g_slots, (size_t)nc * sizeof(GlueSlot *));
+            if (ns) { g_slots = ns; g_capslots = nc; }
+        }
+        if (g_nslots < g_capslots && (s = (GlueSlot *)calloc(1, sizeof(GlueSlot))) != NULL) {
+            s->index = index;
+            s->dirty = 1;
+            g_slots[g_nslots++] = s;
+        }
     }
-    g_slots[g_nslots] = (GlueSlot){index, NULL, 1, NULL, 0, 0, NULL, 0, 0, 0, 0, 0};
-    return &g_slots[g_nslots++];
+    pthread_mutex_unlock(&g_lock);
+    return s;
 }
 
 static int cmp_i64(const void *a, const void *b) {
@@ -117,16 +129,20 @@ void muninn_glue_note_insert(const HnswIndex *index, int64_t id) {
 void muninn_glue_note_delete(const HnswIndex *index, int64_t id) { note_node_and_neighbours(index, id); }
 
 /* process-wide counters (the tests read them through the loaded extension with ctypes) */
-static int64_t g_total_patches, g_total_uploads;
+static int64_t g_total_patches, g_total_uploads; /* updated atomically */
 int64_t muninn_glue_total_patches(void) { return g_total_patches; }
 int64_t muninn_glue_total_uploads(void) { return g_total_uploads; }
 
 void muninn_glue_release(const HnswIndex *index) {
-    GlueSlot *s = slot_find(index, 0);
+    GlueSlot *s = NULL;
+    pthread_mutex_lock(&g_lock);
+    for (int i = 0; i < g_nslots; i++)
+        if (g_slots[i]->index == index) { s = g_slots[i]; g_slots[i] = g_slots[--g_nslots]; break; }
+    pthread_mutex_unlock(&g_lock);
     if (!s) return;
-    muninn_cuda_index_destroy(s->handle);
+    if (s->handle) muninn_cuda_index_destroy(s->handle);
     free(s->ids); free(s->pend);
-    *s = g_slots[--g_nslots];
+    free(s);
 }
 
 /* host HnswIndex → the flat arrays of muninn_cuda_index_upload */
@@ -178,7 +194,7 @@ static int glue_upload(GlueSlot *s, char **err) {
     if (rc == MUNINN_CUDA_OK) {
         free(s->ids);
         s->ids = ids; s->n = n; s->cap = n + 1; s->max_id = n ? ids[n - 1] : 0;
-        s->dirty = 0; s->npend = 0; s->n_uploads++; g_total_uploads++;
+        s->dirty = 0; s->npend = 0; s->n_uploads++; __atomic_add_fetch(&g_total_uploads, 1, __ATOMIC_RELAXED);
     } else free(ids);
     return rc;
 }
@@ -242,7 +258,7 @@ static int glue_patch(GlueSlot *s) {
     }
     free(slots); free(levels); free(deleted); free(vecs); free(offs); free(tg);
     if (getenv("MUNINN_GLUE_TRACE")) fprintf(stderr, "muninn_glue: patch of %lld records (%lld new) -> rc %d\n", (long long)np, (long long)n_new, rc);
-    if (rc == MUNINN_CUDA_OK) { s->n = n_total; s->npend = 0; s->n_patches++; g_total_patches++; }
+    if (rc == MUNINN_CUDA_OK) { s->n = n_total; s->npend = 0; s->n_patches++; __atomic_add_fetch(&g_total_patches, 1, __ATOMIC_RELAXED); }
     return rc;
 }
 

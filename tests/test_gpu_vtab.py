@@ -257,6 +257,40 @@ def test_er_blocking_stage_through_the_batch_tvf(exts, tmp_path):
         c.close()
 
 
+def test_vtab_connections_on_several_threads(exts, tmp_path):
+    """Each thread owns a connection and a table (the reference's supported threading model); the glue's handle
+    table is shared by all of them. Concurrent create / insert / search / drop must give every thread the answers
+    a single-threaded run gives."""
+    import threading
+    base, q = uniform(71, 4 * 150, 8), uniform(72, 30, 8)
+
+    def work(t, ext, out):
+        c = connect(str(tmp_path / f"th{t}_{os.path.basename(ext)}.db"), ext)
+        c.execute("CREATE VIRTUAL TABLE t USING hnsw_index(dimensions=8, metric='l2', m=6, ef_construction=40)")
+        rows = []
+        for i, v in enumerate(base[t * 150:(t + 1) * 150]):
+            c.execute("INSERT INTO t (rowid, vector) VALUES (?, ?)", (i + 1, v.tobytes()))
+            if i % 10 == 9:
+                rows.append(knn(c, q[i % 30], 5))
+        rows += [knn(c, qq, 8, 40) for qq in q]
+        c.execute("DROP TABLE t")
+        c.close()
+        out[t] = rows
+
+    got, want = {}, {}
+    threads = [threading.Thread(target=work, args=(t, exts[0], got)) for t in range(4)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    for t in range(4):
+        work(t, exts[1] if exts[1] else exts[0], want)
+    assert set(got) == {0, 1, 2, 3}
+    for t in range(4):
+        assert len(got[t]) == len(want[t])
+        assert all(same_rows(a, b) for a, b in zip(got[t], want[t])), t
+
+
 def test_vtab_errors_and_drop(exts, tmp_path):
     conn = connect(str(tmp_path / "e.db"), exts[0])
     conn.execute("CREATE VIRTUAL TABLE t USING hnsw_index(dimensions=3, metric='l2')")
