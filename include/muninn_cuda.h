@@ -108,6 +108,8 @@ int muninn_cuda_index_upload(MuninnCudaIndex *idx, int64_t n, const int64_t *ids
  *   entry_slot, max_level   the index's after the change
  * References to a newly deleted slot become holes in every list of the device copy, as upload stores them.
  * Synchronous. A search after the patch returns exactly what it would after a full upload of the new state.
+ * Every record is validated before anything is changed: a patch the library refuses (MUNINN_CUDA_E_ARG) leaves the
+ * handle answering as before. A CUDA failure half-way leaves it unusable until the next muninn_cuda_index_upload.
  */
 int muninn_cuda_index_patch(MuninnCudaIndex *idx, int64_t n_total, int32_t n_patch, const int32_t *slots, const int64_t *ids,
                             const int32_t *levels, const uint8_t *deleted, const float *vectors, const int64_t *list_offsets,
