@@ -568,14 +568,15 @@ exact_tc_rerank(const float *__restrict__ vec, const float *__restrict__ norm2, 
     }
 }
 
-/* Small batches (the HBM-bound regime, nq < 1024): ONE CTA of 8 warps per query instead of one warp. The
+/* Small batches (the HBM-bound regime, nq < 1024): ONE CTA of 16 warps per query instead of one warp. The
  * survivors' exact distances are computed by all warps at once (256 rows in flight per query), the keys that
  * beat the current k-th best are appended to the query's sorted list in shared memory and the union is put in
  * order: a radix select finds the k-th smallest distance, the keys up to it are sorted bitonically — the k smallest
  * keys of R ∪ survivors, the same set in the same (distance, row) order as the warp kernel's sequence of merges.
- * smem: A[P_alloc] | B[P_alloc], P_alloc = pow2 ≥ k + cap. */
+ * smem: A[P_alloc] keys | query | 16 warps × 16-row tiles (re-used for the compacted keys) ; P_alloc = pow2 ≥ k + cap. */
+constexpr int RR_WARPS = 16, RR_THREADS = RR_WARPS * 32; /* warps of the CTA-per-query re-rank */
 template <int METRIC>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(RR_THREADS)
 exact_tc_rerank_cta(const float *__restrict__ vec, const float *__restrict__ norm2, const uint8_t *__restrict__ deleted, int ld,
                     int dim, const float *__restrict__ queries, int nq, int k, const int *__restrict__ cand,
                     int *__restrict__ cand_count, int cap, unsigned long long *__restrict__ topk, int *__restrict__ topk_size,
@@ -583,13 +584,14 @@ exact_tc_rerank_cta(const float *__restrict__ vec, const float *__restrict__ nor
     extern __shared__ __align__(16) unsigned char smem_raw[];
     unsigned long long *A = reinterpret_cast<unsigned long long *>(smem_raw);
     __shared__ int s_fill, s_hist[256], s_sel[2];
+    constexpr int NT = RR_THREADS, NW = RR_WARPS;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, q = blockIdx.x;
     if (q >= nq) return;
     int cnt = cand_count[q];
     if (cnt > cap) { if (threadIdx.x == 0) overflow[q] = 1; cnt = cap; }
     if (cnt <= 0) return; /* block-uniform */
     const int size = topk_size[q];
-    for (int i = threadIdx.x; i < size; i += 256) A[i] = topk[(size_t)q * k + i];
+    for (int i = threadIdx.x; i < size; i += NT) A[i] = topk[(size_t)q * k + i];
     if (threadIdx.x == 0) s_fill = size;
     __syncthreads();
     const unsigned long long worst = size >= k ? A[k - 1] : KEY_NONE;
@@ -598,22 +600,24 @@ exact_tc_rerank_cta(const float *__restrict__ vec, const float *__restrict__ nor
     SearchParams sp;
     sp.vec = vec; sp.norm2 = norm2; sp.ld = ld; sp.dim = dim;
     TeamSmem sm;
+    unsigned char *tiles;
     {
-        unsigned char *b = smem_raw + (size_t)2 * P_alloc * 8;
+        unsigned char *b = smem_raw + (size_t)P_alloc * 8;
         sm.q = reinterpret_cast<float *>(b); b += ((size_t)ld * 4 + 15) / 16 * 16;
-        sm.P = reinterpret_cast<float *>(b) + (size_t)wib * 16 * PSTRIDE; b += (size_t)8 * 16 * PSTRIDE * 4;
-        sm.Fs = reinterpret_cast<int *>(b) + wib * 16; b += 8 * 16 * 4;
+        tiles = b;
+        sm.P = reinterpret_cast<float *>(b) + (size_t)wib * 16 * PSTRIDE; b += (size_t)NW * 16 * PSTRIDE * 4;
+        sm.Fs = reinterpret_cast<int *>(b) + wib * 16; b += NW * 16 * 4;
         sm.bar = reinterpret_cast<unsigned long long *>(b) + wib;
         sm.phase = 0u;
         sm.R = sm.Fk = sm.S = nullptr;
     }
-    for (int i = threadIdx.x; i < ld; i += 256) sm.q[i] = i < dim ? queries[(size_t)q * dim + i] : 0.0f;
+    for (int i = threadIdx.x; i < ld; i += NT) sm.q[i] = i < dim ? queries[(size_t)q * dim + i] : 0.0f;
     if (lane == 0) bar_init(sm.bar, 1);
     __syncthreads();
     float qn2 = 0.0f;
     if (METRIC == METRIC_COSINE) qn2 = query_norm2(sm.q, dim);
     const unsigned long long pol = l2_evict_first_policy();
-    for (int c0 = wib * 16; c0 < cnt; c0 += 8 * 16) {
+    for (int c0 = wib * 16; c0 < cnt; c0 += NW * 16) {
         const int nb = cnt - c0 < 16 ? cnt - c0 : 16;
         if (lane < nb) sm.Fs[lane] = cand[(size_t)q * cap + c0 + lane];
         __syncwarp();
@@ -644,9 +648,9 @@ exact_tc_rerank_cta(const float *__restrict__ vec, const float *__restrict__ nor
             int want = k;
             for (int pass = 3; pass >= 0; pass--) {
                 const int shift = 8 * pass;
-                s_hist[threadIdx.x] = 0;
+                if (threadIdx.x < 256) s_hist[threadIdx.x] = 0;
                 __syncthreads();
-                for (int i0 = 0; i0 < total; i0 += 256) {
+                for (int i0 = 0; i0 < total; i0 += NT) {
                     const int i = i0 + threadIdx.x;
                     unsigned hi = 0;
                     bool in = i < total;
@@ -684,8 +688,9 @@ exact_tc_rerank_cta(const float *__restrict__ vec, const float *__restrict__ nor
             }
             if (threadIdx.x == 0) s_fill = 0;
             __syncthreads();
-            unsigned long long *B = A + P_alloc;
-            for (int i = threadIdx.x; i < total; i += 256) {
+            /* the row tiles are idle now (every warp has waited for its last copy): they hold the compacted keys */
+            unsigned long long *B = reinterpret_cast<unsigned long long *>(tiles);
+            for (int i = threadIdx.x; i < total; i += NT) {
                 const unsigned long long e = A[i];
                 if ((unsigned)(e >> 32) <= prefix) B[atomicAdd(&s_fill, 1)] = e;
             }
@@ -695,11 +700,11 @@ exact_tc_rerank_cta(const float *__restrict__ vec, const float *__restrict__ nor
         }
         int P = 64;
         while (P < m) P <<= 1;
-        for (int i = m + threadIdx.x; i < P; i += 256) srt[i] = KEY_NONE;
+        for (int i = m + threadIdx.x; i < P; i += NT) srt[i] = KEY_NONE;
         __syncthreads();
         for (int kk = 2; kk <= P; kk <<= 1)
             for (int j = kk >> 1; j > 0; j >>= 1) {
-                for (int i = threadIdx.x; i < P; i += 256) {
+                for (int i = threadIdx.x; i < P; i += NT) {
                     const int ixj = i ^ j;
                     if (ixj > i) {
                         const unsigned long long x = srt[i], y = srt[ixj];
@@ -711,7 +716,7 @@ exact_tc_rerank_cta(const float *__restrict__ vec, const float *__restrict__ nor
             }
     }
     const int nsize = total < k ? total : k;
-    for (int i = threadIdx.x; i < nsize; i += 256) topk[(size_t)q * k + i] = srt[i];
+    for (int i = threadIdx.x; i < nsize; i += NT) topk[(size_t)q * k + i] = srt[i];
     if (threadIdx.x == 0) {
         topk_size[q] = nsize;
         if (nsize >= k) tau[q] = okey_inv((unsigned)(srt[k - 1] >> 32));

@@ -843,7 +843,7 @@ static int exact_knn_tc(MuninnCudaIndex *h, const float *d_queries, int nq, int 
     const bool raw_x = !three; /* 1xTF32: the MMA reads the fp32 rows as they are (it drops the low 13 bits) */
     /* small batches are HBM- and launch-bound: larger survivor lists (re-ranked by a CTA per query) allow ×17..32
      * chunk growth, i.e. 4-5 chunks instead of 9 over millions of rows */
-    const bool small = !d_dbg && nq < 1024 && k <= 512 && h->ld <= 4096; /* the CTA re-rank's shared memory: 128 KB of keys + 68 KB of row tiles + the query */
+    const bool small = !d_dbg && nq < 1024 && k <= 512 && h->ld <= 4096; /* the CTA re-rank's shared memory: 64 KB of keys + 132 KB of row tiles + the query */
     const int cap = d_dbg ? 256 : small ? 4096 : std::max(1024, (4 * k + 255) / 256 * 256);
     const int grow_c = small ? std::min(31, std::max(3, 2 * cap / (5 * k))) : 3; /* expected survivors per chunk ≈ grow_c·k */
     const long long n = d_dbg ? dbg_rows : h->n;
@@ -890,7 +890,9 @@ static int exact_knn_tc(MuninnCudaIndex *h, const float *d_queries, int nq, int 
     if (small) {
         size_t P = 64;
         while (P < (size_t)k + cap) P <<= 1;
-        rr_smem = 2 * P * 8 + ((size_t)h->ld * 4 + 15) / 16 * 16 + (size_t)8 * 16 * PSTRIDE * 4 + 8 * 16 * 4 + 8 * 8;
+        rr_smem = P * 8 + ((size_t)h->ld * 4 + 15) / 16 * 16 + (size_t)tc::RR_WARPS * 16 * PSTRIDE * 4 + tc::RR_WARPS * 16 * 4 + tc::RR_WARPS * 8;
+        /* the compacted keys re-use the tile region: P entries must fit (8192 × 8 B ≤ 16 × 16 × 528 B) */
+        static_assert((size_t)8192 * 8 <= (size_t)tc::RR_WARPS * 16 * PSTRIDE * 4, "re-rank tiles too small for the key buffer");
         rr_P = (int)P;
         CK(h, cudaFuncSetAttribute(tc::exact_tc_rerank_cta<METRIC_L2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rr_smem));
         CK(h, cudaFuncSetAttribute(tc::exact_tc_rerank_cta<METRIC_COSINE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rr_smem));
@@ -942,11 +944,11 @@ static int exact_knn_tc(MuninnCudaIndex *h, const float *d_queries, int nq, int 
         const int rr_grid = (nq + 3) / 4;
         if (small) {
             if (h->metric == MUNINN_METRIC_L2)
-                tc::exact_tc_rerank_cta<METRIC_L2><<<nq, 256, rr_smem, st>>>(h->d_vec, h->d_norm2, h->d_deleted, h->ld, h->dim, d_queries, nq, k, h->d_cand, h->d_cand_count, cap, h->d_topk, h->d_topk_size, h->d_tau, h->d_overflow, h->d_tc_ctr, rr_P);
+                tc::exact_tc_rerank_cta<METRIC_L2><<<nq, tc::RR_THREADS, rr_smem, st>>>(h->d_vec, h->d_norm2, h->d_deleted, h->ld, h->dim, d_queries, nq, k, h->d_cand, h->d_cand_count, cap, h->d_topk, h->d_topk_size, h->d_tau, h->d_overflow, h->d_tc_ctr, rr_P);
             else if (h->metric == MUNINN_METRIC_COSINE)
-                tc::exact_tc_rerank_cta<METRIC_COSINE><<<nq, 256, rr_smem, st>>>(h->d_vec, h->d_norm2, h->d_deleted, h->ld, h->dim, d_queries, nq, k, h->d_cand, h->d_cand_count, cap, h->d_topk, h->d_topk_size, h->d_tau, h->d_overflow, h->d_tc_ctr, rr_P);
+                tc::exact_tc_rerank_cta<METRIC_COSINE><<<nq, tc::RR_THREADS, rr_smem, st>>>(h->d_vec, h->d_norm2, h->d_deleted, h->ld, h->dim, d_queries, nq, k, h->d_cand, h->d_cand_count, cap, h->d_topk, h->d_topk_size, h->d_tau, h->d_overflow, h->d_tc_ctr, rr_P);
             else
-                tc::exact_tc_rerank_cta<METRIC_IP><<<nq, 256, rr_smem, st>>>(h->d_vec, h->d_norm2, h->d_deleted, h->ld, h->dim, d_queries, nq, k, h->d_cand, h->d_cand_count, cap, h->d_topk, h->d_topk_size, h->d_tau, h->d_overflow, h->d_tc_ctr, rr_P);
+                tc::exact_tc_rerank_cta<METRIC_IP><<<nq, tc::RR_THREADS, rr_smem, st>>>(h->d_vec, h->d_norm2, h->d_deleted, h->ld, h->dim, d_queries, nq, k, h->d_cand, h->d_cand_count, cap, h->d_topk, h->d_topk_size, h->d_tau, h->d_overflow, h->d_tc_ctr, rr_P);
         } else if (h->metric == MUNINN_METRIC_L2)
             tc::exact_tc_rerank<METRIC_L2><<<rr_grid, 128, rr_smem, st>>>(h->d_vec, h->d_norm2, h->d_deleted, h->ld, h->dim, d_queries, nq, k, h->d_cand, h->d_cand_count, cap, h->d_topk, h->d_topk_size, h->d_tau, h->d_overflow, h->d_tc_ctr);
         else if (h->metric == MUNINN_METRIC_COSINE)
