@@ -83,7 +83,6 @@ def write_shadow(conn: sqlite3.Connection, name: str, g: FlatGraph, with_distanc
     cur.execute(f'CREATE TABLE IF NOT EXISTS "{name}_edges" (source_id INTEGER NOT NULL, target_id INTEGER NOT NULL, '
                 f'level INTEGER NOT NULL, distance REAL NOT NULL, PRIMARY KEY (source_id, level, target_id)) '
                 f'WITHOUT ROWID')
-    cur.execute(f'CREATE INDEX IF NOT EXISTS "{name}_edges_rev" ON "{name}_edges"(target_id, level)')
     entry_id = int(g.ids[g.entry_slot]) if g.entry_slot >= 0 else -1
     cur.executemany(f'INSERT OR REPLACE INTO "{name}_config" (key, value) VALUES (?, ?)',
                     [("dimensions", str(g.dim)), ("metric", str(g.metric)), ("m", str(g.M)),
@@ -92,22 +91,25 @@ def write_shadow(conn: sqlite3.Connection, name: str, g: FlatGraph, with_distanc
     cur.executemany(f'INSERT INTO "{name}_nodes" (id, vector, level, deleted) VALUES (?, ?, ?, ?)',
                     ((int(g.ids[s]), g.vectors[s].tobytes(), int(g.levels[s]), int(g.deleted[s]))
                      for s in range(g.n)))
+    # edge rows in bulk: list index → (source slot, level) with numpy, one executemany over plain Python lists
+    # (a per-edge Python loop costs minutes at 1M × 32 edges)
+    n_lists = len(g.list_offsets) - 1
+    counts = np.diff(g.list_offsets).astype(np.int64)
     first = g.first_list()
-
-    def edge_rows():
-        for s in range(g.n):
-            for l in range(int(g.levels[s]) + 1):
-                li = int(first[s]) + l
-                for e in range(int(g.list_offsets[li]), int(g.list_offsets[li + 1])):
-                    t = int(g.targets[e])
-                    if t < 0:
-                        continue
-                    d = 0.0
-                    if with_distance:
-                        diff = g.vectors[s] - g.vectors[t]
-                        d = float(np.dot(diff, diff))
-                    yield (int(g.ids[s]), int(g.ids[t]), l, d)
-
+    list_src = np.repeat(np.arange(g.n, dtype=np.int64), g.levels.astype(np.int64) + 1)
+    list_lvl = np.arange(n_lists, dtype=np.int64) - first[list_src]
+    e_src = np.repeat(list_src, counts)
+    e_lvl = np.repeat(list_lvl, counts)
+    e_tgt = g.targets.astype(np.int64)
+    keep = e_tgt >= 0
+    e_src, e_lvl, e_tgt = e_src[keep], e_lvl[keep], e_tgt[keep]
+    if with_distance:
+        diff = g.vectors[e_src] - g.vectors[e_tgt]
+        dist = np.einsum("ij,ij->i", diff, diff).astype(np.float64).tolist()
+    else:
+        dist = [0.0] * int(e_src.shape[0])
     cur.executemany(f'INSERT INTO "{name}_edges" (source_id, target_id, level, distance) VALUES (?, ?, ?, ?)',
-                    edge_rows())
+                    zip(g.ids[e_src].tolist(), g.ids[e_tgt].tolist(), e_lvl.tolist(), dist))
+    # the reverse index (src/hnsw_vtab.c:177) is built once over the finished table, not row by row
+    cur.execute(f'CREATE INDEX IF NOT EXISTS "{name}_edges_rev" ON "{name}_edges"(target_id, level)')
     conn.commit()
