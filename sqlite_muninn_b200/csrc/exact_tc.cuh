@@ -17,11 +17,18 @@
  *                 Fused per-tile selection in the epilogue: thread = one query (one TMEM lane);
  *                 a row survives unless its approximate distance provably exceeds the query's
  *                 current k-th exact distance τ_q:   d̃ > τ_q + ε(q, x).
- *   3. re-rank    one warp per query: reference-order fp32 distance of every survivor, merged into
- *                 the query's sorted (distance, row) list; τ_q ← its k-th entry.
+ *                 Survivors are parked in a per-thread shared-memory list and appended to the
+ *                 query's global list 16 at a time (one atomic per survivor stalled the warp).
+ *                 1xTF32 reads the raw fp32 slab (the MMA drops the low mantissa bits itself): no
+ *                 split pass, the base is read once — the mode of HBM-bound small batches.
+ *   3. re-rank    reference-order fp32 distance of every survivor, k smallest kept as the query's
+ *                 sorted (distance, row) list; τ_q ← its k-th entry. One warp per query for large
+ *                 batches; one CTA of 16 warps per query (TMA-staged rows, radix select) below
+ *                 1 024 queries.
  *
- * The base is processed in chunks whose size doubles (the first chunk is small — max(256, 2k) rows —
- * because every row of it survives, τ being +inf), so each later chunk yields ≈ k survivors per query.
+ * The base is processed in chunks that grow geometrically (×4; ×17–32 for small batches); the first
+ * chunk is small because every row of it survives, τ being +inf. A chunk g times the rows seen so
+ * far yields ≈ g·k survivors per query.
  *
  * Soundness: a row of the true top-k has d_ref ≤ τ_q at all times; with |d̃ − d_ref| ≤ ε it can
  * never satisfy d̃ > τ_q + ε. ε = c·(‖q‖² + ‖x‖²) (L2, inner product) or c (cosine) with

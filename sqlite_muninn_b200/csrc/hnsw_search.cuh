@@ -8,17 +8,19 @@
  *
  * Execution model (B200): a persistent grid of query teams. A team is one warp (one CTA) that
  * pulls query indices from a global counter until the batch is drained, so long and short
- * searches balance across the 148 SMs. Per team, in shared memory: the query, the result list
- * R (ef entries, ascending (distance, slot) 64-bit keys, bit 0 = "expanded"), and a 4 KB
- * staging tile for the distance transposition. Per team, in HBM (L2-resident in practice): an
- * open-addressing visited table of 32-bit slot entries, cleared by the team at the start of each
- * query (a few dozen 16-byte stores).
+ * searches balance across the 148 SMs; 24 teams share an SM at dim ≤ 128. Per team, in shared
+ * memory: the query, the result list R (ef entries, ascending (distance, slot) 64-bit keys,
+ * bit 0 = "expanded"), the fresh-neighbour lists and a row staging tile (13 rows × 528 B for
+ * rows of ≤ 512 B, 16 rows for dim 96 and for wide rows). Per team, in HBM (L2-resident in
+ * practice): a bucketised visited table of 32-bit slot entries, four per 16-byte bucket, cleared
+ * by the team at the start of each query.
  *
- * Distances: for a batch of up to 8 neighbour rows the 32 lanes load one 16-byte chunk of
- * every row each (fully coalesced 512 B per row at dim 128, eight independent 128-bit loads
- * in flight per lane), form the per-component products, and transpose them through shared
- * memory so that lane (n, j) adds chain j of row n in ascending element order — the exact
- * order of the reference's SSE loop — before the fixed ((s0+s1)+s2)+s3 horizontal sum.
+ * Distances: every fresh neighbour row of a batch is brought into the tile by ONE TMA bulk copy
+ * (cp.async.bulk, lane r issues row r, completion on a per-team mbarrier, L2 evict-first hint);
+ * lane (row, h) then walks its row in shared memory and accumulates chains 2h, 2h+1 of the
+ * reference's SSE loop in ascending element order as a packed f32x2 pair (sub / add packed,
+ * multiplies scalar so that nothing is contracted into an FMA), followed by the fixed
+ * ((s0+s1)+s2)+s3 horizontal sum and the scalar tail — bit-identical to src/vec_math.c:78-143.
  *
  * Result-set semantics ("canonical order"): R' = the ef smallest of R ∪ F under
  * (distance, slot); next candidate = smallest unexpanded entry of R. On inputs without
@@ -38,7 +40,7 @@ namespace muninn {
 #define MUNINN_PREFETCH 1
 #endif
 #ifndef MUNINN_RB
-#define MUNINN_RB 0 /* 0 = by row width: 12 rows (24 teams/SM) for one-column-block rows, else 16 */
+#define MUNINN_RB 0 /* 0 = by row width: RB_NARROW rows (24 teams/SM) for one-column-block rows, else 16 */
 #endif
 #ifndef MUNINN_ROW_EVICT_FIRST
 #define MUNINN_ROW_EVICT_FIRST 1 /* gathered rows are streamed: L2 evict-first keeps lists and visited tables resident */
