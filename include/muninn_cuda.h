@@ -103,7 +103,11 @@ int muninn_cuda_index_upload(MuninnCudaIndex *idx, int64_t n, const int64_t *ids
  *                  slots n_old..n_total-1 (otherwise slots shift: re-upload instead)
  *   n_patch        nodes whose record follows; every new node must be among them
  *   slots[n_patch] their slots; ids / levels / deleted / vectors [n_patch × dim]: their records (levels of stored
- *                  nodes cannot change, a deleted node cannot come back)
+ *                  nodes cannot change, a deleted node cannot come back). A stored vector never changes in the
+ *                  reference (no vector update in src/hnsw_algo.c; UPDATE is rejected, src/hnsw_vtab.c:782-783), so
+ *                  only the vectors of NEW nodes are read: vectors[i*dim ..] for a record i of an already stored
+ *                  node need not be addressable (the device-assisted builder puts the new nodes first and passes
+ *                  a pointer into its base array)
  *   list_offsets, targets   their neighbour lists, node-major level-minor, as in muninn_cuda_index_upload
  *   entry_slot, max_level   the index's after the change
  * References to a newly deleted slot become holes in every list of the device copy, as upload stores them.

@@ -39,8 +39,35 @@ def host_lib():
         L.muninn_build_sizes.argtypes = [C.c_void_p] + [C.POINTER(C.c_int64)] * 3 + [C.POINTER(C.c_int32)] * 2
         L.muninn_build_export.argtypes = [C.c_void_p, _i32, _i64, _i32, C.c_int]
         L.muninn_build_destroy.argtypes = [C.c_void_p]
+        # group-at-a-time interface (the device-assisted loop below)
+        L.muninn_build_log_touched.argtypes = [C.c_void_p, C.c_int]
+        L.muninn_build_count.restype = C.c_int64
+        L.muninn_build_count.argtypes = [C.c_void_p]
+        L.muninn_build_group_begin.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+        L.muninn_build_group_levels.argtypes = [C.c_void_p, _i32]
+        L.muninn_build_group_link.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+        L.muninn_build_touched_count.restype = C.c_int64
+        L.muninn_build_touched_count.argtypes = [C.c_void_p]
+        L.muninn_build_touched_take.restype = C.c_int64
+        L.muninn_build_touched_take.argtypes = [C.c_void_p, _i32, C.c_int64]
+        L.muninn_build_export_nodes.argtypes = [C.c_void_p, C.c_int64, _i32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+        L.muninn_build_entry.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
         _lib = L
     return _lib
+
+
+def _export(L, h, n, dim, metric, M, efc, v, ids, sort_lists) -> FlatGraph:
+    nn, nl, ne = C.c_int64(), C.c_int64(), C.c_int64()
+    es, ml = C.c_int32(), C.c_int32()
+    L.muninn_build_sizes(h, C.byref(nn), C.byref(nl), C.byref(ne), C.byref(es), C.byref(ml))
+    n = nn.value
+    levels = np.empty(n, np.int32)
+    offs = np.empty(nl.value + 1, np.int64)
+    tg = np.empty(ne.value, np.int32)
+    L.muninn_build_export(h, levels, offs, tg, 1 if sort_lists else 0)
+    return FlatGraph(dim, metric, M, efc, np.ascontiguousarray(ids[:n]), levels, np.zeros(n, np.uint8), v[:n], offs,
+                     tg, es.value, ml.value)
 
 
 def build_graph(vectors, metric: int = 0, M: int = 16, ef_construction: int = 200, *, ids=None, batch: int = 0,
@@ -64,15 +91,118 @@ def build_graph(vectors, metric: int = 0, M: int = 16, ef_construction: int = 20
             L.muninn_build_seed(h, seed)
         if L.muninn_build_insert(h, n, batch, warm, threads if batch > 0 else 1) != 0:
             raise RuntimeError("muninn_build_insert failed")
-        nn, nl, ne = C.c_int64(), C.c_int64(), C.c_int64()
-        es, ml = C.c_int32(), C.c_int32()
-        L.muninn_build_sizes(h, C.byref(nn), C.byref(nl), C.byref(ne), C.byref(es), C.byref(ml))
-        levels = np.empty(n, np.int32)
-        offs = np.empty(nl.value + 1, np.int64)
-        tg = np.empty(ne.value, np.int32)
-        L.muninn_build_export(h, levels, offs, tg, 1 if sort_lists else 0)
+        ids = np.arange(n, dtype=np.int64) if ids is None else np.ascontiguousarray(ids, np.int64)
+        return _export(L, h, n, dim, metric, M, ef_construction, v, ids, sort_lists)
     finally:
         L.muninn_build_destroy(h)
+
+
+def build_graph_device(vectors, metric: int = 0, M: int = 16, ef_construction: int = 200, *, ids=None,
+                       batch: int = 1024, warm: int = 4096, threads: int | None = None, sort_lists: bool = True,
+                       seed: int | None = None, device: int = 0, index=None, stats: dict | None = None) -> FlatGraph:
+    """Batch-mode construction with the layer-0 candidate searches on the GPU.
+
+    Same group-synchronous rule as `build_graph(batch=...)` (header of csrc/hnsw_build.c), so without bit-equal
+    candidate distances the graph is identical to it. Per group of `batch` nodes:
+
+      1. the host draws the levels (reference generator, src/hnsw_algo.c:19-30, :240-248);
+      2. the level-0 nodes (a fraction 1 - 1/M of them) are searched as ONE `muninn_cuda_search_batch(k = min(2M,
+         efc), ef = efc)` on the device copy of the graph as it stood before the group: for a node of level 0,
+         hnsw_insert's search (src/hnsw_algo.c:553-579) IS hnsw_search with ef = ef_construction, query = its vector;
+      3. the host links the group (upper-level nodes search on the host; reverse edges, MN-RU prune) and logs the
+         nodes whose lists changed;
+      4. those records go back to the device as one `muninn_cuda_index_patch`.
+
+    `index` is the device index to build into: by default an `HnswIndexCuda` on `device` (no CPU path: without a GPU
+    this raises); the tests pass a stand-in with the same three methods (upload / patch_records / search) to check
+    the host logic. Neighbour lists on the device are in insertion order, the order the host builder itself searches.
+    """
+    L = host_lib()
+    v = np.ascontiguousarray(vectors, np.float32)
+    n, dim = v.shape
+    threads = threads or (os.cpu_count() or 1)
     ids = np.arange(n, dtype=np.int64) if ids is None else np.ascontiguousarray(ids, np.int64)
-    return FlatGraph(dim, metric, M, ef_construction, ids, levels, np.zeros(n, np.uint8), v, offs, tg, es.value,
-                     ml.value)
+    assert ids.shape == (n,) and (n < 2 or bool(np.all(np.diff(ids) > 0))), "ids must be strictly ascending"
+    identity_ids = bool(np.array_equal(ids, np.arange(n, dtype=np.int64)))
+    own_index = index is None
+    if own_index:
+        from .cuda import HnswIndexCuda
+        index = HnswIndexCuda(dim, metric, M, device)
+    M0 = 2 * M
+    k = min(M0, ef_construction)
+    st = {"groups": 0, "device_queries": 0, "host_searches": 0, "patched_records": 0, "patches": 0}
+    h = L.muninn_build_create(dim, metric, M, ef_construction, n, v)
+    if not h:
+        raise MemoryError("muninn_build_create failed")
+    try:
+        if seed is not None:
+            L.muninn_build_seed(h, seed)
+        # the first `warm` nodes: exact sequential inserts on the host, then one full upload
+        n_warm = min(n, max(int(warm), 1))
+        if L.muninn_build_insert(h, n_warm, 0, 0, 1) != 0:
+            raise RuntimeError("muninn_build_insert failed")
+        index.upload(_export(L, h, n_warm, dim, metric, M, ef_construction, v, ids, False))
+        L.muninn_build_log_touched(h, 1)
+        n_dev = n_warm  # rows the device copy holds
+
+        def flush():
+            """device copy ← every record the host changed since the last flush"""
+            nonlocal n_dev
+            cnt = L.muninn_build_touched_count(h)
+            n_now = L.muninn_build_count(h)
+            if cnt == 0 and n_now == n_dev:
+                return
+            log = np.empty(max(cnt, 1), np.int32)
+            cnt = L.muninn_build_touched_take(h, log, log.shape[0])
+            old = np.unique(log[:cnt])
+            old = old[old < n_dev]
+            slots = np.concatenate([np.arange(n_dev, n_now, dtype=np.int32), old.astype(np.int32)])  # new nodes first
+            nl, ne = C.c_int64(), C.c_int64()
+            L.muninn_build_export_nodes(h, len(slots), slots, None, None, None, C.byref(nl), C.byref(ne))
+            lv = np.empty(len(slots), np.int32)
+            offs = np.empty(nl.value + 1, np.int64)
+            tg = np.empty(max(ne.value, 1), np.int32)
+            L.muninn_build_export_nodes(h, len(slots), slots, lv.ctypes.data, offs.ctypes.data, tg.ctypes.data,
+                                        C.byref(nl), C.byref(ne))
+            es, ml = C.c_int32(), C.c_int32()
+            L.muninn_build_entry(h, C.byref(es), C.byref(ml))
+            index.patch_records(n_now, slots, ids[slots], lv, None, v[n_dev:].ctypes.data if n_now > n_dev else
+                                v.ctypes.data, offs, tg[:ne.value], es.value, ml.value)
+            st["patches"] += 1
+            st["patched_records"] += len(slots)
+            n_dev = n_now
+
+        g0, gn = C.c_int64(), C.c_int64()
+        while L.muninn_build_count(h) < n:
+            if L.muninn_build_group_begin(h, batch, C.byref(g0), C.byref(gn)) != 0:
+                raise RuntimeError("muninn_build_group_begin failed")
+            flush()  # a level-raising first node was inserted exactly inside group_begin
+            if gn.value == 0:
+                continue
+            a, z = g0.value, g0.value + gn.value
+            glev = np.empty(gn.value, np.int32)
+            L.muninn_build_group_levels(h, glev)
+            on_dev = np.flatnonzero(glev == 0)
+            cand = np.full((gn.value, k), -1, np.int32)
+            cand_cnt = np.full(gn.value, -1, np.int32)
+            if on_dev.size:
+                found, _, cnt = index.search(v[a:z][on_dev], k, ef_construction)
+                found = found[:, :k]
+                rows = found if identity_ids else np.searchsorted(ids[:a], found)
+                cand[on_dev] = np.where(np.arange(k)[None, :] < cnt[:, None], rows, -1).astype(np.int32)
+                cand_cnt[on_dev] = cnt
+            rc = L.muninn_build_group_link(h, cand.ctypes.data, cand_cnt.ctypes.data, k, threads)
+            if rc != 0:
+                raise RuntimeError(f"muninn_build_group_link failed ({rc}): the device returned a slot outside the "
+                                   "graph as it stood before the group")
+            st["groups"] += 1
+            st["device_queries"] += int(on_dev.size)
+            st["host_searches"] += int(gn.value - on_dev.size)
+            flush()
+        if stats is not None:
+            stats.update(st)
+        return _export(L, h, n, dim, metric, M, ef_construction, v, ids, sort_lists)
+    finally:
+        L.muninn_build_destroy(h)
+        if own_index:
+            index.close()

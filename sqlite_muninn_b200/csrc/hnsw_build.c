@@ -69,6 +69,8 @@ typedef struct {
     uint32_t rng; double level_mult;
     int n_scratch; Scratch *scratch;
     int lazy_mn_parallel_skip;
+    int log_touched; int32_t *touched; int64_t n_touched, cap_touched;
+    int64_t pending_g0, pending_g1; int pending_raise; /* group opened by muninn_build_group_begin */
 } Builder;
 
 /* ───────────── distances, reference SSE order ───────────── */
@@ -313,6 +315,23 @@ static void alloc_node(Builder *b, int32_t s, int lv) {
     }
 }
 
+/* Batch mode orders bit-equal distances by slot. The reference's order inside such a group is whatever its
+ * binary heap yields (unspecified, test/test_priority_queue.c:85-99); the exact mode keeps that order, the
+ * batch mode fixes it so that a searcher with the device's (distance, slot) rule selects the same neighbours. */
+static void order_ties_by_slot(int32_t *slot, const float *d, int n) {
+    for (int i = 0; i + 1 < n;) {
+        int j = i + 1;
+        while (j < n && d[j] == d[i]) j++;
+        for (int a = i + 1; a < j; a++) { /* insertion sort of the run [i, j) */
+            int32_t v = slot[a];
+            int b = a - 1;
+            while (b >= i && slot[b] > v) { slot[b + 1] = slot[b]; b--; }
+            slot[b + 1] = v;
+        }
+        i = j;
+    }
+}
+
 /* phase A of an insert: find the per-level selected neighbours of node s (read-only on
  * every other node). Levels searched: min(level, max_level) .. 0 (src/hnsw_algo.c:553-579). */
 static void find_links(const Builder *b, Scratch *sc, int32_t s) {
@@ -325,6 +344,7 @@ static void find_links(const Builder *b, Scratch *sc, int32_t s) {
     for (int l = start; l >= 0; l--) {
         int M_max = l == 0 ? b->M0 : b->M;
         int found = beam(b, sc, q, cur, l, b->efc);
+        order_ties_by_slot(sc->r_slot, sc->r_dist, found);
         int k = found < M_max ? found : M_max;
         memcpy(sc->sel + (size_t)l * (size_t)b->M0, sc->r_slot, (size_t)k * sizeof(int32_t));
         sc->sel_cnt[l] = k;
@@ -393,6 +413,7 @@ void *muninn_build_create(int dim, int metric, int M, int ef_construction, int64
     b->cnt0 = (int32_t *)calloc((size_t)capacity, sizeof(int32_t));
     b->upper_base = (int64_t *)malloc((size_t)capacity * sizeof(int64_t));
     b->entry = -1; b->max_level = -1;
+    b->pending_g0 = b->pending_g1 = -1;
     b->rng = 42; /* src/hnsw_algo.c:205 */
     b->level_mult = 1.0 / log((double)M);
     if (!b->level || !b->nbr0 || !b->cnt0 || !b->upper_base) return NULL;
@@ -401,113 +422,269 @@ void *muninn_build_create(int dim, int metric, int M, int ef_construction, int64
 
 void muninn_build_seed(void *h, uint32_t seed) { ((Builder *)h)->rng = seed ? seed : 1; } /* src/hnsw_algo.c:222-224 */
 
-/* Insert the next `count` vectors (slots n .. n+count-1, in order).
- * batch = 0 → exact sequential mode; batch > 0 → batch-synchronous mode once the graph
- * holds at least `warm` nodes (earlier nodes are inserted exactly). */
-int muninn_build_insert(void *h, int64_t count, int batch, int64_t warm, int nthreads) {
-    Builder *b = (Builder *)h;
-    if (b->n + count > b->cap) return -1;
-    if (nthreads < 1) nthreads = 1;
+/* ───────────── touched-node log (what a device copy of the graph must be patched with) ───────────── */
+
+static void touch(Builder *b, int32_t s) {
+    if (!b->log_touched) return;
+    if (b->n_touched == b->cap_touched) {
+        b->cap_touched = b->cap_touched * 2 + 4096;
+        b->touched = (int32_t *)realloc(b->touched, (size_t)b->cap_touched * sizeof(int32_t));
+    }
+    b->touched[b->n_touched++] = s;
+}
+
+/* insert_exact changes the new node's lists and the lists of the nodes it links itself to
+ * (src/hnsw_algo.c:582-646: a prune rewrites only the over-full list itself). */
+static void insert_exact_logged(Builder *b, int32_t s, int lv) {
+    insert_exact(b, s, lv);
+    if (!b->log_touched) return;
+    touch(b, s);
+    for (int l = 0; l <= lv; l++) {
+        int32_t *cnt;
+        const int32_t *lst = list_ptr(b, s, l, &cnt);
+        for (int i = 0; i < *cnt; i++) touch(b, lst[i]);
+    }
+}
+
+static int ensure_scratch(Builder *b, int nthreads) {
     if (b->n_scratch < nthreads) {
         b->scratch = (Scratch *)realloc(b->scratch, (size_t)nthreads * sizeof(Scratch));
         for (int t = b->n_scratch; t < nthreads; t++) scratch_init(b, &b->scratch[t]);
         b->n_scratch = nthreads;
     }
+    return 0;
+}
+
+/* Draw levels for the next group of at most `batch` nodes (slots b->n ..) and allocate them. A node
+ * that would raise max_level closes the group before it and is left allocated as the pending node
+ * (*raise = 1); when it is the first node drawn it is inserted alone, exactly, and the draw goes on. */
+static void form_group(Builder *b, int64_t end, int batch, int64_t *g0_out, int64_t *g1_out, int *raise_out) {
+    int64_t g0 = b->n, g1 = g0;
+    int raise = 0;
+    while (g1 < end && g1 - g0 < batch) {
+        int lv = next_level(b);
+        if (lv > b->max_level) {
+            if (g1 == g0) { insert_exact_logged(b, (int32_t)g1, lv); b->n++; g0 = g1 = b->n; continue; }
+            alloc_node(b, (int32_t)g1, lv);
+            raise = 1;
+            break;
+        }
+        alloc_node(b, (int32_t)g1, lv);
+        g1++;
+    }
+    *g0_out = g0; *g1_out = g1; *raise_out = raise;
+}
+
+/* Link the group [g0, g1) into the graph as it stood before the group. cand == NULL: every node
+ * searches on the host (find_links). cand != NULL: node g0+i with cand_cnt[i] >= 0 takes the first
+ * min(cand_cnt[i], M0) slots of cand[i*cand_stride ..] as its layer-0 selection — the caller's
+ * (device) search of the same graph with ef = ef_construction; only level-0 nodes may be supplied. */
+static void link_group(Builder *b, int64_t g0, int64_t g1, int raise, int nthreads, const int32_t *cand,
+                       const int32_t *cand_cnt, int cand_stride) {
+    int64_t gn = g1 - g0;
+    if (gn > 0) {
+        /* phase A: parallel read-only searches; each node writes only its own lists */
+        int64_t per = (int64_t)b->M0 + (int64_t)b->M * MB_MAX_LEVELS;
+        RevReq *req = (RevReq *)malloc((size_t)(gn * per) * sizeof(RevReq));
+        int32_t *req_n = (int32_t *)calloc((size_t)gn, sizeof(int32_t));
+#pragma omp parallel for schedule(dynamic, 4) num_threads(nthreads)
+        for (int64_t i = 0; i < gn; i++) {
+#ifdef _OPENMP
+            Scratch *sc = &b->scratch[omp_get_thread_num()];
+#else
+            Scratch *sc = &b->scratch[0];
+#endif
+            int32_t s = (int32_t)(g0 + i);
+            if (cand && cand_cnt[i] >= 0 && b->level[s] == 0) {
+                int k = cand_cnt[i] < b->M0 ? cand_cnt[i] : b->M0;
+                for (int l = 0; l < MB_MAX_LEVELS; l++) sc->sel_cnt[l] = 0;
+                memcpy(sc->sel, cand + (size_t)i * (size_t)cand_stride, (size_t)k * sizeof(int32_t));
+                sc->sel_cnt[0] = k;
+            } else {
+                find_links(b, sc, s);
+            }
+            RevReq *r = req + i * per;
+            int nr = 0;
+            for (int l = b->level[s] < b->max_level ? b->level[s] : b->max_level; l >= 0; l--) {
+                int32_t *mycnt;
+                int32_t *mine = list_ptr(b, s, l, &mycnt);
+                for (int j = 0; j < sc->sel_cnt[l]; j++) {
+                    int32_t t = sc->sel[(size_t)l * (size_t)b->M0 + j];
+                    list_add(mine, mycnt, t);
+                    r[nr++] = (RevReq){t, l, s};
+                }
+            }
+            req_n[i] = nr;
+        }
+        /* compact + sort requests by (target, level, src) */
+        int64_t tot = 0;
+        for (int64_t i = 0; i < gn; i++) {
+            if (tot != i * per) memmove(req + tot, req + i * per, (size_t)req_n[i] * sizeof(RevReq));
+            tot += req_n[i];
+        }
+        free(req_n);
+        qsort(req, (size_t)tot, sizeof(RevReq), cmp_req);
+        /* group boundaries per target */
+        int64_t *grp = (int64_t *)malloc((size_t)(tot + 1) * sizeof(int64_t));
+        int64_t ng = 0;
+        for (int64_t i = 0; i < tot; i++)
+            if (i == 0 || req[i].target != req[i - 1].target) { grp[ng++] = i; touch(b, req[i].target); }
+        grp[ng] = tot;
+        for (int64_t s = g0; s < g1; s++) touch(b, (int32_t)s);
+        /* phase B: one writer per target list */
+#pragma omp parallel for schedule(dynamic, 16) num_threads(nthreads)
+        for (int64_t gi = 0; gi < ng; gi++) {
+            for (int64_t i = grp[gi]; i < grp[gi + 1]; i++) {
+                int32_t t = req[i].target; int l = req[i].level;
+                int M_max = l == 0 ? b->M0 : b->M;
+                int32_t *tc;
+                int32_t *tl = list_ptr(b, t, l, &tc);
+                list_add(tl, tc, req[i].src);
+                if (*tc > M_max) prune(b, t, l, M_max, 0);
+            }
+        }
+        free(req); free(grp);
+        b->n = g1;
+    }
+    if (raise) {
+        /* the pending node: level already drawn and allocated; insert it exactly */
+        int32_t s = (int32_t)b->n;
+        int lv = b->level[s];
+        /* undo alloc so insert_exact can redo it identically */
+        if (lv > 0) b->n_upper -= lv;
+        insert_exact_logged(b, s, lv);
+        b->n++;
+    }
+}
+
+/* Insert the next `count` vectors (slots n .. n+count-1, in order).
+ * batch = 0 → exact sequential mode; batch > 0 → batch-synchronous mode once the graph
+ * holds at least `warm` nodes (earlier nodes are inserted exactly). */
+int muninn_build_insert(void *h, int64_t count, int batch, int64_t warm, int nthreads) {
+    Builder *b = (Builder *)h;
+    if (b->n + count > b->cap || b->pending_g1 >= 0) return -1;
+    if (nthreads < 1) nthreads = 1;
+    ensure_scratch(b, nthreads);
     int64_t end = b->n + count;
-    RevReq *req = NULL; int64_t req_cap = 0;
-    int64_t *grp = NULL; int64_t grp_cap = 0;
     while (b->n < end) {
         if (batch <= 0 || b->n < warm) {
             int lv = next_level(b);
-            insert_exact(b, (int32_t)b->n, lv);
+            insert_exact_logged(b, (int32_t)b->n, lv);
             b->n++;
             continue;
         }
-        /* form a group; a node that would raise max_level is inserted alone, exactly */
-        int64_t g0 = b->n, g1 = g0;
-        int raise = 0;
-        while (g1 < end && g1 - g0 < batch) {
-            int lv = next_level(b);
-            if (lv > b->max_level) {
-                if (g1 == g0) { insert_exact(b, (int32_t)g1, lv); b->n++; g0 = g1 = b->n; continue; }
-                /* close the group before this node; remember its level by allocating now */
-                alloc_node(b, (int32_t)g1, lv);
-                raise = 1;
-                break;
+        int64_t g0, g1; int raise;
+        form_group(b, end, batch, &g0, &g1, &raise);
+        link_group(b, g0, g1, raise, nthreads, NULL, NULL, 0);
+    }
+    return 0;
+}
+
+/* ───────────── group-at-a-time interface for a caller that runs the layer-0 searches itself ─────────────
+ *
+ * The batch mode's phase A for a level-0 node is: greedy descent max_level..1, ef_construction-wide beam on
+ * layer 0, keep the closest min(found, 2M) (find_links; src/hnsw_algo.c:553-579 for a node of level 0) —
+ * which is hnsw_search(k = min(2M, efc), ef = efc) on the graph as it stood before the group. A caller that
+ * keeps a device copy of the graph (muninn_cuda_index_upload / _patch) can therefore run those searches as
+ * one muninn_cuda_search_batch and hand the results in:
+ *
+ *   muninn_build_log_touched(h, 1)
+ *   loop:  muninn_build_group_begin(h, batch, &g0, &gn)        levels drawn, nodes allocated
+ *          [patch the device copy if muninn_build_touched_count(h) > 0: a level-raising first node was
+ *           inserted exactly inside group_begin]
+ *          search the level-0 nodes of [g0, g0+gn) on the device
+ *          muninn_build_group_link(h, cand, cand_cnt, stride, threads)   nodes with cand_cnt < 0 (and all
+ *                                                                       nodes of level > 0) search on the host
+ *          muninn_build_touched_take → muninn_build_export_nodes → muninn_cuda_index_patch
+ *
+ * Without bit-equal candidate distances the graph equals muninn_build_insert's batch mode bit for bit
+ * (tests/test_device_build.py); with ties the device's (distance, slot) order replaces the heap order. */
+
+void muninn_build_log_touched(void *h, int on) {
+    Builder *b = (Builder *)h;
+    b->log_touched = on;
+    b->n_touched = 0;
+}
+
+int64_t muninn_build_count(void *h) { return ((Builder *)h)->n; }
+
+/* Returns 0 and the group [*g0, *g0 + *gn); *gn may be 0 when only exact inserts happened (or nothing is
+ * left). -1 when a group is already open. */
+int muninn_build_group_begin(void *h, int batch, int64_t *g0, int64_t *gn) {
+    Builder *b = (Builder *)h;
+    if (b->pending_g1 >= 0 || batch < 1) return -1;
+    if (b->n >= b->cap) { *g0 = b->n; *gn = 0; return 0; }
+    int64_t a, z; int raise;
+    form_group(b, b->cap, batch, &a, &z, &raise);
+    b->pending_g0 = a; b->pending_g1 = z; b->pending_raise = raise;
+    *g0 = a; *gn = z - a;
+    return 0;
+}
+
+/* levels of the open group's nodes (known after group_begin) */
+int muninn_build_group_levels(void *h, int32_t *levels) {
+    Builder *b = (Builder *)h;
+    if (b->pending_g1 < 0) return -1;
+    for (int64_t s = b->pending_g0; s < b->pending_g1; s++) levels[s - b->pending_g0] = b->level[s];
+    return 0;
+}
+
+int muninn_build_group_link(void *h, const int32_t *cand, const int32_t *cand_cnt, int cand_stride, int nthreads) {
+    Builder *b = (Builder *)h;
+    if (b->pending_g1 < 0) return -1;
+    if (nthreads < 1) nthreads = 1;
+    ensure_scratch(b, nthreads);
+    if (cand) { /* slots must be stored nodes from before the group */
+        int64_t gn = b->pending_g1 - b->pending_g0;
+        for (int64_t i = 0; i < gn; i++) {
+            if (cand_cnt[i] < 0) continue;
+            if (cand_cnt[i] > cand_stride) return -2;
+            for (int j = 0; j < cand_cnt[i] && j < b->M0; j++) {
+                int32_t t = cand[(size_t)i * (size_t)cand_stride + j];
+                if (t < 0 || t >= b->pending_g0) return -2;
             }
-            alloc_node(b, (int32_t)g1, lv);
-            g1++;
-        }
-        int64_t gn = g1 - g0;
-        if (gn > 0) {
-            /* phase A: parallel read-only searches; each node writes only its own lists */
-            int64_t max_req = gn * ((int64_t)b->M0 + (int64_t)b->M * MB_MAX_LEVELS);
-            if (max_req > req_cap) { req = (RevReq *)realloc(req, (size_t)max_req * sizeof(RevReq)); req_cap = max_req; }
-            int64_t *req_off = (int64_t *)malloc((size_t)(gn + 1) * sizeof(int64_t));
-            int64_t per = (int64_t)b->M0 + (int64_t)b->M * MB_MAX_LEVELS;
-            int32_t *req_n = (int32_t *)calloc((size_t)gn, sizeof(int32_t));
-#pragma omp parallel for schedule(dynamic, 4) num_threads(nthreads)
-            for (int64_t i = 0; i < gn; i++) {
-#ifdef _OPENMP
-                Scratch *sc = &b->scratch[omp_get_thread_num()];
-#else
-                Scratch *sc = &b->scratch[0];
-#endif
-                int32_t s = (int32_t)(g0 + i);
-                find_links(b, sc, s);
-                RevReq *r = req + i * per;
-                int nr = 0;
-                for (int l = b->level[s] < b->max_level ? b->level[s] : b->max_level; l >= 0; l--) {
-                    int32_t *mycnt;
-                    int32_t *mine = list_ptr(b, s, l, &mycnt);
-                    for (int j = 0; j < sc->sel_cnt[l]; j++) {
-                        int32_t t = sc->sel[(size_t)l * (size_t)b->M0 + j];
-                        list_add(mine, mycnt, t);
-                        r[nr++] = (RevReq){t, l, s};
-                    }
-                }
-                req_n[i] = nr;
-            }
-            /* compact + sort requests by (target, level, src) */
-            int64_t tot = 0;
-            for (int64_t i = 0; i < gn; i++) {
-                if (tot != i * per) memmove(req + tot, req + i * per, (size_t)req_n[i] * sizeof(RevReq));
-                tot += req_n[i];
-            }
-            free(req_off); free(req_n);
-            qsort(req, (size_t)tot, sizeof(RevReq), cmp_req);
-            /* group boundaries per target */
-            if (tot + 1 > grp_cap) { grp = (int64_t *)realloc(grp, (size_t)(tot + 1) * sizeof(int64_t)); grp_cap = tot + 1; }
-            int64_t ng = 0;
-            for (int64_t i = 0; i < tot; i++)
-                if (i == 0 || req[i].target != req[i - 1].target) grp[ng++] = i;
-            grp[ng] = tot;
-            /* phase B: one writer per target list */
-#pragma omp parallel for schedule(dynamic, 16) num_threads(nthreads)
-            for (int64_t gi = 0; gi < ng; gi++) {
-                for (int64_t i = grp[gi]; i < grp[gi + 1]; i++) {
-                    int32_t t = req[i].target; int l = req[i].level;
-                    int M_max = l == 0 ? b->M0 : b->M;
-                    int32_t *tc;
-                    int32_t *tl = list_ptr(b, t, l, &tc);
-                    list_add(tl, tc, req[i].src);
-                    if (*tc > M_max) prune(b, t, l, M_max, 0);
-                }
-            }
-            b->n = g1;
-        }
-        if (raise) {
-            /* the pending node: level already drawn and allocated; insert it exactly */
-            int32_t s = (int32_t)b->n;
-            int lv = b->level[s];
-            /* undo alloc so insert_exact can redo it identically */
-            if (lv > 0) b->n_upper -= lv;
-            insert_exact(b, s, lv);
-            b->n++;
         }
     }
-    free(req); free(grp);
+    link_group(b, b->pending_g0, b->pending_g1, b->pending_raise, nthreads, cand, cand_cnt, cand_stride);
+    b->pending_g0 = b->pending_g1 = -1; b->pending_raise = 0;
     return 0;
+}
+
+int64_t muninn_build_touched_count(void *h) { return ((Builder *)h)->n_touched; }
+
+/* Copy the log (unsorted, with repeats) and clear it. */
+int64_t muninn_build_touched_take(void *h, int32_t *out, int64_t cap) {
+    Builder *b = (Builder *)h;
+    int64_t n = b->n_touched < cap ? b->n_touched : cap;
+    memcpy(out, b->touched, (size_t)n * sizeof(int32_t));
+    b->n_touched = 0;
+    return n;
+}
+
+/* Records of the given nodes in the list-CSR layout of muninn_cuda_index_patch: neighbour lists in the
+ * builder's own (insertion) order. Pass targets = NULL to obtain the sizes only. */
+void muninn_build_export_nodes(void *h, int64_t n_nodes, const int32_t *slots, int32_t *levels, int64_t *list_offsets,
+                               int32_t *targets, int64_t *n_lists, int64_t *n_edges) {
+    Builder *b = (Builder *)h;
+    int64_t li = 0, e = 0;
+    if (targets) list_offsets[0] = 0;
+    for (int64_t i = 0; i < n_nodes; i++) {
+        int32_t s = slots[i];
+        if (targets) levels[i] = b->level[s];
+        for (int l = 0; l <= b->level[s]; l++) {
+            int32_t *cnt;
+            const int32_t *lst = list_ptr(b, s, l, &cnt);
+            if (targets) { memcpy(targets + e, lst, (size_t)*cnt * sizeof(int32_t)); list_offsets[li + 1] = e + *cnt; }
+            e += *cnt;
+            li++;
+        }
+    }
+    *n_lists = li; *n_edges = e;
+}
+
+void muninn_build_entry(void *h, int32_t *entry, int32_t *max_level) {
+    Builder *b = (Builder *)h;
+    *entry = b->entry; *max_level = b->max_level;
 }
 
 void muninn_build_sizes(void *h, int64_t *n, int64_t *n_lists, int64_t *n_edges, int32_t *entry, int32_t *max_level) {
@@ -553,7 +730,7 @@ void muninn_build_destroy(void *h) {
         Scratch *sc = &b->scratch[t];
         free(sc->stamp); free(sc->cand.a); free(sc->res.a); free(sc->r_slot); free(sc->r_dist); free(sc->sel); free(sc->sel_cnt);
     }
-    free(b->scratch);
+    free(b->scratch); free(b->touched);
     free(b->level); free(b->nbr0); free(b->cnt0); free(b->upper_base); free(b->nbrU); free(b->cntU);
     free(b);
 }

@@ -201,6 +201,19 @@ class HnswIndexCuda:
                                                    _ptr(vec), _ptr(offs), _ptr(tg), g.entry_slot, g.max_level))
         self.n = g.n
 
+    def patch_records(self, n_total: int, slots, ids, levels, deleted, vectors_ptr, list_offsets, targets,
+                      entry_slot: int, max_level: int):
+        """muninn_cuda_index_patch with caller-assembled records (the device-assisted builder). `vectors_ptr` is the
+        address of record 0's vector; only the records of NEW nodes are read from it (include/muninn_cuda.h)."""
+        slots = np.ascontiguousarray(slots, np.int32)
+        ids = np.ascontiguousarray(ids, np.int64); levels = np.ascontiguousarray(levels, np.int32)
+        deleted = None if deleted is None else np.ascontiguousarray(deleted, np.uint8)
+        list_offsets = np.ascontiguousarray(list_offsets, np.int64); targets = np.ascontiguousarray(targets, np.int32)
+        self._check(self.L.muninn_cuda_index_patch(self.h, n_total, len(slots), _ptr(slots), _ptr(ids), _ptr(levels),
+                                                   _ptr(deleted), vectors_ptr, _ptr(list_offsets), _ptr(targets),
+                                                   entry_slot, max_level))
+        self.n = n_total
+
     # -- search ------------------------------------------------------------------------
     def search(self, queries, k: int, ef: int | None = None, want_stats: bool = False):
         """Batched hnsw_search (/root/reference/src/hnsw_algo.c:670-704). ef defaults to 2k, the

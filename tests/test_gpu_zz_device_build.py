@@ -1,0 +1,60 @@
+"""Device-assisted graph construction on the GPU: `build_graph_device` with the product index.
+
+Sorts last among the GPU test files on purpose: it was written after the round's GPU minutes were spent, so its first
+run on hardware is the driver's — the host logic it shares with the CPU tests is covered in tests/test_device_build.py.
+"""
+import numpy as np
+import pytest
+
+from sqlite_muninn_b200.builder import build_graph, build_graph_device
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("n,dim,metric,M,efc,batch,warm", [(8000, 64, 0, 16, 64, 512, 1000),
+                                                           (6000, 96, 2, 32, 48, 256, 500),
+                                                           (5000, 40, 1, 8, 100, 300, 0)])
+def test_device_build_equals_host_batch_mode(n, dim, metric, M, efc, batch, warm):
+    """The product path: searches on the GPU, patches through the C ABI. Gaussian data: no bit-equal distances."""
+    from sqlite_muninn_b200.cuda import HnswIndexCuda
+    rng = np.random.default_rng(n + 1)
+    x = rng.standard_normal((n, dim)).astype(np.float32)
+    want = build_graph(x, metric, M, efc, batch=batch, warm=warm, sort_lists=False)
+    st = {}
+    with HnswIndexCuda(dim, metric, M, 0) as idx:
+        got = build_graph_device(x, metric, M, efc, batch=batch, warm=warm, sort_lists=False, index=idx, stats=st)
+        assert got.same_structure(want)
+        assert st["device_queries"] > 0.8 * (n - warm)
+        # the device copy is the finished graph: it answers like a fresh upload of it
+        q = rng.standard_normal((64, dim)).astype(np.float32)
+        a = idx.search(q, 10, 64)
+        with HnswIndexCuda.from_graph(got, 0) as fresh:
+            b = fresh.search(q, 10, 64)
+        for u, w in zip(a, b):
+            assert np.array_equal(u, w)
+
+
+def test_device_build_at_scale_matches_host_quality():
+    """100k x 64: at this size a bit-equal pair of candidate distances at a selection boundary is possible, where the
+    device's (distance, slot) rule and the host heap may differ: require near-identity and equal search quality."""
+    from sqlite_muninn_b200.cuda import HnswIndexCuda
+    rng = np.random.default_rng(77)
+    z = rng.standard_normal((100_000, 12)).astype(np.float32)
+    x = (z @ rng.standard_normal((12, 64)).astype(np.float32) + 0.05 * rng.standard_normal((100_000, 64))).astype(np.float32)
+    q = x[rng.choice(100_000, 500, replace=False)] + 0.05 * rng.standard_normal((500, 64)).astype(np.float32)
+    host = build_graph(x, 0, 16, 100, batch=1024, warm=4096)
+    st = {}
+    dev = build_graph_device(x, 0, 16, 100, batch=1024, warm=4096, stats=st)
+    assert np.array_equal(dev.levels, host.levels) and dev.entry_slot == host.entry_slot
+    same = dev.same_structure(host)
+    if not same:
+        h0 = [tuple(host.neighbours(s, 0)) for s in range(0, host.n, 50)]
+        d0 = [tuple(dev.neighbours(s, 0)) for s in range(0, dev.n, 50)]
+        assert np.mean([a == b for a, b in zip(h0, d0)]) > 0.98
+    assert st["device_queries"] > 0.9 * (100_000 - 4096)
+    with HnswIndexCuda.from_graph(host, 0) as a, HnswIndexCuda.from_graph(dev, 0) as b:
+        truth, _, _ = a.exact_knn(q, 10)
+        ra = np.mean([len(set(u) & set(t)) / 10 for u, t in zip(a.search(q, 10, 64)[0].tolist(), truth.tolist())])
+        rb = np.mean([len(set(u) & set(t)) / 10 for u, t in zip(b.search(q, 10, 64)[0].tolist(), truth.tolist())])
+    assert abs(ra - rb) < 0.01, (ra, rb)
+
