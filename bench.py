@@ -104,7 +104,16 @@ def get_graph(args, rank: int, world: int, barrier):
     if rank == 0 and not os.path.exists(path):
         base = make_vectors(args.n, args.dim, args.seeds[0], kind=args.data)
         log(f"[bench] building {tag} with {os.cpu_count()} host threads …")
-        g = build_graph(base, args.metric, args.M, args.efc, batch=args.build_batch, warm=8192)
+        if args.device_build and args.impl != "reference":
+            # same group-synchronous rule with the layer-0 candidate searches on the GPU (builder.build_graph_device):
+            # the same graph wherever no two candidate distances are bit-equal
+            from sqlite_muninn_b200.builder import build_graph_device
+            st = {}
+            g = build_graph_device(base, args.metric, args.M, args.efc, batch=args.build_batch, warm=8192, stats=st,
+                                   device=int(os.environ.get("LOCAL_RANK", "0")))
+            log(f"[bench] device-assisted build: {st}")
+        else:
+            g = build_graph(base, args.metric, args.M, args.efc, batch=args.build_batch, warm=8192)
         tmp = path + ".tmp.npz"
         np.savez(tmp, levels=g.levels, list_offsets=g.list_offsets, targets=g.targets, entry_slot=g.entry_slot,
                  max_level=g.max_level)
@@ -628,6 +637,8 @@ def main():
     ap.add_argument("--k", type=int, default=None)
     ap.add_argument("--ef", type=int, default=0, help="0 = smallest ef of the sweep with recall@10 >= 0.95")
     ap.add_argument("--build-batch", type=int, default=1024)
+    ap.add_argument("--device-build", action="store_true",
+                    help="build the input graph with builder.build_graph_device (outside the timed region either way)")
     ap.add_argument("--teams-per-sm", type=int, default=0)
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")

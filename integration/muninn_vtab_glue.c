@@ -262,8 +262,6 @@ static int glue_patch(GlueSlot *s) {
     return rc;
 }
 
-/* Drop-in for hnsw_search (src/hnsw_algo.h:73): same arguments and return value (number of
- * results, 0 for an empty index); on a device failure returns 0 with *err set. */
 /* handle of `index`, created on first use and brought up to date (patch, else full upload); NULL with *err set */
 static GlueSlot *glue_sync(HnswIndex *index, char **err) {
     GlueSlot *s = slot_find(index, 1);
@@ -303,6 +301,8 @@ int muninn_glue_search_batch(HnswIndex *index, const float *queries, int nq, int
     return 0;
 }
 
+/* Drop-in for hnsw_search (src/hnsw_algo.h:73): same arguments and return value (number of
+ * results, 0 for an empty index); on a device failure returns 0 with *err set. */
 int muninn_glue_search(HnswIndex *index, const float *query, int k, int ef_search, HnswSearchResult *results,
                        char **err) {
     if (!index || index->entry_point == -1 || index->node_count == 0 || k < 1) return 0; /* hnsw_algo.c:671 */
