@@ -12,7 +12,7 @@ import subprocess
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-ORACLE_SO = os.path.join(HERE, "liboracle.so")
+ORACLE_SO = os.environ.get("MUNINN_ORACLE_SO") or os.path.join(HERE, "liboracle.so")  # sanitizer builds
 REF_SO = os.path.join(HERE, "_ref", "libmuninn_ref.so")
 REF_EXT_SO = os.path.join(HERE, "_ref", "muninn_ref_ext.so")
 

@@ -15,7 +15,8 @@ import numpy as np
 from .graph import FlatGraph
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-HOST_SO = os.path.join(_HERE, "csrc", "libmuninn_host.so")
+# MUNINN_HOST_SO: alternative build of the same library (tools/sanitize_host.sh: ASan + UBSan)
+HOST_SO = os.environ.get("MUNINN_HOST_SO") or os.path.join(_HERE, "csrc", "libmuninn_host.so")
 
 _p = np.ctypeslib.ndpointer
 _f32 = _p(np.float32, flags="C_CONTIGUOUS")
