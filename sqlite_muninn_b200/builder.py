@@ -9,6 +9,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import time
 
 import numpy as np
 
@@ -54,6 +55,7 @@ def host_lib():
         L.muninn_build_export_nodes.argtypes = [C.c_void_p, C.c_int64, _i32, C.c_void_p, C.c_void_p, C.c_void_p,
                                                 C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
         L.muninn_build_entry.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+        L.muninn_build_phase_seconds.argtypes = [C.c_void_p, C.POINTER(C.c_double * 3)]
         _lib = L
     return _lib
 
@@ -131,7 +133,9 @@ def build_graph_device(vectors, metric: int = 0, M: int = 16, ef_construction: i
         index = HnswIndexCuda(dim, metric, M, device)
     M0 = 2 * M
     k = min(M0, ef_construction)
-    st = {"groups": 0, "device_queries": 0, "host_searches": 0, "patched_records": 0, "patches": 0}
+    st = {"groups": 0, "device_queries": 0, "host_searches": 0, "patched_records": 0, "patches": 0,
+          "warm_s": 0.0, "search_s": 0.0, "link_s": 0.0, "patch_s": 0.0}
+    clock = time.perf_counter
     h = L.muninn_build_create(dim, metric, M, ef_construction, n, v)
     if not h:
         raise MemoryError("muninn_build_create failed")
@@ -140,9 +144,11 @@ def build_graph_device(vectors, metric: int = 0, M: int = 16, ef_construction: i
             L.muninn_build_seed(h, seed)
         # the first `warm` nodes: exact sequential inserts on the host, then one full upload
         n_warm = min(n, max(int(warm), 1))
+        t = clock()
         if L.muninn_build_insert(h, n_warm, 0, 0, 1) != 0:
             raise RuntimeError("muninn_build_insert failed")
         index.upload(_export(L, h, n_warm, dim, metric, M, ef_construction, v, ids, False))
+        st["warm_s"] = clock() - t
         L.muninn_build_log_touched(h, 1)
         n_dev = n_warm  # rows the device copy holds
 
@@ -153,6 +159,7 @@ def build_graph_device(vectors, metric: int = 0, M: int = 16, ef_construction: i
             n_now = L.muninn_build_count(h)
             if cnt == 0 and n_now == n_dev:
                 return
+            t = clock()
             log = np.empty(max(cnt, 1), np.int32)
             cnt = L.muninn_build_touched_take(h, log, log.shape[0])
             old = np.unique(log[:cnt])
@@ -171,6 +178,7 @@ def build_graph_device(vectors, metric: int = 0, M: int = 16, ef_construction: i
                                 v.ctypes.data, offs, tg[:ne.value], es.value, ml.value)
             st["patches"] += 1
             st["patched_records"] += len(slots)
+            st["patch_s"] += clock() - t
             n_dev = n_now
 
         g0, gn = C.c_int64(), C.c_int64()
@@ -186,13 +194,17 @@ def build_graph_device(vectors, metric: int = 0, M: int = 16, ef_construction: i
             on_dev = np.flatnonzero(glev == 0)
             cand = np.full((gn.value, k), -1, np.int32)
             cand_cnt = np.full(gn.value, -1, np.int32)
+            t = clock()
             if on_dev.size:
                 found, _, cnt = index.search(v[a:z][on_dev], k, ef_construction)
                 found = found[:, :k]
                 rows = found if identity_ids else np.searchsorted(ids[:a], found)
                 cand[on_dev] = np.where(np.arange(k)[None, :] < cnt[:, None], rows, -1).astype(np.int32)
                 cand_cnt[on_dev] = cnt
+            st["search_s"] += clock() - t
+            t = clock()
             rc = L.muninn_build_group_link(h, cand.ctypes.data, cand_cnt.ctypes.data, k, threads)
+            st["link_s"] += clock() - t
             if rc != 0:
                 raise RuntimeError(f"muninn_build_group_link failed ({rc}): the device returned a slot outside the "
                                    "graph as it stood before the group")
@@ -200,8 +212,11 @@ def build_graph_device(vectors, metric: int = 0, M: int = 16, ef_construction: i
             st["device_queries"] += int(on_dev.size)
             st["host_searches"] += int(gn.value - on_dev.size)
             flush()
+        ph = (C.c_double * 3)()
+        L.muninn_build_phase_seconds(h, C.byref(ph))
+        st["link_host_search_s"], st["link_sort_s"], st["link_reverse_prune_s"] = ph[0], ph[1], ph[2]
         if stats is not None:
-            stats.update(st)
+            stats.update({k_: round(v_, 3) if isinstance(v_, float) else v_ for k_, v_ in st.items()})
         return _export(L, h, n, dim, metric, M, ef_construction, v, ids, sort_lists)
     finally:
         L.muninn_build_destroy(h)
