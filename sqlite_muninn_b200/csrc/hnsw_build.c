@@ -54,6 +54,7 @@ typedef struct {
     Heap cand, res;
     int32_t *r_slot; float *r_dist; /* beam output, ascending, capacity efc */
     int32_t *sel;                   /* per level selected: [MB_MAX_LEVELS][M0] */
+    float *sel_d;                   /* their distances to the new node */
     int32_t *sel_cnt;               /* [MB_MAX_LEVELS] */
 } Scratch;
 
@@ -63,6 +64,8 @@ typedef struct {
     const float *vecs;
     int32_t *level;
     int32_t *nbr0; int32_t *cnt0;       /* layer 0: stride M0+1 */
+    float *d0, *dU;                     /* distance of every stored edge, parallel to nbr0 / nbrU (the reference
+                                           persists the same number in _edges.distance, src/hnsw_vtab.c:163-169) */
     int64_t *upper_base;                /* first upper list of a node, or -1 */
     int32_t *nbrU; int32_t *cntU;       /* upper lists: stride M+1 */
     int64_t n_upper, cap_upper;
@@ -174,9 +177,15 @@ static inline int32_t *list_ptr(const Builder *b, int32_t s, int l, int32_t **cn
     return b->nbrU + (size_t)u * (size_t)(b->M + 1);
 }
 
-static int list_add(int32_t *lst, int32_t *cnt, int32_t t) { /* src/hnsw_algo.c:142-163 */
+static inline float *dlist_ptr(const Builder *b, int32_t s, int l) {
+    if (l == 0) return b->d0 + (size_t)s * (size_t)(b->M0 + 1);
+    return b->dU + (size_t)(b->upper_base[s] + (l - 1)) * (size_t)(b->M + 1);
+}
+
+static int list_add(int32_t *lst, float *dl, int32_t *cnt, int32_t t, float d) { /* src/hnsw_algo.c:142-163 */
     for (int i = 0; i < *cnt; i++) if (lst[i] == t) return 0;
-    lst[(*cnt)++] = t;
+    lst[*cnt] = t; dl[*cnt] = d;
+    (*cnt)++;
     return 1;
 }
 
@@ -191,7 +200,10 @@ static int mutual_count(const Builder *b, int32_t x, int32_t y, int l) { /* src/
     return c;
 }
 
-/* MN-RU prune of s's over-full list at level l (src/hnsw_algo.c:601-646). The reference
+/* MN-RU prune of s's over-full list at level l (src/hnsw_algo.c:601-646). The reference recomputes the distance
+ * from s to every entry; here each edge keeps the distance it was created with, which is the same number: all
+ * three metrics are bit-symmetric in their arguments (a−b and b−a differ in sign only, products commute, cosine's
+ * two norms swap places in a commutative product). The reference
  * evaluates the mutual-neighbour count of every entry up front; it is consulted only
  * when two distances compare equal, so it is evaluated on demand here (use_mn = 0 in the
  * batch linker, where other lists are being written concurrently: ties keep the earlier
@@ -209,8 +221,8 @@ static void prune(Builder *b, int32_t s, int l, int M_max, int use_mn) {
         mp = (int *)malloc((size_t)nc * sizeof(int));
         ip = (int32_t *)malloc((size_t)nc * sizeof(int32_t));
     }
-    const float *vs = vec_of(b, s);
-    for (int j = 0; j < nc; j++) { ip[j] = lst[j]; dp[j] = dist(b, vs, vec_of(b, lst[j])); mp[j] = -2; }
+    float *dl = dlist_ptr(b, s, l);
+    for (int j = 0; j < nc; j++) { ip[j] = lst[j]; dp[j] = dl[j]; mp[j] = -2; }
     for (int a = 0; a < M_max && a < nc; a++) {
         int best = a;
         for (int c = a + 1; c < nc; c++) {
@@ -228,6 +240,7 @@ static void prune(Builder *b, int32_t s, int l, int M_max, int use_mn) {
         }
     }
     memcpy(lst, ip, (size_t)M_max * sizeof(int32_t));
+    memcpy(dl, dp, (size_t)M_max * sizeof(float));
     *cnt = M_max;
     if (dp != d) { free(dp); free(mp); free(ip); }
 }
@@ -309,6 +322,7 @@ static void alloc_node(Builder *b, int32_t s, int lv) {
             int64_t nc = b->cap_upper * 2 + lv + 1024;
             b->nbrU = (int32_t *)realloc(b->nbrU, (size_t)nc * (size_t)(b->M + 1) * sizeof(int32_t));
             b->cntU = (int32_t *)realloc(b->cntU, (size_t)nc * sizeof(int32_t));
+            b->dU = (float *)realloc(b->dU, (size_t)nc * (size_t)(b->M + 1) * sizeof(float));
             b->cap_upper = nc;
         }
         b->upper_base[s] = b->n_upper;
@@ -349,6 +363,7 @@ static void find_links(const Builder *b, Scratch *sc, int32_t s) {
         order_ties_by_slot(sc->r_slot, sc->r_dist, found);
         int k = found < M_max ? found : M_max;
         memcpy(sc->sel + (size_t)l * (size_t)b->M0, sc->r_slot, (size_t)k * sizeof(int32_t));
+        memcpy(sc->sel_d + (size_t)l * (size_t)b->M0, sc->r_dist, (size_t)k * sizeof(float));
         sc->sel_cnt[l] = k;
         if (found > 0) cur = sc->r_slot[0];
     }
@@ -370,13 +385,14 @@ static void insert_exact(Builder *b, int32_t s, int lv) {
         int k = found < M_max ? found : M_max;
         int32_t *mycnt;
         int32_t *mine = list_ptr(b, s, l, &mycnt);
+        float *mine_d = dlist_ptr(b, s, l);
         for (int i = 0; i < k; i++) {
             int32_t t = sc->r_slot[i];
-            list_add(mine, mycnt, t);
+            list_add(mine, mine_d, mycnt, t, sc->r_dist[i]);
             if (l <= b->level[t]) {
                 int32_t *tc;
                 int32_t *tl = list_ptr(b, t, l, &tc);
-                list_add(tl, tc, s);
+                list_add(tl, dlist_ptr(b, t, l), tc, s, sc->r_dist[i]);
                 if (*tc > M_max) prune(b, t, l, M_max, 1);
             }
         }
@@ -385,7 +401,7 @@ static void insert_exact(Builder *b, int32_t s, int lv) {
     if (lv > b->max_level) { b->entry = s; b->max_level = lv; }
 }
 
-typedef struct { int32_t target, level, src; } RevReq;
+typedef struct { int32_t target, level, src; float d; } RevReq;
 
 static int cmp_req(const void *a, const void *b) {
     const RevReq *x = (const RevReq *)a, *y = (const RevReq *)b;
@@ -398,33 +414,37 @@ static int cmp_req(const void *a, const void *b) {
  * (src − g0) when the group is small enough for 21 bits (a serial qsort of the ≈ 33 requests per node was 8 % of a
  * 1 024-node group's time); otherwise qsort. */
 static void sort_requests(RevReq *req, int64_t tot, int32_t g0) {
+    typedef struct { uint64_t key; float d; } KD;
     int ok = tot > 256;
     for (int64_t i = 0; ok && i < tot; i++)
         if (req[i].src - g0 >= (1 << 21) || req[i].src < g0) ok = 0;
-    uint64_t *key = ok ? (uint64_t *)malloc((size_t)tot * 2 * sizeof(uint64_t)) : NULL;
+    KD *key = ok ? (KD *)malloc((size_t)tot * 2 * sizeof(KD)) : NULL;
     if (!key) { qsort(req, (size_t)tot, sizeof(RevReq), cmp_req); return; }
-    uint64_t *tmp = key + tot, top = 0;
+    KD *base = key, *tmp = key + tot;
+    uint64_t top = 0;
     for (int64_t i = 0; i < tot; i++) {
-        key[i] = ((uint64_t)(uint32_t)req[i].target << 26) | ((uint64_t)req[i].level << 21) | (uint64_t)(req[i].src - g0);
-        if (key[i] > top) top = key[i];
+        key[i].key = ((uint64_t)(uint32_t)req[i].target << 26) | ((uint64_t)req[i].level << 21) | (uint64_t)(req[i].src - g0);
+        key[i].d = req[i].d;
+        if (key[i].key > top) top = key[i].key;
     }
-    static const int BITS = 11;
+    enum { BITS = 11 };
     size_t *cnt = (size_t *)malloc(((size_t)1 << BITS) * sizeof(size_t));
     for (int shift = 0; shift < 64 && (top >> shift) != 0; shift += BITS) {
         memset(cnt, 0, ((size_t)1 << BITS) * sizeof(size_t));
-        for (int64_t i = 0; i < tot; i++) cnt[(key[i] >> shift) & ((1u << BITS) - 1)]++;
+        for (int64_t i = 0; i < tot; i++) cnt[(key[i].key >> shift) & ((1u << BITS) - 1)]++;
         size_t run = 0;
         for (size_t d = 0; d < ((size_t)1 << BITS); d++) { size_t c = cnt[d]; cnt[d] = run; run += c; }
-        for (int64_t i = 0; i < tot; i++) tmp[cnt[(key[i] >> shift) & ((1u << BITS) - 1)]++] = key[i];
-        uint64_t *sw = key; key = tmp; tmp = sw;
+        for (int64_t i = 0; i < tot; i++) tmp[cnt[(key[i].key >> shift) & ((1u << BITS) - 1)]++] = key[i];
+        KD *sw = key; key = tmp; tmp = sw;
     }
     for (int64_t i = 0; i < tot; i++) {
-        req[i].target = (int32_t)(key[i] >> 26);
-        req[i].level = (int32_t)((key[i] >> 21) & 31);
-        req[i].src = g0 + (int32_t)(key[i] & ((1u << 21) - 1));
+        req[i].target = (int32_t)(key[i].key >> 26);
+        req[i].level = (int32_t)((key[i].key >> 21) & 31);
+        req[i].src = g0 + (int32_t)(key[i].key & ((1u << 21) - 1));
+        req[i].d = key[i].d;
     }
     free(cnt);
-    free(key < tmp ? key : tmp);
+    free(base);
 }
 
 /* ───────────── public C API ───────────── */
@@ -435,6 +455,7 @@ static void scratch_init(Builder *b, Scratch *sc) {
     sc->r_slot = (int32_t *)malloc((size_t)b->efc * sizeof(int32_t));
     sc->r_dist = (float *)malloc((size_t)b->efc * sizeof(float));
     sc->sel = (int32_t *)malloc((size_t)MB_MAX_LEVELS * (size_t)b->M0 * sizeof(int32_t));
+    sc->sel_d = (float *)malloc((size_t)MB_MAX_LEVELS * (size_t)b->M0 * sizeof(float));
     sc->sel_cnt = (int32_t *)calloc(MB_MAX_LEVELS, sizeof(int32_t));
 }
 
@@ -446,12 +467,13 @@ void *muninn_build_create(int dim, int metric, int M, int ef_construction, int64
     b->level = (int32_t *)malloc((size_t)capacity * sizeof(int32_t));
     b->nbr0 = (int32_t *)malloc((size_t)capacity * (size_t)(b->M0 + 1) * sizeof(int32_t));
     b->cnt0 = (int32_t *)calloc((size_t)capacity, sizeof(int32_t));
+    b->d0 = (float *)malloc((size_t)capacity * (size_t)(b->M0 + 1) * sizeof(float));
     b->upper_base = (int64_t *)malloc((size_t)capacity * sizeof(int64_t));
     b->entry = -1; b->max_level = -1;
     b->pending_g0 = b->pending_g1 = -1;
     b->rng = 42; /* src/hnsw_algo.c:205 */
     b->level_mult = 1.0 / log((double)M);
-    if (!b->level || !b->nbr0 || !b->cnt0 || !b->upper_base) return NULL;
+    if (!b->level || !b->nbr0 || !b->cnt0 || !b->d0 || !b->upper_base) return NULL;
     return b;
 }
 
@@ -541,6 +563,7 @@ static void link_group(Builder *b, int64_t g0, int64_t g1, int raise, int nthrea
                 int k = cand_cnt[i] < b->M0 ? cand_cnt[i] : b->M0;
                 for (int l = 0; l < MB_MAX_LEVELS; l++) sc->sel_cnt[l] = 0;
                 memcpy(sc->sel, cand + (size_t)i * (size_t)cand_stride, (size_t)k * sizeof(int32_t));
+                for (int j = 0; j < k; j++) sc->sel_d[j] = dist(b, vec_of(b, s), vec_of(b, sc->sel[j]));
                 sc->sel_cnt[0] = k;
             } else {
                 find_links(b, sc, s);
@@ -550,10 +573,12 @@ static void link_group(Builder *b, int64_t g0, int64_t g1, int raise, int nthrea
             for (int l = b->level[s] < b->max_level ? b->level[s] : b->max_level; l >= 0; l--) {
                 int32_t *mycnt;
                 int32_t *mine = list_ptr(b, s, l, &mycnt);
+                float *mine_d = dlist_ptr(b, s, l);
                 for (int j = 0; j < sc->sel_cnt[l]; j++) {
                     int32_t t = sc->sel[(size_t)l * (size_t)b->M0 + j];
-                    list_add(mine, mycnt, t);
-                    r[nr++] = (RevReq){t, l, s};
+                    float d = sc->sel_d[(size_t)l * (size_t)b->M0 + j];
+                    list_add(mine, mine_d, mycnt, t, d);
+                    r[nr++] = (RevReq){t, l, s, d};
                 }
             }
             req_n[i] = nr;
@@ -583,7 +608,7 @@ static void link_group(Builder *b, int64_t g0, int64_t g1, int raise, int nthrea
                 int M_max = l == 0 ? b->M0 : b->M;
                 int32_t *tc;
                 int32_t *tl = list_ptr(b, t, l, &tc);
-                list_add(tl, tc, req[i].src);
+                list_add(tl, dlist_ptr(b, t, l), tc, req[i].src, req[i].d);
                 if (*tc > M_max) prune(b, t, l, M_max, 0);
             }
         }
@@ -780,9 +805,9 @@ void muninn_build_destroy(void *h) {
     if (!b) return;
     for (int t = 0; t < b->n_scratch; t++) {
         Scratch *sc = &b->scratch[t];
-        free(sc->stamp); free(sc->cand.a); free(sc->res.a); free(sc->r_slot); free(sc->r_dist); free(sc->sel); free(sc->sel_cnt);
+        free(sc->stamp); free(sc->cand.a); free(sc->res.a); free(sc->r_slot); free(sc->r_dist); free(sc->sel); free(sc->sel_d); free(sc->sel_cnt);
     }
     free(b->scratch); free(b->touched);
-    free(b->level); free(b->nbr0); free(b->cnt0); free(b->upper_base); free(b->nbrU); free(b->cntU);
+    free(b->level); free(b->nbr0); free(b->cnt0); free(b->d0); free(b->dU); free(b->upper_base); free(b->nbrU); free(b->cntU);
     free(b);
 }
