@@ -183,3 +183,14 @@ def test_tie_free_quality_equals_host():
     check_graph_invariants(dev)
     assert recall_at_10(dev, q) >= 0.9
 
+
+
+def test_no_device_no_build():
+    """Without an index argument the searches go to the GPU or nowhere: there is no host fallback behind this call."""
+    from sqlite_muninn_b200 import cuda
+    if cuda.device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    x = np.random.default_rng(2).standard_normal((200, 8)).astype(np.float32)
+    with pytest.raises(cuda.MuninnCudaError) as e:
+        build_graph_device(x, 0, 4, 20, batch=32, warm=50)
+    assert e.value.code == -2  # MUNINN_CUDA_E_NODEVICE
