@@ -103,9 +103,16 @@ def write_shadow(conn: sqlite3.Connection, name: str, g: FlatGraph, with_distanc
     e_tgt = g.targets.astype(np.int64)
     keep = e_tgt >= 0
     e_src, e_lvl, e_tgt = e_src[keep], e_lvl[keep], e_tgt[keep]
-    if with_distance:
-        diff = g.vectors[e_src] - g.vectors[e_tgt]
-        dist = np.einsum("ij,ij->i", diff, diff).astype(np.float64).tolist()
+    if with_distance:  # informational: plain numpy sums, not the reference's summation order
+        a, b = g.vectors[e_src], g.vectors[e_tgt]
+        if g.metric == 0:
+            dist = np.einsum("ij,ij->i", a - b, a - b)
+        elif g.metric == 2:
+            dist = -np.einsum("ij,ij->i", a, b)
+        else:
+            den = np.sqrt(np.einsum("ij,ij->i", a, a)) * np.sqrt(np.einsum("ij,ij->i", b, b))
+            dist = np.where(den < 1e-30, 1.0, 1.0 - np.einsum("ij,ij->i", a, b) / np.maximum(den, 1e-30))
+        dist = dist.astype(np.float64).tolist()
     else:
         dist = [0.0] * int(e_src.shape[0])
     cur.executemany(f'INSERT INTO "{name}_edges" (source_id, target_id, level, distance) VALUES (?, ?, ?, ?)',
@@ -113,3 +120,19 @@ def write_shadow(conn: sqlite3.Connection, name: str, g: FlatGraph, with_distanc
     # the reverse index (src/hnsw_vtab.c:177) is built once over the finished table, not row by row
     cur.execute(f'CREATE INDEX IF NOT EXISTS "{name}_edges_rev" ON "{name}_edges"(target_id, level)')
     conn.commit()
+
+
+def register_vtab(conn: sqlite3.Connection, name: str, g: FlatGraph) -> None:
+    """Make the shadow tables written by `write_shadow` a virtual table of this database without running xCreate
+    (which would start an empty index): the schema row `CREATE VIRTUAL TABLE <name> USING hnsw_index(...)`
+    (arguments as parsed at src/hnsw_vtab.c:80-134) is stored directly, so the next connection that has the
+    extension loaded xConnects to the stored graph (src/hnsw_vtab.c:286-341)."""
+    from .graph import METRIC_NAMES
+    sql = (f"CREATE VIRTUAL TABLE {name} USING hnsw_index(dimensions={g.dim}, metric='{METRIC_NAMES[g.metric]}', "
+           f"m={g.M}, ef_construction={g.ef_construction})")
+    conn.execute("PRAGMA writable_schema=ON")
+    conn.execute("INSERT INTO sqlite_master(type, name, tbl_name, rootpage, sql) VALUES('table', ?, ?, 0, ?)",
+                 (name, name, sql))
+    conn.execute("PRAGMA writable_schema=OFF")
+    conn.commit()
+

@@ -4,6 +4,7 @@ import ctypes
 import os
 import re
 import sqlite3
+import sys
 
 import numpy as np
 import pytest
@@ -174,3 +175,34 @@ def test_batch_tvf_argument_errors_need_no_device(tmp_path):
     if cuda.device_count() == 0:
         with pytest.raises(sqlite3.OperationalError, match="no CUDA device"):
             c.execute("SELECT * FROM hnsw_knn_batch('t', ?, 3)", (q,)).fetchall()
+
+
+def test_bulk_loader_output_is_a_table_of_the_unmodified_reference(tmp_path, oracle):
+    """tools/bulk_load.py (host searches here; the GPU variant builds the same graph): the next connection with the
+    unmodified extension loaded sees a populated hnsw_index and answers MATCH like the oracle on that graph."""
+    from oracle.bindings import REF_EXT_SO
+    if not os.path.exists(REF_EXT_SO):
+        pytest.skip("reference extension not built")
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import bulk_load
+    base = uniform(31, 700, 12)
+    np.save(tmp_path / "v.npy", base)
+    db = str(tmp_path / "bulk.db")
+    bulk_load.main([str(tmp_path / "v.npy"), db, "docs", "--metric", "cosine", "--m", "8", "--ef-construction", "48",
+                    "--batch", "64", "--host", "--with-distance"])
+    g = build_graph(base, 1, 8, 48, ids=np.arange(1, 701, dtype=np.int64), batch=64)
+    conn = sqlite3.connect(db)
+    conn.enable_load_extension(True)
+    conn.load_extension(REF_EXT_SO, entrypoint="sqlite3_muninn_init")
+    assert conn.execute("SELECT count(*) FROM docs_nodes").fetchone()[0] == 700
+    q = uniform(32, 10, 12)
+    ids, dist, cnt, _, _ = oracle.graph(g).search(q, 5, 40)
+    for i in range(10):
+        rows = conn.execute("SELECT rowid, distance FROM docs WHERE vector MATCH ? AND k = 5 AND ef_search = 40",
+                            (q[i].tobytes(),)).fetchall()
+        assert [r[0] for r in rows] == list(ids[i, :cnt[i]])
+        assert [r[1] for r in rows] == [float(x) for x in dist[i, :cnt[i]]]
+    # and it is a live table: the reference's own INSERT extends it
+    conn.execute("INSERT INTO docs(rowid, vector) VALUES (?, ?)", (1000, q[0].tobytes()))
+    row = conn.execute("SELECT rowid FROM docs WHERE vector MATCH ? AND k = 1", (q[0].tobytes(),)).fetchone()
+    assert row[0] == 1000
