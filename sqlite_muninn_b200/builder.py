@@ -162,7 +162,7 @@ def build_graph_device(vectors, metric: int = 0, M: int = 16, ef_construction: i
             t = clock()
             log = np.empty(max(cnt, 1), np.int32)
             cnt = L.muninn_build_touched_take(h, log, log.shape[0])
-            old = np.unique(log[:cnt])
+            old = log[:cnt]  # each slot once (the builder de-duplicates while logging)
             old = old[old < n_dev]
             slots = np.concatenate([np.arange(n_dev, n_now, dtype=np.int32), old.astype(np.int32)])  # new nodes first
             nl, ne = C.c_int64(), C.c_int64()

@@ -74,6 +74,7 @@ typedef struct {
     int n_scratch; Scratch *scratch;
     int lazy_mn_parallel_skip;
     int log_touched; int32_t *touched; int64_t n_touched, cap_touched;
+    uint32_t *touch_stamp; uint32_t touch_epoch; /* a slot is logged once per epoch (= until the log is taken) */
     int64_t pending_g0, pending_g1; int pending_raise; /* group opened by muninn_build_group_begin */
     double t_phase[3]; /* seconds in link_group: searches + own lists, request sort, reverse edges + prune */
 } Builder;
@@ -488,7 +489,8 @@ static double now_s(void) {
 /* ───────────── touched-node log (what a device copy of the graph must be patched with) ───────────── */
 
 static void touch(Builder *b, int32_t s) {
-    if (!b->log_touched) return;
+    if (!b->log_touched || b->touch_stamp[s] == b->touch_epoch) return;
+    b->touch_stamp[s] = b->touch_epoch;
     if (b->n_touched == b->cap_touched) {
         b->cap_touched = b->cap_touched * 2 + 4096;
         b->touched = (int32_t *)realloc(b->touched, (size_t)b->cap_touched * sizeof(int32_t));
@@ -672,8 +674,10 @@ int muninn_build_insert(void *h, int64_t count, int batch, int64_t warm, int nth
 
 void muninn_build_log_touched(void *h, int on) {
     Builder *b = (Builder *)h;
-    b->log_touched = on;
+    if (on && !b->touch_stamp) b->touch_stamp = (uint32_t *)calloc((size_t)b->cap, sizeof(uint32_t));
+    b->log_touched = on && b->touch_stamp;
     b->n_touched = 0;
+    if (++b->touch_epoch == 0) { memset(b->touch_stamp, 0, (size_t)b->cap * sizeof(uint32_t)); b->touch_epoch = 1; }
 }
 
 int64_t muninn_build_count(void *h) { return ((Builder *)h)->n; }
@@ -722,12 +726,13 @@ int muninn_build_group_link(void *h, const int32_t *cand, const int32_t *cand_cn
 
 int64_t muninn_build_touched_count(void *h) { return ((Builder *)h)->n_touched; }
 
-/* Copy the log (unsorted, with repeats) and clear it. */
+/* Copy the log (each touched slot once, in no particular order) and clear it. */
 int64_t muninn_build_touched_take(void *h, int32_t *out, int64_t cap) {
     Builder *b = (Builder *)h;
     int64_t n = b->n_touched < cap ? b->n_touched : cap;
     memcpy(out, b->touched, (size_t)n * sizeof(int32_t));
     b->n_touched = 0;
+    if (b->touch_stamp && ++b->touch_epoch == 0) { memset(b->touch_stamp, 0, (size_t)b->cap * sizeof(uint32_t)); b->touch_epoch = 1; }
     return n;
 }
 
@@ -807,7 +812,7 @@ void muninn_build_destroy(void *h) {
         Scratch *sc = &b->scratch[t];
         free(sc->stamp); free(sc->cand.a); free(sc->res.a); free(sc->r_slot); free(sc->r_dist); free(sc->sel); free(sc->sel_d); free(sc->sel_cnt);
     }
-    free(b->scratch); free(b->touched);
+    free(b->scratch); free(b->touched); free(b->touch_stamp);
     free(b->level); free(b->nbr0); free(b->cnt0); free(b->d0); free(b->dU); free(b->upper_base); free(b->nbrU); free(b->cntU);
     free(b);
 }
