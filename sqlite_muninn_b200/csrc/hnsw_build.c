@@ -20,14 +20,24 @@
  *   exact  (batch = 0): one insert at a time. O(1) visited stamps and a lazily evaluated
  *          mutual-neighbour count (it only matters when two distances are bit-equal) are
  *          pure representation changes, so the graph is IDENTICAL to the reference's —
- *          entry point, levels and ordered neighbour lists (tests/test_builder.py diffs it
+ *          entry point, levels and ordered neighbour lists (tests/test_host.py diffs it
  *          against the real reference).
  *   batch  (batch > 0): nodes are inserted in id order in groups; each group searches the
  *          graph as it stood before the group (parallel, read-only) and is then linked in
  *          id order, reverse edges grouped per target so every list has one writer.  The
  *          result is deterministic for a given batch size, independent of thread count,
  *          and is a graph of the reference's construction rule but not its exact
- *          sequential graph.  Used only to make full-size benchmark inputs in minutes.
+ *          sequential graph.  Bit-equal candidate distances are ordered by slot here (the
+ *          reference's heap order among equal keys is unspecified).  Makes full-size benchmark
+ *          inputs and bulk-loaded tables (tools/bulk_load.py) in minutes.
+ *   group  the batch mode one group at a time (muninn_build_group_begin / _group_link), for a
+ *          caller that runs the layer-0 candidate searches itself — builder.build_graph_device
+ *          runs them as one muninn_cuda_search_batch per group on a device copy of the graph
+ *          and writes the touched records back with muninn_cuda_index_patch.  Same graph as
+ *          the batch mode wherever no two candidate distances are bit-equal.
+ *
+ * Every stored edge keeps the distance it was created with (as the reference's _edges table
+ * does, src/hnsw_vtab.c:163-169), so a prune re-reads 2M+1 floats instead of recomputing them.
  *
  * Distances are evaluated in the reference's SSE order (src/vec_math.c:78-143) so that
  * the exact mode reproduces its comparisons bit for bit.
