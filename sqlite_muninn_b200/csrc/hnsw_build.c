@@ -86,6 +86,7 @@ typedef struct {
     int log_touched; int32_t *touched; int64_t n_touched, cap_touched;
     uint32_t *touch_stamp; uint32_t touch_epoch; /* a slot is logged once per epoch (= until the log is taken) */
     int64_t pending_g0, pending_g1; int pending_raise; /* group opened by muninn_build_group_begin */
+    void *req_buf; int64_t req_cap; int64_t *grp_buf; int64_t grp_cap; /* link_group scratch, kept across groups */
     double t_phase[3]; /* seconds in link_group: searches + own lists, request sort, reverse edges + prune */
 } Builder;
 
@@ -560,7 +561,12 @@ static void link_group(Builder *b, int64_t g0, int64_t g1, int raise, int nthrea
     if (gn > 0) {
         /* phase A: parallel read-only searches; each node writes only its own lists */
         int64_t per = (int64_t)b->M0 + (int64_t)b->M * MB_MAX_LEVELS;
-        RevReq *req = (RevReq *)malloc((size_t)(gn * per) * sizeof(RevReq));
+        if (gn * per > b->req_cap) {
+            free(b->req_buf);
+            b->req_buf = malloc((size_t)(gn * per) * sizeof(RevReq));
+            b->req_cap = gn * per;
+        }
+        RevReq *req = (RevReq *)b->req_buf;
         int32_t *req_n = (int32_t *)calloc((size_t)gn, sizeof(int32_t));
         double t0 = now_s();
 #pragma omp parallel for schedule(dynamic, 4) num_threads(nthreads)
@@ -605,7 +611,12 @@ static void link_group(Builder *b, int64_t g0, int64_t g1, int raise, int nthrea
         free(req_n);
         sort_requests(req, tot, (int32_t)g0);
         /* group boundaries per target */
-        int64_t *grp = (int64_t *)malloc((size_t)(tot + 1) * sizeof(int64_t));
+        if (tot + 1 > b->grp_cap) {
+            free(b->grp_buf);
+            b->grp_buf = (int64_t *)malloc((size_t)(tot + 1) * sizeof(int64_t));
+            b->grp_cap = tot + 1;
+        }
+        int64_t *grp = b->grp_buf;
         int64_t ng = 0;
         for (int64_t i = 0; i < tot; i++)
             if (i == 0 || req[i].target != req[i - 1].target) { grp[ng++] = i; touch(b, req[i].target); }
@@ -624,7 +635,6 @@ static void link_group(Builder *b, int64_t g0, int64_t g1, int raise, int nthrea
                 if (*tc > M_max) prune(b, t, l, M_max, 0);
             }
         }
-        free(req); free(grp);
         b->n = g1;
         b->t_phase[0] += t1 - t0; b->t_phase[1] += t2 - t1; b->t_phase[2] += now_s() - t2;
     }
@@ -822,7 +832,7 @@ void muninn_build_destroy(void *h) {
         Scratch *sc = &b->scratch[t];
         free(sc->stamp); free(sc->cand.a); free(sc->res.a); free(sc->r_slot); free(sc->r_dist); free(sc->sel); free(sc->sel_d); free(sc->sel_cnt);
     }
-    free(b->scratch); free(b->touched); free(b->touch_stamp);
+    free(b->scratch); free(b->touched); free(b->touch_stamp); free(b->req_buf); free(b->grp_buf);
     free(b->level); free(b->nbr0); free(b->cnt0); free(b->d0); free(b->dU); free(b->upper_base); free(b->nbrU); free(b->cntU);
     free(b);
 }
