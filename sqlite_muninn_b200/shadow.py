@@ -16,11 +16,14 @@ format so that the unmodified reference extension can xConnect to graphs built h
 """
 from __future__ import annotations
 
+import itertools
 import sqlite3
 
 import numpy as np
 
 from .graph import FlatGraph
+
+_CHUNK = 262144  # rows per fetchmany
 
 
 def read_config(conn: sqlite3.Connection, name: str) -> dict:
@@ -33,20 +36,40 @@ def load_from_shadow(conn: sqlite3.Connection, name: str) -> FlatGraph:
     dim, metric, M = int(cfg["dimensions"]), int(cfg["metric"]), int(cfg["m"])
     efc = int(cfg["ef_construction"])
     entry_id, max_level = int(cfg.get("entry_point", -1)), int(cfg.get("max_level", -1))
-    nodes = conn.execute(f'SELECT id, vector, level, deleted FROM "{name}_nodes" ORDER BY id').fetchall()
-    n = len(nodes)
-    ids = np.fromiter((r[0] for r in nodes), np.int64, n)
-    levels = np.fromiter((r[2] for r in nodes), np.int32, n)
-    deleted = np.fromiter((1 if r[3] else 0 for r in nodes), np.uint8, n)
+    # rows are streamed in chunks into flat numpy arrays: a fetchall() of 32M edge tuples would hold several GB of
+    # Python objects at 1M x 32 edges
+    n = int(conn.execute(f'SELECT count(*) FROM "{name}_nodes"').fetchone()[0])
+    ids, levels, deleted = np.empty(n, np.int64), np.empty(n, np.int32), np.empty(n, np.uint8)
     vectors = np.empty((n, dim), np.float32)
-    for i, r in enumerate(nodes):
-        vectors[i] = np.frombuffer(r[1], np.float32, dim)
+    cur = conn.execute(f'SELECT id, level, deleted, vector FROM "{name}_nodes" ORDER BY id')
+    at = 0
+    while True:
+        rows = cur.fetchmany(_CHUNK)
+        if not rows:
+            break
+        m = len(rows)
+        meta = np.fromiter(itertools.chain.from_iterable((r[0], r[1], 1 if r[2] else 0) for r in rows), np.int64, 3 * m)
+        meta = meta.reshape(m, 3)
+        ids[at:at + m], levels[at:at + m], deleted[at:at + m] = meta[:, 0], meta[:, 1], meta[:, 2]
+        blob = b"".join(r[3] for r in rows)
+        if len(blob) != m * dim * 4:
+            raise ValueError(f"{name}_nodes: a vector blob is not {dim * 4} bytes")
+        vectors[at:at + m] = np.frombuffer(blob, np.float32).reshape(m, dim)
+        at += m
     first = np.zeros(n + 1, np.int64)
     np.cumsum(levels.astype(np.int64) + 1, out=first[1:])
     n_lists = int(first[-1])
-    edges = np.array(conn.execute(
-        f'SELECT source_id, level, target_id FROM "{name}_edges" ORDER BY source_id, level, target_id').fetchall(),
-        dtype=np.int64).reshape(-1, 3)
+    n_edges = int(conn.execute(f'SELECT count(*) FROM "{name}_edges"').fetchone()[0])
+    edges = np.empty((n_edges, 3), np.int64)
+    cur = conn.execute(f'SELECT source_id, level, target_id FROM "{name}_edges" ORDER BY source_id, level, target_id')
+    at = 0
+    while True:
+        rows = cur.fetchmany(_CHUNK)
+        if not rows:
+            break
+        m = len(rows)
+        edges[at:at + m] = np.fromiter(itertools.chain.from_iterable(rows), np.int64, 3 * m).reshape(m, 3)
+        at += m
     counts = np.zeros(n_lists, np.int64)
     if edges.shape[0]:
         src = np.searchsorted(ids, edges[:, 0])
