@@ -126,20 +126,23 @@ def write_shadow(conn: sqlite3.Connection, name: str, g: FlatGraph, with_distanc
     e_tgt = g.targets.astype(np.int64)
     keep = e_tgt >= 0
     e_src, e_lvl, e_tgt = e_src[keep], e_lvl[keep], e_tgt[keep]
-    if with_distance:  # informational: plain numpy sums, not the reference's summation order
-        a, b = g.vectors[e_src], g.vectors[e_tgt]
-        if g.metric == 0:
-            dist = np.einsum("ij,ij->i", a - b, a - b)
-        elif g.metric == 2:
-            dist = -np.einsum("ij,ij->i", a, b)
+    id_src, id_tgt = g.ids[e_src], g.ids[e_tgt]
+    for lo in range(0, int(e_src.shape[0]), _CHUNK * 4):  # chunks bound the Python-object footprint (32M edges at 1M x 32)
+        hi = min(lo + _CHUNK * 4, int(e_src.shape[0]))
+        if with_distance:  # informational: plain numpy sums, not the reference's summation order
+            a, b = g.vectors[e_src[lo:hi]], g.vectors[e_tgt[lo:hi]]
+            if g.metric == 0:
+                dist = np.einsum("ij,ij->i", a - b, a - b)
+            elif g.metric == 2:
+                dist = -np.einsum("ij,ij->i", a, b)
+            else:
+                den = np.sqrt(np.einsum("ij,ij->i", a, a)) * np.sqrt(np.einsum("ij,ij->i", b, b))
+                dist = np.where(den < 1e-30, 1.0, 1.0 - np.einsum("ij,ij->i", a, b) / np.maximum(den, 1e-30))
+            dist = dist.astype(np.float64).tolist()
         else:
-            den = np.sqrt(np.einsum("ij,ij->i", a, a)) * np.sqrt(np.einsum("ij,ij->i", b, b))
-            dist = np.where(den < 1e-30, 1.0, 1.0 - np.einsum("ij,ij->i", a, b) / np.maximum(den, 1e-30))
-        dist = dist.astype(np.float64).tolist()
-    else:
-        dist = [0.0] * int(e_src.shape[0])
-    cur.executemany(f'INSERT INTO "{name}_edges" (source_id, target_id, level, distance) VALUES (?, ?, ?, ?)',
-                    zip(g.ids[e_src].tolist(), g.ids[e_tgt].tolist(), e_lvl.tolist(), dist))
+            dist = itertools.repeat(0.0, hi - lo)
+        cur.executemany(f'INSERT INTO "{name}_edges" (source_id, target_id, level, distance) VALUES (?, ?, ?, ?)',
+                        zip(id_src[lo:hi].tolist(), id_tgt[lo:hi].tolist(), e_lvl[lo:hi].tolist(), dist))
     # the reverse index (src/hnsw_vtab.c:177) is built once over the finished table, not row by row
     cur.execute(f'CREATE INDEX IF NOT EXISTS "{name}_edges_rev" ON "{name}_edges"(target_id, level)')
     conn.commit()
