@@ -1,10 +1,13 @@
 """CPU: the pieces of bench.py the reported numbers rest on — the algorithmic-bytes formula of SURVEY.md §8(d),
 recall as `benchmarks/harness/treatments/vss.py:96-102` computes it, the workload generators' determinism, and
 that the oracle's per-query counters (what the GPU must reproduce) feed the formula."""
+import os
+
 import numpy as np
+import pytest
 
 import bench
-from tests.conftest import uniform
+from tests.conftest import ROOT, uniform
 
 
 def test_algorithmic_bytes_formula():
@@ -45,3 +48,29 @@ def test_oracle_counters_feed_the_formula(oracle):
     assert (cnt == 5).all()
     b = bench.algorithmic_bytes(stats, 16, 8, 5)
     assert b > 20 * 40 * 16 * 4  # at least ef distances per query
+
+
+def test_reference_arm_prints_the_contract_line(tmp_path):
+    """`bench.py --impl reference` (the unmodified reference on the host cores) at a reduced size: one JSON line with
+    the keys the driver reads. Needs oracle/_ref (built where /root/reference is present; prebuilt on the GPU box)."""
+    import json
+    import subprocess
+    import sys
+    from oracle.bindings import have_reference
+    if not have_reference():
+        pytest.skip("oracle/_ref not built")
+    env = dict(os.environ, MUNINN_BENCH_CACHE=str(tmp_path))
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--n", "6000", "--nq", "200",
+                          "--efc", "40", "--steps", "2", "--warmup", "1", "--ef", "32"], capture_output=True, text=True,
+                         env=env, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [l for l in out.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"].startswith("HNSW QPS") and d["unit"] == "queries/s"
+    assert d["higher_is_better"] is True and d["n_gpus"] == 1 and d["steps"] == 2 and d["warmup"] == 1
+    assert d["value"] > 0 and d["ms_per_step"] > 0 and "workload" in d["config"]
+    cb = d["cpu_baseline"]
+    assert cb["kind"] == "reference" and cb["cores"] >= 1 and cb["sample"] and cb["value"] == d["value"]
+    assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert d["gpu_launches"] == 0
