@@ -18,14 +18,16 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tools"))
 import bulk_load  # noqa: E402
-from oracle.bindings import REF_EXT_SO, Oracle  # noqa: E402  (checker: brute-force ground truth)
+
+REF_EXT_SO = os.path.join(ROOT, "oracle", "_ref", "muninn_ref_ext.so")  # the unmodified reference extension: the arm timed
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 10_000
 dim, M, efc, nq = 128, 16, 200, 1000
 base = np.random.default_rng(1).uniform(-1, 1, (n, dim)).astype(np.float32)
 queries = np.random.default_rng(2).uniform(-1, 1, (nq, dim)).astype(np.float32)
-truth, _, _, _ = Oracle().exact_knn(base, queries, 10, 0, threads=os.cpu_count())
-truth += 1  # rowids 1..n
+# ground truth as the reference's harness computes it (numpy brute force, benchmarks/harness/treatments/vss.py:70-93)
+d2 = (queries ** 2).sum(1)[:, None] - 2.0 * queries.astype(np.float64) @ base.astype(np.float64).T + (base.astype(np.float64) ** 2).sum(1)[None, :]
+truth = np.argsort(d2, axis=1, kind="stable")[:, :10] + 1  # rowids 1..n
 
 
 def connect(path):
