@@ -41,6 +41,7 @@ def host_lib():
         L.muninn_build_sizes.argtypes = [C.c_void_p] + [C.POINTER(C.c_int64)] * 3 + [C.POINTER(C.c_int32)] * 2
         L.muninn_build_export.argtypes = [C.c_void_p, _i32, _i64, _i32, C.c_int]
         L.muninn_build_destroy.argtypes = [C.c_void_p]
+        L.muninn_build_set_avx2.argtypes = [C.c_int]
         # group-at-a-time interface (the device-assisted loop below)
         L.muninn_build_log_touched.argtypes = [C.c_void_p, C.c_int]
         L.muninn_build_count.restype = C.c_int64

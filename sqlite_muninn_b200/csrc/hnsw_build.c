@@ -51,7 +51,7 @@
 #ifdef _OPENMP
 #include <omp.h>
 #endif
-#include <xmmintrin.h>
+#include <immintrin.h>
 
 enum { MB_L2 = 0, MB_COSINE = 1, MB_IP = 2 };
 #define MB_MAX_LEVELS 32 /* src/hnsw_algo.h:14 */
@@ -65,6 +65,7 @@ typedef struct {
     int32_t *r_slot; float *r_dist; /* beam output, ascending, capacity efc */
     int32_t *sel;                   /* per level selected: [MB_MAX_LEVELS][M0] */
     float *sel_d;                   /* their distances to the new node */
+    int32_t *fresh; float *fresh_d; /* unvisited entries of the list being expanded: [M0 + 1] */
     int32_t *sel_cnt;               /* [MB_MAX_LEVELS] */
 } Scratch;
 
@@ -143,6 +144,93 @@ static float dist_cos(const float *a, const float *b, int dim) {
 static inline float dist(const Builder *b, const float *x, const float *y) {
     return b->metric == MB_L2 ? dist_l2(x, y, b->dim) : b->metric == MB_COSINE ? dist_cos(x, y, b->dim)
                                                                                 : dist_ip(x, y, b->dim);
+}
+
+/* Two rows at once on AVX2 hosts: the low and the high 128-bit half of every register run the reference's 4-lane
+ * SSE chain for row x0 and row x1 respectively (the query is broadcast to both halves), so each row's result is
+ * the same sequence of IEEE operations as dist_*() above — bit-identical, checked against the unmodified reference
+ * by tests/test_host.py through the graphs it produces. target("avx2") does not enable FMA: mul and add stay two
+ * roundings, as in the reference's SSE path. */
+#define AVX2_FN __attribute__((target("avx2")))
+
+AVX2_FN static inline __m256 two_rows(const float *x0, const float *x1) {
+    return _mm256_insertf128_ps(_mm256_castps128_ps256(_mm_loadu_ps(x0)), _mm_loadu_ps(x1), 1);
+}
+
+AVX2_FN static void dist2_l2(const float *q, const float *x0, const float *x1, int dim, float *o0, float *o1) {
+    __m256 acc = _mm256_setzero_ps();
+    int i = 0;
+    for (; i + 4 <= dim; i += 4) {
+        __m256 d = _mm256_sub_ps(_mm256_broadcast_ps((const __m128 *)(q + i)), two_rows(x0 + i, x1 + i));
+        acc = _mm256_add_ps(acc, _mm256_mul_ps(d, d));
+    }
+    float t[8];
+    _mm256_storeu_ps(t, acc);
+    float s0 = t[0] + t[1] + t[2] + t[3], s1 = t[4] + t[5] + t[6] + t[7];
+    for (; i < dim; i++) {
+        float d0 = q[i] - x0[i], d1 = q[i] - x1[i];
+        float p0 = d0 * d0, p1 = d1 * d1;
+        s0 = s0 + p0; s1 = s1 + p1;
+    }
+    *o0 = s0; *o1 = s1;
+}
+
+AVX2_FN static void dist2_ip(const float *q, const float *x0, const float *x1, int dim, float *o0, float *o1) {
+    __m256 acc = _mm256_setzero_ps();
+    int i = 0;
+    for (; i + 4 <= dim; i += 4)
+        acc = _mm256_add_ps(acc, _mm256_mul_ps(_mm256_broadcast_ps((const __m128 *)(q + i)), two_rows(x0 + i, x1 + i)));
+    float t[8];
+    _mm256_storeu_ps(t, acc);
+    float s0 = t[0] + t[1] + t[2] + t[3], s1 = t[4] + t[5] + t[6] + t[7];
+    for (; i < dim; i++) {
+        float p0 = q[i] * x0[i], p1 = q[i] * x1[i];
+        s0 = s0 + p0; s1 = s1 + p1;
+    }
+    *o0 = -s0; *o1 = -s1;
+}
+
+AVX2_FN static void dist2_cos(const float *q, const float *x0, const float *x1, int dim, float *o0, float *o1) {
+    __m256 ad = _mm256_setzero_ps(), aa = _mm256_setzero_ps(), ab = _mm256_setzero_ps();
+    int i = 0;
+    for (; i + 4 <= dim; i += 4) {
+        __m256 va = _mm256_broadcast_ps((const __m128 *)(q + i)), vb = two_rows(x0 + i, x1 + i);
+        ad = _mm256_add_ps(ad, _mm256_mul_ps(va, vb));
+        aa = _mm256_add_ps(aa, _mm256_mul_ps(va, va));
+        ab = _mm256_add_ps(ab, _mm256_mul_ps(vb, vb));
+    }
+    float td[8], ta[8], tb[8];
+    _mm256_storeu_ps(td, ad); _mm256_storeu_ps(ta, aa); _mm256_storeu_ps(tb, ab);
+    const float *x[2] = {x0, x1};
+    float *o[2] = {o0, o1};
+    for (int h = 0; h < 2; h++) {
+        float dot = td[4 * h] + td[4 * h + 1] + td[4 * h + 2] + td[4 * h + 3];
+        float na = ta[4 * h] + ta[4 * h + 1] + ta[4 * h + 2] + ta[4 * h + 3];
+        float nb = tb[4 * h] + tb[4 * h + 1] + tb[4 * h + 2] + tb[4 * h + 3];
+        for (int j = i; j < dim; j++) {
+            float p;
+            p = q[j] * x[h][j]; dot = dot + p;
+            p = q[j] * q[j]; na = na + p;
+            p = x[h][j] * x[h][j]; nb = nb + p;
+        }
+        float denom = sqrtf(na) * sqrtf(nb);
+        *o[h] = denom < 1e-30f ? 1.0f : 1.0f - (dot / denom);
+    }
+}
+
+static int g_avx2 = -1;
+int muninn_build_set_avx2(int on);
+
+/* distances from q to two rows; same values as two dist() calls */
+static inline void dist_pair(const Builder *b, const float *q, const float *x0, const float *x1, float *o0, float *o1) {
+    if (g_avx2 > 0) {
+        if (b->metric == MB_L2) dist2_l2(q, x0, x1, b->dim, o0, o1);
+        else if (b->metric == MB_COSINE) dist2_cos(q, x0, x1, b->dim, o0, o1);
+        else dist2_ip(q, x0, x1, b->dim, o0, o1);
+    } else {
+        *o0 = dist(b, q, x0);
+        *o1 = dist(b, q, x1);
+    }
 }
 
 /* ───────────── heap with the reference's sift rules (src/priority_queue.c:18-42) ───────────── */
@@ -291,17 +379,23 @@ static int beam(const Builder *b, Scratch *sc, const float *q, int32_t entry, in
         if (stale >= patience_max && sc->res.size >= ef) break;
         int32_t *cnt;
         const int32_t *lst = list_ptr(b, c.slot, l, &cnt);
-        int n = *cnt, improved = 0;
-        for (int i = 0; i < n; i++) {
-            int32_t t = lst[i];
-            if (sc->stamp[t] == sc->cur) continue;
-            __builtin_prefetch(vec_of(b, t));
-        }
+        int n = *cnt, improved = 0, nf = 0;
+        int32_t *fresh = sc->fresh;
+        float *fd = sc->fresh_d;
+        /* a list holds a slot at most once (list_add), so marking the unvisited entries first and evaluating them
+         * afterwards — two rows per call — visits the same nodes in the same order as the reference's single loop */
         for (int i = 0; i < n; i++) {
             int32_t t = lst[i];
             if (sc->stamp[t] == sc->cur) continue;
             sc->stamp[t] = sc->cur;
-            float d = dist(b, q, vec_of(b, t));
+            __builtin_prefetch(vec_of(b, t));
+            fresh[nf++] = t;
+        }
+        for (int i = 0; i + 1 < nf; i += 2) dist_pair(b, q, vec_of(b, fresh[i]), vec_of(b, fresh[i + 1]), &fd[i], &fd[i + 1]);
+        if (nf & 1) fd[nf - 1] = dist(b, q, vec_of(b, fresh[nf - 1]));
+        for (int i = 0; i < nf; i++) {
+            int32_t t = fresh[i];
+            float d = fd[i];
             if (sc->res.size < ef) { hp_push(&sc->cand, t, d); hp_push(&sc->res, t, -d); improved = 1; }
             else if (d < -sc->res.a[1].key) { hp_push(&sc->cand, t, d); hp_pop(&sc->res); hp_push(&sc->res, t, -d); improved = 1; }
         }
@@ -469,11 +563,14 @@ static void scratch_init(Builder *b, Scratch *sc) {
     sc->sel = (int32_t *)malloc((size_t)MB_MAX_LEVELS * (size_t)b->M0 * sizeof(int32_t));
     sc->sel_d = (float *)malloc((size_t)MB_MAX_LEVELS * (size_t)b->M0 * sizeof(float));
     sc->sel_cnt = (int32_t *)calloc(MB_MAX_LEVELS, sizeof(int32_t));
+    sc->fresh = (int32_t *)malloc((size_t)(b->M0 + 1) * sizeof(int32_t));
+    sc->fresh_d = (float *)malloc((size_t)(b->M0 + 1) * sizeof(float));
 }
 
 void *muninn_build_create(int dim, int metric, int M, int ef_construction, int64_t capacity, const float *vectors) {
     Builder *b = (Builder *)calloc(1, sizeof(Builder));
     if (!b) return NULL;
+    if (g_avx2 < 0) muninn_build_set_avx2(-1);
     b->dim = dim; b->metric = metric; b->M = M; b->M0 = 2 * M; /* src/hnsw_algo.c:188 */
     b->efc = ef_construction; b->cap = capacity; b->vecs = vectors;
     b->level = (int32_t *)malloc((size_t)capacity * sizeof(int32_t));
@@ -487,6 +584,14 @@ void *muninn_build_create(int dim, int metric, int M, int ef_construction, int64
     b->level_mult = 1.0 / log((double)M);
     if (!b->level || !b->nbr0 || !b->cnt0 || !b->d0 || !b->upper_base) return NULL;
     return b;
+}
+
+/* Two-rows-per-call AVX2 distances on (1) / off (0) / as detected (-1); returns what is in effect. The graphs do not
+ * depend on it (tests/test_host.py); MUNINN_BUILD_NO_AVX2 in the environment also turns it off. */
+int muninn_build_set_avx2(int on) {
+    if (on < 0) g_avx2 = getenv("MUNINN_BUILD_NO_AVX2") ? 0 : (__builtin_cpu_supports("avx2") ? 1 : 0);
+    else g_avx2 = on && __builtin_cpu_supports("avx2");
+    return g_avx2;
 }
 
 void muninn_build_seed(void *h, uint32_t seed) { ((Builder *)h)->rng = seed ? seed : 1; } /* src/hnsw_algo.c:222-224 */
@@ -830,7 +935,7 @@ void muninn_build_destroy(void *h) {
     if (!b) return;
     for (int t = 0; t < b->n_scratch; t++) {
         Scratch *sc = &b->scratch[t];
-        free(sc->stamp); free(sc->cand.a); free(sc->res.a); free(sc->r_slot); free(sc->r_dist); free(sc->sel); free(sc->sel_d); free(sc->sel_cnt);
+        free(sc->stamp); free(sc->cand.a); free(sc->res.a); free(sc->r_slot); free(sc->r_dist); free(sc->sel); free(sc->sel_d); free(sc->sel_cnt); free(sc->fresh); free(sc->fresh_d);
     }
     free(b->scratch); free(b->touched); free(b->touch_stamp); free(b->req_buf); free(b->grp_buf);
     free(b->level); free(b->nbr0); free(b->cnt0); free(b->d0); free(b->dU); free(b->upper_base); free(b->nbrU); free(b->cntU);

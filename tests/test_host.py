@@ -206,3 +206,23 @@ def test_bulk_loader_output_is_a_table_of_the_unmodified_reference(tmp_path, ora
     conn.execute("INSERT INTO docs(rowid, vector) VALUES (?, ?)", (1000, q[0].tobytes()))
     row = conn.execute("SELECT rowid FROM docs WHERE vector MATCH ? AND k = 1", (q[0].tobytes(),)).fetchone()
     assert row[0] == 1000
+
+
+@pytest.mark.parametrize("dim", [1, 3, 7, 10, 131])
+@pytest.mark.parametrize("metric", [0, 1, 2])
+def test_builder_avx2_path_changes_nothing(metric, dim):
+    """The builder's two-rows-per-call AVX2 distances run the reference's 4-lane SSE chain in each register half:
+    same graphs as the scalar-pair path, row tails (dim % 4 != 0) included, in exact and in batch mode."""
+    from sqlite_muninn_b200.builder import host_lib
+    L = host_lib()
+    if L.muninn_build_set_avx2(1) != 1:
+        L.muninn_build_set_avx2(-1)
+        pytest.skip("host CPU has no AVX2")
+    try:
+        x = np.random.default_rng(dim * 3 + metric).standard_normal((900, dim)).astype(np.float32)
+        got = [build_graph(x, metric, 8, 40, batch=b, warm=150, sort_lists=False, threads=2) for b in (0, 96)]
+        L.muninn_build_set_avx2(0)
+        want = [build_graph(x, metric, 8, 40, batch=b, warm=150, sort_lists=False, threads=2) for b in (0, 96)]
+        assert got[0].same_structure(want[0]) and got[1].same_structure(want[1])
+    finally:
+        L.muninn_build_set_avx2(-1)
