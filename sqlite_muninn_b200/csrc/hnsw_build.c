@@ -373,6 +373,7 @@ static int beam(const Builder *b, Scratch *sc, const float *q, int32_t entry, in
     hp_push(&sc->res, entry, -d0);
     sc->stamp[entry] = sc->cur;
     int patience_max = ef / 4 < 10 ? 10 : ef / 4, stale = 0;
+    const int row_bytes = b->dim * (int)sizeof(float);
     while (sc->cand.size > 0) {
         HItem c = hp_pop(&sc->cand);
         if (sc->res.size >= ef && c.key > -sc->res.a[1].key) break;
@@ -388,7 +389,7 @@ static int beam(const Builder *b, Scratch *sc, const float *q, int32_t entry, in
             int32_t t = lst[i];
             if (sc->stamp[t] == sc->cur) continue;
             sc->stamp[t] = sc->cur;
-            __builtin_prefetch(vec_of(b, t));
+            { const char *pv = (const char *)vec_of(b, t); for (int o = 0; o < row_bytes; o += 64) __builtin_prefetch(pv + o); }
             fresh[nf++] = t;
         }
         for (int i = 0; i + 1 < nf; i += 2) dist_pair(b, q, vec_of(b, fresh[i]), vec_of(b, fresh[i + 1]), &fd[i], &fd[i + 1]);
