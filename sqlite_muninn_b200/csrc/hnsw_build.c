@@ -53,6 +53,8 @@
 #endif
 #include <immintrin.h>
 
+#include "muninn_build.h" /* include/: the ABI this file implements */
+
 enum { MB_L2 = 0, MB_COSINE = 1, MB_IP = 2 };
 #define MB_MAX_LEVELS 32 /* src/hnsw_algo.h:14 */
 
@@ -219,7 +221,6 @@ AVX2_FN static void dist2_cos(const float *q, const float *x0, const float *x1, 
 }
 
 static int g_avx2 = -1;
-int muninn_build_set_avx2(int on);
 
 /* distances from q to two rows; same values as two dist() calls */
 static inline void dist_pair(const Builder *b, const float *q, const float *x0, const float *x1, float *o0, float *o1) {

@@ -95,6 +95,19 @@ def test_abi_exports_every_declared_symbol():
         assert hasattr(L, sym), sym
 
 
+def test_host_library_exports_every_declared_symbol():
+    from sqlite_muninn_b200.builder import HOST_SO
+    header = open(os.path.join(ROOT, "include", "muninn_build.h")).read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)  # the usage sketch in the comment is not a declaration
+    declared = set(re.findall(r"\b(muninn_build_[a-z0-9_]+)\s*\(", header))
+    assert len(declared) == 17
+    L = ctypes.CDLL(HOST_SO)
+    for sym in declared:
+        assert hasattr(L, sym), sym
+    exported = set(re.findall(rb"\bmuninn_build_[a-z0-9_]+", open(HOST_SO, "rb").read()))
+    assert {e.decode() for e in exported} <= declared | {"muninn_build.h"}, "an exported entry point is missing from the header"
+
+
 def test_abi_host_only_calls():
     L = cuda.lib()
     assert L.muninn_cuda_version().startswith(b"muninn-b200")

@@ -9,7 +9,7 @@ OUT="$ROOT/build/sanitize"
 CC=/usr/bin/gcc
 mkdir -p "$OUT"
 SAN="-g -O1 -fno-omit-frame-pointer -fsanitize=address,undefined -fno-sanitize-recover=all"
-$CC $SAN -std=c11 -fPIC -fopenmp -Wall -Wextra -shared -o "$OUT/libmuninn_host.so" "$ROOT/sqlite_muninn_b200/csrc/hnsw_build.c" -lm
+$CC $SAN -std=c11 -fPIC -fopenmp -Wall -Wextra -I"$ROOT/include" -shared -o "$OUT/libmuninn_host.so" "$ROOT/sqlite_muninn_b200/csrc/hnsw_build.c" -lm
 $CC $SAN -std=c11 -fPIC -Wall -Wextra -shared -o "$OUT/liboracle.so" "$ROOT/oracle/hnsw_oracle.c" -lm -lpthread
 cd "$ROOT"
 # python itself is not instrumented: preload the runtime; CPython's own allocations make leak reports useless
