@@ -80,6 +80,37 @@ void muninn_build_entry(void *h, int32_t *entry, int32_t *max_level);
  * edges + MN-RU prune. */
 void muninn_build_phase_seconds(void *h, double out[3]);
 
+/* ── the group loop in C ──
+ * The searcher a group loop drives: a device copy of the graph behind three calls with the argument meaning of
+ * muninn_cuda_index_upload / muninn_cuda_index_patch (no deleted flags: a graph under construction has none) /
+ * muninn_cuda_search_batch (no stats). Each returns 0 on success. muninn_cuda_build_device (include/muninn_cuda.h)
+ * fills one in for a MuninnCudaIndex; the CPU tests fill one in with callbacks that answer from the oracle. */
+typedef struct MuninnBuildDevice {
+    void *ctx;
+    int (*upload)(void *ctx, int64_t n, const int64_t *ids, const int32_t *levels, const float *vectors,
+                  const int64_t *list_offsets, const int32_t *targets, int32_t entry_slot, int32_t max_level);
+    int (*patch)(void *ctx, int64_t n_total, int32_t n_patch, const int32_t *slots, const int64_t *ids,
+                 const int32_t *levels, const float *vectors, const int64_t *list_offsets, const int32_t *targets,
+                 int32_t entry_slot, int32_t max_level);
+    int (*search)(void *ctx, const float *queries, int nq, int k, int ef, int64_t *out_ids, float *out_dist,
+                  int32_t *out_count);
+} MuninnBuildDevice;
+
+typedef struct {
+    int64_t groups, device_queries, host_searches, patches, patched_records;
+    double warm_s, search_s, link_s, patch_s; /* wall seconds: exact warm-up inserts + upload, device searches,
+                                                 host linking, record export + patch */
+} MuninnBuildRunStats;
+
+/* Fill the (empty) builder to its capacity with the group loop sketched at the top of this file: `warm` exact
+ * inserts, one upload, then per group one dev->search over its level-0 nodes and one dev->patch with the touched
+ * records (new nodes first; `vectors` of a patch points at the first new node's row). ids[capacity] are the rowids,
+ * strictly ascending (NULL = 0..capacity-1). Returns 0, -1 on a bad argument / allocation failure / a candidate
+ * outside the graph, or the device call's own non-zero code. st may be NULL. There is no host fallback: a failing
+ * device call ends the build. */
+int muninn_build_run(void *h, const int64_t *ids, int batch, int64_t warm, int nthreads, const MuninnBuildDevice *dev,
+                     MuninnBuildRunStats *st);
+
 /* ── whole-graph export (the layout of muninn_cuda_index_upload) ── */
 void muninn_build_sizes(void *h, int64_t *n, int64_t *n_lists, int64_t *n_edges, int32_t *entry, int32_t *max_level);
 /* sort_lists = 1: neighbour lists ascending by target, the order load_index_from_shadow rebuilds

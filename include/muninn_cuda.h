@@ -16,6 +16,8 @@
  *   muninn_cuda_set_exact_mode / _exact_stats / _exact_filter_probe   evaluation strategy of the same
  *   muninn_cuda_distance_batch            vec_get_distance_func(metric)(a,b) src/vec_math.c:180-190
  *   muninn_cuda_parse_metric              vec_parse_metric                   src/vec_math.c:192-204
+ *   muninn_cuda_build_device              the searches inside a loop of hnsw_insert calls (bulk build)
+ *                                                                            src/hnsw_algo.c:553-579
  *
  * Plain C types only: pointers, sizes and ints.  No CPU fallback exists anywhere in the
  * library: without a CUDA device every compute entry point returns MUNINN_CUDA_E_NODEVICE.
@@ -201,6 +203,13 @@ int muninn_cuda_topk_merge_device(MuninnCudaIndex *idx, int parts, int nq, int k
 /* n distances metric(a[i], b[i]) with the reference's summation order (src/vec_math.c:78-143).
  * Host buffers [n × dim]; used by the known-answer tests of test/test_vec_math.c. */
 int muninn_cuda_distance_batch(int device, int metric, int dim, int64_t n, const float *a, const float *b, float *out);
+
+/* The handle as the searcher of the host builder's group loop (include/muninn_build.h: muninn_build_run): fills
+ * `out` with this handle and thin wrappers over muninn_cuda_index_upload / _index_patch / _search_batch, so that a bulk
+ * build — the reference's `for each row: hnsw_insert(...)` (src/hnsw_algo.c:520-666) — runs its layer-0 candidate
+ * searches on the device. Host-only call. */
+struct MuninnBuildDevice;
+int muninn_cuda_build_device(MuninnCudaIndex *idx, struct MuninnBuildDevice *out);
 
 /* Diagnostic for the roofline report (no reference counterpart): GB/s this device delivers for
  * independent random gathers of row_bytes-byte rows out of a slab_bytes slab (slab >> L2) — the

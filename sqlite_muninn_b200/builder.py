@@ -24,6 +24,25 @@ _f32 = _p(np.float32, flags="C_CONTIGUOUS")
 _i64 = _p(np.int64, flags="C_CONTIGUOUS")
 _i32 = _p(np.int32, flags="C_CONTIGUOUS")
 
+_UPLOAD_T = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                        C.c_int32, C.c_int32)
+_PATCH_T = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                       C.c_void_p, C.c_void_p, C.c_int32, C.c_int32)
+_SEARCH_T = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p)
+
+
+class BuildDevice(C.Structure):
+    """MuninnBuildDevice (include/muninn_build.h)."""
+    _fields_ = [("ctx", C.c_void_p), ("upload", _UPLOAD_T), ("patch", _PATCH_T), ("search", _SEARCH_T)]
+
+
+class BuildRunStats(C.Structure):
+    """MuninnBuildRunStats (include/muninn_build.h)."""
+    _fields_ = [("groups", C.c_int64), ("device_queries", C.c_int64), ("host_searches", C.c_int64),
+                ("patches", C.c_int64), ("patched_records", C.c_int64), ("warm_s", C.c_double),
+                ("search_s", C.c_double), ("link_s", C.c_double), ("patch_s", C.c_double)]
+
+
 _lib = None
 
 
@@ -57,6 +76,8 @@ def host_lib():
                                                 C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
         L.muninn_build_entry.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
         L.muninn_build_phase_seconds.argtypes = [C.c_void_p, C.POINTER(C.c_double * 3)]
+        L.muninn_build_run.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_int, C.POINTER(BuildDevice),
+                                       C.POINTER(BuildRunStats)]
         _lib = L
     return _lib
 
@@ -223,3 +244,99 @@ def build_graph_device(vectors, metric: int = 0, M: int = 16, ef_construction: i
         L.muninn_build_destroy(h)
         if own_index:
             index.close()
+
+
+def _arr(ptr, n, dtype):
+    return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(np.ctypeslib.as_ctypes_type(dtype))), shape=(max(int(n), 0),)) \
+        if n else np.empty(0, dtype)
+
+
+def _callbacks(index, dim, metric, M, efc):
+    """A MuninnBuildDevice whose three calls land in a Python object with upload / patch_records / search (the test
+    stand-in). Exceptions cannot cross the C frame: they are kept and turned into a non-zero return code."""
+    box = {"err": None}
+
+    def guard(fn):
+        def run(*a):
+            try:
+                fn(*a)
+                return 0
+            except BaseException as e:  # noqa: BLE001
+                box["err"] = e
+                return -100
+        return run
+
+    def upload(ctx, n, ids, levels, vectors, offs, tg, entry, max_level):
+        lv = _arr(levels, n, np.int32).copy()
+        nl = int(lv.astype(np.int64).sum()) + n
+        o = _arr(offs, nl + 1, np.int64).copy()
+        index.upload(FlatGraph(dim, metric, M, efc, _arr(ids, n, np.int64).copy(), lv, np.zeros(n, np.uint8),
+                               _arr(vectors, n * dim, np.float32).reshape(n, dim).copy(), o,
+                               _arr(tg, int(o[-1]), np.int32).copy(), entry, max_level))
+
+    def patch(ctx, n_total, n_patch, slots, ids, levels, vectors, offs, tg, entry, max_level):
+        lv = _arr(levels, n_patch, np.int32).copy()
+        nl = int(lv.astype(np.int64).sum()) + n_patch
+        o = _arr(offs, nl + 1, np.int64).copy()
+        index.patch_records(n_total, _arr(slots, n_patch, np.int32).copy(), _arr(ids, n_patch, np.int64).copy(), lv,
+                            None, vectors, o, _arr(tg, int(o[-1]), np.int32).copy(), entry, max_level)
+
+    def search(ctx, q, nq, k, ef, out_ids, out_dist, out_cnt):
+        ids, dist, cnt = index.search(_arr(q, nq * dim, np.float32).reshape(nq, dim).copy(), k, ef)
+        _arr(out_ids, nq * k, np.int64)[:] = np.ascontiguousarray(ids[:, :k], np.int64).ravel()
+        _arr(out_dist, nq * k, np.float32)[:] = np.ascontiguousarray(dist[:, :k], np.float32).ravel()
+        _arr(out_cnt, nq, np.int32)[:] = cnt
+
+    dev = BuildDevice(None, _UPLOAD_T(guard(upload)), _PATCH_T(guard(patch)), _SEARCH_T(guard(search)))
+    return dev, box
+
+
+def build_graph_device_c(vectors, metric: int = 0, M: int = 16, ef_construction: int = 200, *, ids=None,
+                         batch: int = 1024, warm: int = 4096, threads: int | None = None, sort_lists: bool = True,
+                         seed: int | None = None, device: int = 0, index=None, stats: dict | None = None) -> FlatGraph:
+    """`build_graph_device` with the group loop in C (`muninn_build_run`, include/muninn_build.h): the form a C host
+    links — libmuninn_host drives libmuninn_cuda through the `MuninnBuildDevice` that `muninn_cuda_build_device`
+    fills in; nothing of the loop runs in Python. Same graph as `build_graph_device` and as the host batch mode.
+    `index`: an `HnswIndexCuda` (default: a new one on `device`), or for the CPU tests any object with upload /
+    patch_records / search, reached through callbacks."""
+    L = host_lib()
+    v = np.ascontiguousarray(vectors, np.float32)
+    n, dim = v.shape
+    threads = threads or (os.cpu_count() or 1)
+    ids = np.arange(n, dtype=np.int64) if ids is None else np.ascontiguousarray(ids, np.int64)
+    assert ids.shape == (n,) and (n < 2 or bool(np.all(np.diff(ids) > 0))), "ids must be strictly ascending"
+    from .cuda import HnswIndexCuda, lib as cuda_lib
+    own_index = index is None
+    if own_index:
+        index = HnswIndexCuda(dim, metric, M, device)
+    box = {"err": None}
+    if isinstance(index, HnswIndexCuda):
+        dev = BuildDevice()
+        if cuda_lib().muninn_cuda_build_device(index.h, C.byref(dev)) != 0:
+            raise RuntimeError("muninn_cuda_build_device failed")
+    else:
+        dev, box = _callbacks(index, dim, metric, M, ef_construction)
+    h = L.muninn_build_create(dim, metric, M, ef_construction, n, v)
+    if not h:
+        raise MemoryError("muninn_build_create failed")
+    try:
+        if seed is not None:
+            L.muninn_build_seed(h, seed)
+        st = BuildRunStats()
+        rc = L.muninn_build_run(h, ids.ctypes.data, batch, warm, threads, C.byref(dev), C.byref(st))
+        if box["err"] is not None:
+            raise box["err"]
+        if rc != 0:
+            msg = index.L.muninn_cuda_last_error(index.h).decode() if isinstance(index, HnswIndexCuda) else ""
+            raise RuntimeError(f"muninn_build_run failed ({rc}) {msg}")
+        if isinstance(index, HnswIndexCuda):
+            index.n = n
+        if stats is not None:
+            stats.update({f: (round(getattr(st, f), 3) if f.endswith("_s") else int(getattr(st, f)))
+                          for f, _ in BuildRunStats._fields_})
+        return _export(L, h, n, dim, metric, M, ef_construction, v, ids, sort_lists)
+    finally:
+        L.muninn_build_destroy(h)
+        if own_index:
+            index.close()
+

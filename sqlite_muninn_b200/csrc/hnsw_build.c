@@ -33,7 +33,8 @@
  *   group  the batch mode one group at a time (muninn_build_group_begin / _group_link), for a
  *          caller that runs the layer-0 candidate searches itself — builder.build_graph_device
  *          runs them as one muninn_cuda_search_batch per group on a device copy of the graph
- *          and writes the touched records back with muninn_cuda_index_patch.  Same graph as
+ *          and writes the touched records back with muninn_cuda_index_patch; muninn_build_run is
+ *          the same loop in C over a MuninnBuildDevice (three function pointers).  Same graph as
  *          the batch mode wherever no two candidate distances are bit-equal.
  *
  * Every stored edge keeps the distance it was created with (as the reference's _edges table
@@ -857,7 +858,7 @@ int64_t muninn_build_touched_count(void *h) { return ((Builder *)h)->n_touched; 
 int64_t muninn_build_touched_take(void *h, int32_t *out, int64_t cap) {
     Builder *b = (Builder *)h;
     int64_t n = b->n_touched < cap ? b->n_touched : cap;
-    memcpy(out, b->touched, (size_t)n * sizeof(int32_t));
+    if (out && n > 0) memcpy(out, b->touched, (size_t)n * sizeof(int32_t));
     b->n_touched = 0;
     if (b->touch_stamp && ++b->touch_epoch == 0) { memset(b->touch_stamp, 0, (size_t)b->cap * sizeof(uint32_t)); b->touch_epoch = 1; }
     return n;
@@ -930,6 +931,161 @@ void muninn_build_export(void *h, int32_t *levels, int64_t *list_offsets, int32_
             list_offsets[++li] = e;
         }
     }
+}
+
+/* ───────────── the group loop (muninn_build.h: muninn_build_run) ───────────── */
+
+typedef struct {
+    int32_t *slots, *levels, *targets;
+    int64_t *ids, *offs;
+    int64_t cap_slots, cap_lists, cap_edges;
+} FlushBuf;
+
+/* device copy ← every record the host changed since the last flush; *n_dev = rows the device copy holds */
+static int run_flush(Builder *b, const int64_t *ids, const MuninnBuildDevice *dev, FlushBuf *f, int64_t *n_dev,
+                     MuninnBuildRunStats *st) {
+    const int64_t n_now = b->n, n_new = n_now - *n_dev;
+    if (b->n_touched == 0 && n_new == 0) return 0;
+    double t0 = now_s();
+    const int64_t need = n_new + b->n_touched;
+    if (need > f->cap_slots) {
+        f->cap_slots = need + need / 2 + 1024;
+        f->slots = (int32_t *)realloc(f->slots, (size_t)f->cap_slots * sizeof(int32_t));
+        f->levels = (int32_t *)realloc(f->levels, (size_t)f->cap_slots * sizeof(int32_t));
+        f->ids = (int64_t *)realloc(f->ids, (size_t)f->cap_slots * sizeof(int64_t));
+        if (!f->slots || !f->levels || !f->ids) return -1;
+    }
+    int64_t ns = 0;
+    for (int64_t s = *n_dev; s < n_now; s++) f->slots[ns++] = (int32_t)s; /* new nodes first */
+    for (int64_t i = 0; i < b->n_touched; i++)
+        if (b->touched[i] < *n_dev) f->slots[ns++] = b->touched[i];
+    muninn_build_touched_take(b, NULL, 0); /* clears the log */
+    int64_t nl = 0, ne = 0;
+    muninn_build_export_nodes(b, ns, f->slots, NULL, NULL, NULL, &nl, &ne);
+    if (nl + 1 > f->cap_lists) {
+        f->cap_lists = nl + nl / 2 + 1024;
+        f->offs = (int64_t *)realloc(f->offs, (size_t)f->cap_lists * sizeof(int64_t));
+        if (!f->offs) return -1;
+    }
+    if (ne + 1 > f->cap_edges) {
+        f->cap_edges = ne + ne / 2 + 1024;
+        f->targets = (int32_t *)realloc(f->targets, (size_t)f->cap_edges * sizeof(int32_t));
+        if (!f->targets) return -1;
+    }
+    muninn_build_export_nodes(b, ns, f->slots, f->levels, f->offs, f->targets, &nl, &ne);
+    for (int64_t i = 0; i < ns; i++) f->ids[i] = ids ? ids[f->slots[i]] : (int64_t)f->slots[i];
+    const float *vec = n_new > 0 ? b->vecs + (size_t)*n_dev * (size_t)b->dim : b->vecs;
+    int rc = dev->patch(dev->ctx, n_now, (int32_t)ns, f->slots, f->ids, f->levels, vec, f->offs, f->targets, b->entry,
+                        b->max_level);
+    if (rc) return rc;
+    *n_dev = n_now;
+    if (st) { st->patches++; st->patched_records += ns; st->patch_s += now_s() - t0; }
+    return 0;
+}
+
+int muninn_build_run(void *h, const int64_t *ids, int batch, int64_t warm, int nthreads, const MuninnBuildDevice *dev,
+                     MuninnBuildRunStats *st) {
+    Builder *b = (Builder *)h;
+    if (!b || !dev || !dev->upload || !dev->patch || !dev->search || batch < 1 || b->n != 0 || b->pending_g1 >= 0) return -1;
+    if (st) memset(st, 0, sizeof(*st));
+    const int64_t n = b->cap;
+    if (n == 0) return 0;
+    const int k = b->M0 < b->efc ? b->M0 : b->efc;
+    int rc = -1;
+    FlushBuf f;
+    memset(&f, 0, sizeof f);
+    int32_t *glev = NULL, *cand = NULL, *cand_cnt = NULL, *where = NULL, *cnt = NULL;
+    int64_t *found = NULL;
+    float *q = NULL, *fdist = NULL;
+    int64_t *ident = NULL;
+
+    /* the first `warm` nodes: exact sequential inserts on the host, then one full upload */
+    double t0 = now_s();
+    const int64_t n_warm = n < (warm > 1 ? warm : 1) ? n : (warm > 1 ? warm : 1);
+    if (muninn_build_insert(b, n_warm, 0, 0, 1) != 0) goto done;
+    {
+        int64_t nn, nl, ne; int32_t es, ml;
+        muninn_build_sizes(b, &nn, &nl, &ne, &es, &ml);
+        int32_t *lv = (int32_t *)malloc((size_t)nn * sizeof(int32_t));
+        int64_t *offs = (int64_t *)malloc((size_t)(nl + 1) * sizeof(int64_t));
+        int32_t *tg = (int32_t *)malloc((size_t)(ne + 1) * sizeof(int32_t));
+        if (!ids) {
+            ident = (int64_t *)malloc((size_t)n_warm * sizeof(int64_t));
+            for (int64_t i = 0; ident && i < n_warm; i++) ident[i] = i;
+        }
+        if (lv && offs && tg && (ids || ident)) {
+            muninn_build_export(b, lv, offs, tg, 0);
+            rc = dev->upload(dev->ctx, nn, ids ? ids : ident, lv, b->vecs, offs, tg, es, ml);
+        }
+        free(lv); free(offs); free(tg);
+        if (rc) goto done;
+        rc = -1;
+    }
+    if (st) st->warm_s = now_s() - t0;
+    muninn_build_log_touched(b, 1);
+    if (!b->log_touched) goto done;
+    int64_t n_dev = n_warm;
+    glev = (int32_t *)malloc((size_t)batch * sizeof(int32_t));
+    where = (int32_t *)malloc((size_t)batch * sizeof(int32_t));
+    cnt = (int32_t *)malloc((size_t)batch * sizeof(int32_t));
+    cand_cnt = (int32_t *)malloc((size_t)batch * sizeof(int32_t));
+    cand = (int32_t *)malloc((size_t)batch * (size_t)k * sizeof(int32_t));
+    found = (int64_t *)malloc((size_t)batch * (size_t)k * sizeof(int64_t));
+    fdist = (float *)malloc((size_t)batch * (size_t)k * sizeof(float));
+    q = (float *)malloc((size_t)batch * (size_t)b->dim * sizeof(float));
+    if (!glev || !where || !cnt || !cand_cnt || !cand || !found || !fdist || !q) goto done;
+
+    while (b->n < n) {
+        int64_t g0, gn;
+        if (muninn_build_group_begin(b, batch, &g0, &gn) != 0) goto done;
+        if ((rc = run_flush(b, ids, dev, &f, &n_dev, st)) != 0) goto done; /* a level-raising first node was inserted exactly */
+        rc = -1;
+        if (gn == 0) continue;
+        muninn_build_group_levels(b, glev);
+        int nq = 0;
+        for (int64_t i = 0; i < gn; i++) {
+            cand_cnt[i] = -1;
+            if (glev[i] == 0) {
+                memcpy(q + (size_t)nq * (size_t)b->dim, vec_of(b, (int32_t)(g0 + i)), (size_t)b->dim * sizeof(float));
+                where[nq++] = (int32_t)i;
+            }
+        }
+        t0 = now_s();
+        if (nq > 0) {
+            if ((rc = dev->search(dev->ctx, q, nq, k, b->efc, found, fdist, cnt)) != 0) goto done;
+            rc = -1;
+            for (int j = 0; j < nq; j++) {
+                int32_t *row = cand + (size_t)where[j] * (size_t)k;
+                int c = cnt[j] < 0 ? 0 : (cnt[j] > k ? k : cnt[j]);
+                for (int r = 0; r < c; r++) {
+                    const int64_t id = found[(size_t)j * (size_t)k + r];
+                    int64_t sl = id;
+                    if (ids) { /* rowid → slot among the nodes stored before the group */
+                        int64_t lo = 0, hi = g0 - 1;
+                        sl = -1;
+                        while (lo <= hi) {
+                            int64_t mid = lo + (hi - lo) / 2;
+                            if (ids[mid] == id) { sl = mid; break; }
+                            if (ids[mid] < id) lo = mid + 1; else hi = mid - 1;
+                        }
+                    }
+                    row[r] = (int32_t)sl; /* out-of-graph values are refused by muninn_build_group_link */
+                }
+                cand_cnt[where[j]] = c;
+            }
+        }
+        if (st) st->search_s += now_s() - t0;
+        t0 = now_s();
+        if (muninn_build_group_link(b, cand, cand_cnt, k, nthreads) != 0) goto done;
+        if (st) { st->link_s += now_s() - t0; st->groups++; st->device_queries += nq; st->host_searches += gn - nq; }
+        if ((rc = run_flush(b, ids, dev, &f, &n_dev, st)) != 0) goto done;
+        rc = -1;
+    }
+    rc = 0;
+done:
+    free(glev); free(where); free(cnt); free(cand_cnt); free(cand); free(found); free(fdist); free(q); free(ident);
+    free(f.slots); free(f.levels); free(f.targets); free(f.ids); free(f.offs);
+    return rc;
 }
 
 void muninn_build_destroy(void *h) {

@@ -12,6 +12,7 @@
  * There is no CPU path: without a device every entry point fails with MUNINN_CUDA_E_NODEVICE.
  */
 #include "../../include/muninn_cuda.h"
+#include "../../include/muninn_build.h" /* MuninnBuildDevice: the searcher interface of the host builder */
 #include "exact_knn.cuh"
 #include "exact_tc.cuh"
 #include "hnsw_search.cuh"
@@ -507,6 +508,27 @@ extern "C" int muninn_cuda_index_patch(MuninnCudaIndex *h, int64_t n_total, int3
     h->n_upper += add_upper;
     h->n = n_total; h->entry_slot = entry_slot; h->max_level = max_level;
     if (n_new > 0) h->last_id = prev_id;
+    return MUNINN_CUDA_OK;
+}
+
+/* ───────────────────────── searcher for the host builder's group loop ───────────────────────── */
+
+static int bd_upload(void *ctx, int64_t n, const int64_t *ids, const int32_t *levels, const float *vectors,
+                     const int64_t *list_offsets, const int32_t *targets, int32_t entry_slot, int32_t max_level) {
+    return muninn_cuda_index_upload((MuninnCudaIndex *)ctx, n, ids, levels, nullptr, vectors, list_offsets, targets, entry_slot, max_level);
+}
+static int bd_patch(void *ctx, int64_t n_total, int32_t n_patch, const int32_t *slots, const int64_t *ids, const int32_t *levels,
+                    const float *vectors, const int64_t *list_offsets, const int32_t *targets, int32_t entry_slot, int32_t max_level) {
+    return muninn_cuda_index_patch((MuninnCudaIndex *)ctx, n_total, n_patch, slots, ids, levels, nullptr, vectors, list_offsets, targets,
+                                   entry_slot, max_level);
+}
+static int bd_search(void *ctx, const float *queries, int nq, int k, int ef, int64_t *out_ids, float *out_dist, int32_t *out_count) {
+    return muninn_cuda_search_batch((MuninnCudaIndex *)ctx, queries, nq, k, ef, out_ids, out_dist, out_count, nullptr);
+}
+
+extern "C" int muninn_cuda_build_device(MuninnCudaIndex *h, MuninnBuildDevice *out) {
+    if (!h || !out) return MUNINN_CUDA_E_ARG;
+    out->ctx = h; out->upload = bd_upload; out->patch = bd_patch; out->search = bd_search;
     return MUNINN_CUDA_OK;
 }
 

@@ -30,7 +30,7 @@ ABI_SYMBOLS = (
     "muninn_cuda_last_kernel_ms", "muninn_cuda_launch_count", "muninn_cuda_set_tuning", "muninn_cuda_exact_knn",
     "muninn_cuda_exact_knn_device", "muninn_cuda_topk_merge_device", "muninn_cuda_distance_batch",
     "muninn_cuda_set_exact_mode", "muninn_cuda_exact_stats", "muninn_cuda_exact_filter_probe",
-    "muninn_cuda_gather_ceiling", "muninn_cuda_index_patch",
+    "muninn_cuda_gather_ceiling", "muninn_cuda_index_patch", "muninn_cuda_build_device",
 )
 
 EXACT_CUDA_CORE, EXACT_TC_3XTF32, EXACT_TC_1XTF32, EXACT_TC_AUTO = 0, 1, 2, 3
@@ -91,6 +91,7 @@ def lib():
         L.muninn_cuda_exact_filter_probe.argtypes = [_vp, _vp, C.c_int, C.c_int64, _vp]
         L.muninn_cuda_index_patch.argtypes = [_vp, C.c_int64, C.c_int32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int32, C.c_int32]
         L.muninn_cuda_gather_ceiling.argtypes = [C.c_int, C.c_int, C.c_int64, C.POINTER(C.c_float)]
+        L.muninn_cuda_build_device.argtypes = [_vp, _vp]
         _lib = L
     return _lib
 

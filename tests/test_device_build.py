@@ -15,7 +15,7 @@ import numpy as np
 import pytest
 
 from oracle.bindings import Oracle
-from sqlite_muninn_b200.builder import build_graph, build_graph_device
+from sqlite_muninn_b200.builder import build_graph, build_graph_device, build_graph_device_c
 from sqlite_muninn_b200.graph import FlatGraph
 
 
@@ -194,3 +194,37 @@ def test_no_device_no_build():
     with pytest.raises(cuda.MuninnCudaError) as e:
         build_graph_device(x, 0, 4, 20, batch=32, warm=50)
     assert e.value.code == -2  # MUNINN_CUDA_E_NODEVICE
+
+
+@pytest.mark.parametrize("n,dim,metric,M,efc,batch,warm", CASES)
+def test_c_group_loop_equals_host_batch_mode(n, dim, metric, M, efc, batch, warm):
+    """muninn_build_run (the loop in C, include/muninn_build.h) driving the stand-in through callbacks."""
+    x = np.random.default_rng(n).standard_normal((n, dim)).astype(np.float32)
+    want = build_graph(x, metric, M, efc, batch=batch, warm=warm, sort_lists=False, threads=4)
+    idx = OracleBackedIndex(dim, metric, M)
+    st = {}
+    got = build_graph_device_c(x, metric, M, efc, batch=batch, warm=warm, sort_lists=False, threads=4, index=idx, stats=st)
+    assert got.same_structure(want)
+    assert idx.graph().same_structure(want)
+    st_py = {}
+    build_graph_device(x, metric, M, efc, batch=batch, warm=warm, sort_lists=False, threads=4,
+                       index=OracleBackedIndex(dim, metric, M), stats=st_py)
+    for key in ("groups", "device_queries", "host_searches", "patches", "patched_records"):
+        assert st[key] == st_py[key], key
+
+
+def test_c_group_loop_with_rowids_and_device_failure():
+    rng = np.random.default_rng(6)
+    x = rng.standard_normal((800, 16)).astype(np.float32)
+    ids = np.cumsum(rng.integers(1, 9, 800)).astype(np.int64) + 7
+    want = build_graph(x, 0, 8, 32, ids=ids, batch=128, warm=200, threads=2)
+    got = build_graph_device_c(x, 0, 8, 32, ids=ids, batch=128, warm=200, threads=2, index=OracleBackedIndex(16, 0, 8))
+    assert got.same_structure(want)
+
+    class Failing(OracleBackedIndex):
+        def search(self, queries, k, ef):
+            raise RuntimeError("device lost")
+
+    with pytest.raises(RuntimeError, match="device lost"):  # no host fallback: the build ends
+        build_graph_device_c(x, 0, 8, 32, batch=128, warm=200, threads=2, index=Failing(16, 0, 8))
+

@@ -6,7 +6,7 @@ run on hardware is the driver's — the host logic it shares with the CPU tests 
 import numpy as np
 import pytest
 
-from sqlite_muninn_b200.builder import build_graph, build_graph_device
+from sqlite_muninn_b200.builder import build_graph, build_graph_device, build_graph_device_c
 
 pytestmark = pytest.mark.gpu
 
@@ -56,4 +56,25 @@ def test_device_build_at_scale_matches_host_quality():
         ra = np.mean([len(set(u) & set(t)) / 10 for u, t in zip(a.search(q, 10, 64)[0].tolist(), truth.tolist())])
         rb = np.mean([len(set(u) & set(t)) / 10 for u, t in zip(b.search(q, 10, 64)[0].tolist(), truth.tolist())])
     assert abs(ra - rb) < 0.01, (ra, rb)
+
+
+def test_c_group_loop_on_the_device():
+    """muninn_build_run (libmuninn_host) driving libmuninn_cuda through muninn_cuda_build_device: no Python in the loop.
+    Same graph as the host batch mode, and the handle ends up holding it."""
+    from sqlite_muninn_b200.cuda import HnswIndexCuda
+    rng = np.random.default_rng(123)
+    x = rng.standard_normal((7000, 48)).astype(np.float32)
+    ids = np.arange(7000, dtype=np.int64) * 2 + 5
+    want = build_graph(x, 0, 16, 80, ids=ids, batch=400, warm=600, sort_lists=False)
+    st = {}
+    with HnswIndexCuda(48, 0, 16, 0) as idx:
+        got = build_graph_device_c(x, 0, 16, 80, ids=ids, batch=400, warm=600, sort_lists=False, index=idx, stats=st)
+        assert got.same_structure(want)
+        assert st["device_queries"] > 0.9 * (7000 - 600) and st["patches"] >= st["groups"]
+        q = rng.standard_normal((32, 48)).astype(np.float32)
+        a = idx.search(q, 10, 64)
+        with HnswIndexCuda.from_graph(got, 0) as fresh:
+            b = fresh.search(q, 10, 64)
+        for u, w in zip(a, b):
+            assert np.array_equal(u, w)
 
