@@ -239,3 +239,19 @@ def test_builder_avx2_path_changes_nothing(metric, dim):
         assert got[0].same_structure(want[0]) and got[1].same_structure(want[1])
     finally:
         L.muninn_build_set_avx2(-1)
+
+
+def test_c_bulk_build_example_compiles_and_refuses_without_a_device(tmp_path):
+    """integration/bulk_build_example.c: the two public headers are valid C together, the call signatures match the
+    libraries, and without a GPU the program stops at index creation (no host fallback)."""
+    import subprocess
+    exe = str(tmp_path / "bulk_build_example")
+    csrc = os.path.join(ROOT, "sqlite_muninn_b200", "csrc")
+    cc = "/usr/bin/gcc" if os.path.exists("/usr/bin/gcc") else "gcc"
+    subprocess.run([cc, "-O2", "-std=c11", "-D_POSIX_C_SOURCE=200809L", "-Wall", "-Wextra", "-Werror",
+                    "-I" + os.path.join(ROOT, "include"), os.path.join(ROOT, "integration", "bulk_build_example.c"),
+                    "-L" + csrc, "-lmuninn_host", "-lmuninn_cuda", "-Wl,-rpath," + csrc, "-lm", "-o", exe], check=True)
+    if cuda.device_count() > 0:
+        pytest.skip("a device is present: the example would run a full build")
+    out = subprocess.run([exe, "1000", "16"], capture_output=True, text=True)
+    assert out.returncode == 2 and "no CUDA device" in out.stderr
