@@ -43,7 +43,7 @@ EF_SWEEP = (64, 96, 128, 192, 256)
 CONFIGS = {
     2: dict(name="SIFT1M-shape", n=1_000_000, dim=128, metric=0, M=16, efc=200, nq=10_000, k=10, ef_sweep=EF_SWEEP,
             data="latent16", seeds=(11, 12), scaling="weak", ef_calibrated=64),
-    3: dict(name="text-embedding shape", n=1_000_000, dim=768, metric=1, M=32, efc=100, nq=10_000, k=10, ef_sweep=(128,),
+    3: dict(name="text-embedding shape", n=1_000_000, dim=768, metric=1, M=32, efc=100, nq=10_000, k=10, ef_sweep=(128, 192, 256, 384),
             data="spectrum", seeds=(21, 22), scaling="strong", ef_calibrated=128),
     4: dict(name="Deep10M-shape", n=10_000_000, dim=96, metric=2, M=32, efc=64, nq=10_000, k=10, ef_sweep=(64, 128, 256),
             data="latent16n", seeds=(31, 32), scaling="strong", ef_calibrated=64),
