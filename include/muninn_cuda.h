@@ -147,9 +147,16 @@ int muninn_cuda_set_stream(MuninnCudaIndex *idx, void *stream);
 float muninn_cuda_last_kernel_ms(MuninnCudaIndex *idx);
 /* Number of kernels this handle has launched since creation (bench.py's gpu_launches). */
 int64_t muninn_cuda_launch_count(const MuninnCudaIndex *idx);
-/* Launch geometry knobs for tuning: warps cooperating on one query (1, 2 or 4) and query
- * teams resident per SM (0 = automatic). Results do not depend on them. */
+/* Launch geometry knobs for tuning: warps cooperating on one query (1, 2 or 4; 0 = automatic: the widest
+ * team that still keeps every query of the batch resident at once, so a lone MATCH gets 4 warps and a full
+ * batch one warp per query) and query teams resident per SM (0 = automatic). Results do not depend on them. */
 int muninn_cuda_set_tuning(MuninnCudaIndex *idx, int warps_per_query, int teams_per_sm);
+/* Team width the handle's most recent search launched with. */
+int muninn_cuda_last_team_width(const MuninnCudaIndex *idx);
+/* Diagnostic options (no reference counterpart; results do not depend on them): "kernel_gen" = 8 (default,
+ * hnsw_beam.cuh) or 7 (the round-1 one-warp kernel, kept for A/B timing); "vis_factor" = size of a team's
+ * first-level visited table in units of ef·2M entries (default 2). */
+int muninn_cuda_set_option(MuninnCudaIndex *idx, const char *name, double value);
 
 /*
  * Exact k-NN over the uploaded rows of this handle (deleted rows skipped), reference
@@ -199,6 +206,30 @@ int muninn_cuda_exact_filter_probe(MuninnCudaIndex *idx, const float *queries, i
 int muninn_cuda_topk_merge_device(MuninnCudaIndex *idx, int parts, int nq, int k, const int64_t *d_idx_parts,
                                   const float *d_dist_parts, const int32_t *d_count_parts, int64_t *d_idx,
                                   float *d_dist, int32_t *d_count);
+
+/*
+ * Sharded exact k-NN: the base rows are split over `world` handles (one per GPU, one process per GPU),
+ * every rank calls this with the SAME queries and the first global row index of its shard. Each rank scans its shard,
+ * packs its lists into 64-bit keys (ordered distance << 32 | global row index), the lists are exchanged with ONE
+ * ncclAllGather of nq·k·8 bytes per rank on the handle's stream, and every rank merges them under the (distance,
+ * index) rule of test/test_hnsw_algo.c:10-34 — all ranks end with the identical global answer in d_idx / d_dist /
+ * d_count (device buffers). Global row indices must fit 32 bits. `nccl_comm` is an ncclComm_t passed as void*: the
+ * host's own (e.g. torch.distributed's) or one made by muninn_cuda_comm_create. NCCL is bound at run time from the
+ * libnccl.so.2 already loaded in the process, else the system's.
+ */
+int muninn_cuda_exact_knn_sharded_device(MuninnCudaIndex *idx, void *nccl_comm, const float *d_queries, int nq, int k,
+                                         int64_t index_base, int64_t *d_idx, float *d_dist, int32_t *d_count);
+/* A communicator for hosts that have none: rank 0 calls _unique_id (128 bytes, ncclUniqueId) and ships the bytes to the
+ * other ranks by any means; every rank then calls _create (collective). */
+int muninn_cuda_comm_unique_id(void *out_id128);
+int muninn_cuda_comm_create(int device, int world, int rank, const void *id128, void **out_comm);
+void muninn_cuda_comm_destroy(void *comm);
+/* The two halves of the exchange for callers that move the keys themselves: result lists → keys, and the merge of
+ * `parts` gathered key lists [parts × nq × k]. Device buffers. */
+int muninn_cuda_topk_pack_keys_device(MuninnCudaIndex *idx, int nq, int k, const int64_t *d_idx, const float *d_dist,
+                                      const int32_t *d_count, uint64_t *d_keys);
+int muninn_cuda_topk_merge_keys_device(MuninnCudaIndex *idx, int parts, int nq, int k, const uint64_t *d_keys,
+                                       int64_t *d_idx, float *d_dist, int32_t *d_count);
 
 /* n distances metric(a[i], b[i]) with the reference's summation order (src/vec_math.c:78-143).
  * Host buffers [n × dim]; used by the known-answer tests of test/test_vec_math.c. */

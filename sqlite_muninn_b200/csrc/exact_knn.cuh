@@ -205,6 +205,51 @@ __global__ void exact_emit(const unsigned long long *__restrict__ topk, const in
     if (j == 0) out_count[qo] = sz;
 }
 
+/* per-shard result lists → ONE array of 64-bit keys (ordered distance << 32 | global row index), unused tail =
+ * KEY_NONE: the payload of the single all-gather of the sharded exact k-NN (nq·k·8 bytes per rank) */
+__global__ void topk_pack_keys(int nq, int k, const int64_t *__restrict__ idx, const float *__restrict__ dist,
+                               const int32_t *__restrict__ count, unsigned long long *__restrict__ keys) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nq * k) return;
+    const int q = i / k, j = i % k;
+    keys[i] = j < count[q] ? make_key(dist[i], (unsigned)idx[i]) : KEY_NONE;
+}
+
+/* merge the gathered key lists [parts × nq × k] (each ascending, KEY_NONE padded) per query; one warp per query */
+__global__ void __launch_bounds__(128)
+topk_merge_keys(int parts, int nq, int k, const unsigned long long *__restrict__ keys, int64_t *out_idx, float *out_dist,
+                int32_t *out_count) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int q = blockIdx.x * 4 + wib;
+    unsigned long long *R = reinterpret_cast<unsigned long long *>(smem_raw) + (size_t)wib * (k + 32);
+    unsigned long long *S = R + k;
+    if (q >= nq) return;
+    int size = 0, ev = 0, mp;
+    for (int pth = 0; pth < parts; pth++) {
+        const unsigned long long *src = keys + ((size_t)pth * nq + q) * k;
+        for (int j0 = 0; j0 < k; j0 += 32) {
+            const int j = j0 + lane;
+            const unsigned long long worst = size >= k ? R[k - 1] : KEY_NONE;
+            const unsigned long long f = j < k ? src[j] : KEY_NONE;
+            const bool keep = f < worst; /* KEY_NONE never enters */
+            const unsigned km = __ballot_sync(FULL, keep);
+            const int ns = __popc(km);
+            if (ns == 0) break; /* lists ascend: nothing further of this part can enter */
+            if (keep) S[__popc(km & ((1u << lane) - 1))] = f;
+            __syncwarp();
+            size = warp_merge_sorted(R, size, k, S, ns, lane, &mp, &ev);
+        }
+    }
+    __syncwarp();
+    for (int j = lane; j < k; j += 32) {
+        const size_t o = (size_t)q * k + j;
+        if (j < size) { out_idx[o] = (long long)(unsigned)R[j]; out_dist[o] = okey_inv((unsigned)(R[j] >> 32)); }
+        else { out_idx[o] = -1; out_dist[o] = 0.0f; }
+    }
+    if (lane == 0) out_count[q] = size;
+}
+
 /* merge `parts` gathered lists per query under (distance, index); one warp per query */
 __global__ void __launch_bounds__(128)
 topk_merge_parts(int parts, int nq, int k, const int64_t *__restrict__ idx_parts, const float *__restrict__ dist_parts,

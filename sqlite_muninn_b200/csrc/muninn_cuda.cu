@@ -16,6 +16,7 @@
 #include "exact_knn.cuh"
 #include "exact_tc.cuh"
 #include "hnsw_search.cuh"
+#include "hnsw_beam.cuh"
 
 #ifndef MUNINN_D128
 #define MUNINN_D128 1 /* constant-trip-count instances of the search kernel for dim 96 / 128 / 768 */
@@ -53,7 +54,7 @@ struct MuninnCudaIndex {
     cudaStream_t own_stream = nullptr, stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool have_timing = false;
-    int num_sms = 0, teams_per_sm = 0, warps_per_query = 1;
+    int num_sms = 0, teams_per_sm = 0, warps_per_query = 0;
     int64_t launches = 0;
     unsigned *d_vis = nullptr; size_t vis_entries = 0;  /* visited arena: teams × cap 32-bit slots */
     int *d_ctl = nullptr;        /* [8]: work counters ×3, retry counts ×2 */
@@ -61,7 +62,8 @@ struct MuninnCudaIndex {
     /* staging for the host-buffer entry points */
     void *d_stage = nullptr; size_t stage_bytes = 0;
     void *h_pinned = nullptr; size_t pinned_bytes = 0;
-    size_t occ_smem = 0; int occ_val = 0; /* cached occupancy of the search kernel for the last shared-memory size */
+    size_t occ_smem[4] = {0, 0, 0, 0}; int occ_val[4] = {0, 0, 0, 0}; /* cached occupancy per (generation, team width) */
+    int kernel_gen = 8, last_W = 1; double vis_factor = MUNINN_VIS_FACTOR;
     /* exact k-NN scratch */
     float *d_panel = nullptr; size_t panel_floats = 0;
     unsigned long long *d_topk = nullptr; int *d_topk_size = nullptr; size_t topk_cap = 0, topk_q = 0;
@@ -78,6 +80,7 @@ struct MuninnCudaIndex {
     unsigned long long *d_tc_ctr = nullptr;                /* [0] survivors re-ranked, [1] flagged queries (int) */
     std::vector<cudaEvent_t> tc_ev;
     MuninnExactStats exact_stats = {};
+    unsigned long long *d_shard_keys = nullptr; size_t shard_keys_cap = 0; /* sharded exact k-NN: own keys | gathered keys */
     std::string err;
 };
 
@@ -166,6 +169,11 @@ extern "C" int muninn_cuda_index_create(int device, int dim, int metric, int M, 
         return rc;
     }
     h->stream = h->own_stream;
+    /* experiment knobs (A/B runs of one build): same meaning as muninn_cuda_set_option / _set_tuning */
+    if (const char *e = getenv("MUNINN_KERNEL")) { const int g = atoi(e); if (g == 7 || g == 8) h->kernel_gen = g; }
+    if (const char *e = getenv("MUNINN_VIS_FACTOR")) { const double f = atof(e); if (f >= 0.5 && f <= 64.0) h->vis_factor = f; }
+    if (const char *e = getenv("MUNINN_WARPS")) { const int w = atoi(e); if (w == 0 || w == 1 || w == 2 || w == 4) h->warps_per_query = w; }
+    if (const char *e = getenv("MUNINN_TEAMS_PER_SM")) { const int t = atoi(e); if (t >= 0 && t <= 32) h->teams_per_sm = t; }
     *out = h;
     return MUNINN_CUDA_OK;
 }
@@ -179,7 +187,7 @@ extern "C" void muninn_cuda_index_destroy(MuninnCudaIndex *h) {
     cudaFree(h->d_panel); cudaFree(h->d_topk); cudaFree(h->d_topk_size);
     cudaFree(h->d_qsplit); cudaFree(h->d_xsplit); cudaFree(h->d_qaux); cudaFree(h->d_tau); cudaFree(h->d_cand_count);
     cudaFree(h->d_overflow); cudaFree(h->d_qmap); cudaFree(h->d_cand); cudaFree(h->d_qgather); cudaFree(h->d_dbg);
-    cudaFree(h->d_tc_ctr);
+    cudaFree(h->d_tc_ctr); cudaFree(h->d_shard_keys);
     for (cudaEvent_t e : h->tc_ev) cudaEventDestroy(e);
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
     if (h->ev0) cudaEventDestroy(h->ev0);
@@ -198,12 +206,27 @@ extern "C" int64_t muninn_cuda_launch_count(const MuninnCudaIndex *h) { return h
 
 extern "C" int muninn_cuda_set_tuning(MuninnCudaIndex *h, int warps_per_query, int teams_per_sm) {
     if (!h) return MUNINN_CUDA_E_ARG;
-    if (warps_per_query != 1) return fail(h, MUNINN_CUDA_E_ARG, "warps_per_query %d not supported (1)", warps_per_query);
+    if (warps_per_query != 0 && warps_per_query != 1 && warps_per_query != 2 && warps_per_query != 4)
+        return fail(h, MUNINN_CUDA_E_ARG, "warps_per_query must be 0 (automatic), 1, 2 or 4 (got %d)", warps_per_query);
     if (teams_per_sm < 0 || teams_per_sm > 32) return fail(h, MUNINN_CUDA_E_ARG, "teams_per_sm must be in [0, 32]");
     h->warps_per_query = warps_per_query;
     h->teams_per_sm = teams_per_sm;
     return MUNINN_CUDA_OK;
 }
+
+extern "C" int muninn_cuda_set_option(MuninnCudaIndex *h, const char *name, double value) {
+    if (!h || !name) return MUNINN_CUDA_E_ARG;
+    if (!strcmp(name, "kernel_gen")) {
+        if (value != 7 && value != 8) return fail(h, MUNINN_CUDA_E_ARG, "kernel_gen must be 7 or 8");
+        h->kernel_gen = (int)value;
+    } else if (!strcmp(name, "vis_factor")) {
+        if (!(value >= 0.5 && value <= 64.0)) return fail(h, MUNINN_CUDA_E_ARG, "vis_factor must be in [0.5, 64]");
+        h->vis_factor = value;
+    } else return fail(h, MUNINN_CUDA_E_ARG, "unknown option %s", name);
+    return MUNINN_CUDA_OK;
+}
+
+extern "C" int muninn_cuda_last_team_width(const MuninnCudaIndex *h) { return h ? h->last_W : 0; }
 
 extern "C" float muninn_cuda_last_kernel_ms(MuninnCudaIndex *h) {
     if (!h || !h->have_timing) return -1.0f;
@@ -541,51 +564,93 @@ static unsigned pow2_at_least(unsigned long long v) {
 }
 static unsigned log2u(unsigned v) { unsigned l = 0; while ((1u << l) < v) l++; return l; }
 
-template <int METRIC, int RB, int CD>
-static cudaError_t launch_levels_rb(MuninnCudaIndex *h, SearchParams p, size_t smem, const int teams[3],
-                                    const unsigned caps[3], int nlevels, int nq) {
-    cudaError_t e = cudaFuncSetAttribute(hnsw_search_kernel<METRIC, RB, CD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    for (int lv = 0; lv < nlevels; lv++) {
-        p.vis_cap = caps[lv];
-        p.vis_shift = 32 - log2u(caps[lv]);
-        p.work_counter = h->d_ctl + lv;
-        p.in_list = lv == 0 ? nullptr : h->d_retry + (size_t)(lv - 1) * nq;
-        p.in_count = lv == 0 ? nullptr : h->d_ctl + 3 + (lv - 1);
-        p.out_list = h->d_retry + (size_t)(lv < 2 ? lv : 0) * nq;
-        p.out_count_retry = h->d_ctl + 3 + lv;
-        hnsw_search_kernel<METRIC, RB, CD><<<teams[lv], 32, smem, h->stream>>>(p, lv);
-        h->launches++;
-        e = cudaGetLastError();
-        if (e != cudaSuccess) return e;
+/* ── kernel selection ──
+ * Generation 8 (hnsw_beam.cuh) is the product kernel; generation 7 (hnsw_search.cuh, one warp per query, whole-row
+ * tile) is kept for A/B runs (MUNINN_KERNEL=7 in the environment, or muninn_cuda_set_tuning_ex). A kernel is picked as
+ * a plain function pointer so that occupancy query, attribute and launch share one code path. Ring geometry (U floats
+ * per unit, NST stages) per constant-dimension instance: */
+#ifndef MUNINN_U_D128
+#define MUNINN_U_D128 64
+#endif
+#ifndef MUNINN_NST_D128
+#define MUNINN_NST_D128 2
+#endif
+#ifndef MUNINN_U_D96
+#define MUNINN_U_D96 32
+#endif
+#ifndef MUNINN_NST_D96
+#define MUNINN_NST_D96 3
+#endif
+#ifndef MUNINN_U_D768
+#define MUNINN_U_D768 128
+#endif
+#ifndef MUNINN_NST_D768
+#define MUNINN_NST_D768 2
+#endif
+#ifndef MUNINN_U_GEN
+#define MUNINN_U_GEN 64
+#endif
+#ifndef MUNINN_NST_GEN
+#define MUNINN_NST_GEN 2
+#endif
+
+struct KernelSel {
+    const void *fn = nullptr;
+    int gen = 8, W = 1, U = 0, NST = 0;
+    size_t smem = 0;
+};
+
+template <int METRIC, int W>
+static const void *beam_fn(int dim, int *U, int *NST) {
+    if (MUNINN_D128 && dim == 128) { *U = MUNINN_U_D128; *NST = MUNINN_NST_D128; return (const void *)beam::hnsw_beam_kernel<METRIC, 128, MUNINN_U_D128, MUNINN_NST_D128, W>; }
+    if (MUNINN_D128 && dim == 96) { *U = MUNINN_U_D96; *NST = MUNINN_NST_D96; return (const void *)beam::hnsw_beam_kernel<METRIC, 96, MUNINN_U_D96, MUNINN_NST_D96, W>; }
+    if (MUNINN_D128 && dim == 768) { *U = MUNINN_U_D768; *NST = MUNINN_NST_D768; return (const void *)beam::hnsw_beam_kernel<METRIC, 768, MUNINN_U_D768, MUNINN_NST_D768, W>; }
+    *U = MUNINN_U_GEN; *NST = MUNINN_NST_GEN;
+    return (const void *)beam::hnsw_beam_kernel<METRIC, 0, MUNINN_U_GEN, MUNINN_NST_GEN, W>;
+}
+template <int METRIC>
+static const void *beam_fn_w(int W, int dim, int *U, int *NST) {
+    return W == 4 ? beam_fn<METRIC, 4>(dim, U, NST) : W == 2 ? beam_fn<METRIC, 2>(dim, U, NST) : beam_fn<METRIC, 1>(dim, U, NST);
+}
+template <int METRIC>
+static const void *v7_fn(int dim, int ld) {
+    if (MUNINN_D128 && dim == 128) return (const void *)hnsw_search_kernel<METRIC, RB_NARROW, 128>;
+    if (MUNINN_D128 && dim == 96) return (const void *)hnsw_search_kernel<METRIC, RB_D96, 96>;
+    if (MUNINN_D128 && dim == 768) return (const void *)hnsw_search_kernel<METRIC, RB_WIDE, 768>;
+    return beam_rows(ld) == RB_NARROW ? (const void *)hnsw_search_kernel<METRIC, RB_NARROW, 0> : (const void *)hnsw_search_kernel<METRIC, RB_WIDE, 0>;
+}
+
+static KernelSel select_kernel(const MuninnCudaIndex *h, int gen, int W, int ef) {
+    KernelSel k;
+    k.gen = gen;
+    if (gen == 7) {
+        k.W = 1;
+        k.fn = h->metric == MUNINN_METRIC_L2 ? v7_fn<METRIC_L2>(h->dim, h->ld)
+               : h->metric == MUNINN_METRIC_COSINE ? v7_fn<METRIC_COSINE>(h->dim, h->ld) : v7_fn<METRIC_IP>(h->dim, h->ld);
+        k.smem = search_smem_bytes(ef, h->ld, h->M0, MUNINN_D128 ? h->dim : -1);
+        return k;
     }
+    k.W = W;
+    k.fn = h->metric == MUNINN_METRIC_L2 ? beam_fn_w<METRIC_L2>(W, h->dim, &k.U, &k.NST)
+           : h->metric == MUNINN_METRIC_COSINE ? beam_fn_w<METRIC_COSINE>(W, h->dim, &k.U, &k.NST)
+                                               : beam_fn_w<METRIC_IP>(W, h->dim, &k.U, &k.NST);
+    k.smem = beam::smem_bytes(ef, h->ld, h->M0, k.U, k.NST, W);
+    return k;
+}
+
+/* resident teams per SM of a selection, cached per (generation, W, shared-memory size) */
+static cudaError_t occupancy_cached(MuninnCudaIndex *h, const KernelSel &k, int *occ) {
+    const int wi = k.gen == 7 ? 3 : (k.W == 4 ? 2 : k.W == 2 ? 1 : 0);
+    if (h->occ_smem[wi] == k.smem && h->occ_val[wi] > 0) { *occ = h->occ_val[wi]; return cudaSuccess; }
+    cudaError_t e = cudaFuncSetAttribute(k.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k.smem);
+    if (e != cudaSuccess) return e;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k.fn, 32 * k.W, k.smem);
+    if (e != cudaSuccess) return e;
+    h->occ_smem[wi] = k.smem; h->occ_val[wi] = *occ;
     return cudaSuccess;
 }
 
-template <int METRIC>
-static cudaError_t launch_levels(MuninnCudaIndex *h, SearchParams p, size_t smem, const int teams[3],
-                                 const unsigned caps[3], int nlevels, int nq) {
-    /* constant-dimension instances for the shapes BASELINE.json names; any other dim runs the generic ones */
-    if (MUNINN_D128 && h->dim == 128) return launch_levels_rb<METRIC, RB_NARROW, 128>(h, p, smem, teams, caps, nlevels, nq);
-    if (MUNINN_D128 && h->dim == 96) return launch_levels_rb<METRIC, RB_D96, 96>(h, p, smem, teams, caps, nlevels, nq);
-    if (MUNINN_D128 && h->dim == 768) return launch_levels_rb<METRIC, RB_WIDE, 768>(h, p, smem, teams, caps, nlevels, nq);
-    return beam_rows(h->ld) == RB_NARROW ? launch_levels_rb<METRIC, RB_NARROW, 0>(h, p, smem, teams, caps, nlevels, nq)
-                                         : launch_levels_rb<METRIC, RB_WIDE, 0>(h, p, smem, teams, caps, nlevels, nq);
-}
-
-template <int METRIC, int RB, int CD>
-static cudaError_t occupancy_of_rb(int *occ, size_t smem) {
-    cudaError_t e = cudaFuncSetAttribute(hnsw_search_kernel<METRIC, RB, CD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, hnsw_search_kernel<METRIC, RB, CD>, 32, smem);
-}
-template <int METRIC>
-static cudaError_t occupancy_of(int *occ, size_t smem, int ld, int dim) {
-    if (MUNINN_D128 && dim == 128) return occupancy_of_rb<METRIC, RB_NARROW, 128>(occ, smem);
-    if (MUNINN_D128 && dim == 96) return occupancy_of_rb<METRIC, RB_D96, 96>(occ, smem);
-    if (MUNINN_D128 && dim == 768) return occupancy_of_rb<METRIC, RB_WIDE, 768>(occ, smem);
-    return beam_rows(ld) == RB_NARROW ? occupancy_of_rb<METRIC, RB_NARROW, 0>(occ, smem) : occupancy_of_rb<METRIC, RB_WIDE, 0>(occ, smem);
-}
+static const size_t SEARCH_SMEM_LIMIT = 200 * 1024;
 
 extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *d_queries, int nq, int k, int ef,
                                                int64_t *d_ids, float *d_dist, int32_t *d_count,
@@ -596,19 +661,34 @@ extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *
     if (nq == 0) return MUNINN_CUDA_OK;
     if (!d_queries || !d_ids || !d_dist || !d_count) return fail(h, MUNINN_CUDA_E_ARG, "NULL buffer");
     if (ef < k) ef = k; /* src/hnsw_algo.c:673 */
-    const size_t smem = search_smem_bytes(ef, h->ld, h->M0, MUNINN_D128 ? h->dim : -1);
-    if (smem > 200 * 1024) return fail(h, MUNINN_CUDA_E_ARG, "ef=%d with dim=%d needs %zu B of shared memory per query (limit 200 KiB)", ef, h->dim, smem);
     CK(h, cudaSetDevice(h->device));
 
-    int occ = h->occ_val;
-    if (smem != h->occ_smem) { /* the occupancy query costs microseconds: once per (ef, index shape) */
-        cudaError_t oe = h->metric == MUNINN_METRIC_L2       ? occupancy_of<METRIC_L2>(&occ, smem, h->ld, h->dim)
-                         : h->metric == MUNINN_METRIC_COSINE ? occupancy_of<METRIC_COSINE>(&occ, smem, h->ld, h->dim)
-                                                             : occupancy_of<METRIC_IP>(&occ, smem, h->ld, h->dim);
-        CK(h, oe);
-        h->occ_smem = smem; h->occ_val = occ;
+    /* team width: the caller's choice, else the widest team that still keeps every query of the batch resident
+     * at once (a lone query is a dependent chain of instructions: more warps shorten it; a full batch wants
+     * as many independent queries per SM as fit) */
+    KernelSel sel;
+    int occ = 0;
+    const int gen = h->kernel_gen;
+    if (gen == 7) {
+        sel = select_kernel(h, 7, 1, ef);
+        if (sel.smem > SEARCH_SMEM_LIMIT) return fail(h, MUNINN_CUDA_E_ARG, "ef=%d with dim=%d needs %zu B of shared memory per query (limit 200 KiB)", ef, h->dim, sel.smem);
+        CK(h, occupancy_cached(h, sel, &occ));
+    } else {
+        const int forced = h->warps_per_query;
+        bool found = false;
+        for (int W = forced ? forced : 4; W >= 1 && !found; W >>= 1) {
+            sel = select_kernel(h, 8, W, ef);
+            if (sel.smem > SEARCH_SMEM_LIMIT) {
+                if (W == 1) return fail(h, MUNINN_CUDA_E_ARG, "ef=%d with dim=%d needs %zu B of shared memory per query (limit 200 KiB)", ef, h->dim, sel.smem);
+                continue;
+            }
+            CK(h, occupancy_cached(h, sel, &occ));
+            found = forced || W == 1 || (occ >= 1 && (long long)nq <= (long long)h->num_sms * occ);
+            if (forced) break;
+        }
     }
     if (occ < 1) return fail(h, MUNINN_CUDA_E_CUDA, "search kernel does not fit on an SM");
+    const size_t smem = sel.smem;
     int tps = h->teams_per_sm > 0 ? std::min(h->teams_per_sm, occ) : occ;
     int teams[3];
     unsigned caps[3];
@@ -617,7 +697,7 @@ extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *
     /* first-level table: 2·ef·2M slots. A search visits ≈ 0.8·ef·2M nodes on the bench graphs, so the table
      * runs at ≈ 40 % load at the end of a typical query and the whole arena (teams × cap × 4 B = 58 MB at
      * config 2) stays L2-resident; the rare query that would pass 3/4 load is redone at the next level. */
-    caps[0] = std::min(pow2_at_least((unsigned long long)MUNINN_VIS_FACTOR * (unsigned long long)ef * h->M0), cap_all);
+    caps[0] = std::min(pow2_at_least((unsigned long long)(h->vis_factor * (double)ef * h->M0)), cap_all);
     caps[1] = (unsigned)std::min<unsigned long long>(16ull * caps[0], cap_all);
     caps[2] = cap_all;
     int nlevels = caps[0] == cap_all ? 1 : (caps[1] == cap_all ? 2 : 3);
@@ -650,12 +730,22 @@ extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *
     p.vis = h->d_vis;
 
     CK(h, cudaEventRecord(h->ev0, h->stream));
-    cudaError_t e = h->metric == MUNINN_METRIC_L2       ? launch_levels<METRIC_L2>(h, p, smem, teams, caps, nlevels, nq)
-                    : h->metric == MUNINN_METRIC_COSINE ? launch_levels<METRIC_COSINE>(h, p, smem, teams, caps, nlevels, nq)
-                                                        : launch_levels<METRIC_IP>(h, p, smem, teams, caps, nlevels, nq);
-    CK(h, e);
+    for (int lv = 0; lv < nlevels; lv++) {
+        p.vis_cap = caps[lv];
+        p.vis_shift = 32 - log2u(caps[lv]);
+        p.work_counter = h->d_ctl + lv;
+        p.in_list = lv == 0 ? nullptr : h->d_retry + (size_t)(lv - 1) * nq;
+        p.in_count = lv == 0 ? nullptr : h->d_ctl + 3 + (lv - 1);
+        p.out_list = h->d_retry + (size_t)(lv < 2 ? lv : 0) * nq;
+        p.out_count_retry = h->d_ctl + 3 + lv;
+        int level = lv;
+        void *args[2] = {(void *)&p, (void *)&level};
+        CK(h, cudaLaunchKernel(sel.fn, dim3((unsigned)teams[lv]), dim3((unsigned)(32 * sel.W)), args, smem, h->stream));
+        h->launches++;
+    }
     CK(h, cudaEventRecord(h->ev1, h->stream));
     h->have_timing = true;
+    h->last_W = sel.W;
     return MUNINN_CUDA_OK;
 }
 
@@ -1111,6 +1201,139 @@ extern "C" int muninn_cuda_topk_merge_device(MuninnCudaIndex *h, int parts, int 
         CK(h, cudaFuncSetAttribute(topk_merge_parts, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     topk_merge_parts<<<(nq + 3) / 4, 128, smem, h->stream>>>(parts, nq, k, d_idx_parts, d_dist_parts, d_count_parts, d_idx,
                                                              d_dist, d_count);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    return MUNINN_CUDA_OK;
+}
+
+/* ───────────────────────── sharded exact k-NN: one NCCL all-gather ───────────────────────── */
+
+/* NCCL is bound at run time: the library a host process already carries (torch's, an MPI launcher's) is the one whose
+ * communicators it hands us, so the entry points are looked up in that instance first; a plain C host gets the
+ * system's libnccl.so.2. Only the five calls below are used; their prototypes are NCCL's public ABI (nccl.h). */
+namespace {
+typedef int nccl_result_t;
+typedef struct { char internal[128]; } nccl_unique_id_t;
+struct NcclApi {
+    nccl_result_t (*AllGather)(const void *, void *, size_t, int, void *, cudaStream_t) = nullptr;
+    nccl_result_t (*GetUniqueId)(nccl_unique_id_t *) = nullptr;
+    nccl_result_t (*CommInitRank)(void **, int, nccl_unique_id_t, int) = nullptr;
+    nccl_result_t (*CommDestroy)(void *) = nullptr;
+    nccl_result_t (*CommCount)(void *, int *) = nullptr;
+    const char *(*GetErrorString)(nccl_result_t) = nullptr;
+    bool ok = false;
+    std::string why;
+};
+const int NCCL_UINT64 = 5; /* ncclUint64, nccl.h ncclDataType_t */
+}
+#include <dlfcn.h>
+static NcclApi &nccl_api() {
+    static NcclApi api;
+    static bool tried = false;
+    if (tried) return api;
+    tried = true;
+    void *lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD); /* the instance already in this process, if any */
+    if (!lib) lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
+    if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_LOCAL);
+    if (!lib) { api.why = std::string("libnccl.so.2 not found: ") + (dlerror() ? dlerror() : ""); return api; }
+    api.AllGather = (decltype(api.AllGather))dlsym(lib, "ncclAllGather");
+    api.GetUniqueId = (decltype(api.GetUniqueId))dlsym(lib, "ncclGetUniqueId");
+    api.CommInitRank = (decltype(api.CommInitRank))dlsym(lib, "ncclCommInitRank");
+    api.CommDestroy = (decltype(api.CommDestroy))dlsym(lib, "ncclCommDestroy");
+    api.CommCount = (decltype(api.CommCount))dlsym(lib, "ncclCommCount");
+    api.GetErrorString = (decltype(api.GetErrorString))dlsym(lib, "ncclGetErrorString");
+    api.ok = api.AllGather && api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.CommCount && api.GetErrorString;
+    if (!api.ok) api.why = "libnccl.so.2 lacks an expected symbol";
+    return api;
+}
+
+extern "C" int muninn_cuda_comm_unique_id(void *out_id128) {
+    if (!out_id128) return MUNINN_CUDA_E_ARG;
+    NcclApi &n = nccl_api();
+    if (!n.ok) return fail(nullptr, MUNINN_CUDA_E_STATE, "%s", n.why.c_str());
+    nccl_unique_id_t id;
+    const nccl_result_t r = n.GetUniqueId(&id);
+    if (r != 0) return fail(nullptr, MUNINN_CUDA_E_CUDA, "ncclGetUniqueId: %s", n.GetErrorString(r));
+    memcpy(out_id128, &id, sizeof id);
+    return MUNINN_CUDA_OK;
+}
+
+extern "C" int muninn_cuda_comm_create(int device, int world, int rank, const void *id128, void **out_comm) {
+    if (!id128 || !out_comm || world < 1 || rank < 0 || rank >= world) return MUNINN_CUDA_E_ARG;
+    *out_comm = nullptr;
+    if (muninn_cuda_device_count() <= 0) return fail(nullptr, MUNINN_CUDA_E_NODEVICE, "no CUDA device visible");
+    NcclApi &n = nccl_api();
+    if (!n.ok) return fail(nullptr, MUNINN_CUDA_E_STATE, "%s", n.why.c_str());
+    if (cudaSetDevice(device) != cudaSuccess) return fail(nullptr, MUNINN_CUDA_E_ARG, "device %d not usable", device);
+    nccl_unique_id_t id;
+    memcpy(&id, id128, sizeof id);
+    const nccl_result_t r = n.CommInitRank(out_comm, world, id, rank);
+    if (r != 0) return fail(nullptr, MUNINN_CUDA_E_CUDA, "ncclCommInitRank: %s", n.GetErrorString(r));
+    return MUNINN_CUDA_OK;
+}
+
+extern "C" void muninn_cuda_comm_destroy(void *comm) {
+    NcclApi &n = nccl_api();
+    if (comm && n.ok) n.CommDestroy(comm);
+}
+
+extern "C" int muninn_cuda_exact_knn_sharded_device(MuninnCudaIndex *h, void *nccl_comm, const float *d_queries, int nq, int k,
+                                                    int64_t index_base, int64_t *d_idx, float *d_dist, int32_t *d_count) {
+    if (!h) return MUNINN_CUDA_E_ARG;
+    if (!nccl_comm) return fail(h, MUNINN_CUDA_E_ARG, "NULL communicator");
+    if (index_base < 0 || index_base + h->n > 0xffffffffLL) return fail(h, MUNINN_CUDA_E_ARG, "global row indices must fit 32 bits");
+    NcclApi &n = nccl_api();
+    if (!n.ok) return fail(h, MUNINN_CUDA_E_STATE, "%s", n.why.c_str());
+    int world = 0;
+    nccl_result_t r = n.CommCount(nccl_comm, &world);
+    if (r != 0 || world < 1) return fail(h, MUNINN_CUDA_E_CUDA, "ncclCommCount: %s", n.GetErrorString(r));
+    /* this shard's lists land in the caller's output arrays first (global indices), are packed into keys … */
+    int rc = muninn_cuda_exact_knn_device(h, d_queries, nq, k, index_base, d_idx, d_dist, d_count);
+    if (rc || nq == 0) return rc;
+    const size_t cnt = (size_t)nq * k;
+    if ((size_t)(world + 1) * cnt > h->shard_keys_cap) {
+        CK(h, cudaStreamSynchronize(h->stream));
+        cudaFree(h->d_shard_keys); h->d_shard_keys = nullptr; h->shard_keys_cap = 0;
+        CK(h, cudaMalloc((void **)&h->d_shard_keys, (size_t)(world + 1) * cnt * 8));
+        h->shard_keys_cap = (size_t)(world + 1) * cnt;
+    }
+    unsigned long long *mine = h->d_shard_keys, *all = h->d_shard_keys + cnt;
+    topk_pack_keys<<<(unsigned)((cnt + 255) / 256), 256, 0, h->stream>>>(nq, k, d_idx, d_dist, d_count, mine);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    /* … exchanged with ONE all-gather of nq·k·8 bytes per rank over NVLink, and merged under (distance, index) */
+    r = n.AllGather(mine, all, cnt, NCCL_UINT64, nccl_comm, h->stream);
+    if (r != 0) return fail(h, MUNINN_CUDA_E_CUDA, "ncclAllGather: %s", n.GetErrorString(r));
+    const size_t smem = (size_t)4 * (k + 32) * 8;
+    if (smem > 48 * 1024) CK(h, cudaFuncSetAttribute(topk_merge_keys, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    topk_merge_keys<<<(nq + 3) / 4, 128, smem, h->stream>>>(world, nq, k, all, d_idx, d_dist, d_count);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    CK(h, cudaEventRecord(h->ev1, h->stream)); /* last_kernel_ms now spans scan + exchange + merge */
+    return MUNINN_CUDA_OK;
+}
+
+/* the merge alone, for callers that gathered the key lists themselves (tests: gloo on CPU, shards on one GPU) */
+extern "C" int muninn_cuda_topk_pack_keys_device(MuninnCudaIndex *h, int nq, int k, const int64_t *d_idx, const float *d_dist,
+                                                 const int32_t *d_count, uint64_t *d_keys) {
+    if (!h || nq < 0 || k < 1) return MUNINN_CUDA_E_ARG;
+    if (nq == 0) return MUNINN_CUDA_OK;
+    CK(h, cudaSetDevice(h->device));
+    const size_t cnt = (size_t)nq * k;
+    topk_pack_keys<<<(unsigned)((cnt + 255) / 256), 256, 0, h->stream>>>(nq, k, d_idx, d_dist, d_count, (unsigned long long *)d_keys);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    return MUNINN_CUDA_OK;
+}
+extern "C" int muninn_cuda_topk_merge_keys_device(MuninnCudaIndex *h, int parts, int nq, int k, const uint64_t *d_keys,
+                                                  int64_t *d_idx, float *d_dist, int32_t *d_count) {
+    if (!h) return MUNINN_CUDA_E_ARG;
+    if (parts < 1 || nq < 0 || k < 1 || k > 2048) return fail(h, MUNINN_CUDA_E_ARG, "bad parts/nq/k");
+    if (nq == 0) return MUNINN_CUDA_OK;
+    CK(h, cudaSetDevice(h->device));
+    const size_t smem = (size_t)4 * (k + 32) * 8;
+    if (smem > 48 * 1024) CK(h, cudaFuncSetAttribute(topk_merge_keys, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    topk_merge_keys<<<(nq + 3) / 4, 128, smem, h->stream>>>(parts, nq, k, (const unsigned long long *)d_keys, d_idx, d_dist, d_count);
     h->launches++;
     CK(h, cudaGetLastError());
     return MUNINN_CUDA_OK;

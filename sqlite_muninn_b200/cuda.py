@@ -31,6 +31,9 @@ ABI_SYMBOLS = (
     "muninn_cuda_exact_knn_device", "muninn_cuda_topk_merge_device", "muninn_cuda_distance_batch",
     "muninn_cuda_set_exact_mode", "muninn_cuda_exact_stats", "muninn_cuda_exact_filter_probe",
     "muninn_cuda_gather_ceiling", "muninn_cuda_index_patch", "muninn_cuda_build_device",
+    "muninn_cuda_last_team_width", "muninn_cuda_set_option", "muninn_cuda_exact_knn_sharded_device",
+    "muninn_cuda_comm_unique_id", "muninn_cuda_comm_create", "muninn_cuda_comm_destroy",
+    "muninn_cuda_topk_pack_keys_device", "muninn_cuda_topk_merge_keys_device",
 )
 
 EXACT_CUDA_CORE, EXACT_TC_3XTF32, EXACT_TC_1XTF32, EXACT_TC_AUTO = 0, 1, 2, 3
@@ -92,6 +95,15 @@ def lib():
         L.muninn_cuda_index_patch.argtypes = [_vp, C.c_int64, C.c_int32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int32, C.c_int32]
         L.muninn_cuda_gather_ceiling.argtypes = [C.c_int, C.c_int, C.c_int64, C.POINTER(C.c_float)]
         L.muninn_cuda_build_device.argtypes = [_vp, _vp]
+        L.muninn_cuda_last_team_width.argtypes = [_vp]
+        L.muninn_cuda_set_option.argtypes = [_vp, C.c_char_p, C.c_double]
+        L.muninn_cuda_exact_knn_sharded_device.argtypes = [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int64, _vp, _vp, _vp]
+        L.muninn_cuda_comm_unique_id.argtypes = [_vp]
+        L.muninn_cuda_comm_create.argtypes = [C.c_int, C.c_int, C.c_int, _vp, C.POINTER(_vp)]
+        L.muninn_cuda_comm_destroy.argtypes = [_vp]
+        L.muninn_cuda_comm_destroy.restype = None
+        L.muninn_cuda_topk_pack_keys_device.argtypes = [_vp, C.c_int, C.c_int, _vp, _vp, _vp, _vp]
+        L.muninn_cuda_topk_merge_keys_device.argtypes = [_vp, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _vp]
         _lib = L
     return _lib
 
@@ -123,6 +135,28 @@ def gather_ceiling(row_bytes: int, slab_bytes: int = 1 << 30, device: int = 0) -
     if rc != 0:
         raise MuninnCudaError(rc, lib().muninn_cuda_strerror(rc).decode())
     return float(out.value)
+
+
+def comm_unique_id() -> bytes:
+    """ncclGetUniqueId through the library (rank 0), to be shipped to the other ranks."""
+    buf = C.create_string_buffer(128)
+    rc = lib().muninn_cuda_comm_unique_id(buf)
+    if rc != 0:
+        raise MuninnCudaError(rc, lib().muninn_cuda_last_error(None).decode())
+    return buf.raw
+
+
+def comm_create(device: int, world: int, rank: int, uid: bytes) -> int:
+    """ncclCommInitRank through the library (collective); returns the communicator as an integer address."""
+    out = _vp()
+    rc = lib().muninn_cuda_comm_create(device, world, rank, C.create_string_buffer(uid, 128), C.byref(out))
+    if rc != 0:
+        raise MuninnCudaError(rc, lib().muninn_cuda_last_error(None).decode())
+    return out.value
+
+
+def comm_destroy(comm: int):
+    lib().muninn_cuda_comm_destroy(comm)
 
 
 def _ptr(a: np.ndarray | None):
@@ -279,12 +313,30 @@ class HnswIndexCuda:
         self._check(self.L.muninn_cuda_topk_merge_device(self.h, parts, nq, k, idx_parts, dist_parts, cnt_parts,
                                                          idx_ptr, dist_ptr, cnt_ptr))
 
+    def exact_knn_sharded_device(self, comm_ptr: int, q_ptr: int, nq: int, k: int, index_base: int, idx_ptr: int,
+                                 dist_ptr: int, cnt_ptr: int):
+        """This rank's shard scan + ONE ncclAllGather of 64-bit keys + merge. Device addresses."""
+        self._check(self.L.muninn_cuda_exact_knn_sharded_device(self.h, comm_ptr, q_ptr, nq, k, index_base, idx_ptr,
+                                                                dist_ptr, cnt_ptr))
+
+    def topk_pack_keys_device(self, nq: int, k: int, idx_ptr: int, dist_ptr: int, cnt_ptr: int, keys_ptr: int):
+        self._check(self.L.muninn_cuda_topk_pack_keys_device(self.h, nq, k, idx_ptr, dist_ptr, cnt_ptr, keys_ptr))
+
+    def topk_merge_keys_device(self, parts: int, nq: int, k: int, keys_ptr: int, idx_ptr: int, dist_ptr: int, cnt_ptr: int):
+        self._check(self.L.muninn_cuda_topk_merge_keys_device(self.h, parts, nq, k, keys_ptr, idx_ptr, dist_ptr, cnt_ptr))
+
     # -- plumbing ----------------------------------------------------------------------
     def set_stream(self, stream_ptr: int | None):
         self._check(self.L.muninn_cuda_set_stream(self.h, stream_ptr))
 
-    def set_tuning(self, warps_per_query: int = 1, teams_per_sm: int = 0):
+    def set_tuning(self, warps_per_query: int = 0, teams_per_sm: int = 0):
         self._check(self.L.muninn_cuda_set_tuning(self.h, warps_per_query, teams_per_sm))
+
+    def set_option(self, name: str, value: float):
+        self._check(self.L.muninn_cuda_set_option(self.h, name.encode(), float(value)))
+
+    def last_team_width(self) -> int:
+        return int(self.L.muninn_cuda_last_team_width(self.h))
 
     def last_kernel_ms(self) -> float:
         return float(self.L.muninn_cuda_last_kernel_ms(self.h))

@@ -4,8 +4,12 @@
   [r·nq/W, (r+1)·nq/W); there is no data-path collective. `gather_search_results` only exists to
   hand the concatenated answer to a caller that wants it on every rank.
 * Exact k-NN shards the BASE rows: every rank scans its rows for all queries, the per-shard
-  [nq × k] lists are exchanged with ONE all-gather (NCCL over NVLink on GPUs, gloo in the CPU
-  tests) and merged under (distance, row index) by muninn_cuda_topk_merge_device.
+  [nq × k] lists are packed into 64-bit keys (ordered distance << 32 | global row index, unused
+  tail = all ones) and exchanged with ONE all-gather of nq·k·8 bytes per rank, then merged under
+  (distance, row index). On GPUs all of it happens inside the C ABI
+  (muninn_cuda_exact_knn_sharded_device: scan + ncclAllGather + merge on the handle's stream);
+  `ShardedExactKnn` only does the rendezvous. The host statements of the packing and the merge
+  below exist for the gloo CPU tests of the gathered layout.
 """
 from __future__ import annotations
 
@@ -63,6 +67,79 @@ def allgather_topk_parts(idx, dist, cnt, group=None):
         dist_.all_gather(list(buf.unbind(0)), t.contiguous(), group=group)  # one collective per array; gloo-compatible
         outs.append(buf)
     return tuple(outs)
+
+
+KEY_NONE = np.uint64(0xFFFFFFFFFFFFFFFF)
+
+
+def pack_keys_host(idx: np.ndarray, dist: np.ndarray, cnt: np.ndarray) -> np.ndarray:
+    """Host statement of topk_pack_keys (csrc/exact_knn.cuh): ordered-distance << 32 | index, tail = all ones.
+    The float → uint32 map is order preserving with -0 folded into +0 (csrc/muninn_dev.cuh okey)."""
+    d = (np.asarray(dist, np.float32) + np.float32(0.0)).view(np.uint32)
+    ok = np.where(d & np.uint32(0x80000000), ~d, d | np.uint32(0x80000000)).astype(np.uint64)
+    keys = (ok << np.uint64(32)) | (np.asarray(idx, np.int64).astype(np.uint64) & np.uint64(0xFFFFFFFF))
+    k = keys.shape[1]
+    keys[np.arange(k)[None, :] >= np.asarray(cnt)[:, None]] = KEY_NONE
+    return keys
+
+
+def unpack_keys_host(keys: np.ndarray):
+    """Inverse of pack_keys_host → (idx int64 with -1 tail, dist float32 with 0 tail, cnt int32)."""
+    valid = keys != KEY_NONE
+    ok = (keys >> np.uint64(32)).astype(np.uint32)
+    bits = np.where(ok & np.uint32(0x80000000), ok & np.uint32(0x7FFFFFFF), ~ok).astype(np.uint32)
+    dist = np.where(valid, bits.view(np.float32), np.float32(0.0)).astype(np.float32)
+    idx = np.where(valid, (keys & np.uint64(0xFFFFFFFF)).astype(np.int64), np.int64(-1))
+    return idx, dist, valid.sum(axis=1).astype(np.int32)
+
+
+def allgather_topk_keys(keys, group=None):
+    """THE collective of the sharded exact k-NN: one all-gather of the [nq × k] key array → [W × nq × k].
+    `keys` is a torch tensor of int64 (the uint64 keys reinterpreted; gloo and NCCL both move int64)."""
+    import torch
+    import torch.distributed as dist_
+
+    world = dist_.get_world_size(group)
+    buf = torch.empty((world,) + tuple(keys.shape), dtype=keys.dtype, device=keys.device)
+    dist_.all_gather(list(buf.unbind(0)), keys.contiguous(), group=group)
+    return buf
+
+
+def merge_topk_keys_reference(keys_parts: np.ndarray, k: int):
+    """Host statement of topk_merge_keys: the k smallest keys over all parts, per query."""
+    parts, nq, _ = keys_parts.shape
+    allk = np.sort(np.transpose(keys_parts, (1, 0, 2)).reshape(nq, -1), axis=1)[:, :k]
+    return unpack_keys_host(allk)
+
+
+class ShardedExactKnn:
+    """Rendezvous for muninn_cuda_exact_knn_sharded_device under torch.distributed: rank 0 draws an ncclUniqueId through
+    the C ABI, torch.distributed ships the 128 bytes, every rank joins its own communicator (so the library's
+    collective never interleaves with torch's on one communicator). `use_torch_comm=True` hands the library torch's
+    ncclComm_t instead (ProcessGroupNCCL._comm_ptr)."""
+
+    def __init__(self, idx, device: int, use_torch_comm: bool = False, group=None):
+        import torch
+        import torch.distributed as dist_
+        from . import cuda as C_
+        self.idx, self.own = idx, not use_torch_comm
+        self.world, self.rank = dist_.get_world_size(group), dist_.get_rank(group)
+        if use_torch_comm:
+            pg = group or dist_.distributed_c10d._get_default_group()
+            self.comm = pg._get_backend(torch.device("cuda", device))._comm_ptr()
+        else:
+            box = [C_.comm_unique_id() if self.rank == 0 else None]
+            dist_.broadcast_object_list(box, src=0, group=group)
+            self.comm = C_.comm_create(device, self.world, self.rank, box[0])
+
+    def __call__(self, q_ptr: int, nq: int, k: int, index_base: int, idx_ptr: int, dist_ptr: int, cnt_ptr: int):
+        self.idx.exact_knn_sharded_device(self.comm, q_ptr, nq, k, index_base, idx_ptr, dist_ptr, cnt_ptr)
+
+    def close(self):
+        if self.own and self.comm:
+            from . import cuda as C_
+            C_.comm_destroy(self.comm)
+        self.comm = None
 
 
 def merge_topk_parts_reference(idx_parts: np.ndarray, dist_parts: np.ndarray, cnt_parts: np.ndarray, k: int):

@@ -17,6 +17,19 @@ def cuda():
     return c
 
 
+# Every search test runs once per kernel shape: generation 8 (hnsw_beam.cuh) with query teams of 1, 2 and 4 warps and
+# with the automatic choice, and the round-1 one-warp kernel kept for A/B timing. Results must not depend on it.
+TEAMS = {"v8-w1": ("8", "1"), "v8-w2": ("8", "2"), "v8-w4": ("8", "4"), "v8-auto": ("8", "0"), "v7": ("7", "1")}
+
+
+@pytest.fixture(params=sorted(TEAMS))
+def team(request, monkeypatch):
+    gen, w = TEAMS[request.param]
+    monkeypatch.setenv("MUNINN_KERNEL", gen)  # read by muninn_cuda_index_create
+    monkeypatch.setenv("MUNINN_WARPS", w)
+    return request.param
+
+
 # ── distances: test/test_vec_math.c known answers and bit-exactness vs the oracle ──
 def test_distance_known_answers(cuda):
     cases = [(L2, [1, 2, 3], [1, 2, 3], 0.0), (L2, [1, 0, 0], [0, 1, 0], 2.0), (COS, [1, 2, 3], [1, 2, 3], 0.0),
@@ -39,7 +52,7 @@ def test_distance_bit_exact(cuda, oracle, metric, dim):
 
 # ── search: committed outputs of the unmodified reference ──
 @pytest.mark.parametrize("name", GOLDEN)
-def test_search_reproduces_reference_golden(cuda, name):
+def test_search_reproduces_reference_golden(cuda, name, team):
     g, queries, k, cases = load_golden(name)
     with cuda.HnswIndexCuda.from_graph(g) as idx:
         for c in cases:
@@ -57,7 +70,7 @@ CONFIGS = [  # metric, M, dim, n, efc
 
 
 @pytest.mark.parametrize("metric,M,dim,n,efc", CONFIGS)
-def test_search_equals_oracle(cuda, oracle, metric, M, dim, n, efc):
+def test_search_equals_oracle(cuda, oracle, metric, M, dim, n, efc, team):
     from sqlite_muninn_b200.builder import build_graph
     base = uniform(n + dim, n, dim)
     if metric == IP:
@@ -78,7 +91,7 @@ def test_search_equals_oracle(cuda, oracle, metric, M, dim, n, efc):
             assert_results_match(ids, dist, cnt, r_ids, r_dist, r_cnt, "vs reference order")
 
 
-def test_search_tie_heavy_data_follows_canonical_order(cuda, oracle):
+def test_search_tie_heavy_data_follows_canonical_order(cuda, oracle, team):
     """Integer-valued rows: many bit-equal distances. The kernel must follow the documented
     (distance, slot) rule exactly, and stay a valid search (same distance multiset quality)."""
     from sqlite_muninn_b200.builder import build_graph
@@ -94,7 +107,7 @@ def test_search_tie_heavy_data_follows_canonical_order(cuda, oracle):
             assert np.array_equal(st["n_dist"], o_st["n_dist"])
 
 
-def test_edge_cases(cuda, oracle):
+def test_edge_cases(cuda, oracle, team):
     """test/test_hnsw_algo.c:72-94,147-180 and pytests/test_hnsw_vtab.py:93-119."""
     from sqlite_muninn_b200.builder import build_graph
     from sqlite_muninn_b200.graph import FlatGraph
@@ -137,7 +150,7 @@ def test_edge_cases(cuda, oracle):
         assert np.array_equal(b[0], o[0]) and not np.array_equal(a[0], b[0])
 
 
-def test_visited_table_overflow_retries_are_exact(cuda, oracle):
+def test_visited_table_overflow_retries_are_exact(cuda, oracle, team):
     """A query whose visited set outgrows its level-0 table is redone in a larger one: force it
     with ef small relative to the graph walk (huge patience via duplicates is not needed: use
     a dense small-M0 table by searching with ef=k=1 on a graph where the walk is long)."""
@@ -152,7 +165,7 @@ def test_visited_table_overflow_retries_are_exact(cuda, oracle):
             assert np.array_equal(ids, o[0]) and np.array_equal(dist, o[1]) and np.array_equal(st["n_dist"], o[3]["n_dist"])
 
 
-def test_full_size_properties(cuda, oracle):
+def test_full_size_properties(cuda, oracle, team):
     """BASELINE config-1 shape (10k×128, M=16) at batch 2k: idempotence, sortedness, counts, and
     agreement with exact k-NN as recall; oracle equality on a 200-query sample."""
     from sqlite_muninn_b200.builder import build_graph
