@@ -1,25 +1,32 @@
 #!/usr/bin/env python
 """bench.py — HNSW QPS at recall@10 >= 0.95 on the SIFT1M-shape config (BASELINE.json configs[1]).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--extras LIST]
 
-One "step" = one batched hnsw_search pass over a 10k-query batch (k=10) on the 1M×128 L2,
-M=16, ef_construction=200 graph, at the smallest ef of the sweep {64,96,128,192,256} whose
-recall@10 against exact k-NN is >= 0.95 (measured before the timed region, reported in
-`config`). Under torchrun every rank holds a replica of the graph and searches its own 10k
-batch (no data-path collective: weak scaling); `value` = total queries / max-over-ranks time.
+Headline (`value`, `e2e`, `roofline`): ONE fixed job — 80 000 queries = 8 x the 10k-query batch of configs[1], k=10 —
+searched on the 1M x 128 L2, M=16, ef_construction=200 graph at the smallest ef of {64,96,128,192,256} whose
+recall@10 against exact k-NN is >= 0.95. Under torchrun the graph is replicated and the job is SPLIT across the
+ranks (strong scaling, no data-path collective): rank r takes queries [r*Q/N, (r+1)*Q/N); at N=8 every GPU runs the
+named 10k batch. One step = one pass over the job; `value` = job queries / max-over-ranks device time.
+`e2e` = the same through host buffers: pinned queries in (H2D), search, results gathered to rank 0 and copied to
+its host memory (D2H), all inside the timed region; the gathered answer is compared with rank 0 running the whole
+job alone (`verified`).
 
-JSON keys beyond the base contract: `roofline` (algorithmic bytes of the search kernel ÷ its
-CUDA-event duration vs the measured HBM peak), `cpu_baseline` (the reference's own hnsw_search
-on the host cores, bounded sample), `e2e` (same metric through muninn_cuda_search_batch with
-pinned HOST buffers, copies inside the timed region), `gpu_launches`, `clocks`.
+Blocks under `extra` (each timed the same way at the current N, with its own roofline and `verified`):
+  split_10k  the literal 10k-query batch of configs[1] split over the N ranks (the latency-bound end of the split)
+  config3    1M x 768 cosine, M=32, 10k-query batch split over the ranks
+  config4    10M x 96 inner product, M=32, 10k-query batch split over the ranks
+  config5    exact brute-force k-NN, 50M x 128 L2, k=100: base rows sharded over the ranks, ONE ncclAllGather of
+             64-bit keys + merge inside muninn_cuda_exact_knn_sharded_device; checked against an independent scan
+`--extras none` (or MUNINN_BENCH_EXTRAS=none) runs the headline only; `--config 3|4|5` makes that config the headline.
 
-`--impl reference` times the reference's CPU hnsw_search (oracle/_ref when it was built, else
-the oracle port) on all host threads over bounded samples of the same workload.
+`--impl reference` times the reference's own CPU hnsw_search (oracle/_ref when it was built, else the oracle port)
+on all host threads over bounded samples of the same job; it never loads libmuninn_cuda.
 """
 from __future__ import annotations
 
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -27,6 +34,7 @@ import sys
 import tempfile
 import threading
 import time
+from types import SimpleNamespace
 
 import numpy as np
 
@@ -35,26 +43,29 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 METRIC_NAME = "HNSW QPS at recall@10>=0.95"
+METRIC_MISSED = "HNSW QPS (recall@10 target 0.95 NOT met at any ef of the sweep)"
 EF_SWEEP = (64, 96, 128, 192, 256)
+JOB_BATCHES = 8  # the headline job = 8 x the named 10k-query batch (one batch per GPU at N=8)
 
-# BASELINE.json `configs` (1-based like SURVEY.md §8d). Config 2 is the bench line the driver reads;
-# 3-5 are run by hand (`--config N`) and their lines are kept under profiles/. efc of configs 3/4 is
-# not fixed by BASELINE.json: the values below are the ones used.
+# BASELINE.json `configs` (1-based like SURVEY.md §8d). efc of configs 3/4 is not fixed by BASELINE.json: the values
+# below are the ones used. ef_calibrated / recall_calibrated: what the recall sweep picks on these (deterministic)
+# inputs — the reference arm, which has no exact k-NN, reports them.
 CONFIGS = {
     2: dict(name="SIFT1M-shape", n=1_000_000, dim=128, metric=0, M=16, efc=200, nq=10_000, k=10, ef_sweep=EF_SWEEP,
-            data="latent16", seeds=(11, 12), scaling="weak", ef_calibrated=64),
-    3: dict(name="text-embedding shape", n=1_000_000, dim=768, metric=1, M=32, efc=100, nq=10_000, k=10, ef_sweep=(128, 192, 256, 384),
-            data="spectrum", seeds=(21, 22), scaling="strong", ef_calibrated=128),
+            data="latent16", seeds=(11, 12), ef_calibrated=64, recall_calibrated=0.9525),
+    3: dict(name="text-embedding shape", n=1_000_000, dim=768, metric=1, M=32, efc=100, nq=10_000, k=10,
+            ef_sweep=(128, 192, 256, 384), data="spectrum", seeds=(21, 22), ef_calibrated=384, recall_calibrated=0.9563),
     4: dict(name="Deep10M-shape", n=10_000_000, dim=96, metric=2, M=32, efc=64, nq=10_000, k=10, ef_sweep=(64, 128, 256),
-            data="latent16n", seeds=(31, 32), scaling="strong", ef_calibrated=64),
-    5: dict(name="exact brute-force kNN", n=6_250_000, dim=128, metric=0, M=8, efc=0, nq=10_000, k=100, ef_sweep=(),
-            data="latent16", seeds=(41, 42), scaling="weak", ef_calibrated=0),
+            data="latent16n", seeds=(31, 32), ef_calibrated=64, recall_calibrated=0.9964),
+    5: dict(name="exact brute-force kNN", n=50_000_000, dim=128, metric=0, M=8, efc=0, nq=10_000, k=100, ef_sweep=(),
+            data="latent16", seeds=(41, 42), ef_calibrated=0, recall_calibrated=1.0),
 }
 METRIC_TEXT = {0: "L2", 1: "cosine", 2: "inner product"}
 DATA_TEXT = {"latent16": "rank-16 Gaussian latent embedded in dim-d + 0.05 isotropic noise",
              "latent16n": "rank-16 Gaussian latent embedded in dim-d + 0.05 isotropic noise, rows L2-normalised",
              "spectrum": "Gaussian with eigenvalue spectrum i^-1.5 (text-embedding-like anisotropy), rows L2-normalised"}
 CACHE_DIR = os.environ.get("MUNINN_BENCH_CACHE", os.path.join(tempfile.gettempdir(), "muninn_bench_cache"))
+KERNEL_SOURCES = ("hnsw_search.cuh", "hnsw_beam.cuh", "muninn_dev.cuh")
 
 
 def log(*a):
@@ -88,48 +99,65 @@ def make_vectors(n: int, dim: int, seed: int, latent: int = 16, noise: float = 0
     return out
 
 
-def graph_tag(args) -> str:
-    return (f"n{args.n}_d{args.dim}_m{args.metric}_M{args.M}_efc{args.efc}_b{args.build_batch}_{args.data}"
-            f"_s{args.seeds[0]}")
+def job_queries(c, batches: int) -> np.ndarray:
+    """Batch b of a job = make_vectors(nq, seed_q + b): batch 0 is the named 10k-query batch."""
+    return np.concatenate([make_vectors(c.nq, c.dim, c.seeds[1] + b, kind=c.data) for b in range(batches)], 0)
 
 
-def get_graph(args, rank: int, world: int, barrier):
+def cfg_of(num: int, args=None) -> SimpleNamespace:
+    c = SimpleNamespace(**CONFIGS[num])
+    c.config = num
+    c.build_batch = 1024
+    if args is not None and num == args.config:  # size overrides apply to the headline config (dry runs)
+        for key in ("n", "dim", "M", "efc", "nq", "k"):
+            if getattr(args, key, None) is not None:
+                setattr(c, key, getattr(args, key))
+        c.build_batch = args.build_batch
+    return c
+
+
+def graph_tag(c) -> str:
+    return f"n{c.n}_d{c.dim}_m{c.metric}_M{c.M}_efc{c.efc}_b{c.build_batch}_{c.data}_s{c.seeds[0]}"
+
+
+def get_graph(c, rank: int, world: int, barrier, device_build: bool = False):
     """Rank 0 builds (or loads) the graph; the other ranks load the cached copy."""
     from sqlite_muninn_b200.builder import build_graph
     from sqlite_muninn_b200.graph import FlatGraph
     os.makedirs(CACHE_DIR, exist_ok=True)
-    tag = graph_tag(args)
+    tag = graph_tag(c)
     path = os.path.join(CACHE_DIR, tag + ".npz")
     t0 = time.time()
+    base = None
     if rank == 0 and not os.path.exists(path):
-        base = make_vectors(args.n, args.dim, args.seeds[0], kind=args.data)
+        base = make_vectors(c.n, c.dim, c.seeds[0], kind=c.data)
         log(f"[bench] building {tag} with {os.cpu_count()} host threads …")
-        if args.device_build and args.impl != "reference":
-            # same group-synchronous rule with the layer-0 candidate searches on the GPU (builder.build_graph_device):
-            # the same graph wherever no two candidate distances are bit-equal
+        if device_build:
+            # same group-synchronous rule with the layer-0 candidate searches on the GPU (builder.build_graph_device)
             from sqlite_muninn_b200.builder import build_graph_device
             st = {}
-            g = build_graph_device(base, args.metric, args.M, args.efc, batch=args.build_batch, warm=8192, stats=st,
+            g = build_graph_device(base, c.metric, c.M, c.efc, batch=c.build_batch, warm=8192, stats=st,
                                    device=int(os.environ.get("LOCAL_RANK", "0")))
             log(f"[bench] device-assisted build: {st}")
         else:
-            g = build_graph(base, args.metric, args.M, args.efc, batch=args.build_batch, warm=8192)
+            g = build_graph(base, c.metric, c.M, c.efc, batch=c.build_batch, warm=8192)
         tmp = path + ".tmp.npz"
         np.savez(tmp, levels=g.levels, list_offsets=g.list_offsets, targets=g.targets, entry_slot=g.entry_slot,
                  max_level=g.max_level)
         os.replace(tmp, path)
         log(f"[bench] graph built in {time.time() - t0:.1f}s")
     barrier()
-    base = make_vectors(args.n, args.dim, args.seeds[0], kind=args.data)
+    if base is None:
+        base = make_vectors(c.n, c.dim, c.seeds[0], kind=c.data)
     z = np.load(path)
-    g = FlatGraph(args.dim, args.metric, args.M, args.efc, np.arange(args.n, dtype=np.int64), z["levels"],
-                  np.zeros(args.n, np.uint8), base, z["list_offsets"], z["targets"], int(z["entry_slot"]),
+    g = FlatGraph(c.dim, c.metric, c.M, c.efc, np.arange(c.n, dtype=np.int64), z["levels"],
+                  np.zeros(c.n, np.uint8), base, z["list_offsets"], z["targets"], int(z["entry_slot"]),
                   int(z["max_level"]))
-    log(f"[bench] rank {rank}: graph ready in {time.time() - t0:.1f}s (n={g.n}, max_level={g.max_level})")
+    log(f"[bench] rank {rank}: graph {tag} ready in {time.time() - t0:.1f}s (max_level={g.max_level})")
     return g
 
 
-# ───────────────────────── clocks ─────────────────────────
+# ───────────────────────── clocks / host ─────────────────────────
 
 class ClockSampler:
     """nvidia-smi sampled every 200 ms during the timed region (B200_PROFILING.md)."""
@@ -148,6 +176,7 @@ class ClockSampler:
             threading.Thread(target=self._read, daemon=True).start()
         except OSError:
             self.proc = None
+        return self
 
     def _read(self):
         for line in self.proc.stdout:
@@ -163,6 +192,16 @@ class ClockSampler:
         reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i] == "Active"})
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_model() -> str:
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
 
 
 # ───────────────────────── CPU reference leg ─────────────────────────
@@ -196,7 +235,7 @@ class CpuReference:
 
     def run(self, queries, k, ef):
         ids, dist, cnt, secs = self._run(queries, k, ef)
-        return ids, secs
+        return ids, dist, secs
 
 
 def recall_at_k(ids: np.ndarray, truth: np.ndarray) -> float:
@@ -204,62 +243,92 @@ def recall_at_k(ids: np.ndarray, truth: np.ndarray) -> float:
     return float(np.mean([len(set(a) & set(b)) / k for a, b in zip(ids, truth)]))
 
 
-def run_reference_arm(args, rank: int, world: int) -> None:
-    """`--impl reference`: rank 0 alone times the CPU path; the other ranks exit 0."""
-    if rank != 0:
-        return
-    g = get_graph(args, 0, 1, lambda: None)
-    queries = make_vectors(args.nq, args.dim, args.seeds[1], kind=args.data)
-    cpu = CpuReference(g)
-    # the ef the GPU arm times: its cached choice when it ran first on this box, else the calibrated
-    # value (the graph and the queries are deterministic, so the recall sweep always picks the same ef)
-    ef = args.ef or int(os.environ.get("MUNINN_BENCH_EF", "0")) or load_chosen_ef(args) or CONFIGS[args.config]["ef_calibrated"]
-    n_s = cpu.sample_size(queries, args.k, ef, args.cpu_seconds / max(1, args.steps + args.warmup) * 2)
-    sample = queries[:n_s]
-    for _ in range(args.warmup):
-        cpu.run(sample[: max(cpu.threads * 2, n_s // 8)], args.k, ef)
-    secs = 0.0
-    for _ in range(args.steps):
-        secs += cpu.run(sample, args.k, ef)[1]
-    qps = args.steps * n_s / secs
-    desc = {"value": qps, "unit": "queries/s", "cores": cpu.threads, "kind": cpu.kind,
-            "sample": f"{n_s} of the {args.nq} queries per step, ef={ef}, k={args.k}, {cpu.threads} host threads"}
-    print(json.dumps({
-        "impl": "reference", "metric": METRIC_NAME, "value": qps, "unit": "queries/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * secs / args.steps,
-        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, ef, None), "cpu_baseline": desc,
-        "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0}), flush=True)
+def workload_config(c, ef, recall, job_q: int):
+    slab_mb, list_mb = c.n * c.dim * 4 / 1e6, c.n * 2 * c.M * 4 / 1e6
+    return {"workload": f"{c.name} {c.n}x{c.dim} fp32 {METRIC_TEXT[c.metric]}, M={c.M}, ef_construction={c.efc}, "
+                        f"{c.nq}-query batch, k={c.k} (BASELINE.json configs[{c.config - 1}])",
+            "job": f"{job_q} queries ({job_q // c.nq} x the {c.nq}-query batch) per step, split evenly across the GPUs",
+            "ef": ef, "ef_sweep": list(c.ef_sweep), "recall_at_10": recall,
+            "data_distribution": f"{DATA_TEXT[c.data]}, seeds {c.seeds[0]}/{c.seeds[1]}+batch",
+            "graph": f"reference construction rule, batch-synchronous inserts (groups of {c.build_batch}), "
+                     "neighbour lists in shadow-table order",
+            "l2_policy": f"inputs ({slab_mb:.0f} MB slab + {list_mb:.0f} MB lists) exceed the 126 MB L2; no flush between steps",
+            "parallelism": "graph replicated, one job split by query across the GPUs, no data-path collective"}
 
 
-def chosen_ef_path(args) -> str:
-    return os.path.join(CACHE_DIR, "ef_" + graph_tag(args) + ".json")
+def chosen_ef_path(c) -> str:
+    return os.path.join(CACHE_DIR, "ef_" + graph_tag(c) + ".json")
 
 
-def load_chosen_ef(args):
+def load_chosen(c):
     try:
-        return int(json.load(open(chosen_ef_path(args)))["ef"])
+        d = json.load(open(chosen_ef_path(c)))
+        return int(d["ef"]), float(d["recall"])
     except Exception:
         return None
 
 
-def workload_config(args, ef, recall):
-    slab_mb, list_mb = args.n * args.dim * 4 / 1e6, args.n * 2 * args.M * 4 / 1e6
-    per_gpu = (f"one {args.nq}-query batch per GPU" if args.scaling == "weak"
-               else f"the {args.nq}-query batch split evenly across the GPUs")
-    return {"workload": f"{args.cfg_name} {args.n}x{args.dim} fp32 {METRIC_TEXT[args.metric]}, M={args.M}, "
-                        f"ef_construction={args.efc}, {args.nq}-query batch, k={args.k} "
-                        f"(BASELINE.json configs[{args.config - 1}])",
-            "ef": ef, "ef_sweep": list(args.ef_sweep), "recall_at_10": recall,
-            "data_distribution": f"{DATA_TEXT[args.data]}, seeds {args.seeds[0]}/{args.seeds[1]}",
-            "graph": f"reference construction rule, batch-synchronous inserts (groups of {args.build_batch}), "
-                     "neighbour lists in shadow-table order",
-            "l2_policy": f"inputs ({slab_mb:.0f} MB slab + {list_mb:.0f} MB lists) exceed the 126 MB L2; no flush between steps",
-            "parallelism": f"graph replicated, {per_gpu}, no collective"}
+def run_reference_arm(args, rank: int, world: int) -> None:
+    """`--impl reference`: rank 0 alone times the CPU path; the other ranks exit 0."""
+    if rank != 0:
+        return
+    c = cfg_of(args.config, args)
+    if args.config == 5:
+        return run_reference_arm_exact(args, c)
+    g = get_graph(c, 0, 1, lambda: None)
+    job_q = c.nq * JOB_BATCHES
+    queries = make_vectors(c.nq, c.dim, c.seeds[1], kind=c.data)  # the sample comes from batch 0 of the job
+    cpu = CpuReference(g)
+    # the ef the GPU arm times and the recall it measured: its cached choice when it ran first on this box, else the
+    # calibrated values (graph and queries are deterministic, so the recall sweep always lands on the same pair)
+    ef, recall = load_chosen(c) or (c.ef_calibrated, c.recall_calibrated)
+    if args.ef:
+        ef = args.ef
+    n_s = cpu.sample_size(queries, c.k, ef, args.cpu_seconds / max(1, args.steps + args.warmup) * 2)
+    sample = queries[:n_s]
+    for _ in range(args.warmup):
+        cpu.run(sample[: max(cpu.threads * 2, n_s // 8)], c.k, ef)
+    per_step = [cpu.run(sample, c.k, ef)[2] for _ in range(args.steps)]
+    secs = float(np.sum(per_step))
+    qps = args.steps * n_s / secs
+    desc = {"value": qps, "unit": "queries/s", "cores": cpu.threads, "cpu_model": cpu_model(), "kind": cpu.kind,
+            "median_qps": n_s / float(np.median(per_step)), "best_qps": n_s / float(np.min(per_step)),
+            "sample": f"{n_s} queries of the job per step, ef={ef}, k={c.k}, {cpu.threads} host threads, {args.steps} repeats"}
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC_NAME, "value": qps, "unit": "queries/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * secs / args.steps,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(c, ef, recall, job_q), "cpu_baseline": desc,
+        "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}), flush=True)
 
 
-# ───────────────────────── GPU arm ─────────────────────────
+def run_reference_arm_exact(args, c) -> None:
+    """`--impl reference --config 5`: the oracle's brute-force k-NN on a bounded sample (rows and queries)."""
+    from oracle.bindings import Oracle
+    threads = os.cpu_count() or 1
+    rows = min(c.n, 2_000_000)
+    base = make_vectors(rows, c.dim, c.seeds[0], kind=c.data)
+    queries = make_vectors(c.nq, c.dim, c.seeds[1], kind=c.data)
+    n_s = max(threads, min(c.nq, int(args.cpu_seconds / max(1, args.steps + args.warmup) * threads * 2.0e9 / (3.0 * rows * c.dim))))
+    per_step = []
+    for i in range(args.warmup + args.steps):
+        secs = Oracle().exact_knn(base, queries[:n_s], c.k, c.metric, threads=threads)[3]
+        if i >= args.warmup:
+            per_step.append(secs)
+    qps = n_s / float(np.mean(per_step)) * rows / c.n  # the scan is linear in the rows: scaled to the full base
+    print(json.dumps({"impl": "reference", "metric": "exact k-NN queries/s (k=100, base sharded, top-k all-gather merge)",
+                      "value": qps, "unit": "queries/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+                      "ms_per_step": 1000.0 * float(np.mean(per_step)), "higher_is_better": True, "scaling": "strong",
+                      "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                      "config": {"workload": f"exact brute-force kNN {c.n}x{c.dim} L2, k={c.k}, {c.nq}-query batch (BASELINE.json configs[4])"},
+                      "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": threads, "cpu_model": cpu_model(), "kind": "port",
+                                       "sample": f"{n_s} queries x {rows} rows per step, scaled linearly to {c.n} rows"},
+                      "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                      "gpu_launches": 0}), flush=True)
+
+
+# ───────────────────────── GPU arm: helpers ─────────────────────────
 
 def algorithmic_bytes(stats: np.ndarray, dim: int, M: int, k: int) -> float:
     """B(q) = n_dist·d·4 (rows gathered) + n_expand·M0·4 (layer-0 lists)
@@ -272,364 +341,554 @@ def algorithmic_bytes(stats: np.ndarray, dim: int, M: int, k: int) -> float:
     return float(nd * dim * 4 + ne * 2 * M * 4 + ng * M * 4 + nq * (dim * 4 + k * 12))
 
 
-def measured_peak_tf32():
-    """Dense TF32 runs at half the bf16 rate; the bf16 burst figure is the driver-measured one."""
+def measured_peaks() -> dict:
     try:
-        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"]) / 2.0, "measured bf16 burst / 2"
+        d = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return {"hbm_gbs": float(d["hbm_gbs"]), "bf16_tflops": float(d["bf16_tflops"]), "source": "measured"}
     except Exception:
-        return 1590.0 / 2.0, "fallback bf16 / 2"
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "source": "fallback"}
 
 
-def exact_summary(args, nq: int, total_ms: float, st: dict, n_rows: int | None = None) -> dict:
-    """Ground-truth pass: exact k-NN through the tensor-core filter. Tensor roofline = TF32 MMA flops
-    the filter ISSUES (3 per product for 3xTF32) ÷ its own CUDA-event time; algorithmic = 2·nq·n·d."""
-    n_rows = n_rows or args.n
-    flops = 2.0 * nq * n_rows * args.dim
-    issued = flops * {0: 0, 1: 3, 2: 1}[st["mode"]]
-    peak, which = measured_peak_tf32()
-    out = {"ms": round(total_ms, 3), "mode": {0: "cuda-core chains", 1: "3xTF32 filter + exact re-rank", 2: "1xTF32 filter + exact re-rank"}[st["mode"]],
-           "filter_ms": round(st["filter_ms"], 3), "chunks": st["chunks"],
-           "survivors_per_query": round(st["candidates"] / max(nq, 1), 1), "overflow_queries": st["overflow_queries"],
-           "algorithmic_TFLOPs": round(flops / max(total_ms, 1e-9) / 1e9, 1)}
-    if st["mode"] == 2 and st["filter_ms"] > 0:  # small batches: one TF32 product off the raw slab, HBM-bound
-        hbm, hw = measured_peak_gbs()
-        ach = n_rows * args.dim * 4.0 / st["filter_ms"] / 1e6
-        out["roofline"] = {"bound": "hbm", "achieved": round(ach, 1), "peak": hbm, "unit": "GB/s", "frac": round(ach / hbm, 4),
-                           "peak_source": hw, "kernel": "exact_tc_filter (base rows read once / its CUDA-event time)"}
-    elif st["mode"] != 0 and st["filter_ms"] > 0:
-        ach = issued / st["filter_ms"] / 1e9
-        out["roofline"] = {"bound": "tensor", "achieved": round(ach, 1), "peak": round(peak, 1), "unit": "TFLOP/s",
-                           "frac": round(ach / peak, 4), "peak_source": which, "kernel": "exact_tc_filter",
-                           "of_nominal_1100": round(ach / 1100.0, 4)}
-    return out
+def kernel_source_sha() -> str:
+    h = hashlib.sha256()
+    for f in KERNEL_SOURCES:
+        h.update(open(os.path.join(ROOT, "sqlite_muninn_b200", "csrc", f), "rb").read())
+    return h.hexdigest()[:16]
 
 
-def ncu_traffic(args, ef):
-    """dram__bytes_read.sum + dram__bytes_write.sum of ONE level-0 search launch, from the `ncu --set full` capture
-    of this command summarised in profiles/r1_search_kernel_v7_ncu_full.txt (6.812 GB + 0.284 GB; algorithmic bytes
-    of the same launch: 8.472 GB — the 58 MB visited arena leaves the rest of the 126 MB L2 to the hot rows and lists,
-    so DRAM moves 0.84x of the algorithmic bytes). Only the captured configuration has a number."""
-    if (args.config, args.n, args.nq, ef) == (2, 1_000_000, 10_000, 64):
-        return 7.096e9
+def ncu_traffic(config: int, ef: int, nq: int):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE level-0 search launch, read at run time from the committed
+    summary of an `ncu --set full` capture (profiles/search_traffic.json, written by tools/ncu_traffic.py from the
+    report). The record carries the hash of the kernel sources it was captured with: after any kernel change the
+    hashes differ and the figure is withheld (null) until a new capture is committed."""
+    try:
+        recs = json.load(open(os.path.join(ROOT, "profiles", "search_traffic.json")))
+    except Exception:
+        return None
+    sha = kernel_source_sha()
+    for r in recs:
+        if (r.get("config"), r.get("ef"), r.get("nq")) == (config, ef, nq) and r.get("kernel_src_sha") == sha:
+            return float(r["dram_bytes"])
     return None
 
 
-def measured_peak_gbs():
-    try:
-        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "measured"
-    except Exception:
-        return 6650.0, "fallback"
+def exact_summary(dim: int, nq: int, n_rows: int, total_ms: float, st: dict) -> dict:
+    """Exact k-NN through the tensor-core filter. Tensor roofline, SURVEY §8(d): ALGORITHMIC flops 2·nq·n·d (one product
+    per pair, "not x3") ÷ the filter kernels' CUDA-event time, against the measured TF32 peak (bf16 burst / 2); the
+    issued-MMA rate (3 products per pair in 3xTF32) is reported beside it."""
+    flops = 2.0 * nq * n_rows * dim
+    issued = flops * {0: 0, 1: 3, 2: 1}[st["mode"]]
+    pk = measured_peaks()
+    peak = pk["bf16_tflops"] / 2.0
+    out = {"ms": round(total_ms, 3), "mode": {0: "cuda-core chains", 1: "3xTF32 filter + exact re-rank", 2: "1xTF32 filter + exact re-rank"}[st["mode"]],
+           "filter_ms": round(st["filter_ms"], 3), "chunks": st["chunks"],
+           "survivors_per_query": round(st["candidates"] / max(nq, 1), 1), "overflow_queries": st["overflow_queries"],
+           "algorithmic_TFLOPs_whole_call": round(flops / max(total_ms, 1e-9) / 1e9, 1)}
+    if st["mode"] != 0 and st["filter_ms"] > 0:
+        hbm_ach = n_rows * dim * 4.0 / st["filter_ms"] / 1e6
+        alg = flops / st["filter_ms"] / 1e9
+        if hbm_ach / pk["hbm_gbs"] > alg / peak:  # small batches: the row stream is the bound
+            out["roofline"] = {"bound": "hbm", "achieved": round(hbm_ach, 1), "peak": pk["hbm_gbs"], "unit": "GB/s",
+                               "frac": round(hbm_ach / pk["hbm_gbs"], 4), "peak_source": pk["source"],
+                               "kernel": "exact_tc_filter (base rows read once / its CUDA-event time)"}
+        else:
+            out["roofline"] = {"bound": "tensor", "achieved": round(alg, 1), "peak": round(peak, 1), "unit": "TFLOP/s",
+                               "frac": round(alg / peak, 4), "peak_source": pk["source"] + " bf16 burst / 2",
+                               "what": "algorithmic 2*nq*n*d over the filter kernels' time (SURVEY 8d)",
+                               "issued_TFLOPs": round(issued / st["filter_ms"] / 1e9, 1),
+                               "issued_frac": round(issued / st["filter_ms"] / 1e9 / peak, 4), "kernel": "exact_tc_filter"}
+    return out
 
 
-def run_gpu_arm(args, rank: int, local_rank: int, world: int) -> None:
-    import torch
-    import torch.distributed as dist
-    from sqlite_muninn_b200.cuda import STATS_DTYPE, HnswIndexCuda
+class Dist:
+    """torch.distributed plumbing of one bench process (NCCL, one rank per GPU)."""
 
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
-    torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-
-    def barrier():
+    def __init__(self, rank, local_rank, world):
+        import torch
+        self.torch, self.rank, self.local_rank, self.world = torch, rank, local_rank, world
+        torch.cuda.set_device(local_rank)
         if world > 1:
-            dist.barrier()
+            import torch.distributed as dist
+            self.dist = dist
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        self.stream = torch.cuda.Stream()  # a real stream: the legacy default stream (0) means "handle's own" to the ABI
+        torch.cuda.set_stream(self.stream)
 
-    g = get_graph(args, rank, world, barrier)
-    idx = HnswIndexCuda.from_graph(g, device=local_rank)
-    stream = torch.cuda.Stream()  # a real stream: the legacy default stream (0) means "handle's own" to the ABI
-    torch.cuda.set_stream(stream)
-    idx.set_stream(stream.cuda_stream)
-    if args.teams_per_sm:
-        idx.set_tuning(1, args.teams_per_sm)
-    k, dim = args.k, args.dim
-    if args.scaling == "weak":  # every rank searches its own batch
-        queries = make_vectors(args.nq, dim, args.seeds[1] + rank, kind=args.data)
-    else:  # one batch, rank r takes queries [r·nq/W, (r+1)·nq/W)
-        from sqlite_muninn_b200.multi import shard_range
-        lo, hi = shard_range(args.nq, rank, world)
-        queries = np.ascontiguousarray(make_vectors(args.nq, dim, args.seeds[1], kind=args.data)[lo:hi])
-    nq = queries.shape[0]
-    nq_job = world * nq if args.scaling == "weak" else args.nq
-    h_q = torch.from_numpy(queries).pin_memory()
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+
+    def max_over_ranks(self, *vals):
+        t = self.torch.tensor(list(vals), device="cuda", dtype=self.torch.float64)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return [float(x) for x in t]
+
+    def bcast_int(self, v: int) -> int:
+        if self.world == 1:
+            return v
+        t = self.torch.tensor([v], device="cuda")
+        self.dist.broadcast(t, 0)
+        return int(t.item())
+
+    def gather_rows(self, t, pad_rows: int):
+        """Device tensor [rows_r, …] of every rank → on rank 0 a list of W tensors [pad_rows, …] (rows past a rank's
+        own count are padding); None elsewhere. One collective."""
+        torch = self.torch
+        if t.shape[0] != pad_rows:
+            p = torch.zeros((pad_rows,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+            p[: t.shape[0]] = t
+            t = p
+        if self.world == 1:
+            return [t]
+        out = [torch.empty_like(t) for _ in range(self.world)] if self.rank == 0 else None
+        self.dist.gather(t.contiguous(), out, dst=0)
+        return out
+
+    def close(self):
+        if self.world > 1:
+            self.dist.destroy_process_group()
+
+
+# ───────────────────────── GPU arm: one search job ─────────────────────────
+
+def run_search_job(D: Dist, idx, c, queries_job: np.ndarray, ef: int, steps: int, warmup: int, label: str) -> dict:
+    """One fixed job (`queries_job`) split over the ranks: device-resident timing, end-to-end timing with the results
+    gathered to rank 0, verification of the gathered answer against rank 0 running the whole job alone."""
+    torch = D.torch
+    from sqlite_muninn_b200.cuda import STATS_DTYPE
+    from sqlite_muninn_b200.multi import shard_range
+    k, dim, job_q = c.k, c.dim, queries_job.shape[0]
+    lo, hi = shard_range(job_q, D.rank, D.world)
+    nq = hi - lo
+    pad = max(shard_range(job_q, r, D.world)[1] - shard_range(job_q, r, D.world)[0] for r in range(D.world))
+    h_q = torch.from_numpy(np.ascontiguousarray(queries_job[lo:hi])).pin_memory()
     d_q = h_q.cuda(non_blocking=True)
     d_ids = torch.empty((nq, k), dtype=torch.int64, device="cuda")
     d_dist = torch.empty((nq, k), dtype=torch.float32, device="cuda")
     d_cnt = torch.empty(nq, dtype=torch.int32, device="cuda")
     d_stats = torch.empty(nq * STATS_DTYPE.itemsize, dtype=torch.uint8, device="cuda")
 
-    # ground truth (exact k-NN on the GPU, bit-exact vs the CPU oracle in tests) and ef choice
-    t_idx = torch.empty((nq, k), dtype=torch.int64, device="cuda")
-    t_dist = torch.empty((nq, k), dtype=torch.float32, device="cuda")
-    t_cnt = torch.empty(nq, dtype=torch.int32, device="cuda")
-    idx.exact_knn_device(d_q.data_ptr(), nq, k, 0, t_idx.data_ptr(), t_dist.data_ptr(), t_cnt.data_ptr())
-    torch.cuda.synchronize()
-    exact_ms = idx.last_kernel_ms()
-    exact_st = idx.exact_stats()
-    truth = t_idx.cpu().numpy()
-
-    def search_dev(ef, stats=False):
+    def search_dev(stats=False):
         idx.search_device(d_q.data_ptr(), nq, k, ef, d_ids.data_ptr(), d_dist.data_ptr(), d_cnt.data_ptr(),
                           d_stats.data_ptr() if stats else None)
 
-    sweep = []
-    chosen = args.ef or None
-    for ef in ([args.ef] if args.ef else args.ef_sweep):
-        search_dev(ef, stats=True)
-        torch.cuda.synchronize()
-        ms = idx.last_kernel_ms()
-        rec = recall_at_k(d_ids.cpu().numpy(), truth)
-        st = d_stats.cpu().numpy().view(STATS_DTYPE)
-        sweep.append({"ef": ef, "recall_at_10": round(rec, 4), "kernel_ms": round(ms, 3),
-                      "qps_kernel": round(nq / ms * 1000.0), "n_dist_mean": float(st["n_dist"].mean()),
-                      "n_expand_mean": float(st["n_expand"].mean()),
-                      "algo_GBps": round(algorithmic_bytes(st, dim, args.M, k) / ms / 1e6, 1)})
-        if chosen is None and rec >= 0.95:
-            chosen = ef
-    if rank == 0:
-        log("[bench] ef sweep: " + json.dumps(sweep))
-    if chosen is None:
-        chosen = args.ef_sweep[-1]
-        if rank == 0:
-            log(f"[bench] NOTE: recall@10 < 0.95 at every ef of the sweep; timing ef={chosen}")
-    if world > 1:  # all ranks time the same ef: rank 0's choice
-        t = torch.tensor([chosen], device="cuda")
-        dist.broadcast(t, 0)
-        chosen = int(t.item())
-    ef = chosen
-    if rank == 0:
-        json.dump({"ef": ef}, open(chosen_ef_path(args), "w"))
-    search_dev(ef, stats=True)
+    search_dev(stats=True)
     torch.cuda.synchronize()
     stats = d_stats.cpu().numpy().view(STATS_DTYPE).copy()
-    recall = recall_at_k(d_ids.cpu().numpy(), truth)
-    algo_bytes = algorithmic_bytes(stats, dim, args.M, k)
+    algo_bytes = algorithmic_bytes(stats, dim, c.M, k)
+    team_w = idx.last_team_width()
 
-    # ── device-resident timing: W warm-up, K timed steps, events on the launching stream ──
-    for _ in range(args.warmup):
-        search_dev(ef)
+    # ── device-resident timing: W warm-up, K timed steps, events on the launching stream; one event pair per step
+    # gives the search kernel's own launch duration live, inside the timed region ──
+    for _ in range(warmup):
+        search_dev()
     torch.cuda.synchronize()
-    barrier()
-    clocks = ClockSampler(local_rank)
-    clocks.start()
+    D.barrier()
+    clocks = ClockSampler(D.local_rank).start()
     launches0 = idx.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    # the search kernel's own launch duration, live, inside the timed region: one event pair per step on the
-    # launching stream (recording is asynchronous; the pairs are read after the final synchronize). A pair spans the
-    # level-0 launch and the two retry-level launches that exit at once.
-    step_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    step_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     torch.cuda.synchronize()
-    e0.record(stream)
+    e0.record(D.stream)
     for a, b in step_ev:
-        a.record(stream)
-        search_dev(ef)
-        b.record(stream)
-    e1.record(stream)
+        a.record(D.stream)
+        search_dev()
+        b.record(D.stream)
+    e1.record(D.stream)
     torch.cuda.synchronize()
-    barrier()
+    D.barrier()
     total_ms = e0.elapsed_time(e1)
     launches = idx.launch_count() - launches0
     kernel_ms = [a.elapsed_time(b) for a, b in step_ev]
-    # ── end-to-end: host (pinned) buffers through muninn_cuda_search_batch ──
-    h_ids = torch.empty((nq, k), dtype=torch.int64).pin_memory()
-    h_dist = torch.empty((nq, k), dtype=torch.float32).pin_memory()
-    h_cnt = torch.empty(nq, dtype=torch.int32).pin_memory()
-    for _ in range(max(1, args.warmup // 2)):
-        idx.search_into(h_q.data_ptr(), nq, k, ef, h_ids.data_ptr(), h_dist.data_ptr(), h_cnt.data_ptr())
-    barrier()
+
+    # ── end to end: pinned host queries in, results on rank 0's host, every step ──
+    if D.world == 1:
+        h_ids = torch.empty((nq, k), dtype=torch.int64).pin_memory()
+        h_dist = torch.empty((nq, k), dtype=torch.float32).pin_memory()
+        h_cnt = torch.empty(nq, dtype=torch.int32).pin_memory()
+
+        def e2e_step():  # the C-ABI call a host makes: H2D + kernel + D2H inside muninn_cuda_search_batch
+            idx.search_into(h_q.data_ptr(), nq, k, ef, h_ids.data_ptr(), h_dist.data_ptr(), h_cnt.data_ptr())
+    else:
+        h_ids = torch.empty((D.world * pad, k), dtype=torch.int64).pin_memory() if D.rank == 0 else None
+        h_dist = torch.empty((D.world * pad, k), dtype=torch.float32).pin_memory() if D.rank == 0 else None
+        d_q2 = torch.empty_like(d_q)
+
+        def e2e_step():  # H2D of the slice, search, ids+distances gathered to rank 0 over NVLink, D2H there
+            d_q2.copy_(h_q, non_blocking=True)
+            idx.search_device(d_q2.data_ptr(), nq, k, ef, d_ids.data_ptr(), d_dist.data_ptr(), d_cnt.data_ptr(), None)
+            gi, gd = D.gather_rows(d_ids, pad), D.gather_rows(d_dist, pad)
+            if D.rank == 0:
+                h_ids.copy_(torch.cat(gi, 0), non_blocking=True)
+                h_dist.copy_(torch.cat(gd, 0), non_blocking=True)
+            torch.cuda.synchronize()
+    for _ in range(max(1, warmup // 2)):
+        e2e_step()
+    D.barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        idx.search_into(h_q.data_ptr(), nq, k, ef, h_ids.data_ptr(), h_dist.data_ptr(), h_cnt.data_ptr())
+    for _ in range(steps):
+        e2e_step()
     e2e_s = time.perf_counter() - t0
     clk = clocks.stop()
-    assert np.array_equal(h_ids.numpy(), d_ids.cpu().numpy()), "host-buffer path and device path disagree"
+    total_ms, e2e_ms = D.max_over_ranks(total_ms, e2e_s * 1000.0)
 
-    tmax = torch.tensor([total_ms, e2e_s * 1000.0], device="cuda", dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-    total_ms, e2e_ms = float(tmax[0]), float(tmax[1])
+    # ── verification: the gathered answer == rank 0 running the whole job alone ──
+    verified = None
+    if D.rank == 0:
+        if D.world == 1:
+            got_ids, got_dist = h_ids.numpy(), h_dist.numpy()
+            verified = bool(np.array_equal(got_ids, d_ids.cpu().numpy()) and np.array_equal(got_dist, d_dist.cpu().numpy()))
+        else:
+            parts_i, parts_d = [], []
+            for r in range(D.world):
+                rl, rh = shard_range(job_q, r, D.world)
+                parts_i.append(h_ids.numpy()[r * pad: r * pad + (rh - rl)])
+                parts_d.append(h_dist.numpy()[r * pad: r * pad + (rh - rl)])
+            got_ids, got_dist = np.concatenate(parts_i, 0), np.concatenate(parts_d, 0)
+            a_q = torch.from_numpy(queries_job).cuda()
+            a_ids = torch.empty((job_q, k), dtype=torch.int64, device="cuda")
+            a_dist = torch.empty((job_q, k), dtype=torch.float32, device="cuda")
+            a_cnt = torch.empty(job_q, dtype=torch.int32, device="cuda")
+            idx.search_device(a_q.data_ptr(), job_q, k, ef, a_ids.data_ptr(), a_dist.data_ptr(), a_cnt.data_ptr(), None)
+            torch.cuda.synchronize()
+            verified = bool(np.array_equal(got_ids, a_ids.cpu().numpy()) and np.array_equal(got_dist, a_dist.cpu().numpy()))
+        if not verified:
+            log(f"[bench] {label}: VERIFICATION FAILED (gathered answer differs from the single-GPU answer)")
+    D.barrier()
 
+    pk = measured_peaks()
+    k_ms = float(np.mean(kernel_ms))
+    achieved = algo_bytes / k_ms / 1e6
+    return {"label": label, "job_queries": job_q, "queries_per_gpu": nq, "team_warps": team_w, "ef": ef,
+            "value": job_q * steps / total_ms * 1000.0, "unit": "queries/s", "ms_per_step": total_ms / steps,
+            "steps": steps, "warmup": warmup,
+            "e2e": {"value": job_q * steps / e2e_ms * 1000.0, "unit": "queries/s", "h2d_bytes_per_step": nq * dim * 4,
+                    "d2h_bytes_per_step": (job_q if D.world > 1 else nq) * k * 12 + (nq * 4 if D.world == 1 else 0),
+                    "gathered_to_rank0": D.world > 1},
+            "verified": verified, "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": pk["hbm_gbs"], "unit": "GB/s",
+                         "frac": round(achieved / pk["hbm_gbs"], 4), "traffic": ncu_traffic(c.config, ef, nq),
+                         "peak_source": pk["source"], "kernel": f"hnsw search kernel <{METRIC_TEXT[c.metric]}>, rank 0's slice",
+                         "kernel_ms": round(k_ms, 4), "of_nominal_8TBps": round(achieved / 8000.0, 4),
+                         "algorithmic_bytes_per_launch": algo_bytes, "bytes_per_query": round(algo_bytes / max(nq, 1), 1)},
+            "clocks": clk, "_h_ids": h_ids if D.world == 1 else None, "_h_dist": h_dist if D.world == 1 else None}
+
+
+def choose_ef(D: Dist, idx, c, queries: np.ndarray, forced_ef: int):
+    """Rank 0 sweeps ef on the full named batch against exact k-NN; every rank then uses its choice."""
+    torch = D.torch
+    from sqlite_muninn_b200.cuda import STATS_DTYPE
+    sweep, chosen, recall_chosen, exact = [], None, None, None
+    if D.rank == 0:
+        nq, k = queries.shape[0], c.k
+        d_q = torch.from_numpy(queries).cuda()
+        t_idx = torch.empty((nq, k), dtype=torch.int64, device="cuda")
+        t_dist = torch.empty((nq, k), dtype=torch.float32, device="cuda")
+        t_cnt = torch.empty(nq, dtype=torch.int32, device="cuda")
+        idx.exact_knn_device(d_q.data_ptr(), nq, k, 0, t_idx.data_ptr(), t_dist.data_ptr(), t_cnt.data_ptr())
+        torch.cuda.synchronize()
+        exact = exact_summary(c.dim, nq, c.n, idx.last_kernel_ms(), idx.exact_stats())
+        truth = t_idx.cpu().numpy()
+        d_ids = torch.empty((nq, k), dtype=torch.int64, device="cuda")
+        d_dist = torch.empty((nq, k), dtype=torch.float32, device="cuda")
+        d_cnt = torch.empty(nq, dtype=torch.int32, device="cuda")
+        d_stats = torch.empty(nq * STATS_DTYPE.itemsize, dtype=torch.uint8, device="cuda")
+        for ef in ([forced_ef] if forced_ef else c.ef_sweep):
+            for _ in range(2):  # the second launch is the one timed (tables allocated, caches warm)
+                idx.search_device(d_q.data_ptr(), nq, k, ef, d_ids.data_ptr(), d_dist.data_ptr(), d_cnt.data_ptr(), d_stats.data_ptr())
+                torch.cuda.synchronize()
+            ms = idx.last_kernel_ms()
+            rec = recall_at_k(d_ids.cpu().numpy(), truth)
+            st = d_stats.cpu().numpy().view(STATS_DTYPE)
+            ab = algorithmic_bytes(st, c.dim, c.M, k)
+            sweep.append({"ef": ef, "recall_at_10": round(rec, 4), "kernel_ms": round(ms, 3), "qps_kernel": round(nq / ms * 1000.0),
+                          "n_dist_mean": float(st["n_dist"].mean()), "n_expand_mean": float(st["n_expand"].mean()),
+                          "algo_GBps": round(ab / ms / 1e6, 1), "frac": round(ab / ms / 1e6 / measured_peaks()["hbm_gbs"], 4)})
+            if chosen is None and (rec >= 0.95 or forced_ef):
+                chosen, recall_chosen = ef, rec
+        log(f"[bench] config {c.config} ef sweep: " + json.dumps(sweep))
+        if chosen is None:
+            chosen, recall_chosen = sweep[-1]["ef"], sweep[-1]["recall_at_10"]
+            log(f"[bench] NOTE: recall@10 < 0.95 at every ef of the sweep; timing ef={chosen}")
+        json.dump({"ef": chosen, "recall": round(float(recall_chosen), 4)}, open(chosen_ef_path(c), "w"))
+    chosen = D.bcast_int(chosen or 0)
+    return chosen, (round(float(recall_chosen), 4) if recall_chosen is not None else None), sweep, exact
+
+
+def search_config_block(D: Dist, args, num: int, steps: int, warmup: int, jobs, want_cpu: bool):
+    """Graph + index of one config, recall sweep, then the given jobs [(label, batches)]. Returns (blocks, context)."""
+    from sqlite_muninn_b200.cuda import HnswIndexCuda, gather_ceiling
+    c = cfg_of(num, args)
+    g = get_graph(c, D.rank, D.world, D.barrier, device_build=args.device_build)
+    idx = HnswIndexCuda.from_graph(g, device=D.local_rank)
+    idx.set_stream(D.stream.cuda_stream)
+    if args.teams_per_sm or args.warps:
+        idx.set_tuning(args.warps, args.teams_per_sm)
+    batch0 = make_vectors(c.nq, c.dim, c.seeds[1], kind=c.data)
+    ef, recall, sweep, exact = choose_ef(D, idx, c, batch0, args.ef if num == args.config else 0)
+    blocks = {}
+    for label, batches in jobs:
+        q = batch0 if batches == 1 else job_queries(c, batches)
+        blocks[label] = run_search_job(D, idx, c, q, ef, steps, warmup, f"config{num}/{label}")
     cpu_desc = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    first = blocks[jobs[0][0]]
+    if D.rank == 0:
+        row_bytes = ((c.dim + 3) // 4) * 16
+        gp = gather_ceiling(row_bytes, 1 << 30, D.local_rank)  # measured live, after the timed region
+        for b in blocks.values():
+            b["roofline"]["random_row_gather_peak"] = {
+                "GBps": round(gp, 1), "frac": round(b["roofline"]["achieved"] / gp, 4),
+                "what": f"independent random {row_bytes}-byte row gathers from a 1 GiB slab, measured in this run"}
+    if want_cpu and D.rank == 0 and D.world == 1:
         cpu = CpuReference(g)
-        n_s = cpu.sample_size(queries, k, ef, args.cpu_seconds)
-        c_ids, secs = cpu.run(queries[:n_s], k, ef)
-        same = float(np.mean((c_ids == h_ids.numpy()[:n_s]).all(axis=1)))
-        cpu_desc = {"value": n_s / secs, "unit": "queries/s", "cores": cpu.threads, "kind": cpu.kind,
-                    "sample": f"first {n_s} of the {nq} queries, ef={ef}, k={k}, {secs:.1f}s on {cpu.threads} host threads",
-                    "id_exact_fraction_vs_gpu": same}
+        n_s = cpu.sample_size(batch0, c.k, ef, args.cpu_seconds / 5.0)
+        runs = [cpu.run(batch0[:n_s], c.k, ef) for _ in range(5)]  # BASELINE.md §3: median of >= 5 repeats
+        secs = [r[2] for r in runs]
+        c_ids, c_dist = runs[0][0], runs[0][1]
+        g_ids, g_dist = first["_h_ids"].numpy()[:n_s], first["_h_dist"].numpy()[:n_s]  # batch 0 = the job's first queries
+        cpu_desc = {"value": n_s / float(np.median(secs)), "unit": "queries/s", "cores": cpu.threads, "cpu_model": cpu_model(),
+                    "kind": cpu.kind, "best": n_s / float(np.min(secs)), "repeats": 5,
+                    "sample": f"first {n_s} queries of the job, ef={ef}, k={c.k}, median of 5 repeats ({np.median(secs):.2f}s each) on {cpu.threads} host threads",
+                    "id_exact_fraction_vs_gpu": float(np.mean((c_ids == g_ids).all(axis=1))),
+                    "distance_exact_fraction_vs_gpu": float(np.mean((c_dist == g_dist).all(axis=1)))}
         # SURVEY §8d (iii): the same search with only the linear visited scan swapped for O(1) stamps
         # (oracle/hnsw_oracle.c, results bit-identical to the reference's) — the stronger CPU comparison
         from oracle.bindings import Oracle
-        o_ids, _, _, _, o_secs = Oracle().graph(g).search(queries[:n_s], k, ef, threads=cpu.threads, want_stats=False)
+        o_ids, _, _, _, o_secs = Oracle().graph(g).search(batch0[:n_s], c.k, ef, threads=cpu.threads, want_stats=False)
         cpu_desc["modified_reference_o1_visited"] = {
             "value": n_s / max(o_secs, 1e-9), "unit": "queries/s", "cores": cpu.threads, "kind": "port",
             "ids_identical_to_reference": bool(np.array_equal(o_ids, c_ids))}
-    if rank == 0:
-        peak, which = measured_peak_gbs()
-        k_ms = float(np.mean(kernel_ms))
-        achieved = algo_bytes / k_ms / 1e6
-        from sqlite_muninn_b200.cuda import gather_ceiling
-        gather_peak = gather_ceiling(((dim + 3) // 4) * 16, 1 << 30, local_rank)  # measured live, after the timed region
-        out = {
-            "metric": METRIC_NAME, "value": nq_job * args.steps / total_ms * 1000.0, "unit": "queries/s",
-            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
-            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(args, ef, round(recall, 4)),
-            "e2e": {"value": nq_job * args.steps / e2e_ms * 1000.0, "unit": "queries/s",
-                    "h2d_bytes_per_step": nq * dim * 4, "d2h_bytes_per_step": nq * k * 12 + nq * 4},
-            "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                         "frac": round(achieved / peak, 4), "traffic": ncu_traffic(args, ef), "peak_source": which,
-                         "kernel": f"hnsw_search_kernel<{METRIC_TEXT[args.metric]}>", "kernel_ms": round(k_ms, 3),
-                         "of_nominal_8TBps": round(achieved / 8000.0, 4),
-                         "random_row_gather_peak": {"GBps": round(gather_peak, 1), "frac": round(achieved / gather_peak, 4),
-                                                    "what": f"independent random {((dim + 3) // 4) * 16}-byte row gathers from a 1 GiB slab, "
-                                                            "measured in this run (muninn_cuda_gather_ceiling): the ceiling of "
-                                                            "this access pattern, below the streaming-copy peak"},
-                         "algorithmic_bytes_per_launch": algo_bytes,
-                         "bytes_per_query": round(algo_bytes / nq, 1)},
-            "cpu_baseline": cpu_desc, "clocks": clk, "ef_sweep": sweep,
-            "exact_knn": exact_summary(args, nq, exact_ms, exact_st),
-        }
-        print(json.dumps(out), flush=True)
+    for b in blocks.values():
+        for key in [k_ for k_ in b if k_.startswith("_")]:
+            del b[key]
     idx.close()
-    if world > 1:
-        dist.destroy_process_group()
+    del g
+    return blocks, SimpleNamespace(c=c, ef=ef, recall=recall, sweep=sweep, exact=exact, cpu=cpu_desc)
 
 
-def run_exact_arm(args, rank: int, local_rank: int, world: int) -> None:
-    """`--config 5`: exact brute-force k-NN, base rows sharded across the GPUs (args.n rows per GPU —
-    8 GPUs make BASELINE.json's 50M), every GPU sees all queries; per step each rank scans its shard
-    (tensor-core filter + exact re-rank), the per-shard top-k lists are exchanged with one NCCL
-    all-gather per array and merged under (distance, row index) on every rank."""
-    import torch
-    import torch.distributed as dist
-    from sqlite_muninn_b200.cuda import HnswIndexCuda
-    from sqlite_muninn_b200.graph import FlatGraph
-    from sqlite_muninn_b200.multi import allgather_topk_parts
+# ───────────────────────── GPU arm: sharded exact k-NN (config 5) ─────────────────────────
 
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
-    torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+def device_rows(torch, c, lo: int, hi: int, block: int = 1_250_000):
+    """Rows [lo, hi) of the config-5 base, generated on the device block by block (block b = rows [b·block, (b+1)·block),
+    seed = seeds[0]·1000 + b: the base does not depend on how many GPUs share it). Same distribution as
+    make_vectors("latent16")."""
+    A = torch.from_numpy((np.random.default_rng(999).standard_normal((16, c.dim)) / np.sqrt(16)).astype(np.float32)).cuda()
+    out = torch.empty((hi - lo, c.dim), dtype=torch.float32, device="cuda")
+    b = lo // block
+    while b * block < hi:
+        g = torch.Generator(device="cuda")
+        g.manual_seed(c.seeds[0] * 1000 + b)
+        z = torch.randn((block, 16), generator=g, device="cuda", dtype=torch.float32)
+        blk = z @ A
+        blk += 0.05 * torch.randn((block, c.dim), generator=g, device="cuda", dtype=torch.float32)
+        s, e = max(lo, b * block), min(hi, (b + 1) * block)
+        out[s - lo: e - lo] = blk[s - b * block: e - b * block]
+        b += 1
+    return out
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
 
-    n, dim, k, nq = args.n, args.dim, args.k, args.nq
+def run_exact_block(D: Dist, args, steps: int, warmup: int, want_cpu: bool) -> dict:
+    """BASELINE config 5: the base rows sharded over the ranks, every rank sees all queries; one step =
+    muninn_cuda_exact_knn_sharded_device (tensor-core filter + exact re-rank of the shard, ONE ncclAllGather of
+    nq·k·8 bytes per rank, merge) — every rank ends with the global answer."""
+    torch = D.torch
+    from sqlite_muninn_b200.cuda import EXACT_CUDA_CORE, EXACT_TC_AUTO, HnswIndexCuda
+    from sqlite_muninn_b200.multi import ShardedExactKnn, merge_topk_parts_reference, shard_range
+    c = cfg_of(5, args)
+    n, dim, k, nq = c.n, c.dim, c.k, c.nq
+    lo, hi = shard_range(n, D.rank, D.world)
     t0 = time.time()
-    base = make_vectors(n, dim, args.seeds[0] + 100 * rank, kind=args.data)  # this rank's shard
-    g = FlatGraph(dim, args.metric, args.M, 10, np.arange(n, dtype=np.int64), np.zeros(n, np.int32), np.zeros(n, np.uint8),
-                  base, np.zeros(n + 1, np.int64), np.empty(0, np.int32), 0, 0)
-    idx = HnswIndexCuda.from_graph(g, device=local_rank)
-    log(f"[bench] rank {rank}: shard of {n} rows resident after {time.time() - t0:.1f}s")
-    stream = torch.cuda.Stream()
-    torch.cuda.set_stream(stream)
-    idx.set_stream(stream.cuda_stream)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    rows = device_rows(torch, c, lo, hi)
+    idx = HnswIndexCuda(dim, c.metric, c.M, device=D.local_rank)
+    idx.set_stream(D.stream.cuda_stream)
+    torch.cuda.synchronize()
+    idx.upload_rows(rows.data_ptr(), hi - lo)
     if args.exact_mode is not None:
         idx.set_exact_mode(args.exact_mode, 0)
-    queries = make_vectors(nq, dim, args.seeds[1], kind=args.data)
+    log(f"[bench] rank {D.rank}: shard rows [{lo}, {hi}) resident after {time.time() - t0:.1f}s")
+    queries = make_vectors(nq, dim, c.seeds[1], kind=c.data)
     h_q = torch.from_numpy(queries).pin_memory()
     d_q = h_q.cuda(non_blocking=True)
-    mk = lambda *shape, dt: torch.empty(shape, dtype=dt, device="cuda")
-    s_idx, s_dist, s_cnt = mk(nq, k, dt=torch.int64), mk(nq, k, dt=torch.float32), mk(nq, dt=torch.int32)
-    o_idx, o_dist, o_cnt = mk(nq, k, dt=torch.int64), mk(nq, k, dt=torch.float32), mk(nq, dt=torch.int32)
+    o_idx = torch.empty((nq, k), dtype=torch.int64, device="cuda")
+    o_dist = torch.empty((nq, k), dtype=torch.float32, device="cuda")
+    o_cnt = torch.empty(nq, dtype=torch.int32, device="cuda")
+    sharded = ShardedExactKnn(idx, D.local_rank) if D.world > 1 else None
 
     def step(dq):
-        idx.exact_knn_device(dq.data_ptr(), nq, k, rank * n, s_idx.data_ptr(), s_dist.data_ptr(), s_cnt.data_ptr())
-        if world == 1:
-            return s_idx, s_dist, s_cnt
-        pi, pd, pc = allgather_topk_parts(s_idx, s_dist, s_cnt)
-        idx.topk_merge_device(world, nq, k, pi.data_ptr(), pd.data_ptr(), pc.data_ptr(), o_idx.data_ptr(), o_dist.data_ptr(),
-                              o_cnt.data_ptr())
-        return o_idx, o_dist, o_cnt
+        if sharded:
+            sharded(dq.data_ptr(), nq, k, lo, o_idx.data_ptr(), o_dist.data_ptr(), o_cnt.data_ptr())
+        else:
+            idx.exact_knn_device(dq.data_ptr(), nq, k, lo, o_idx.data_ptr(), o_dist.data_ptr(), o_cnt.data_ptr())
 
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         step(d_q)
     torch.cuda.synchronize()
     st = idx.exact_stats()
     shard_ms = idx.last_kernel_ms()
-    barrier()
-    clocks = ClockSampler(local_rank)
-    clocks.start()
+    D.barrier()
+    clocks = ClockSampler(D.local_rank).start()
     launches0 = idx.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
-    for _ in range(args.steps):
+    e0.record(D.stream)
+    for _ in range(steps):
         step(d_q)
-    e1.record(stream)
+    e1.record(D.stream)
     torch.cuda.synchronize()
-    barrier()
+    D.barrier()
     total_ms = e0.elapsed_time(e1)
     launches = idx.launch_count() - launches0
-    # end to end: pinned host queries in, merged lists out, every step
+    # end to end: pinned host queries in, the merged lists on the host, every step
     h_idx = torch.empty((nq, k), dtype=torch.int64).pin_memory()
     h_dist = torch.empty((nq, k), dtype=torch.float32).pin_memory()
     d_q2 = torch.empty_like(d_q)
-    barrier()
+    D.barrier()
     t1 = time.perf_counter()
-    for _ in range(args.steps):
+    for _ in range(steps):
         d_q2.copy_(h_q, non_blocking=True)
-        ri, rd, _ = step(d_q2)
-        h_idx.copy_(ri, non_blocking=True)
-        h_dist.copy_(rd, non_blocking=True)
+        step(d_q2)
+        h_idx.copy_(o_idx, non_blocking=True)
+        h_dist.copy_(o_dist, non_blocking=True)
         torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t1
     clk = clocks.stop()
-    tmax = torch.tensor([total_ms, e2e_s * 1000.0], device="cuda", dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-    total_ms, e2e_ms = float(tmax[0]), float(tmax[1])
+    total_ms, e2e_ms = D.max_over_ranks(total_ms, e2e_s * 1000.0)
 
-    cpu_desc = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    # ── verification 1 (every N): an independent scan of a 64-query sample — CUDA-core chains over every (query, row)
+    # pair on each shard, lists moved with torch's own gather, merged on the host with a lexsort — must equal the product's
+    # merged answer bit for bit ──
+    ns = min(64, nq)
+    idx.set_exact_mode(EXACT_CUDA_CORE, 0)
+    s_idx = torch.empty((ns, k), dtype=torch.int64, device="cuda")
+    s_dist = torch.empty((ns, k), dtype=torch.float32, device="cuda")
+    s_cnt = torch.empty(ns, dtype=torch.int32, device="cuda")
+    idx.exact_knn_device(d_q.data_ptr(), ns, k, lo, s_idx.data_ptr(), s_dist.data_ptr(), s_cnt.data_ptr())
+    torch.cuda.synchronize()
+    idx.set_exact_mode(args.exact_mode if args.exact_mode is not None else EXACT_TC_AUTO, 0)
+    gi, gd, gc = D.gather_rows(s_idx, ns), D.gather_rows(s_dist, ns), D.gather_rows(s_cnt, ns)
+    verified, cpu_desc = None, None
+    if D.rank == 0:
+        m_idx, m_dist, m_cnt = merge_topk_parts_reference(torch.stack(gi).cpu().numpy(), torch.stack(gd).cpu().numpy(),
+                                                          torch.stack(gc).cpu().numpy(), k)
+        verified = bool(np.array_equal(m_idx, h_idx.numpy()[:ns]) and m_dist.tobytes() == h_dist.numpy()[:ns].tobytes()
+                        and np.array_equal(m_cnt, o_cnt.cpu().numpy()[:ns]))
+        if not verified:
+            log("[bench] config5: VERIFICATION FAILED (sharded answer differs from the independent scan)")
+    # ── verification 2 + CPU baseline (N=1): the CPU oracle over the whole base on a bounded query sample ──
+    if want_cpu and D.rank == 0 and D.world == 1:
         from oracle.bindings import Oracle
         threads = os.cpu_count() or 1
-        n_s = max(threads, min(nq, int(args.cpu_seconds * threads * 2.0e9 / (3.0 * n * dim))))  # ~cpu_seconds of SSE chains
-        c_idx, c_dist, c_cnt, secs = Oracle().exact_knn(base, queries[:n_s], k, args.metric, threads=threads)
-        same = bool(np.array_equal(c_idx, h_idx.numpy()[:n_s]) and c_dist.tobytes() == h_dist.numpy()[:n_s].tobytes())
-        cpu_desc = {"value": n_s / secs, "unit": "queries/s", "cores": threads, "kind": "port",
-                    "sample": f"first {n_s} of the {nq} queries against the {n}-row shard, k={k}, {secs:.1f}s on {threads} host threads",
+        n_c = max(4, min(nq, int(args.cpu_seconds * threads * 2.0e9 / (3.0 * n * dim))))  # ~cpu_seconds of SSE chains
+        base = rows.cpu().numpy()
+        c_idx, c_dist, c_cnt, secs = Oracle().exact_knn(base, queries[:n_c], k, c.metric, threads=threads)
+        same = bool(np.array_equal(c_idx, h_idx.numpy()[:n_c]) and c_dist.tobytes() == h_dist.numpy()[:n_c].tobytes())
+        cpu_desc = {"value": n_c / secs, "unit": "queries/s", "cores": threads, "cpu_model": cpu_model(), "kind": "port",
+                    "sample": f"first {n_c} of the {nq} queries against all {n} rows, k={k}, {secs:.1f}s on {threads} host threads",
                     "bit_identical_to_gpu": same}
-    if rank == 0:
-        ex = exact_summary(args, nq, shard_ms, st, n_rows=n)
+        del base
+    D.barrier()
+    out = None
+    if D.rank == 0:
+        ex = exact_summary(dim, nq, hi - lo, shard_ms, st)
         roof = dict(ex.get("roofline") or {"bound": "tensor", "achieved": None, "peak": None, "unit": "TFLOP/s", "frac": None})
         roof["traffic"] = None
+        out = {"label": "config5", "metric": "exact k-NN queries/s (k=100, base sharded, top-k all-gather merge)",
+               "value": nq * steps / total_ms * 1000.0, "unit": "queries/s", "ms_per_step": total_ms / steps, "steps": steps,
+               "warmup": warmup, "scaling": "strong",
+               "config": {"workload": f"exact brute-force kNN {n}x{dim} {METRIC_TEXT[c.metric]}, k={k}, {nq}-query batch, base rows "
+                                      f"sharded over {D.world} GPU(s) ({hi - lo} rows on rank 0) (BASELINE.json configs[4])",
+                          "data_distribution": f"{DATA_TEXT[c.data]}, generated on the device in 1.25M-row blocks, seed {c.seeds[0]}*1000+block / queries {c.seeds[1]}",
+                          "l2_policy": f"the {(hi - lo) * dim * 4 / 1e9:.1f} GB shard exceeds the 126 MB L2; no flush between steps",
+                          "parallelism": "base rows sharded, every GPU sees all queries, ONE ncclAllGather of nq*k*8 bytes per rank per step, merge on every rank"},
+               "e2e": {"value": nq * steps / e2e_ms * 1000.0, "unit": "queries/s", "h2d_bytes_per_step": nq * dim * 4,
+                       "d2h_bytes_per_step": nq * k * 12},
+               "collective_bytes_per_rank_per_step": nq * k * 8 if D.world > 1 else 0,
+               "verified": verified,
+               "verified_how": f"{ns}-query sample: CUDA-core scan of every shard + torch gather + host lexsort merge, bit for bit",
+               "gpu_launches": int(launches), "roofline": roof, "exact_knn": ex,
+               "algorithmic_TFLOPs_job": round(2.0 * nq * n * dim * steps / total_ms / 1e9, 1),
+               "cpu_baseline": cpu_desc, "clocks": clk}
+    if sharded:
+        sharded.close()
+    idx.close()
+    del rows
+    torch.cuda.empty_cache()
+    return out
+
+
+# ───────────────────────── GPU arm: driver ─────────────────────────
+
+def run_gpu_arm(args, rank: int, local_rank: int, world: int) -> None:
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    D = Dist(rank, local_rank, world)
+    extras = [e for e in args.extras.split(",") if e and e != "none"]
+    want_cpu = not args.no_cpu_baseline
+    x_steps, x_warm = max(3, min(args.steps, 10)), max(3, min(args.warmup, 5))
+
+    if args.config == 5:
+        out = run_exact_block(D, args, max(1, min(args.steps, 20)), max(3, args.warmup), want_cpu)
+        if rank == 0:
+            out.update({"n_gpus": world, "higher_is_better": True, "vs_baseline": None, "data": "synthetic",
+                        "dtype": "f32 (tf32 filter, f32 re-rank)"})
+            print(json.dumps(out), flush=True)
+        D.close()
+        return
+
+    jobs = [("job", JOB_BATCHES)] + ([("split_10k", 1)] if "split10k" in extras else [])
+    blocks, ctx = search_config_block(D, args, args.config, args.steps, args.warmup, jobs, want_cpu)
+    head = blocks["job"]
+    extra = {}
+    if "split_10k" in blocks:
+        extra["split_10k"] = blocks["split_10k"]
+    for num in (3, 4):
+        if str(num) in extras and num != args.config:
+            try:
+                b, cx = search_config_block(D, args, num, x_steps, x_warm, [("split_10k", 1)], False)
+                blk = b["split_10k"]
+                blk["config"] = workload_config(cx.c, cx.ef, cx.recall, cx.c.nq)
+                blk["metric"] = METRIC_NAME if (cx.recall is None or cx.recall >= 0.95) else METRIC_MISSED
+                blk["ef_sweep"] = cx.sweep
+                extra[f"config{num}"] = blk
+            except Exception as e:  # an extra block must never take the headline line down
+                log(f"[bench] extra config{num} failed: {e!r}")
+                extra[f"config{num}"] = {"error": repr(e)}
+    if "5" in extras:
+        try:
+            extra["config5"] = run_exact_block(D, args, 3, 3, want_cpu)
+        except Exception as e:
+            log(f"[bench] extra config5 failed: {e!r}")
+            extra["config5"] = {"error": repr(e)}
+    if rank == 0:
+        c = ctx.c
         out = {
-            "metric": "exact k-NN queries/s (k=100, base sharded, top-k all-gather merge)",
-            "value": nq * args.steps / total_ms * 1000.0, "unit": "queries/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32 (tf32x3 filter, f32 re-rank)", "data": "synthetic",
-            "config": {"workload": f"exact brute-force kNN {world * n}x{dim} {METRIC_TEXT[args.metric]} ({n} rows per GPU x {world}), "
-                                   f"k={k}, {nq}-query batch (BASELINE.json configs[4])",
-                       "data_distribution": f"{DATA_TEXT[args.data]}, seeds {args.seeds[0]}+100*rank/{args.seeds[1]}",
-                       "l2_policy": f"the {n * dim * 4 / 1e9:.1f} GB shard exceeds the 126 MB L2; no flush between steps",
-                       "parallelism": "base rows sharded, every GPU sees all queries, one all-gather of the [nq x k] lists per step"},
-            "e2e": {"value": nq * args.steps / e2e_ms * 1000.0, "unit": "queries/s", "h2d_bytes_per_step": nq * dim * 4,
-                    "d2h_bytes_per_step": nq * k * 12},
-            "gpu_launches": int(launches), "roofline": roof, "exact_knn": ex,
-            "algorithmic_TFLOPs_job": round(2.0 * nq * world * n * dim * args.steps / total_ms / 1e9, 1),
-            "cpu_baseline": cpu_desc, "clocks": clk,
+            "metric": METRIC_NAME if (ctx.recall or 0) >= 0.95 else METRIC_MISSED,
+            "value": head["value"], "unit": "queries/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(c, ctx.ef, ctx.recall, head["job_queries"]),
+            "e2e": head["e2e"], "gpu_launches": head["gpu_launches"], "roofline": head["roofline"],
+            "cpu_baseline": ctx.cpu, "clocks": head["clocks"], "verified": head["verified"],
+            "queries_per_gpu": head["queries_per_gpu"], "team_warps": head["team_warps"],
+            "ef_sweep": ctx.sweep, "exact_knn": ctx.exact, "extra": extra,
         }
         print(json.dumps(out), flush=True)
-    idx.close()
-    if world > 1:
-        dist.destroy_process_group()
+    D.close()
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=300)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", type=int, default=2, choices=sorted(CONFIGS),
-                    help="BASELINE.json config (1-based); 2 = the headline bench line")
-    ap.add_argument("--n", type=int, default=None, help="override the config's size (dry runs)")
+                    help="BASELINE.json config (1-based) timed as the headline; 2 = the bench line the driver reads")
+    ap.add_argument("--extras", default=os.environ.get("MUNINN_BENCH_EXTRAS", "split10k,3,4,5"),
+                    help="comma list of extra blocks: split10k, 3, 4, 5, or none")
+    ap.add_argument("--n", type=int, default=None, help="override the headline config's size (dry runs)")
     ap.add_argument("--dim", type=int, default=None)
     ap.add_argument("--M", type=int, default=None)
     ap.add_argument("--efc", type=int, default=None)
@@ -640,28 +899,20 @@ def main():
     ap.add_argument("--device-build", action="store_true",
                     help="build the input graph with builder.build_graph_device (outside the timed region either way)")
     ap.add_argument("--teams-per-sm", type=int, default=0)
+    ap.add_argument("--warps", type=int, default=0, help="warps per query team (0 = automatic)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--per-step-kernel-time", action="store_true", help="kept for compatibility: per-step event pairs are always recorded")
-    ap.add_argument("--exact-mode", type=int, default=None, help="config 5: 0 cuda-core, 1 3xTF32 (default), 2 1xTF32")
+    ap.add_argument("--exact-mode", type=int, default=None, help="config 5: 0 cuda-core, 1 3xTF32, 2 1xTF32 (default: automatic)")
     args = ap.parse_args()
-    cfg = CONFIGS[args.config]
-    for key in ("n", "dim", "M", "efc", "nq", "k"):
-        if getattr(args, key) is None:
-            setattr(args, key, cfg[key])
-    args.metric, args.data, args.seeds, args.scaling = cfg["metric"], cfg["data"], cfg["seeds"], cfg["scaling"]
-    args.ef_sweep, args.cfg_name = cfg["ef_sweep"], cfg["name"]
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     import __graft_entry__ as ge
     if rank == 0:
-        ge.build()
+        ge.build(load_cuda=args.impl != "reference")
     if args.impl == "reference":
         run_reference_arm(args, rank, world)
-    elif args.config == 5:
-        run_exact_arm(args, rank, local_rank, world)
     else:
         run_gpu_arm(args, rank, local_rank, world)
 

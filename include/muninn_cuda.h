@@ -95,6 +95,12 @@ int muninn_cuda_index_upload(MuninnCudaIndex *idx, int64_t n, const int64_t *ids
                              const uint8_t *deleted, const float *vectors, const int64_t *list_offsets,
                              const int32_t *targets, int32_t entry_slot, int32_t max_level);
 
+/* Rows only — an index without a graph, for exact k-NN over a shard of base rows (BASELINE.json config 5; the
+ * reference's brute_force_knn helper, test/test_hnsw_algo.c:10-34, needs nothing but the vectors). `rows` [n × dim] fp32
+ * may be host OR device memory (a shard already resident on the device is adopted with one copy); row indices are
+ * 0..n-1 and nothing is deleted. Search and patch refuse such a handle (MUNINN_CUDA_E_STATE). */
+int muninn_cuda_index_upload_rows(MuninnCudaIndex *idx, int64_t n, const float *rows);
+
 /*
  * Incremental form of muninn_cuda_index_upload for the vtab's xUpdate path, so that an INSERT or DELETE does not
  * re-send the whole index. The reference mutates little per call: hnsw_insert (src/hnsw_algo.c:520-666) creates

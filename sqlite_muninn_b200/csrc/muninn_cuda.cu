@@ -39,7 +39,7 @@ struct MuninnCudaIndex {
     int device = 0, dim = 0, ld = 0, metric = 0, M = 0, M0 = 0;
     long long n = 0, n_live = 0;
     int entry_slot = -1, max_level = -1;
-    bool uploaded = false;
+    bool uploaded = false, rows_only = false; /* rows_only: muninn_cuda_index_upload_rows, exact k-NN only */
     /* host mirrors muninn_cuda_index_patch needs, and the device capacities it grows */
     std::vector<int32_t> h_levels, h_upper_base;
     std::vector<uint8_t> h_deleted;
@@ -142,7 +142,7 @@ static void free_graph(MuninnCudaIndex *h) {
     cudaFree(h->d_nbrU); cudaFree(h->d_deleted); cudaFree(h->d_ids);
     h->d_vec = h->d_norm2 = nullptr; h->d_nbr0 = h->d_upper_base = h->d_nbrU = nullptr;
     h->d_deleted = nullptr; h->d_ids = nullptr;
-    h->uploaded = false;
+    h->uploaded = false; h->rows_only = false;
 }
 
 extern "C" int muninn_cuda_index_create(int device, int dim, int metric, int M, MuninnCudaIndex **out) {
@@ -322,6 +322,34 @@ extern "C" int muninn_cuda_index_upload(MuninnCudaIndex *h, int64_t n, const int
     return MUNINN_CUDA_OK;
 }
 
+/* Rows only: an index without a graph, for exact k-NN over a shard of base rows (BASELINE config 5). `rows` may be
+ * host or device memory (unified addressing): a shard generated or already resident on the device is adopted with
+ * one device-to-device copy. Row indices are 0..n-1, nothing is deleted. */
+extern "C" int muninn_cuda_index_upload_rows(MuninnCudaIndex *h, int64_t n, const float *rows) {
+    if (!h) return MUNINN_CUDA_E_ARG;
+    if (n < 0 || n > 0x7ffffff0LL) return fail(h, MUNINN_CUDA_E_ARG, "n = %lld out of range", (long long)n);
+    if (n > 0 && !rows) return fail(h, MUNINN_CUDA_E_ARG, "NULL array");
+    CK(h, cudaSetDevice(h->device));
+    CK(h, cudaStreamSynchronize(h->stream));
+    free_graph(h);
+    cudaStream_t st = h->stream;
+    CK(h, cudaMalloc((void **)&h->d_vec, std::max<size_t>((size_t)n * h->ld, 4) * sizeof(float)));
+    CK(h, cudaMalloc((void **)&h->d_norm2, std::max<size_t>((size_t)n, 1) * sizeof(float)));
+    if (n) {
+        if (h->ld != h->dim) CK(h, cudaMemsetAsync(h->d_vec, 0, (size_t)n * h->ld * sizeof(float), st));
+        CK(h, cudaMemcpy2DAsync(h->d_vec, (size_t)h->ld * 4, rows, (size_t)h->dim * 4, (size_t)h->dim * 4, (size_t)n, cudaMemcpyDefault, st));
+        row_norm2_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(h->d_vec, h->ld, h->dim, n, h->d_norm2);
+        h->launches++;
+        CK(h, cudaGetLastError());
+    }
+    CK(h, cudaStreamSynchronize(st));
+    h->n = n; h->n_live = n; h->entry_slot = -1; h->max_level = -1;
+    h->h_levels.clear(); h->h_upper_base.clear(); h->h_deleted.clear();
+    h->n_upper = 0; h->cap_n = std::max<long long>(n, 1); h->cap_upper = 1; h->last_id = n - 1;
+    h->uploaded = true; h->rows_only = true;
+    return MUNINN_CUDA_OK;
+}
+
 /* ───────────────────────── incremental update ───────────────────────── */
 
 /* every reference to a slot flagged deleted becomes a hole (-1), as upload stores it: one pass over the lists,
@@ -366,7 +394,7 @@ extern "C" int muninn_cuda_index_patch(MuninnCudaIndex *h, int64_t n_total, int3
                                        const int64_t *list_offsets, const int32_t *targets, int32_t entry_slot,
                                        int32_t max_level) {
     if (!h) return MUNINN_CUDA_E_ARG;
-    if (!h->uploaded) return fail(h, MUNINN_CUDA_E_STATE, "patch before muninn_cuda_index_upload");
+    if (!h->uploaded || h->rows_only) return fail(h, MUNINN_CUDA_E_STATE, "patch before muninn_cuda_index_upload");
     if (n_total < h->n || n_total > 0x7ffffff0LL || n_patch < 0) return fail(h, MUNINN_CUDA_E_ARG, "bad n_total / n_patch");
     if (n_patch > 0 && (!slots || !ids || !levels || !vectors || !list_offsets)) return fail(h, MUNINN_CUDA_E_ARG, "NULL array");
     if (entry_slot < -1 || entry_slot >= n_total) return fail(h, MUNINN_CUDA_E_ARG, "entry_slot %d out of range", entry_slot);
@@ -657,6 +685,7 @@ extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *
                                                MuninnSearchStats *d_stats) {
     if (!h) return MUNINN_CUDA_E_ARG;
     if (!h->uploaded) return fail(h, MUNINN_CUDA_E_STATE, "search before muninn_cuda_index_upload");
+    if (h->rows_only) return fail(h, MUNINN_CUDA_E_STATE, "this handle holds rows only (muninn_cuda_index_upload_rows): no graph to search");
     if (nq < 0 || k < 1) return fail(h, MUNINN_CUDA_E_ARG, "nq must be >= 0 and k >= 1 (nq=%d k=%d)", nq, k);
     if (nq == 0) return MUNINN_CUDA_OK;
     if (!d_queries || !d_ids || !d_dist || !d_count) return fail(h, MUNINN_CUDA_E_ARG, "NULL buffer");

@@ -33,7 +33,7 @@ ABI_SYMBOLS = (
     "muninn_cuda_gather_ceiling", "muninn_cuda_index_patch", "muninn_cuda_build_device",
     "muninn_cuda_last_team_width", "muninn_cuda_set_option", "muninn_cuda_exact_knn_sharded_device",
     "muninn_cuda_comm_unique_id", "muninn_cuda_comm_create", "muninn_cuda_comm_destroy",
-    "muninn_cuda_topk_pack_keys_device", "muninn_cuda_topk_merge_keys_device",
+    "muninn_cuda_topk_pack_keys_device", "muninn_cuda_topk_merge_keys_device", "muninn_cuda_index_upload_rows",
 )
 
 EXACT_CUDA_CORE, EXACT_TC_3XTF32, EXACT_TC_1XTF32, EXACT_TC_AUTO = 0, 1, 2, 3
@@ -97,6 +97,7 @@ def lib():
         L.muninn_cuda_build_device.argtypes = [_vp, _vp]
         L.muninn_cuda_last_team_width.argtypes = [_vp]
         L.muninn_cuda_set_option.argtypes = [_vp, C.c_char_p, C.c_double]
+        L.muninn_cuda_index_upload_rows.argtypes = [_vp, C.c_int64, _vp]
         L.muninn_cuda_exact_knn_sharded_device.argtypes = [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int64, _vp, _vp, _vp]
         L.muninn_cuda_comm_unique_id.argtypes = [_vp]
         L.muninn_cuda_comm_create.argtypes = [C.c_int, C.c_int, C.c_int, _vp, C.POINTER(_vp)]
@@ -211,6 +212,11 @@ class HnswIndexCuda:
                                                     _ptr(g.vectors), _ptr(g.list_offsets), _ptr(g.targets),
                                                     g.entry_slot, g.max_level))
         self.n = g.n
+
+    def upload_rows(self, rows_ptr: int, n: int):
+        """Rows only (exact k-NN over a shard): `rows_ptr` is the address of [n × dim] fp32 in host or device memory."""
+        self._check(self.L.muninn_cuda_index_upload_rows(self.h, n, rows_ptr))
+        self.n = n
 
     def patch(self, g: FlatGraph, slots):
         """Send only the records of `slots` (every new node included) of the new state `g`: what hnsw_insert /

@@ -74,3 +74,17 @@ def test_reference_arm_prints_the_contract_line(tmp_path):
     assert cb["kind"] == "reference" and cb["cores"] >= 1 and cb["sample"] and cb["value"] == d["value"]
     assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert d["gpu_launches"] == 0
+    assert d["scaling"] == "strong" and d["config"]["recall_at_10"] is not None and cb["cpu_model"]
+
+
+def test_reference_arm_never_loads_the_cuda_library(tmp_path):
+    """The reference arm is the CPU path only: libmuninn_cuda.so is built but must not be mapped into the process."""
+    import subprocess
+    import sys
+    code = ("import sys, os; sys.argv=['bench.py','--impl','reference','--n','3000','--nq','64','--efc','30','--steps','1',"
+            "'--warmup','0','--ef','16']; import runpy; runpy.run_path(os.path.join(%r,'bench.py'), run_name='__main__');"
+            "maps=open('/proc/self/maps').read(); print('CUDA_LOADED' if 'libmuninn_cuda' in maps else 'CUDA_NOT_LOADED')" % ROOT)
+    env = dict(os.environ, MUNINN_BENCH_CACHE=str(tmp_path))
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert "CUDA_NOT_LOADED" in out.stdout

@@ -33,14 +33,13 @@ def main():
     ap.add_argument("--reps", type=int, default=15)
     ap.add_argument("--tag", default="")
     a = ap.parse_args()
-    cfg = dict(bench.CONFIGS[a.config])
+    c = bench.cfg_of(a.config)
     if a.n:
-        cfg["n"] = a.n
+        c.n = a.n
     if a.efc:
-        cfg["efc"] = a.efc
-    ns = argparse.Namespace(n=cfg["n"], dim=cfg["dim"], metric=cfg["metric"], M=cfg["M"], efc=cfg["efc"], build_batch=1024,
-                            data=cfg["data"], seeds=cfg["seeds"], device_build=False, impl="ours")
-    g = bench.get_graph(ns, 0, 1, lambda: None)
+        c.efc = a.efc
+    cfg = vars(c)
+    g = bench.get_graph(c, 0, 1, lambda: None)
     nq_all = max(int(x) for x in a.nq.split(","))
     queries = bench.make_vectors(nq_all, cfg["dim"], cfg["seeds"][1], kind=cfg["data"])
     k = cfg["k"]
