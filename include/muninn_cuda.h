@@ -157,11 +157,14 @@ int64_t muninn_cuda_launch_count(const MuninnCudaIndex *idx);
  * team that still keeps every query of the batch resident at once, so a lone MATCH gets 4 warps and a full
  * batch one warp per query) and query teams resident per SM (0 = automatic). Results do not depend on them. */
 int muninn_cuda_set_tuning(MuninnCudaIndex *idx, int warps_per_query, int teams_per_sm);
-/* Team width the handle's most recent search launched with. */
+/* Team width and kernel generation (7 = hnsw_search.cuh, 8 = hnsw_beam.cuh) the handle's most recent search launched with. */
 int muninn_cuda_last_team_width(const MuninnCudaIndex *idx);
-/* Diagnostic options (no reference counterpart; results do not depend on them): "kernel_gen" = 8 (default,
- * hnsw_beam.cuh) or 7 (the round-1 one-warp kernel, kept for A/B timing); "vis_factor" = size of a team's
- * first-level visited table in units of ef·2M entries (default 2). */
+int muninn_cuda_last_kernel_gen(const MuninnCudaIndex *idx);
+/* Diagnostic options (no reference counterpart; results do not depend on them): "kernel_gen" = 0 (default: by
+ * shape), 7 (hnsw_search.cuh: one warp per query, 13-row tile) or 8 (hnsw_beam.cuh: teams of 1/2/4 warps, 16-row
+ * batches); "vis_factor" = size of a team's
+ * first-level visited table in units of ef·2M entries (default 2); "exact_qs" (1/0), "exact_qs_min_nq",
+ * "exact_superblock_mb", "exact_auto_3x_min_nq": shape of the exact k-NN tensor-core filter. */
 int muninn_cuda_set_option(MuninnCudaIndex *idx, const char *name, double value);
 
 /*
@@ -183,8 +186,9 @@ int muninn_cuda_exact_knn_device(MuninnCudaIndex *idx, const float *d_queries, i
  *                            distance; only the survivors are evaluated in the reference's order
  *   MUNINN_EXACT_TC_1XTF32   same with a single TF32 product and a correspondingly wider margin; the
  *                            MMA reads the fp32 rows as stored (no split pass: the base is read once)
- *   MUNINN_EXACT_TC_AUTO     (default) 3xTF32 for batches of >= 1024 queries (tensor-bound), 1xTF32 below
- *                            (HBM-bound); muninn_cuda_exact_stats reports which one ran
+ *   MUNINN_EXACT_TC_AUTO     (default) 1xTF32 for every batch size: below 1024 queries the rows stream once past all
+ *                            queries (HBM-bound), above it the query-stationary filter keeps a 128-query tile in shared
+ *                            memory and sweeps L2-sized super-blocks of rows; muninn_cuda_exact_stats reports the mode
  * tile_rows = base rows per CTA tile (0 = default 256, or 128). In the tensor-core modes the
  * device entry point synchronises once with the host before it returns.
  */

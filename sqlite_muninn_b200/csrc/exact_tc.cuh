@@ -394,6 +394,260 @@ exact_tc_filter(const __grid_constant__ CUtensorMap tm_qhi, const __grid_constan
     if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, Cfg::TMEM_COLS); }
 }
 
+/* ───────────── filter kernel, query-stationary form (one TF32 product) ─────────────
+ *
+ * The streaming kernel above re-fetches BOTH operands of every tile: 192 KB of TMA traffic for 8.4 MFLOP at K = 128,
+ * i.e. ≈ 19 TB/s of L2→shared-memory traffic to keep the tensor pipe busy — more than the L2 delivers (measured
+ * 3.2 µs per tile against 1.47 µs of MMA). Here the QUERY tile (128 × K, ≤ 128 KB) stays in shared memory and only
+ * base-row tiles stream past it, a third less traffic per tile; to keep the base rows coming out of L2 rather than
+ * HBM while ⌈nq/128⌉ query tiles each walk them, the row tiles are taken in super-blocks of SB tiles (≈ 32 MB of
+ * rows): inside a super-block the (query tile, row tile) pairs are dealt out query-major in contiguous runs, so a
+ * CTA keeps one query tile for ≈ 100 row tiles, and all CTAs sweep the same L2-resident super-block together.
+ */
+struct TileWalk {
+    int n_qt, n_xt, SB, sb, nx;
+    long long j, end;
+    __device__ __forceinline__ void start_sb(int cta, int grid) {
+        nx = n_xt - sb * SB < SB ? n_xt - sb * SB : SB;
+        const long long T = (long long)n_qt * nx;
+        j = T * cta / grid;
+        end = T * (cta + 1) / grid;
+    }
+    __device__ __forceinline__ TileWalk(int n_qt_, int n_xt_, int SB_, int cta, int grid) : n_qt(n_qt_), n_xt(n_xt_), SB(SB_), sb(0) {
+        start_sb(cta, grid);
+        skip_empty(cta, grid);
+    }
+    __device__ __forceinline__ void skip_empty(int cta, int grid) {
+        while (j >= end && (sb + 1) * SB < n_xt) { sb++; start_sb(cta, grid); }
+    }
+    __device__ __forceinline__ bool done() const { return j >= end; }
+    __device__ __forceinline__ int qt() const { return (int)(j / nx); }
+    __device__ __forceinline__ int xt() const { return sb * SB + (int)(j % nx); }
+    __device__ __forceinline__ void advance(int cta, int grid) { j++; skip_empty(cta, grid); }
+};
+
+constexpr int QS_MAX_KBLOCKS = 8; /* query tile ≤ 128 × 256 fp32 = 128 KB */
+__host__ __device__ inline int qs_stages(int kblocks, int BN) {
+    const int left = 196 * 1024 - kblocks * BM * BK * 4;
+    int n = left / (BN * BK * 4);
+    return n > 6 ? 6 : n;
+}
+__host__ __device__ inline size_t qs_smem_bytes(int kblocks, int BN) {
+    return 1024 + (size_t)kblocks * BM * BK * 4 + (size_t)qs_stages(kblocks, BN) * BN * BK * 4 + 2 * BN * 4 + (2 * 6 + 6) * 8 + 16 + 256 * SBUF * 4;
+}
+
+/* The epilogue was the bound of the one-product filter (ncu, profiles/r2_ncu/exact_*: the compare + mask-building
+ * lines were 46 % of all instructions, one epilogue warp per scheduler issuing at 0.37 IPC, tensor pipe 51 % busy), so
+ * here it gets EIGHT warps — two per TMEM lane quarter, each taking half of the tile's columns — and a cheaper inner
+ * loop: per 32 columns one subtract and one predicate-chained compare per element decide "no survivor in this group"
+ * (the common case by far); only a group with a survivor is walked again to extract it. */
+constexpr int QS_EPI_WARPS = 8, QS_THREADS = 64 + 32 * QS_EPI_WARPS;
+
+template <int METRIC, int BN>
+__global__ void __launch_bounds__(QS_THREADS, 1)
+exact_tc_filter_qs(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_x, const FilterParams p, const int SB) {
+    constexpr int A_BYTES = BM * BK * 4, B_BYTES = BN * BK * 4;
+    constexpr int EPT = 32 * QS_EPI_WARPS;   /* epilogue threads */
+    constexpr int HALF = BN / 2;             /* columns per epilogue thread */
+    extern __shared__ unsigned char smem_dyn[];
+    unsigned char *base = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
+    const int NST = qs_stages(p.kblocks, BN);
+    unsigned char *qsm = base;                                   /* [kblocks][128 × 32 fp32], 128B-swizzled */
+    unsigned char *stages = qsm + (size_t)p.kblocks * A_BYTES;   /* [NST][BN × 32 fp32] */
+    float *xaux = reinterpret_cast<float *>(stages + (size_t)NST * B_BYTES);
+    uint64_t *full = reinterpret_cast<uint64_t *>(xaux + 2 * BN);
+    uint64_t *empty = full + 6;
+    uint64_t *tmem_full = empty + 6;
+    uint64_t *tmem_empty = tmem_full + 2;
+    uint64_t *q_full = tmem_empty + 2;
+    uint64_t *q_empty = q_full + 1;
+    uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(q_empty + 1);
+    int *sbuf = reinterpret_cast<int *>(tmem_ptr + 4);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_qt = (p.nq + BM - 1) / BM, n_xt = (p.rows + BN - 1) / BN;
+    const int cta = blockIdx.x, grid = gridDim.x;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tm_q); prefetch_tmap(&tm_x);
+        for (int s = 0; s < NST; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (int a = 0; a < 2; a++) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], QS_EPI_WARPS); }
+        mbar_init(q_full, 1); mbar_init(q_empty, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_ptr, 2 * BN);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp == 0) {
+        if (lane == 0) { /* ── TMA producer ── */
+            int s = 0; uint32_t ph = 0, qe_ph = 0; int qt_have = -1;
+            for (TileWalk w(n_qt, n_xt, SB, cta, grid); !w.done(); w.advance(cta, grid)) {
+                const int qt = w.qt(), xt = w.xt();
+                if (qt != qt_have) {
+                    if (qt_have >= 0) { mbar_wait(q_empty, qe_ph); qe_ph ^= 1; } /* every MMA on the old query tile has retired */
+                    mbar_expect_tx(q_full, (uint32_t)(p.kblocks * A_BYTES));
+                    for (int kb = 0; kb < p.kblocks; kb++) tma_load_2d(qsm + (size_t)kb * A_BYTES, &tm_q, q_full, kb * BK, qt * BM);
+                    qt_have = qt;
+                }
+                for (int kb = 0; kb < p.kblocks; kb++) {
+                    mbar_wait(&empty[s], ph ^ 1);
+                    mbar_expect_tx(&full[s], B_BYTES);
+                    tma_load_2d(stages + (size_t)s * B_BYTES, &tm_x, &full[s], kb * BK, xt * BN);
+                    if (++s == NST) { s = 0; ph ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) { /* ── MMA issuer ── */
+            constexpr uint32_t idesc = make_idesc_tf32(BN);
+            int s = 0; uint32_t ph = 0, qf_ph = 0; int a = 0; uint32_t aph = 0; int qt_have = -1;
+            TileWalk w(n_qt, n_xt, SB, cta, grid);
+            while (!w.done()) {
+                const int qt = w.qt();
+                if (qt != qt_have) { mbar_wait(q_full, qf_ph); qf_ph ^= 1; qt_have = qt; tc_fence_after(); }
+                mbar_wait(&tmem_empty[a], aph ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(a * BN);
+                for (int kb = 0; kb < p.kblocks; kb++) {
+                    mbar_wait(&full[s], ph);
+                    tc_fence_after();
+                    const uint64_t a_d = make_desc_k128(smem_u32(qsm + (size_t)kb * A_BYTES));
+                    const uint64_t b_d = make_desc_k128(smem_u32(stages + (size_t)s * B_BYTES));
+#pragma unroll
+                    for (int k4 = 0; k4 < BK / UK; k4++) mma_tf32_ss(d_tmem, a_d + 2 * k4, b_d + 2 * k4, idesc, (kb | k4) ? 1u : 0u);
+                    tc_commit(&empty[s]);
+                    if (++s == NST) { s = 0; ph ^= 1; }
+                }
+                tc_commit(&tmem_full[a]);
+                w.advance(cta, grid);
+                if (w.done() || w.qt() != qt_have) tc_commit(q_empty); /* the query tile may be replaced once these MMAs retire */
+                if (++a == 2) { a = 0; aph ^= 1; }
+            }
+        }
+    } else {
+        /* ── epilogue: 8 warps; warp w reads TMEM lanes 32·(w mod 4)…, thread = one query × one half of the columns ──
+         * (the compare is the one of exact_tc_filter: prune iff s < [h·qn − τ/2] + [h·xn] etc., NaN keeps the row) */
+        const int ew = warp - 2;                       /* 0..7 */
+        const int quarter = warp & 3, half = ew >> 2;  /* TMEM lane quarter (hardware: warp id mod 4), column half */
+        const int et = ew * 32 + lane;                 /* 0..255: also the column this thread stages */
+        const int qrow = quarter * 32 + lane;
+        const float c = p.c_eps, hh = 0.5f * (1.0f - c);
+        int a = 0; uint32_t aph = 0;
+        static_assert(BN == EPT, "one staged column per epilogue thread");
+        float xn_pre = 0.0f;
+        auto fetch_xn = [&](bool have, int xt2) {
+            xn_pre = 0.0f;
+            if (have && xt2 * BN + et < p.rows) xn_pre = __ldg(p.xnorm2 + p.row0 + (long long)xt2 * BN + et);
+        };
+        TileWalk w(n_qt, n_xt, SB, cta, grid);
+        fetch_xn(!w.done(), w.done() ? 0 : w.xt());
+        int qt_have = -1;
+        float qa = 0.0f;
+        bool qvalid = false;
+        int q = 0;
+        int *mybuf = sbuf + et * SBUF;
+        int nbuf = 0;
+        auto flush = [&]() {
+            if (nbuf == 0) return;
+            const int pos = atomicAdd(p.cand_count + q, nbuf);
+            for (int i = 0; i < nbuf; i++)
+                if (pos + i < p.cand_cap) p.cand[(size_t)q * p.cand_cap + pos + i] = mybuf[i];
+            nbuf = 0;
+        };
+        while (!w.done()) {
+            const int qt = w.qt(), xt = w.xt();
+            const int ncols = p.rows - xt * BN < BN ? p.rows - xt * BN : BN;
+            const long long xrow0 = p.row0 + (long long)xt * BN;
+            if (qt != qt_have) {
+                flush();
+                qt_have = qt;
+                q = qt * BM + qrow;
+                qvalid = q < p.nq;
+                qa = 0.0f;
+                if (qvalid) {
+                    const float qn = p.qaux[q], tq = __ldcg(p.tau + q) + 1e-30f;
+                    if (METRIC == METRIC_L2) qa = fmaf(hh, qn, -0.5f * tq);
+                    else if (METRIC == METRIC_IP) qa = fmaf(-c, qn, -tq);
+                    else qa = qn < 1e-18f ? __int_as_float(0x7fc00000) : (1.0f - tq - c) * sqrtf(qn);
+                }
+            }
+            float *xa = xaux + a * BN;
+            {
+                float v = 0.0f;
+                if (et < ncols) {
+                    const float xn = xn_pre;
+                    if (METRIC == METRIC_L2) v = hh * xn;
+                    else if (METRIC == METRIC_IP) v = -c * xn;
+                    else v = xn < 1e-18f ? __int_as_float(0x7fc00000) : rsqrtf(xn);
+                }
+                xa[et] = v;
+            }
+            w.advance(cta, grid);
+            fetch_xn(!w.done(), w.done() ? 0 : w.xt()); /* the next tile's row terms, in flight during this tile's columns */
+            asm volatile("bar.sync 1, %0;" ::"n"(EPT) : "memory");
+            mbar_wait(&tmem_full[a], aph);
+            tc_fence_after();
+            const int cbeg = half * HALF, cend = ncols < cbeg + HALF ? ncols : cbeg + HALF; /* this thread's columns */
+            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(a * BN);
+            auto consume = [&](const uint32_t (&v)[32], int c0) {
+                /* fast path: "every one of these 32 columns is pruned" as one predicate chain */
+                bool all_pruned = true;
+#pragma unroll
+                for (int j4 = 0; j4 < 32; j4 += 4) {
+                    const float4 x4 = *reinterpret_cast<const float4 *>(xa + c0 + j4);
+                    const float xs[4] = {x4.x, x4.y, x4.z, x4.w};
+#pragma unroll
+                    for (int jj = 0; jj < 4; jj++) {
+                        const float sdot = __uint_as_float(v[j4 + jj]);
+                        all_pruned = all_pruned && (METRIC == METRIC_COSINE ? (sdot * xs[jj] < qa) : (sdot - xs[jj] < qa));
+                    }
+                }
+                if (all_pruned || !qvalid) return;
+                uint32_t keep = 0;
+#pragma unroll
+                for (int j = 0; j < 32; j++) {
+                    const float sdot = __uint_as_float(v[j]), x = xa[c0 + j];
+                    const bool prune = METRIC == METRIC_COSINE ? (sdot * x < qa) : (sdot - x < qa);
+                    keep |= prune ? 0u : (1u << j);
+                }
+                if (cend - c0 < 32) keep &= (1u << (cend - c0)) - 1u;
+                while (keep) {
+                    const int j = __ffs(keep) - 1;
+                    keep &= keep - 1;
+                    mybuf[nbuf++] = (int)(xrow0 + c0 + j);
+                    if (nbuf == SBUF) flush();
+                }
+            };
+            if (cbeg < cend) {
+                uint32_t va[32], vb[32];
+                tmem_ld32(taddr + (uint32_t)cbeg, va);
+                for (int c0 = cbeg; c0 < cend; c0 += 64) {
+                    tmem_ld_wait();
+                    const bool more = c0 + 32 < cend;
+                    if (more) tmem_ld32(taddr + (uint32_t)(c0 + 32), vb);
+                    consume(va, c0);
+                    if (more) {
+                        tmem_ld_wait();
+                        if (c0 + 64 < cend) tmem_ld32(taddr + (uint32_t)(c0 + 64), va);
+                        consume(vb, c0 + 32);
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[a]);
+            if (++a == 2) { a = 0; aph ^= 1; }
+        }
+        flush();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, 2 * BN); }
+}
+
 /* ───────────── split / prepare ───────────── */
 
 __device__ __forceinline__ void split_tf32(float x, float &hi, float &lo) {

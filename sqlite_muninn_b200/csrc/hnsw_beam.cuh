@@ -40,7 +40,7 @@ constexpr int RB = 16;     /* rows per batch: two lanes per row, chains (2h, 2h+
 constexpr int SPEC_CH = 2; /* 32-entry chunks of a neighbour list held in registers ahead of time (M0 ≤ 64) */
 
 #ifndef MUNINN_SPEC
-#define MUNINN_SPEC 2 /* 0 = off, 1 = next candidate's list only, 2 = list + visited peek + row prefetch */
+#define MUNINN_SPEC 0 /* 0 = off (default: measured slower everywhere, profiles/r2_bench/ab_a_ring_spec_teams.jsonl), 1 = next candidate's list only, 2 = list + visited peek + row prefetch */
 #endif
 
 __host__ __device__ inline size_t a16(size_t v) { return (v + 15) & ~(size_t)15; }
@@ -185,7 +185,7 @@ __device__ __forceinline__ void team_sync() {
     else __syncwarp();
 }
 
-template <int W> struct MinBlocks { static constexpr int v = W == 1 ? MUNINN_SEARCH_MIN_BLOCKS : (W == 2 ? 8 : 4); };
+template <int W> struct MinBlocks { static constexpr int v = W == 1 ? MUNINN_SEARCH_MIN_BLOCKS : (W == 2 ? 10 : 4); }; /* W = 2: 10 teams/SM keep a 1 250-query slice resident */
 
 template <int METRIC, int CD, int U, int NST, int W>
 __global__ void __launch_bounds__(32 * W, MinBlocks<W>::v) hnsw_beam_kernel(const SearchParams p, const int level) {
@@ -434,7 +434,7 @@ __global__ void __launch_bounds__(32 * W, MinBlocks<W>::v) hnsw_beam_kernel(cons
                 for (int base = 0; base < nf; base += 32) {
                     const unsigned long long worst = size >= ef ? R[ef - 1] : KEY_NONE;
                     const unsigned long long f = base + lane < nf ? Fk[base + lane] : KEY_NONE;
-                    const bool keep = f < worst;
+                    const bool keep = (unsigned)(f >> 32) < (unsigned)(worst >> 32); /* strict on the DISTANCE, as :419 — the slot only orders */
                     const unsigned km = __ballot_sync(FULL, keep);
                     const int ns = __popc(km);
                     if (ns == 0) continue;

@@ -655,7 +655,7 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
                     for (int base = 0; base < nf; base += 32) {
                         unsigned long long worst = size >= ef ? sm.R[ef - 1] : KEY_NONE;
                         unsigned long long f = base + lane < nf ? sm.Fk[base + lane] : KEY_NONE;
-                        bool keep = f < worst;
+                        bool keep = (unsigned)(f >> 32) < (unsigned)(worst >> 32); /* strict on the DISTANCE, as :419 — the slot only orders */
                         unsigned km = __ballot_sync(FULL, keep);
                         int ns = __popc(km);
                         if (ns == 0) continue;

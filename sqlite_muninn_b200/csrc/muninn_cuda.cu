@@ -37,6 +37,8 @@ using namespace muninn;
 
 struct MuninnCudaIndex {
     int device = 0, dim = 0, ld = 0, metric = 0, M = 0, M0 = 0;
+    int W0 = 0, WU = 0; /* device row widths of the layer-0 / upper-layer tables: 2M / M, or the longest stored list when the
+                           reference's delete-time reconnection grew one past its nominal capacity (src/hnsw_algo.c:780-781) */
     long long n = 0, n_live = 0;
     int entry_slot = -1, max_level = -1;
     bool uploaded = false, rows_only = false; /* rows_only: muninn_cuda_index_upload_rows, exact k-NN only */
@@ -63,12 +65,14 @@ struct MuninnCudaIndex {
     void *d_stage = nullptr; size_t stage_bytes = 0;
     void *h_pinned = nullptr; size_t pinned_bytes = 0;
     size_t occ_smem[4] = {0, 0, 0, 0}; int occ_val[4] = {0, 0, 0, 0}; /* cached occupancy per (generation, team width) */
-    int kernel_gen = 8, last_W = 1; double vis_factor = MUNINN_VIS_FACTOR;
+    int kernel_gen = 0, last_W = 1, last_gen = 7; double vis_factor = MUNINN_VIS_FACTOR; /* kernel_gen 0 = by shape */
     /* exact k-NN scratch */
     float *d_panel = nullptr; size_t panel_floats = 0;
     unsigned long long *d_topk = nullptr; int *d_topk_size = nullptr; size_t topk_cap = 0, topk_q = 0;
     /* exact k-NN, tensor-core filter (exact_tc.cuh) */
     int exact_mode = MUNINN_EXACT_TC_AUTO, tc_tile_rows = 256;
+    int tc_qs = 1, tc_qs_min_nq = 1024, tc_superblock_mb = 32, tc_x_stride = 0; /* query-stationary 1xTF32 filter (exact_tc_filter_qs) */
+    int tc_auto_1x_min_nq = 1 << 30; /* AUTO: batches of at least this many queries still take 3xTF32 (none by default) */
     int exact_mode_run = MUNINN_EXACT_TC_3XTF32; /* what AUTO resolved to for the current call */
     float *d_qsplit = nullptr; size_t qsplit_floats = 0;   /* q_hi | q_lo, [nq × kp] each */
     float *d_xsplit = nullptr; size_t xsplit_floats = 0;   /* x_hi | x_lo of one chunk */
@@ -83,6 +87,10 @@ struct MuninnCudaIndex {
     unsigned long long *d_shard_keys = nullptr; size_t shard_keys_cap = 0; /* sharded exact k-NN: own keys | gathered keys */
     std::string err;
 };
+
+/* the last-resort visited table holds 2·(n + row width + 1) 32-bit entries rounded up to a power of two: beyond
+ * 2^30 nodes that size no longer fits the 32-bit capacity the kernels index with */
+static const long long MAX_NODES = (1LL << 30) - 1024;
 
 static thread_local std::string g_create_err;
 
@@ -156,7 +164,7 @@ extern "C" int muninn_cuda_index_create(int device, int dim, int metric, int M, 
     if (device < 0 || device >= ndev) return fail(nullptr, MUNINN_CUDA_E_ARG, "device %d out of range (0..%d)", device, ndev - 1);
     MuninnCudaIndex *h = new (std::nothrow) MuninnCudaIndex();
     if (!h) return fail(nullptr, MUNINN_CUDA_E_NOMEM, "host allocation failed");
-    h->device = device; h->dim = dim; h->ld = (dim + 3) & ~3; h->metric = metric; h->M = M; h->M0 = 2 * M;
+    h->device = device; h->dim = dim; h->ld = (dim + 3) & ~3; h->metric = metric; h->M = M; h->M0 = 2 * M; h->W0 = h->M0; h->WU = M;
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
@@ -170,9 +178,11 @@ extern "C" int muninn_cuda_index_create(int device, int dim, int metric, int M, 
     }
     h->stream = h->own_stream;
     /* experiment knobs (A/B runs of one build): same meaning as muninn_cuda_set_option / _set_tuning */
-    if (const char *e = getenv("MUNINN_KERNEL")) { const int g = atoi(e); if (g == 7 || g == 8) h->kernel_gen = g; }
+    if (const char *e = getenv("MUNINN_KERNEL")) { const int g = atoi(e); if (g == 0 || g == 7 || g == 8) h->kernel_gen = g; }
     if (const char *e = getenv("MUNINN_VIS_FACTOR")) { const double f = atof(e); if (f >= 0.5 && f <= 64.0) h->vis_factor = f; }
     if (const char *e = getenv("MUNINN_WARPS")) { const int w = atoi(e); if (w == 0 || w == 1 || w == 2 || w == 4) h->warps_per_query = w; }
+    if (const char *e = getenv("MUNINN_EXACT_QS")) h->tc_qs = atoi(e) != 0;
+    if (const char *e = getenv("MUNINN_EXACT_SB_MB")) { const int v = atoi(e); if (v >= 1 && v <= 4096) h->tc_superblock_mb = v; }
     if (const char *e = getenv("MUNINN_TEAMS_PER_SM")) { const int t = atoi(e); if (t >= 0 && t <= 32) h->teams_per_sm = t; }
     *out = h;
     return MUNINN_CUDA_OK;
@@ -217,16 +227,26 @@ extern "C" int muninn_cuda_set_tuning(MuninnCudaIndex *h, int warps_per_query, i
 extern "C" int muninn_cuda_set_option(MuninnCudaIndex *h, const char *name, double value) {
     if (!h || !name) return MUNINN_CUDA_E_ARG;
     if (!strcmp(name, "kernel_gen")) {
-        if (value != 7 && value != 8) return fail(h, MUNINN_CUDA_E_ARG, "kernel_gen must be 7 or 8");
+        if (value != 0 && value != 7 && value != 8) return fail(h, MUNINN_CUDA_E_ARG, "kernel_gen must be 0 (by shape), 7 or 8");
         h->kernel_gen = (int)value;
     } else if (!strcmp(name, "vis_factor")) {
         if (!(value >= 0.5 && value <= 64.0)) return fail(h, MUNINN_CUDA_E_ARG, "vis_factor must be in [0.5, 64]");
         h->vis_factor = value;
+    } else if (!strcmp(name, "exact_qs")) { /* 0 = the streaming 1xTF32 filter for every batch size */
+        h->tc_qs = value != 0;
+    } else if (!strcmp(name, "exact_qs_min_nq")) {
+        h->tc_qs_min_nq = (int)value;
+    } else if (!strcmp(name, "exact_superblock_mb")) {
+        if (!(value >= 1 && value <= 4096)) return fail(h, MUNINN_CUDA_E_ARG, "exact_superblock_mb must be in [1, 4096]");
+        h->tc_superblock_mb = (int)value;
+    } else if (!strcmp(name, "exact_auto_3x_min_nq")) {
+        h->tc_auto_1x_min_nq = value <= 0 ? (1 << 30) : (int)value;
     } else return fail(h, MUNINN_CUDA_E_ARG, "unknown option %s", name);
     return MUNINN_CUDA_OK;
 }
 
 extern "C" int muninn_cuda_last_team_width(const MuninnCudaIndex *h) { return h ? h->last_W : 0; }
+extern "C" int muninn_cuda_last_kernel_gen(const MuninnCudaIndex *h) { return h ? h->last_gen : 0; }
 
 extern "C" float muninn_cuda_last_kernel_ms(MuninnCudaIndex *h) {
     if (!h || !h->have_timing) return -1.0f;
@@ -251,21 +271,37 @@ extern "C" int muninn_cuda_index_upload(MuninnCudaIndex *h, int64_t n, const int
                                         const uint8_t *deleted, const float *vectors, const int64_t *list_offsets,
                                         const int32_t *targets, int32_t entry_slot, int32_t max_level) {
     if (!h) return MUNINN_CUDA_E_ARG;
-    if (n < 0 || n > 0x7ffffff0LL) return fail(h, MUNINN_CUDA_E_ARG, "n = %lld out of range", (long long)n);
+    if (n < 0 || n > MAX_NODES) return fail(h, MUNINN_CUDA_E_ARG, "n = %lld out of range (at most %lld nodes)", (long long)n, (long long)MAX_NODES);
     if (n > 0 && (!ids || !levels || !vectors || !list_offsets)) return fail(h, MUNINN_CUDA_E_ARG, "NULL array");
     if (entry_slot < -1 || entry_slot >= n) return fail(h, MUNINN_CUDA_E_ARG, "entry_slot %d out of range", entry_slot);
     CK(h, cudaSetDevice(h->device));
     CK(h, cudaStreamSynchronize(h->stream));
     free_graph(h);
 
-    const int M = h->M, M0 = h->M0;
+    /* row widths: the nominal capacities, or the longest stored list. hnsw_delete's reconnection step appends to a
+     * neighbour's list with no capacity check (src/hnsw_algo.c:780-781), so after heavy deletion the reference holds —
+     * and keeps answering from — lists longer than 2M / M; the device tables are sized to hold what it holds */
+    int W0 = h->M0, WU = h->M;
+    {
+        int64_t li0 = 0;
+        for (int64_t s = 0; s < n; s++) {
+            if (levels[s] < 0 || levels[s] >= 32) /* HNSW_MAX_LEVELS, src/hnsw_algo.h:14 */
+                return fail(h, MUNINN_CUDA_E_ARG, "level %d of slot %lld out of range", levels[s], (long long)s);
+            for (int l = 0; l <= levels[s]; l++, li0++) {
+                const int64_t len = list_offsets[li0 + 1] - list_offsets[li0];
+                if (len < 0) return fail(h, MUNINN_CUDA_E_ARG, "list offsets must not decrease");
+                if (len > MAX_M0) return fail(h, MUNINN_CUDA_E_ARG, "list (slot %lld, level %d) has %lld entries; at most %d are supported", (long long)s, l, (long long)len, MAX_M0);
+                if (l == 0 && len > W0) W0 = (int)((len + 3) & ~3);
+                if (l > 0 && len > WU) WU = (int)((len + 3) & ~3);
+            }
+        }
+    }
+    const int M = WU, M0 = W0; /* from here on: device row widths */
     /* host re-layout */
     std::vector<int32_t> nbr0((size_t)n * M0, -1), upper_base((size_t)n, -1);
     std::vector<uint8_t> del((size_t)n, 0);
     long long n_upper = 0, n_live = 0;
     for (int64_t s = 0; s < n; s++) {
-        if (levels[s] < 0 || levels[s] >= 32) /* HNSW_MAX_LEVELS, src/hnsw_algo.h:14 */
-            return fail(h, MUNINN_CUDA_E_ARG, "level %d of slot %lld out of range", levels[s], (long long)s);
         if (s > 0 && ids[s] <= ids[s - 1]) return fail(h, MUNINN_CUDA_E_ARG, "ids must be strictly ascending");
         if (levels[s] > 0) { upper_base[s] = (int32_t)n_upper; n_upper += levels[s]; }
         del[s] = deleted ? (deleted[s] != 0) : 0;
@@ -280,10 +316,6 @@ extern "C" int muninn_cuda_index_upload(MuninnCudaIndex *h, int64_t n, const int
     for (int64_t s = 0; s < n; s++) {
         for (int l = 0; l <= levels[s]; l++, li++) {
             const int64_t b = list_offsets[li], e = list_offsets[li + 1];
-            const int capl = l == 0 ? M0 : M;
-            if (e < b || e - b > capl)
-                return fail(h, MUNINN_CUDA_E_ARG, "list (slot %lld, level %d) has %lld entries, capacity %d",
-                            (long long)s, l, (long long)(e - b), capl);
             int32_t *dst = l == 0 ? &nbr0[(size_t)s * M0] : &nbrU[((size_t)upper_base[s] + (l - 1)) * M];
             for (int64_t j = b; j < e; j++) {
                 int32_t t = targets[j];
@@ -315,6 +347,7 @@ extern "C" int muninn_cuda_index_upload(MuninnCudaIndex *h, int64_t n, const int
     }
     CK(h, cudaStreamSynchronize(st)); /* host vectors above go out of scope */
     h->n = n; h->n_live = n_live; h->entry_slot = entry_slot; h->max_level = max_level;
+    h->W0 = W0; h->WU = WU;
     h->h_levels.assign(levels, levels + n); h->h_upper_base = upper_base; h->h_deleted = del;
     h->n_upper = n_upper; h->cap_n = std::max<long long>(n, 1); h->cap_upper = std::max<long long>(n_upper, 1);
     h->last_id = n ? ids[n - 1] : 0;
@@ -346,6 +379,7 @@ extern "C" int muninn_cuda_index_upload_rows(MuninnCudaIndex *h, int64_t n, cons
     h->n = n; h->n_live = n; h->entry_slot = -1; h->max_level = -1;
     h->h_levels.clear(); h->h_upper_base.clear(); h->h_deleted.clear();
     h->n_upper = 0; h->cap_n = std::max<long long>(n, 1); h->cap_upper = 1; h->last_id = n - 1;
+    h->W0 = h->M0; h->WU = h->M;
     h->uploaded = true; h->rows_only = true;
     return MUNINN_CUDA_OK;
 }
@@ -395,12 +429,12 @@ extern "C" int muninn_cuda_index_patch(MuninnCudaIndex *h, int64_t n_total, int3
                                        int32_t max_level) {
     if (!h) return MUNINN_CUDA_E_ARG;
     if (!h->uploaded || h->rows_only) return fail(h, MUNINN_CUDA_E_STATE, "patch before muninn_cuda_index_upload");
-    if (n_total < h->n || n_total > 0x7ffffff0LL || n_patch < 0) return fail(h, MUNINN_CUDA_E_ARG, "bad n_total / n_patch");
+    if (n_total < h->n || n_total > MAX_NODES || n_patch < 0) return fail(h, MUNINN_CUDA_E_ARG, "bad n_total / n_patch");
     if (n_patch > 0 && (!slots || !ids || !levels || !vectors || !list_offsets)) return fail(h, MUNINN_CUDA_E_ARG, "NULL array");
     if (entry_slot < -1 || entry_slot >= n_total) return fail(h, MUNINN_CUDA_E_ARG, "entry_slot %d out of range", entry_slot);
     CK(h, cudaSetDevice(h->device));
     cudaStream_t st = h->stream;
-    const int M = h->M, M0 = h->M0;
+    const int M = h->WU, M0 = h->W0; /* device row widths (muninn_cuda_index_upload) */
     const long long n_old = h->n, n_new = n_total - n_old;
 
     /* ── phase 1: validate everything; the handle is not touched until the whole patch is known to be sound ── */
@@ -460,7 +494,8 @@ extern "C" int muninn_cuda_index_patch(MuninnCudaIndex *h, int64_t n_total, int3
         for (int l = 0; l <= levels[i]; l++, li++) {
             const int64_t b = list_offsets[li], e = list_offsets[li + 1];
             const int capl = l == 0 ? M0 : M;
-            if (e < b || e - b > capl) return fail(h, MUNINN_CUDA_E_ARG, "list (slot %d, level %d) has %lld entries, capacity %d", sl, l, (long long)(e - b), capl);
+            if (e < b || e - b > capl) /* a list that outgrew the device rows (delete-time reconnection): the caller re-uploads */
+                return fail(h, MUNINN_CUDA_E_ARG, "list (slot %d, level %d) has %lld entries, device rows hold %d: upload again", sl, l, (long long)(e - b), capl);
             if (e > b && !targets) return fail(h, MUNINN_CUDA_E_ARG, "NULL array");
             int32_t *dst = l == 0 ? &rows0[(size_t)i * M0] : &rowsU[(size_t)ur * M];
             for (int64_t j = b; j < e; j++) {
@@ -593,21 +628,25 @@ static unsigned pow2_at_least(unsigned long long v) {
 static unsigned log2u(unsigned v) { unsigned l = 0; while ((1u << l) < v) l++; return l; }
 
 /* ── kernel selection ──
- * Generation 8 (hnsw_beam.cuh) is the product kernel; generation 7 (hnsw_search.cuh, one warp per query, whole-row
- * tile) is kept for A/B runs (MUNINN_KERNEL=7 in the environment, or muninn_cuda_set_tuning_ex). A kernel is picked as
- * a plain function pointer so that occupancy query, attribute and launch share one code path. Ring geometry (U floats
- * per unit, NST stages) per constant-dimension instance: */
+ * Two kernels answer the same contract and are tested for identical output in every shape: hnsw_search.cuh (one warp
+ * per query, 13-row whole-row tile: 24 query teams per SM, the best throughput for full batches of narrow rows) and
+ * hnsw_beam.cuh (query teams of W warps, 16-row batches through a row ring). kernel_gen 0 picks by shape from the
+ * measurements in profiles/r2_bench/: teams of 2 warps whenever every query of the batch can be resident at once
+ * (a lone MATCH, the 1 250-query slices of a batch split over 8 GPUs: 8-11 % faster), the 16-row kernel for
+ * ef >= 192 at dim 128 (5 % faster), the 13-row kernel otherwise. MUNINN_KERNEL / muninn_cuda_set_option("kernel_gen")
+ * force one for A/B runs. A kernel is picked as a plain function pointer so that occupancy query, attribute and launch
+ * share one code path. Ring geometry (U floats per unit, NST stages) per constant-dimension instance: */
 #ifndef MUNINN_U_D128
-#define MUNINN_U_D128 64
+#define MUNINN_U_D128 128 /* whole row in one unit: the best of the A/B sweeps (profiles/r2_bench/ab_b_geometry_nospec.jsonl) */
 #endif
 #ifndef MUNINN_NST_D128
-#define MUNINN_NST_D128 2
+#define MUNINN_NST_D128 1
 #endif
 #ifndef MUNINN_U_D96
-#define MUNINN_U_D96 32
+#define MUNINN_U_D96 96
 #endif
 #ifndef MUNINN_NST_D96
-#define MUNINN_NST_D96 3
+#define MUNINN_NST_D96 1
 #endif
 #ifndef MUNINN_U_D768
 #define MUNINN_U_D768 128
@@ -655,14 +694,14 @@ static KernelSel select_kernel(const MuninnCudaIndex *h, int gen, int W, int ef)
         k.W = 1;
         k.fn = h->metric == MUNINN_METRIC_L2 ? v7_fn<METRIC_L2>(h->dim, h->ld)
                : h->metric == MUNINN_METRIC_COSINE ? v7_fn<METRIC_COSINE>(h->dim, h->ld) : v7_fn<METRIC_IP>(h->dim, h->ld);
-        k.smem = search_smem_bytes(ef, h->ld, h->M0, MUNINN_D128 ? h->dim : -1);
+        k.smem = search_smem_bytes(ef, h->ld, h->W0, MUNINN_D128 ? h->dim : -1);
         return k;
     }
     k.W = W;
     k.fn = h->metric == MUNINN_METRIC_L2 ? beam_fn_w<METRIC_L2>(W, h->dim, &k.U, &k.NST)
            : h->metric == MUNINN_METRIC_COSINE ? beam_fn_w<METRIC_COSINE>(W, h->dim, &k.U, &k.NST)
                                                : beam_fn_w<METRIC_IP>(W, h->dim, &k.U, &k.NST);
-    k.smem = beam::smem_bytes(ef, h->ld, h->M0, k.U, k.NST, W);
+    k.smem = beam::smem_bytes(ef, h->ld, h->W0, k.U, k.NST, W);
     return k;
 }
 
@@ -692,29 +731,31 @@ extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *
     if (ef < k) ef = k; /* src/hnsw_algo.c:673 */
     CK(h, cudaSetDevice(h->device));
 
-    /* team width: the caller's choice, else the widest team that still keeps every query of the batch resident
-     * at once (a lone query is a dependent chain of instructions: more warps shorten it; a full batch wants
-     * as many independent queries per SM as fit) */
+    /* team width and kernel: the caller's choice, else by shape (see "kernel selection" above). A lone query is a
+     * dependent chain of instructions: a second warp takes half of each expansion's distance evaluations off it, as
+     * long as every query of the batch can be resident at once; a full batch wants as many independent queries per
+     * SM as fit. */
     KernelSel sel;
     int occ = 0;
-    const int gen = h->kernel_gen;
-    if (gen == 7) {
-        sel = select_kernel(h, 7, 1, ef);
-        if (sel.smem > SEARCH_SMEM_LIMIT) return fail(h, MUNINN_CUDA_E_ARG, "ef=%d with dim=%d needs %zu B of shared memory per query (limit 200 KiB)", ef, h->dim, sel.smem);
-        CK(h, occupancy_cached(h, sel, &occ));
-    } else {
-        const int forced = h->warps_per_query;
-        bool found = false;
-        for (int W = forced ? forced : 4; W >= 1 && !found; W >>= 1) {
-            sel = select_kernel(h, 8, W, ef);
-            if (sel.smem > SEARCH_SMEM_LIMIT) {
-                if (W == 1) return fail(h, MUNINN_CUDA_E_ARG, "ef=%d with dim=%d needs %zu B of shared memory per query (limit 200 KiB)", ef, h->dim, sel.smem);
-                continue;
+    {
+        const int forced_w = h->warps_per_query, forced_gen = h->kernel_gen;
+        int W = forced_w ? forced_w : 1;
+        if (!forced_w && forced_gen != 7) { /* automatic width: 2 warps when the whole batch is resident at that width */
+            KernelSel s2 = select_kernel(h, 8, 2, ef);
+            int o2 = 0;
+            if (s2.smem <= SEARCH_SMEM_LIMIT) {
+                CK(h, occupancy_cached(h, s2, &o2));
+                if (o2 >= 1 && (long long)nq <= (long long)h->num_sms * o2) W = 2;
             }
-            CK(h, occupancy_cached(h, sel, &occ));
-            found = forced || W == 1 || (occ >= 1 && (long long)nq <= (long long)h->num_sms * occ);
-            if (forced) break;
         }
+        int gen = forced_gen;
+        if (gen == 0) gen = W > 1 ? 8 : ((h->dim == 128 && ef >= 192) ? 8 : 7);
+        if (gen == 7 && W > 1) gen = 8; /* the one-warp kernel has no wider shape */
+        sel = select_kernel(h, gen, W, ef);
+        if (sel.smem > SEARCH_SMEM_LIMIT && W > 1) { W = 1; sel = select_kernel(h, gen, W, ef); }
+        if (sel.smem > SEARCH_SMEM_LIMIT)
+            return fail(h, MUNINN_CUDA_E_ARG, "ef=%d with dim=%d needs %zu B of shared memory per query (limit 200 KiB)", ef, h->dim, sel.smem);
+        CK(h, occupancy_cached(h, sel, &occ));
     }
     if (occ < 1) return fail(h, MUNINN_CUDA_E_CUDA, "search kernel does not fit on an SM");
     const size_t smem = sel.smem;
@@ -722,11 +763,11 @@ extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *
     int teams[3];
     unsigned caps[3];
     teams[0] = (int)std::min<long long>((long long)h->num_sms * tps, nq);
-    const unsigned cap_all = pow2_at_least(2ull * (unsigned long long)(h->n + h->M0 + 1));
+    const unsigned cap_all = pow2_at_least(2ull * (unsigned long long)(h->n + h->W0 + 1));
     /* first-level table: 2·ef·2M slots. A search visits ≈ 0.8·ef·2M nodes on the bench graphs, so the table
      * runs at ≈ 40 % load at the end of a typical query and the whole arena (teams × cap × 4 B = 58 MB at
      * config 2) stays L2-resident; the rare query that would pass 3/4 load is redone at the next level. */
-    caps[0] = std::min(pow2_at_least((unsigned long long)(h->vis_factor * (double)ef * h->M0)), cap_all);
+    caps[0] = std::min(pow2_at_least((unsigned long long)(h->vis_factor * (double)ef * h->W0)), cap_all);
     caps[1] = (unsigned)std::min<unsigned long long>(16ull * caps[0], cap_all);
     caps[2] = cap_all;
     int nlevels = caps[0] == cap_all ? 1 : (caps[1] == cap_all ? 2 : 3);
@@ -751,7 +792,7 @@ extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *
     memset(&p, 0, sizeof p);
     p.vec = h->d_vec; p.norm2 = h->d_norm2; p.nbr0 = h->d_nbr0; p.upper_base = h->d_upper_base; p.nbrU = h->d_nbrU;
     p.deleted = h->d_deleted; p.ids = h->d_ids;
-    p.dim = h->dim; p.ld = h->ld; p.M = h->M; p.M0 = h->M0; p.entry_slot = h->entry_slot; p.max_level = h->max_level;
+    p.dim = h->dim; p.ld = h->ld; p.M = h->WU; p.M0 = h->W0; /* row widths: 2M / M unless a stored list is longer */ p.entry_slot = h->entry_slot; p.max_level = h->max_level;
     p.n_live = h->n_live;
     p.queries = d_queries; p.nq = nq; p.k = k; p.ef = ef;
     p.patience_max = std::max(ef / 4, 10); /* src/hnsw_algo.c:372-374 */
@@ -774,7 +815,7 @@ extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *
     }
     CK(h, cudaEventRecord(h->ev1, h->stream));
     h->have_timing = true;
-    h->last_W = sel.W;
+    h->last_W = sel.W; h->last_gen = sel.gen;
     return MUNINN_CUDA_OK;
 }
 
@@ -962,9 +1003,27 @@ static cudaError_t launch_filter(MuninnCudaIndex *h, const CUtensorMap maps[4], 
     return cudaGetLastError();
 }
 
+/* query-stationary form: one TF32 product, query tile resident in shared memory, row tiles in L2-sized super-blocks */
+template <int METRIC>
+static cudaError_t launch_filter_qs(MuninnCudaIndex *h, const CUtensorMap &map_q, const CUtensorMap &map_x, const tc::FilterParams &fp,
+                                    int row_stride_floats) {
+    constexpr int BN = 256;
+    auto kern = tc::exact_tc_filter_qs<METRIC, BN>;
+    const size_t smem = tc::qs_smem_bytes(fp.kblocks, BN);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    const long long tiles = (long long)((fp.nq + tc::BM - 1) / tc::BM) * ((fp.rows + BN - 1) / BN);
+    const int grid = (int)std::min<long long>(tiles, h->num_sms);
+    const int SB = (int)std::max<long long>(1, ((long long)h->tc_superblock_mb << 20) / ((long long)BN * row_stride_floats * 4));
+    kern<<<grid, tc::QS_THREADS, smem, h->stream>>>(map_q, map_x, fp, SB);
+    return cudaGetLastError();
+}
+
 template <int METRIC>
 static cudaError_t launch_filter_m(MuninnCudaIndex *h, const CUtensorMap maps[4], const tc::FilterParams &fp) {
     const bool three = h->exact_mode_run == MUNINN_EXACT_TC_3XTF32;
+    if (!three && !fp.dbg_panel && h->tc_tile_rows == 256 && h->tc_qs && fp.nq >= h->tc_qs_min_nq && fp.kblocks <= tc::QS_MAX_KBLOCKS)
+        return launch_filter_qs<METRIC>(h, maps[0], maps[2], fp, h->tc_x_stride);
     if (fp.dbg_panel) return three ? launch_filter<METRIC, 3, 256, true>(h, maps, fp) : launch_filter<METRIC, 1, 256, true>(h, maps, fp);
     if (h->tc_tile_rows == 128)
         return three ? launch_filter<METRIC, 3, 128>(h, maps, fp) : launch_filter<METRIC, 1, 128>(h, maps, fp);
@@ -976,9 +1035,11 @@ static cudaError_t launch_filter_m(MuninnCudaIndex *h, const CUtensorMap maps[4]
 static int exact_knn_tc(MuninnCudaIndex *h, const float *d_queries, int nq, int k, int64_t index_base, int64_t *d_idx,
                         float *d_dist, int32_t *d_count, float *d_dbg, long long dbg_rows) {
     const int kp = (h->dim + tc::BK - 1) / tc::BK * tc::BK, bn = h->tc_tile_rows;
-    /* AUTO: large batches are tensor-bound → 3xTF32 (tight margin, split slabs); small batches are
-     * HBM-bound → one TF32 product straight off the fp32 slab (no split pass: the base is read once) */
-    h->exact_mode_run = h->exact_mode == MUNINN_EXACT_TC_AUTO ? (nq >= 1024 || d_dbg ? MUNINN_EXACT_TC_3XTF32 : MUNINN_EXACT_TC_1XTF32)
+    /* AUTO: one TF32 product straight off the fp32 slab for every batch size (no split pass: the base is read once).
+     * Small batches are HBM-bound and stream the rows once; large ones run the query-stationary filter, which at
+     * one product per pair needs a third of the tensor work of 3xTF32 and returns the same survivors (measured
+     * 1 133 vs 1 124 per query at 1M×128, k=10): the wider margin of the single product costs next to nothing. */
+    h->exact_mode_run = h->exact_mode == MUNINN_EXACT_TC_AUTO ? (nq >= h->tc_auto_1x_min_nq || d_dbg ? MUNINN_EXACT_TC_3XTF32 : MUNINN_EXACT_TC_1XTF32)
                                                               : h->exact_mode;
     const bool three = h->exact_mode_run == MUNINN_EXACT_TC_3XTF32;
     const bool raw_x = !three; /* 1xTF32: the MMA reads the fp32 rows as they are (it drops the low 13 bits) */
@@ -1056,6 +1117,7 @@ static int exact_knn_tc(MuninnCudaIndex *h, const float *d_queries, int nq, int 
         long long chunk = done == 0 ? std::min<long long>(small ? cap / 2 : std::min(cap, std::max(256, (2 * k + 255) / 256 * 256)), n)
                                     : std::min<long long>(std::min((long long)grow_c * done, chunk_max), n - done); /* ×(1+grow_c) per round */
         if (d_dbg) chunk = n;
+        h->tc_x_stride = raw_x ? h->ld : kp;
         if (raw_x) {
             rc = make_slab_map(h, &maps[2], h->d_vec + (size_t)done * h->ld, h->ld, chunk, bn);
             maps[3] = maps[2];

@@ -31,7 +31,7 @@ ABI_SYMBOLS = (
     "muninn_cuda_exact_knn_device", "muninn_cuda_topk_merge_device", "muninn_cuda_distance_batch",
     "muninn_cuda_set_exact_mode", "muninn_cuda_exact_stats", "muninn_cuda_exact_filter_probe",
     "muninn_cuda_gather_ceiling", "muninn_cuda_index_patch", "muninn_cuda_build_device",
-    "muninn_cuda_last_team_width", "muninn_cuda_set_option", "muninn_cuda_exact_knn_sharded_device",
+    "muninn_cuda_last_team_width", "muninn_cuda_last_kernel_gen", "muninn_cuda_set_option", "muninn_cuda_exact_knn_sharded_device",
     "muninn_cuda_comm_unique_id", "muninn_cuda_comm_create", "muninn_cuda_comm_destroy",
     "muninn_cuda_topk_pack_keys_device", "muninn_cuda_topk_merge_keys_device", "muninn_cuda_index_upload_rows",
 )
@@ -96,6 +96,7 @@ def lib():
         L.muninn_cuda_gather_ceiling.argtypes = [C.c_int, C.c_int, C.c_int64, C.POINTER(C.c_float)]
         L.muninn_cuda_build_device.argtypes = [_vp, _vp]
         L.muninn_cuda_last_team_width.argtypes = [_vp]
+        L.muninn_cuda_last_kernel_gen.argtypes = [_vp]
         L.muninn_cuda_set_option.argtypes = [_vp, C.c_char_p, C.c_double]
         L.muninn_cuda_index_upload_rows.argtypes = [_vp, C.c_int64, _vp]
         L.muninn_cuda_exact_knn_sharded_device.argtypes = [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int64, _vp, _vp, _vp]
@@ -343,6 +344,9 @@ class HnswIndexCuda:
 
     def last_team_width(self) -> int:
         return int(self.L.muninn_cuda_last_team_width(self.h))
+
+    def last_kernel_gen(self) -> int:
+        return int(self.L.muninn_cuda_last_kernel_gen(self.h))
 
     def last_kernel_ms(self) -> float:
         return float(self.L.muninn_cuda_last_kernel_ms(self.h))

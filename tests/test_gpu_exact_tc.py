@@ -59,12 +59,41 @@ def test_tensor_modes_equal_oracle(cuda, oracle, metric, dim, n, nq, k):
             assert np.array_equal(c_g, c_o), (mode, tile)
             assert d_g.tobytes() == d_o.tobytes(), (mode, tile)
             assert np.array_equal(i_g, np.where(i_o >= 0, i_o + 7, -1)), (mode, tile)
-            # AUTO resolves by batch size: tensor-bound batches → 3xTF32, HBM-bound ones → 1xTF32 off the raw slab
-            want_mode = mode if mode != cuda.EXACT_TC_AUTO else (cuda.EXACT_TC_3XTF32 if nq >= 1024 else cuda.EXACT_TC_1XTF32)
+            # AUTO = one TF32 product off the raw slab at every batch size (query-stationary filter from 1024 queries)
+            want_mode = mode if mode != cuda.EXACT_TC_AUTO else cuda.EXACT_TC_1XTF32
             assert st["mode"] == want_mode
             if mode != cuda.EXACT_CUDA_CORE:
-                assert st["chunks"] >= 1 and st["candidates"] >= min(n, 1024) * nq * 0  # counters are live
+                # counters are live: every query re-ranks at least its own top-k (deleted rows pass the filter too)
+                assert st["chunks"] >= 1 and st["candidates"] >= nq * min(k, int((deleted == 0).sum()))
                 assert st["filter_ms"] > 0.0
+
+
+QS_CASES = [  # metric, dim, n, nq, k, super-block MB: the query-stationary filter (nq >= 1024, one TF32 product)
+    (L2, 128, 40000, 2500, 10, 1), (L2, 128, 9000, 1024, 100, 32), (IP, 96, 30000, 1300, 10, 1), (COS, 131, 12000, 1100, 10, 2),
+    (L2, 256, 8000, 1200, 5, 1), (L2, 300, 6000, 1100, 10, 1), (L2, 16, 70000, 4000, 10, 1), (COS, 768, 3000, 1030, 10, 32)]
+
+
+@pytest.mark.parametrize("metric,dim,n,nq,k,sb_mb", QS_CASES)
+def test_query_stationary_filter_equals_oracle(cuda, oracle, metric, dim, n, nq, k, sb_mb):
+    """Large batches: query tile resident in shared memory, row tiles swept in super-blocks (forced small here so that a
+    launch crosses many of them), CTAs switching query tiles mid-run; dims with 1..8 k-blocks (beyond 8 the streaming
+    kernel takes over). Bit-exact against the oracle, and identical to the streaming filter's survivors' result."""
+    base = latent(n + dim, n, dim)
+    q = latent(n + dim, nq + n, dim)[n:]
+    if metric == IP:
+        base /= np.linalg.norm(base, axis=1, keepdims=True)
+    deleted = np.zeros(n, np.uint8)
+    deleted[::29] = 1
+    i_o, d_o, c_o, _ = oracle.exact_knn(base, q, k, metric, deleted=deleted, threads=8)
+    with cuda.HnswIndexCuda.from_graph(flat(base, metric, deleted)) as idx:
+        idx.set_option("exact_superblock_mb", sb_mb)
+        for qs in (1, 0):
+            idx.set_option("exact_qs", qs)
+            idx.set_exact_mode(cuda.EXACT_TC_AUTO, 0)
+            i_g, d_g, c_g = idx.exact_knn(q, k)
+            st = idx.exact_stats()
+            assert st["mode"] == cuda.EXACT_TC_1XTF32 and st["overflow_queries"] == 0
+            assert np.array_equal(c_g, c_o) and d_g.tobytes() == d_o.tobytes() and np.array_equal(i_g, i_o), qs
 
 
 def test_filter_prunes(cuda, oracle):
@@ -151,3 +180,67 @@ def test_filter_error_is_inside_the_margin(cuda, metric, dim, mode):
     ratio = float((err / eps).max())
     print(f"metric={metric} dim={dim} mode={mode}: max |err|/eps = {ratio:.4f} (c_eps={c_eps:.3e})")
     assert ratio < (0.1 if mode == 1 else 0.5)
+
+
+def _margin_ratio(cuda, base, q, metric, mode):
+    n = base.shape[0]
+    with cuda.HnswIndexCuda.from_graph(flat(base, metric)) as idx:
+        idx.set_exact_mode(mode, 256)
+        s_tc = idx.exact_filter_probe(q, n).astype(np.float64)
+        c_eps = idx.exact_stats()["c_eps"]
+    b64, q64 = base.astype(np.float64), q.astype(np.float64)
+    dot = q64 @ b64.T
+    qn, xn = (q64 * q64).sum(1)[:, None], (b64 * b64).sum(1)[None, :]
+    if metric == COS:
+        return float((np.abs(s_tc - dot) / np.sqrt(qn * xn) / c_eps).max())
+    return float(((2 if metric == L2 else 1) * np.abs(s_tc - dot) / (c_eps * (qn + xn))).max())
+
+
+@pytest.mark.parametrize("metric", [L2, IP, COS])
+@pytest.mark.parametrize("mode", [1, 2])
+@pytest.mark.parametrize("kind", ["low_bits_set", "mixed_magnitudes", "cancellation"])
+def test_filter_margin_adversarial(cuda, metric, mode, kind):
+    """Inputs built against the margin (DESIGN.md §5.2 derives it): (a) every one of the 13 mantissa bits the TF32
+    input path drops is SET, all signs equal and |q_i| = |x_i|, so that every truncation error has the same sign and
+    the AM-GM step of the bound is tight — the worst case of the single product, where |err|/eps approaches but must
+    stay below 1/2; (b) magnitudes from 1e-3 to 1e3 inside one vector; (c) q·x cancelling to ~0 with large terms."""
+    dim, n, nq = 128, 1024, 64
+    rng = np.random.default_rng(42)
+    if kind == "low_bits_set":
+        m = rng.uniform(1.0, 1.002, (n + nq, dim)).astype(np.float32)  # mantissa just above 1.0: the dropped bits weigh most
+        v = (m.view(np.uint32) | np.uint32(0x1FFF)).view(np.float32)
+        base, q = v[:n].copy(), v[n:].copy()
+        q[:] = base[:nq]  # |q_i| = |x_i| for the matching pairs
+    elif kind == "mixed_magnitudes":
+        e = rng.integers(-10, 11, (n + nq, dim))
+        v = (rng.uniform(1, 2, (n + nq, dim)) * (2.0 ** e) * rng.choice([-1, 1], (n + nq, dim))).astype(np.float32)
+        v = (v.view(np.uint32) | np.uint32(0x1FFF)).view(np.float32)
+        base, q = v[:n].copy(), v[n:].copy()
+    else:
+        a = rng.uniform(50, 100, (n + nq, dim)).astype(np.float32)
+        a[:, 1::2] = -a[:, 0::2]  # pairs (+a, -a) against a same-sign partner → Σ q·x ≈ 0 out of terms of 1e4
+        base = np.abs(a[:n]) * np.float32(1.0)
+        q = a[n:]
+        base = (base.view(np.uint32) | np.uint32(0x1FFF)).view(np.float32)
+        q = (q.view(np.uint32) | np.uint32(0x1FFF)).view(np.float32)
+    ratio = _margin_ratio(cuda, base, q, metric, mode)
+    print(f"{kind} metric={metric} mode={mode}: max |err|/eps = {ratio:.4f}")
+    assert ratio < (0.2 if mode == 1 else 0.55)
+
+
+@pytest.mark.parametrize("metric", [L2, IP, COS])
+def test_single_product_stays_exact_on_adversarial_rows(cuda, oracle, metric):
+    """End to end on the worst-case rows above (all dropped bits set, near-duplicates a few ulps apart so that the
+    filter's margin decides which rows reach the exact re-rank): ids and distances still bit-exact."""
+    dim, n, nq, k = 128, 20000, 200, 10
+    rng = np.random.default_rng(7)
+    centers = rng.uniform(1.0, 1.002, (50, dim)).astype(np.float32)
+    base = centers[rng.integers(0, 50, n)] + rng.uniform(0, 3e-4, (n, dim)).astype(np.float32)
+    base = (base.view(np.uint32) | np.uint32(0x1FFF)).view(np.float32)
+    q = (centers[rng.integers(0, 50, nq)].view(np.uint32) | np.uint32(0x1FFF)).view(np.float32)
+    i_o, d_o, c_o, _ = oracle.exact_knn(base, q, k, metric, threads=8)
+    with cuda.HnswIndexCuda.from_graph(flat(base, metric)) as idx:
+        for mode in (cuda.EXACT_TC_1XTF32, cuda.EXACT_TC_3XTF32):
+            idx.set_exact_mode(mode, 256)
+            i_g, d_g, c_g = idx.exact_knn(q, k)
+            assert np.array_equal(c_g, c_o) and d_g.tobytes() == d_o.tobytes() and np.array_equal(i_g, i_o), mode

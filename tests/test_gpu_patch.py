@@ -112,3 +112,47 @@ def test_rejected_patch_leaves_the_handle_untouched(reference):
         with HnswIndexCuda.from_graph(g2) as fresh:
             a, b = idx.search(q, 10, 50), fresh.search(q, 10, 50)
             assert all(np.array_equal(x, y) for x, y in zip(a, b))
+
+
+def test_lists_longer_than_capacity_after_heavy_deletion(reference, oracle):
+    """600x8, M=4, ~425 random deletes through the unmodified hnsw_delete leave live nodes with more than M
+    upper-layer (or 2M layer-0) neighbours. Upload must take the graph as the reference holds it (row width = longest
+    list), a patch that would outgrow the device rows must be refused cleanly (the glue then re-uploads), and search
+    must equal the oracle on that graph — ids, distances, counters."""
+    from sqlite_muninn_b200.cuda import HnswIndexCuda, MuninnCudaError
+    n, dim, M = 600, 8, 4
+    base, q = uniform(51, n, dim), uniform(52, 100, dim)
+    ref = reference.build(base, ids=np.arange(n, dtype=np.int64) + 1, metric=0, M=M, efc=40)
+    g0 = ref.export()
+    dev = HnswIndexCuda.from_graph(g0)
+    over, refused = False, 0
+    for step, i in enumerate(np.random.default_rng(3).permutation(n)[:450]):
+        g_prev = ref.export() if step % 50 == 0 else None
+        assert ref.delete(int(i) + 1) == 0
+        if g_prev is None:
+            continue
+        g = ref.export()
+        first = g.first_list()
+        lens0 = np.diff(g.list_offsets)[first[:-1]]
+        lens_all = np.diff(g.list_offsets)
+        upper = np.ones(len(lens_all), bool)
+        upper[first[:-1]] = False
+        over = over or bool(lens0.max() > 2 * M or (upper.any() and lens_all[upper].max() > M))
+        try:
+            dev.patch(g, changed_slots(g_prev, g))
+        except MuninnCudaError as e:  # outgrew the device rows: a clean refusal, then the fallback the glue takes
+            assert "upload again" in str(e)
+            refused += 1
+            dev.upload(g)
+        with HnswIndexCuda.from_graph(g) as fresh:
+            for k, ef in ((10, 40), (5, 5)):
+                a, b = dev.search(q, k, ef, want_stats=True), fresh.search(q, k, ef, want_stats=True)
+                o = oracle.graph(g).search(q, k, ef, canonical=True)
+                for x, y, z in zip(a[:3], b[:3], o[:3]):
+                    assert np.array_equal(x, y) and np.array_equal(x, z), (step, k, ef)
+                assert np.array_equal(a[3]["n_dist"], o[3]["n_dist"])
+            r_ids, r_dist, r_cnt, _ = ref.search(q, 10, 40)
+            a = dev.search(q, 10, 40)
+            assert_results_match(a[0], a[1], a[2], r_ids, r_dist, r_cnt, f"vs reference after {step + 1} deletes")
+    assert over, "the reference never went past its nominal list capacity: the test exercised nothing new"
+    dev.close()

@@ -113,6 +113,42 @@ def test_vtab_equals_unmodified_reference_in_every_state(exts, tmp_path):
         c.close()
 
 
+def test_vtab_heavy_deletion_keeps_answering(exts, tmp_path):
+    """Delete ~75 % of a small-M table: hnsw_delete's reconnection step (src/hnsw_algo.c:780-781) appends to
+    neighbour lists without a capacity check, so the reference ends up holding lists longer than 2M / M — and keeps
+    answering from them. The device tables are sized from the longest stored list, a patch that outgrows them falls
+    back to an upload, and every MATCH keeps returning what the unmodified extension returns."""
+    if exts[1] is None:
+        pytest.skip("reference extension not built")
+    n, dim = 600, 8
+    base, q = uniform(41, n, dim), uniform(42, 25, dim)
+    conns = [connect(str(tmp_path / f"hd{i}.db"), e) for i, e in enumerate(exts)]
+    for c in conns:
+        c.execute(f"CREATE VIRTUAL TABLE t USING hnsw_index(dimensions={dim}, metric='l2', m=4, ef_construction=40)")
+        for i, v in enumerate(base):
+            c.execute("INSERT INTO t (rowid, vector) VALUES (?, ?)", (i + 1, v.tobytes()))
+    order = np.random.default_rng(5).permutation(n)[: int(0.75 * n)]
+    for step, i in enumerate(order):
+        for c in conns:
+            c.execute("DELETE FROM t WHERE rowid = ?", (int(i) + 1,))
+        if step % 15 == 0 or step == len(order) - 1:  # searches interleaved with the deletes: patches, then uploads
+            for qi in range(len(q)):
+                for k, ef in ((5, None), (10, 40)):
+                    a, b = knn(conns[0], q[qi], k, ef), knn(conns[1], q[qi], k, ef)
+                    assert same_rows(a, b), (step, qi, k, ef)
+    # the stored graph really went past its nominal capacity (else this test checks nothing new)
+    rows = conns[1].execute("SELECT source_id, level, COUNT(*) FROM t_edges GROUP BY source_id, level").fetchall()
+    assert max(r[2] for r in rows if r[1] > 0) > 4 or max(r[2] for r in rows if r[1] == 0) > 8
+    for c in conns:
+        c.commit()
+        c.close()
+    conns = [connect(str(tmp_path / f"hd{i}.db"), e) for i, e in enumerate(exts)]
+    for qi in range(len(q)):  # reopened: load_index_from_shadow → upload of the over-full lists
+        assert same_rows(knn(conns[0], q[qi], 10, 40), knn(conns[1], q[qi], 10, 40)), qi
+    for c in conns:
+        c.close()
+
+
 def test_vtab_interleaved_writes_use_incremental_patches(exts, tmp_path):
     """INSERT / DELETE between searches: the glue sends muninn_cuda_index_patch records for the touched
     nodes (src/hnsw_algo.c:hnsw_insert / hnsw_delete) instead of re-uploading, falls back to one full
