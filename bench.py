@@ -250,8 +250,10 @@ def workload_config(c, ef, recall, job_q: int):
             "job": f"{job_q} queries ({job_q // c.nq} x the {c.nq}-query batch) per step, split evenly across the GPUs",
             "ef": ef, "ef_sweep": list(c.ef_sweep), "recall_at_10": recall,
             "data_distribution": f"{DATA_TEXT[c.data]}, seeds {c.seeds[0]}/{c.seeds[1]}+batch",
-            "graph": f"reference construction rule, batch-synchronous inserts (groups of {c.build_batch}), "
-                     "neighbour lists in shadow-table order",
+            "graph": (f"reference construction rule, batch-synchronous inserts (groups of {c.build_batch}), "
+                      "neighbour lists in shadow-table order" if c.build_batch > 0 else
+                      "the graph the reference builds: one hnsw_insert at a time in row order (builder exact mode, bit-identical "
+                      "to the unmodified reference's graph: tests/test_host.py), neighbour lists in shadow-table order"),
             "l2_policy": f"inputs ({slab_mb:.0f} MB slab + {list_mb:.0f} MB lists) exceed the 126 MB L2; no flush between steps",
             "parallelism": "graph replicated, one job split by query across the GPUs, no data-path collective"}
 

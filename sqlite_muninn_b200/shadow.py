@@ -162,3 +162,73 @@ def register_vtab(conn: sqlite3.Connection, name: str, g: FlatGraph) -> None:
     conn.execute("PRAGMA writable_schema=OFF")
     conn.commit()
 
+
+
+# ───────────────────────── host C reader / writer (libmuninn_host: csrc/shadow_io.c) ─────────────────────────
+# The product's bulk I/O (include/muninn_shadow.h): the Python functions above are the readable statement of the same
+# format and the cross-check of the tests; tools and bench.py go through these.
+
+import ctypes as _C
+
+
+class _ShadowGraph(_C.Structure):
+    """MuninnShadowGraph (include/muninn_shadow.h)."""
+    _fields_ = [("dim", _C.c_int32), ("metric", _C.c_int32), ("M", _C.c_int32), ("ef_construction", _C.c_int32),
+                ("n", _C.c_int64), ("n_lists", _C.c_int64), ("n_edges", _C.c_int64),
+                ("ids", _C.POINTER(_C.c_int64)), ("levels", _C.POINTER(_C.c_int32)), ("deleted", _C.POINTER(_C.c_uint8)),
+                ("vectors", _C.POINTER(_C.c_float)), ("list_offsets", _C.POINTER(_C.c_int64)),
+                ("targets", _C.POINTER(_C.c_int32)), ("entry_slot", _C.c_int32), ("max_level", _C.c_int32)]
+
+
+def _host():
+    from .builder import host_lib
+    L = host_lib()
+    if not getattr(L, "_shadow_bound", False):
+        L.muninn_shadow_load_path.argtypes = [_C.c_char_p, _C.c_char_p, _C.POINTER(_ShadowGraph), _C.POINTER(_C.c_char_p)]
+        L.muninn_shadow_write_path.argtypes = [_C.c_char_p, _C.c_char_p, _C.POINTER(_ShadowGraph), _C.c_int, _C.POINTER(_C.c_char_p)]
+        L.muninn_shadow_free.argtypes = [_C.POINTER(_ShadowGraph)]
+        L.muninn_shadow_free_message.argtypes = [_C.c_char_p]
+        L._shadow_bound = True
+    return L
+
+
+def _raise(L, rc, err):
+    msg = err.value.decode() if err.value else f"muninn_shadow error {rc}"
+    raise RuntimeError(msg)
+
+
+def load_from_shadow_c(db_path: str, name: str) -> FlatGraph:
+    """muninn_shadow_load_path: the stored index as a FlatGraph (arrays copied out of the C allocation)."""
+    L = _host()
+    sg, err = _ShadowGraph(), _C.c_char_p()
+    rc = L.muninn_shadow_load_path(db_path.encode(), name.encode(), _C.byref(sg), _C.byref(err))
+    if rc != 0:
+        _raise(L, rc, err)
+    try:
+        n, nl, ne, dim = int(sg.n), int(sg.n_lists), int(sg.n_edges), int(sg.dim)
+        arr = lambda p, cnt, dt: np.ctypeslib.as_array(p, shape=(max(cnt, 1),))[:cnt].astype(dt, copy=True)
+        g = FlatGraph(dim, int(sg.metric), int(sg.M), int(sg.ef_construction), arr(sg.ids, n, np.int64),
+                      arr(sg.levels, n, np.int32), arr(sg.deleted, n, np.uint8),
+                      arr(sg.vectors, n * dim, np.float32).reshape(n, dim), arr(sg.list_offsets, nl + 1, np.int64),
+                      arr(sg.targets, ne, np.int32), int(sg.entry_slot), int(sg.max_level))
+    finally:
+        L.muninn_shadow_free(_C.byref(sg))
+    return g
+
+
+def write_shadow_c(db_path: str, name: str, g: FlatGraph, register: bool = False) -> None:
+    """muninn_shadow_write_path: one transaction, primary-key order; register=True also stores the
+    `CREATE VIRTUAL TABLE … USING hnsw_index(…)` schema row so the unmodified extension xConnects to it."""
+    g.validate()
+    L = _host()
+    ids = np.ascontiguousarray(g.ids, np.int64); levels = np.ascontiguousarray(g.levels, np.int32)
+    deleted = np.ascontiguousarray(g.deleted, np.uint8); vec = np.ascontiguousarray(g.vectors, np.float32)
+    offs = np.ascontiguousarray(g.list_offsets, np.int64); tg = np.ascontiguousarray(g.targets, np.int32)
+    p = lambda a, t: a.ctypes.data_as(_C.POINTER(t))
+    sg = _ShadowGraph(g.dim, g.metric, g.M, g.ef_construction, g.n, len(offs) - 1, len(tg), p(ids, _C.c_int64),
+                      p(levels, _C.c_int32), p(deleted, _C.c_uint8), p(vec, _C.c_float), p(offs, _C.c_int64),
+                      p(tg, _C.c_int32), g.entry_slot, g.max_level)
+    err = _C.c_char_p()
+    rc = L.muninn_shadow_write_path(db_path.encode(), name.encode(), _C.byref(sg), 1 if register else 0, _C.byref(err))
+    if rc != 0:
+        _raise(L, rc, err)

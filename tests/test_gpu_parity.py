@@ -185,6 +185,36 @@ def test_full_size_properties(cuda, oracle, team):
         assert np.array_equal(st["n_dist"][:200], o[3]["n_dist"])
 
 
+@pytest.mark.parametrize("cfg", [3, 4])
+@pytest.mark.parametrize("kernel", ["auto", "8-w1", "8-w2"])
+def test_bench_shapes_at_size_equal_oracle(cuda, oracle, cfg, kernel, monkeypatch):
+    """BASELINE configs 3 and 4 as bench.py runs them — text-embedding shape (768-d cosine, M=32, spectrum data) and
+    Deep10M shape (96-d inner product, M=32, normalised latent data) — at 100k / 200k nodes, batch-mode graph like the
+    benchmark's: ids, distances AND all work counters of a 500-query sample equal the oracle's, at the ef values the
+    bench times; the rest of a 3 000-query batch is checked for sortedness and idempotence."""
+    import bench
+    from sqlite_muninn_b200.builder import build_graph
+    c = bench.cfg_of(cfg)
+    n = 100_000 if cfg == 3 else 200_000
+    base = bench.make_vectors(n, c.dim, c.seeds[0], kind=c.data)
+    q = bench.make_vectors(3000, c.dim, c.seeds[1], kind=c.data)
+    g = build_graph(base, c.metric, c.M, 48, batch=1024, warm=4096)
+    gen, w = {"auto": ("0", "0"), "8-w1": ("8", "1"), "8-w2": ("8", "2")}[kernel]
+    monkeypatch.setenv("MUNINN_KERNEL", gen)
+    monkeypatch.setenv("MUNINN_WARPS", w)
+    og = oracle.graph(g)
+    with cuda.HnswIndexCuda.from_graph(g) as idx:
+        for ef in ((128, 384) if cfg == 3 else (64, 256)):
+            ids, dist, cnt, st = idx.search(q, 10, ef, want_stats=True)
+            o_ids, o_dist, o_cnt, o_st, _ = og.search(q[:500], 10, ef, threads=8, canonical=True)
+            assert np.array_equal(ids[:500], o_ids) and np.array_equal(dist[:500], o_dist) and np.array_equal(cnt[:500], o_cnt), ef
+            for f in ("n_dist", "n_dist_upper", "n_expand", "n_greedy_steps", "entry0"):
+                assert np.array_equal(st[f][:500], o_st[f]), (f, ef)
+            assert (cnt == 10).all() and (np.diff(dist, axis=1) >= 0).all()
+            ids2, dist2, _ = idx.search(q, 10, ef)
+            assert np.array_equal(ids, ids2) and np.array_equal(dist, dist2)
+
+
 # ── exact k-NN: bit-exact ids and distances, ties to the lower index ──
 @pytest.mark.parametrize("metric,dim,n,k", [(L2, 128, 5000, 100), (COS, 24, 3000, 10), (IP, 10, 2000, 7), (L2, 3, 300, 300),
                                             (L2, 6, 4000, 50)])

@@ -102,7 +102,7 @@ def test_rejected_patch_leaves_the_handle_untouched(reference):
         bad.targets = np.concatenate([bad.targets, np.zeros(9, np.int32)])
         bad.list_offsets = bad.list_offsets.copy()
         bad.list_offsets[-1] += 9
-        with pytest.raises(MuninnCudaError, match="capacity"):
+        with pytest.raises(MuninnCudaError, match="device rows hold"):
             idx.patch_unchecked(bad, touched)
         after = idx.search(q, 10, 50, want_stats=True)
         for x, y in zip(before[:3], after[:3]):

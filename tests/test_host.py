@@ -30,6 +30,27 @@ def test_builder_exact_mode_equals_reference(reference, metric, M, dim, n, efc):
     assert build_graph(base, metric, M, efc, sort_lists=True).same_structure(ri.export())
 
 
+def test_builder_exact_mode_equals_reference_at_50k():
+    """the exact mode of csrc/hnsw_build.c against the UNMODIFIED reference's hnsw_insert at 50 000 x 128,
+    M=16, ef_construction=200 (bench.py's config-2 distribution). The reference build takes five minutes, so its graph
+    is pinned as a digest (entry point, max level, every level, every neighbour list in insertion order and in
+    shadow-table order) by tests/golden/make_build_fixture.py; this test rebuilds with the product's builder."""
+    import json
+    import bench
+    sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+    from make_build_fixture import graph_digest
+    fx = json.load(open(os.path.join(ROOT, "tests", "golden", "build_50kx128_M16_efc200.json")))
+    base = bench.make_vectors(fx["n"], fx["dim"], 11)
+    g = build_graph(base, 0, fx["M"], fx["ef_construction"], sort_lists=False)
+    assert (g.entry_slot, g.max_level, int(g.targets.shape[0])) == (fx["entry_slot"], fx["max_level"], fx["n_edges"])
+    assert np.bincount(g.levels).tolist() == fx["level_histogram"]
+    for s_, lst in fx["level0_lists_insertion_order"].items():
+        assert [int(t) for t in g.neighbours(int(s_), 0)] == lst, s_
+    assert graph_digest(g) == fx["digest_insertion_order"]
+    gs = build_graph(base, 0, fx["M"], fx["ef_construction"], sort_lists=True)
+    assert graph_digest(gs) == fx["digest_sorted_lists"]
+
+
 def test_builder_batch_mode_is_deterministic_and_searchable(oracle):
     base = uniform(11, 6000, 32)
     g1 = build_graph(base, 0, 8, 40, batch=256, warm=512, threads=4)
@@ -49,6 +70,64 @@ def test_shadow_roundtrip(tmp_path):
     g2 = load_from_shadow(conn, "t")
     assert g.same_structure(g2) and np.array_equal(g.vectors, g2.vectors) and np.array_equal(g.deleted, g2.deleted)
     assert (g2.dim, g2.metric, g2.M, g2.ef_construction) == (g.dim, g.metric, g.M, g.ef_construction)
+
+
+def test_shadow_host_c_reader_and_writer(tmp_path, reference):
+    """csrc/shadow_io.c (libmuninn_host, against the SQLite C API): (1) it reads what the Python statement of the
+    format writes and vice versa — same graph, same bytes; (2) it reads what the UNMODIFIED reference persisted through
+    its own INSERT / DELETE statements exactly as the reference reloads it; (3) the unmodified extension opens, queries
+    and extends a table the C writer stored and registered."""
+    from oracle.bindings import REF_EXT_SO
+    from sqlite_muninn_b200.shadow import load_from_shadow_c, write_shadow_c
+    g, _, _, _ = load_golden("vtab_l2_delete_200x8")  # deleted rows, dangling-free lists
+    # (1) C writer → Python reader, Python writer → C reader
+    pa, pb = str(tmp_path / "a.db"), str(tmp_path / "b.db")
+    write_shadow_c(pa, "t", g)
+    ga = load_from_shadow(sqlite3.connect(pa), "t")
+    conn = sqlite3.connect(pb)
+    write_shadow(conn, "t", g)
+    conn.close()
+    gb = load_from_shadow_c(pb, "t")
+    for x in (ga, gb):
+        assert g.same_structure(x) and np.array_equal(g.vectors, x.vectors) and np.array_equal(g.deleted, x.deleted)
+        assert np.array_equal(g.ids, x.ids) and (x.dim, x.metric, x.M, x.ef_construction) == (g.dim, g.metric, g.M, g.ef_construction)
+    rows = lambda p, tbl, by: sqlite3.connect(p).execute(f"SELECT * FROM {tbl} ORDER BY {by}").fetchall()
+    for tbl, by in (("t_config", "1"), ("t_nodes", "1"), ("t_edges", "1, 3, 2")):
+        assert rows(pa, tbl, by) == rows(pb, tbl, by), tbl
+    if not os.path.exists(REF_EXT_SO):
+        pytest.skip("reference extension not built")
+    # (2) what the reference itself persisted (INSERTs + DELETEs through its vtab), read back by the C loader
+    pc = str(tmp_path / "c.db")
+    conn = sqlite3.connect(pc)
+    conn.enable_load_extension(True)
+    conn.load_extension(REF_EXT_SO, entrypoint="sqlite3_muninn_init")
+    conn.execute("CREATE VIRTUAL TABLE t USING hnsw_index(dimensions=12, metric='cosine', m=6, ef_construction=40)")
+    base = uniform(61, 300, 12)
+    for i, v in enumerate(base):
+        conn.execute("INSERT INTO t (rowid, vector) VALUES (?, ?)", (3 * i + 2, v.tobytes()))
+    for i in range(0, 300, 9):
+        conn.execute("DELETE FROM t WHERE rowid = ?", (3 * i + 2,))
+    conn.commit()
+    gp = load_from_shadow(conn, "t")
+    conn.close()
+    gc = load_from_shadow_c(pc, "t")
+    assert gp.same_structure(gc) and np.array_equal(gp.vectors, gc.vectors) and np.array_equal(gp.deleted, gc.deleted)
+    assert np.array_equal(gp.ids, gc.ids) and gc.deleted.sum() == len(range(0, 300, 9))
+    # (3) the unmodified extension on a table the C writer stored and registered
+    pd = str(tmp_path / "d.db")
+    gb2 = build_graph(uniform(62, 400, 12), 0, 6, 40, ids=np.arange(400, dtype=np.int64) * 2 + 1)
+    write_shadow_c(pd, "v", gb2, register=True)
+    conn = sqlite3.connect(pd)
+    conn.enable_load_extension(True)
+    conn.load_extension(REF_EXT_SO, entrypoint="sqlite3_muninn_init")
+    q = uniform(63, 12, 12)
+    got = [conn.execute("SELECT rowid FROM v WHERE vector MATCH ? AND k = 5 AND ef_search = 40", (x.tobytes(),)).fetchall() for x in q]
+    from oracle.bindings import Oracle
+    o_ids, _, o_cnt, _, _ = Oracle().graph(gb2).search(q, 5, 40)
+    assert [[r[0] for r in rows_] for rows_ in got] == [list(o_ids[i, :o_cnt[i]]) for i in range(len(q))]
+    conn.execute("INSERT INTO v (rowid, vector) VALUES (?, ?)", (100001, q[0].tobytes()))  # the reference extends it
+    assert conn.execute("SELECT rowid FROM v WHERE vector MATCH ? AND k = 1", (q[0].tobytes(),)).fetchall() == [(100001,)]
+    conn.close()
 
 
 def test_reference_vtab_opens_our_shadow_tables(tmp_path, oracle):

@@ -49,7 +49,7 @@ def main():
             gen, W, vf, tps = s.split(":")
             idx.set_option("kernel_gen", int(gen))
             idx.set_option("vis_factor", float(vf))
-            idx.set_tuning(int(W) if int(gen) == 8 else 1, int(tps))
+            idx.set_tuning(1 if int(gen) == 7 else int(W), int(tps))
             for ef in (int(x) for x in a.ef.split(",")):
                 for nq in (int(x) for x in a.nq.split(",")):
                     q = queries[:nq]
@@ -63,7 +63,7 @@ def main():
                     ab = bench.algorithmic_bytes(st, cfg["dim"], cfg["M"], k)
                     med = float(np.median(ms))
                     print(json.dumps({"so": os.path.basename(CUDA_SO), "tag": a.tag, "config": a.config, "n": cfg["n"], "set": s,
-                                      "W_run": idx.last_team_width(), "ef": ef, "nq": nq, "kernel_ms_med": round(med, 4),
+                                      "W_run": idx.last_team_width(), "gen_run": idx.last_kernel_gen(), "ef": ef, "nq": nq, "kernel_ms_med": round(med, 4),
                                       "kernel_ms_min": round(float(np.min(ms)), 4), "algo_GBps": round(ab / med / 1e6, 1),
                                       "us_per_expansion_team": None,
                                       "n_dist_mean": float(st["n_dist"].mean()), "n_expand_mean": float(st["n_expand"].mean()),
