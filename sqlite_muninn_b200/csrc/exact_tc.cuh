@@ -125,6 +125,49 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+/* ── CTA pair (cta_group::2): two CTAs of a cluster on the two SMs of a TPC issue ONE M = 256 MMA; each keeps its own
+ * 128 rows of A and one half of B in its shared memory, its 128 rows of D in its tensor memory ── */
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ uint32_t cluster_id_x() { uint32_t r; asm volatile("mov.u32 %0, %%clusterid.x;" : "=r"(r)); return r; }
+__device__ __forceinline__ uint32_t cluster_count_x() { uint32_t r; asm volatile("mov.u32 %0, %%nclusterid.x;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+/* shared::cluster address of the same shared-memory variable in CTA `rank` of the cluster */
+__device__ __forceinline__ uint32_t map_to_cta(const void *p, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_u32(p)), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+/* TMA load into THIS CTA's shared memory whose completion is counted on a barrier of the pair's leader */
+__device__ __forceinline__ void tma_load_2d_pair(void *dst, const CUtensorMap *map, uint32_t leader_bar, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(leader_bar), "r"(c0), "r"(c1)
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t *dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+/* arrives on the barrier at this shared-memory offset in BOTH CTAs once every MMA issued so far has completed */
+__device__ __forceinline__ void tc_commit_pair(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void mma_tf32_ss_pair(uint32_t d_tmem, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\t"
+                 "setp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+                 : "memory");
+}
+
 /* shared-memory matrix descriptor of a K-major tile whose rows are 128 bytes, 128B-swizzled (what
  * TMA writes with CU_TENSOR_MAP_SWIZZLE_128B): 8-row groups 1024 bytes apart, sm_100 descriptor
  * version 1. The tile base must be 1024-byte aligned; a K step of UK elements inside the swizzle
@@ -139,8 +182,8 @@ __device__ __forceinline__ uint64_t make_desc_k128(uint32_t saddr) {
     return d;
 }
 /* instruction descriptor: D fp32, A and B TF32, both K-major, M = 128, N = bn */
-__host__ __device__ constexpr uint32_t make_idesc_tf32(int bn) {
-    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(bn >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+__host__ __device__ constexpr uint32_t make_idesc_tf32(int bn, int bm = BM) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(bn >> 3) << 17) | ((uint32_t)(bm >> 4) << 24);
 }
 
 /* ───────────── filter kernel ───────────── */
@@ -427,13 +470,14 @@ struct TileWalk {
 };
 
 constexpr int QS_MAX_KBLOCKS = 8; /* query tile ≤ 128 × 256 fp32 = 128 KB */
-__host__ __device__ inline int qs_stages(int kblocks, int BN) {
+constexpr int QS_MAX_STAGES = 8;
+__host__ __device__ inline int qs_stages(int kblocks, int rows_per_stage) {
     const int left = 196 * 1024 - kblocks * BM * BK * 4;
-    int n = left / (BN * BK * 4);
-    return n > 6 ? 6 : n;
+    int n = left / (rows_per_stage * BK * 4);
+    return n > QS_MAX_STAGES ? QS_MAX_STAGES : n;
 }
-__host__ __device__ inline size_t qs_smem_bytes(int kblocks, int BN) {
-    return 1024 + (size_t)kblocks * BM * BK * 4 + (size_t)qs_stages(kblocks, BN) * BN * BK * 4 + 2 * BN * 4 + (2 * 6 + 6) * 8 + 16 + 256 * SBUF * 4;
+__host__ __device__ inline size_t qs_smem_bytes(int kblocks, int BN, int CG) {
+    return 1024 + (size_t)kblocks * BM * BK * 4 + (size_t)qs_stages(kblocks, BN / CG) * (BN / CG) * BK * 4 + 2 * BN * 4 + (2 * QS_MAX_STAGES + 6) * 8 + 16 + 256 * SBUF * 4;
 }
 
 /* The epilogue was the bound of the one-product filter (ncu, profiles/r2_ncu/exact_*: the compare + mask-building
@@ -443,21 +487,24 @@ __host__ __device__ inline size_t qs_smem_bytes(int kblocks, int BN) {
  * (the common case by far); only a group with a survivor is walked again to extract it. */
 constexpr int QS_EPI_WARPS = 8, QS_THREADS = 64 + 32 * QS_EPI_WARPS;
 
-template <int METRIC, int BN>
+template <int METRIC, int BN, int CG>
 __global__ void __launch_bounds__(QS_THREADS, 1)
 exact_tc_filter_qs(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_x, const FilterParams p, const int SB) {
-    constexpr int A_BYTES = BM * BK * 4, B_BYTES = BN * BK * 4;
+    /* CG = 2: this CTA and its cluster peer form a pair — 256 queries (128 each, resident) against the same 256 rows,
+     * each CTA streaming only ITS half of the row tile: half the L2→shared traffic and twice the look-ahead per byte */
+    constexpr int BNL = BN / CG;             /* rows of the row tile this CTA loads */
+    constexpr int A_BYTES = BM * BK * 4, B_BYTES = BNL * BK * 4;
     constexpr int EPT = 32 * QS_EPI_WARPS;   /* epilogue threads */
     constexpr int HALF = BN / 2;             /* columns per epilogue thread */
     extern __shared__ unsigned char smem_dyn[];
     unsigned char *base = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
-    const int NST = qs_stages(p.kblocks, BN);
+    const int NST = qs_stages(p.kblocks, BNL);
     unsigned char *qsm = base;                                   /* [kblocks][128 × 32 fp32], 128B-swizzled */
     unsigned char *stages = qsm + (size_t)p.kblocks * A_BYTES;   /* [NST][BN × 32 fp32] */
     float *xaux = reinterpret_cast<float *>(stages + (size_t)NST * B_BYTES);
     uint64_t *full = reinterpret_cast<uint64_t *>(xaux + 2 * BN);
-    uint64_t *empty = full + 6;
-    uint64_t *tmem_full = empty + 6;
+    uint64_t *empty = full + QS_MAX_STAGES;
+    uint64_t *tmem_full = empty + QS_MAX_STAGES;
     uint64_t *tmem_empty = tmem_full + 2;
     uint64_t *q_full = tmem_empty + 2;
     uint64_t *q_empty = q_full + 1;
@@ -465,19 +512,22 @@ exact_tc_filter_qs(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
     int *sbuf = reinterpret_cast<int *>(tmem_ptr + 4);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n_qt = (p.nq + BM - 1) / BM, n_xt = (p.rows + BN - 1) / BN;
-    const int cta = blockIdx.x, grid = gridDim.x;
+    const int n_qt = (p.nq + BM * CG - 1) / (BM * CG), n_xt = (p.rows + BN - 1) / BN;
+    const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;      /* 0 = the pair's leader: it alone issues the MMAs */
+    const int cta = CG == 2 ? (int)cluster_id_x() : (int)blockIdx.x, grid = CG == 2 ? (int)cluster_count_x() : (int)gridDim.x;
+    const int QROWS = BM * CG;                                  /* queries per (pair) tile */
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tm_q); prefetch_tmap(&tm_x);
         for (int s = 0; s < NST; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-        for (int a = 0; a < 2; a++) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], QS_EPI_WARPS); }
+        for (int a = 0; a < 2; a++) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], QS_EPI_WARPS * CG); }
         mbar_init(q_full, 1); mbar_init(q_empty, 1);
         fence_barrier_init();
     }
-    if (warp == 1) tmem_alloc(tmem_ptr, 2 * BN);
+    if (warp == 1) { if (CG == 2) tmem_alloc_pair(tmem_ptr, 2 * BN); else tmem_alloc(tmem_ptr, 2 * BN); }
     tc_fence_before();
     __syncthreads();
+    if (CG == 2) cluster_sync_all(); /* the peer's barriers are initialised before anything signals them */
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
 
@@ -488,21 +538,25 @@ exact_tc_filter_qs(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
                 const int qt = w.qt(), xt = w.xt();
                 if (qt != qt_have) {
                     if (qt_have >= 0) { mbar_wait(q_empty, qe_ph); qe_ph ^= 1; } /* every MMA on the old query tile has retired */
-                    mbar_expect_tx(q_full, (uint32_t)(p.kblocks * A_BYTES));
-                    for (int kb = 0; kb < p.kblocks; kb++) tma_load_2d(qsm + (size_t)kb * A_BYTES, &tm_q, q_full, kb * BK, qt * BM);
+                    if (rank == 0) mbar_expect_tx(q_full, (uint32_t)(p.kblocks * A_BYTES * CG)); /* the pair's bytes land on the leader's barrier */
+                    for (int kb = 0; kb < p.kblocks; kb++) {
+                        if (CG == 2) tma_load_2d_pair(qsm + (size_t)kb * A_BYTES, &tm_q, map_to_cta(q_full, 0), kb * BK, qt * QROWS + (int)rank * BM);
+                        else tma_load_2d(qsm + (size_t)kb * A_BYTES, &tm_q, q_full, kb * BK, qt * BM);
+                    }
                     qt_have = qt;
                 }
                 for (int kb = 0; kb < p.kblocks; kb++) {
                     mbar_wait(&empty[s], ph ^ 1);
-                    mbar_expect_tx(&full[s], B_BYTES);
-                    tma_load_2d(stages + (size_t)s * B_BYTES, &tm_x, &full[s], kb * BK, xt * BN);
+                    if (rank == 0) mbar_expect_tx(&full[s], B_BYTES * CG);
+                    if (CG == 2) tma_load_2d_pair(stages + (size_t)s * B_BYTES, &tm_x, map_to_cta(&full[s], 0), kb * BK, xt * BN + (int)rank * BNL);
+                    else tma_load_2d(stages + (size_t)s * B_BYTES, &tm_x, &full[s], kb * BK, xt * BN);
                     if (++s == NST) { s = 0; ph ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) { /* ── MMA issuer ── */
-            constexpr uint32_t idesc = make_idesc_tf32(BN);
+        if (lane == 0 && rank == 0) { /* ── MMA issuer (the pair's leader) ── */
+            constexpr uint32_t idesc = make_idesc_tf32(BN, BM * CG);
             int s = 0; uint32_t ph = 0, qf_ph = 0; int a = 0; uint32_t aph = 0; int qt_have = -1;
             TileWalk w(n_qt, n_xt, SB, cta, grid);
             while (!w.done()) {
@@ -517,13 +571,16 @@ exact_tc_filter_qs(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
                     const uint64_t a_d = make_desc_k128(smem_u32(qsm + (size_t)kb * A_BYTES));
                     const uint64_t b_d = make_desc_k128(smem_u32(stages + (size_t)s * B_BYTES));
 #pragma unroll
-                    for (int k4 = 0; k4 < BK / UK; k4++) mma_tf32_ss(d_tmem, a_d + 2 * k4, b_d + 2 * k4, idesc, (kb | k4) ? 1u : 0u);
-                    tc_commit(&empty[s]);
+                    for (int k4 = 0; k4 < BK / UK; k4++) {
+                        if (CG == 2) mma_tf32_ss_pair(d_tmem, a_d + 2 * k4, b_d + 2 * k4, idesc, (kb | k4) ? 1u : 0u);
+                        else mma_tf32_ss(d_tmem, a_d + 2 * k4, b_d + 2 * k4, idesc, (kb | k4) ? 1u : 0u);
+                    }
+                    if (CG == 2) tc_commit_pair(&empty[s]); else tc_commit(&empty[s]);
                     if (++s == NST) { s = 0; ph ^= 1; }
                 }
-                tc_commit(&tmem_full[a]);
+                if (CG == 2) tc_commit_pair(&tmem_full[a]); else tc_commit(&tmem_full[a]);
                 w.advance(cta, grid);
-                if (w.done() || w.qt() != qt_have) tc_commit(q_empty); /* the query tile may be replaced once these MMAs retire */
+                if (w.done() || w.qt() != qt_have) { if (CG == 2) tc_commit_pair(q_empty); else tc_commit(q_empty); } /* the query tile may be replaced once these MMAs retire */
                 if (++a == 2) { a = 0; aph ^= 1; }
             }
         }
@@ -564,7 +621,7 @@ exact_tc_filter_qs(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
             if (qt != qt_have) {
                 flush();
                 qt_have = qt;
-                q = qt * BM + qrow;
+                q = qt * QROWS + (int)rank * BM + qrow;
                 qvalid = q < p.nq;
                 qa = 0.0f;
                 if (qvalid) {
@@ -638,14 +695,15 @@ exact_tc_filter_qs(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tmem_empty[a]);
+            if (lane == 0) { if (CG == 2) mbar_arrive_cluster(map_to_cta(&tmem_empty[a], 0)); else mbar_arrive(&tmem_empty[a]); }
             if (++a == 2) { a = 0; aph ^= 1; }
         }
         flush();
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, 2 * BN); }
+    if (CG == 2) cluster_sync_all(); /* the leader's MMAs read the peer's shared memory until the last tile has retired */
+    if (warp == 1) { tc_fence_after(); if (CG == 2) tmem_dealloc_pair(tmem_base, 2 * BN); else tmem_dealloc(tmem_base, 2 * BN); }
 }
 
 /* ───────────── split / prepare ───────────── */

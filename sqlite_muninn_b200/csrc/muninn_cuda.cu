@@ -72,6 +72,7 @@ struct MuninnCudaIndex {
     /* exact k-NN, tensor-core filter (exact_tc.cuh) */
     int exact_mode = MUNINN_EXACT_TC_AUTO, tc_tile_rows = 256;
     int tc_qs = 1, tc_qs_min_nq = 1024, tc_superblock_mb = 32, tc_x_stride = 0; /* query-stationary 1xTF32 filter (exact_tc_filter_qs) */
+    int tc_pair = 0; CUtensorMap tc_map_xh; /* CTA-pair form of the query-stationary filter: row-tile map with 128-row boxes */
     int tc_auto_1x_min_nq = 1 << 30; /* AUTO: batches of at least this many queries still take 3xTF32 (none by default) */
     int exact_mode_run = MUNINN_EXACT_TC_3XTF32; /* what AUTO resolved to for the current call */
     float *d_qsplit = nullptr; size_t qsplit_floats = 0;   /* q_hi | q_lo, [nq × kp] each */
@@ -182,6 +183,7 @@ extern "C" int muninn_cuda_index_create(int device, int dim, int metric, int M, 
     if (const char *e = getenv("MUNINN_VIS_FACTOR")) { const double f = atof(e); if (f >= 0.5 && f <= 64.0) h->vis_factor = f; }
     if (const char *e = getenv("MUNINN_WARPS")) { const int w = atoi(e); if (w == 0 || w == 1 || w == 2 || w == 4) h->warps_per_query = w; }
     if (const char *e = getenv("MUNINN_EXACT_QS")) h->tc_qs = atoi(e) != 0;
+    if (const char *e = getenv("MUNINN_EXACT_PAIR")) h->tc_pair = atoi(e) != 0;
     if (const char *e = getenv("MUNINN_EXACT_SB_MB")) { const int v = atoi(e); if (v >= 1 && v <= 4096) h->tc_superblock_mb = v; }
     if (const char *e = getenv("MUNINN_TEAMS_PER_SM")) { const int t = atoi(e); if (t >= 0 && t <= 32) h->teams_per_sm = t; }
     *out = h;
@@ -234,6 +236,8 @@ extern "C" int muninn_cuda_set_option(MuninnCudaIndex *h, const char *name, doub
         h->vis_factor = value;
     } else if (!strcmp(name, "exact_qs")) { /* 0 = the streaming 1xTF32 filter for every batch size */
         h->tc_qs = value != 0;
+    } else if (!strcmp(name, "exact_pair")) { /* 1 = CTA pairs (tcgen05 cta_group::2) in the query-stationary filter */
+        h->tc_pair = value != 0;
     } else if (!strcmp(name, "exact_qs_min_nq")) {
         h->tc_qs_min_nq = (int)value;
     } else if (!strcmp(name, "exact_superblock_mb")) {
@@ -1003,27 +1007,41 @@ static cudaError_t launch_filter(MuninnCudaIndex *h, const CUtensorMap maps[4], 
     return cudaGetLastError();
 }
 
-/* query-stationary form: one TF32 product, query tile resident in shared memory, row tiles in L2-sized super-blocks */
+/* query-stationary form: one TF32 product, query tile resident in shared memory, row tiles in L2-sized super-blocks.
+ * pair = two CTAs of a cluster share every row tile (tcgen05 cta_group::2, M = 256): map_x then has 128-row boxes. */
 template <int METRIC>
 static cudaError_t launch_filter_qs(MuninnCudaIndex *h, const CUtensorMap &map_q, const CUtensorMap &map_x, const tc::FilterParams &fp,
-                                    int row_stride_floats) {
+                                    int row_stride_floats, bool pair) {
     constexpr int BN = 256;
-    auto kern = tc::exact_tc_filter_qs<METRIC, BN>;
-    const size_t smem = tc::qs_smem_bytes(fp.kblocks, BN);
+    const int CG = pair ? 2 : 1;
+    const void *kern = pair ? (const void *)tc::exact_tc_filter_qs<METRIC, BN, 2> : (const void *)tc::exact_tc_filter_qs<METRIC, BN, 1>;
+    const size_t smem = tc::qs_smem_bytes(fp.kblocks, BN, CG);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    const long long tiles = (long long)((fp.nq + tc::BM - 1) / tc::BM) * ((fp.rows + BN - 1) / BN);
-    const int grid = (int)std::min<long long>(tiles, h->num_sms);
-    const int SB = (int)std::max<long long>(1, ((long long)h->tc_superblock_mb << 20) / ((long long)BN * row_stride_floats * 4));
-    kern<<<grid, tc::QS_THREADS, smem, h->stream>>>(map_q, map_x, fp, SB);
-    return cudaGetLastError();
+    const long long tiles = (long long)((fp.nq + tc::BM * CG - 1) / (tc::BM * CG)) * ((fp.rows + BN - 1) / BN);
+    const int groups = (int)std::min<long long>(tiles, h->num_sms / CG);
+    int SB = (int)std::max<long long>(1, ((long long)h->tc_superblock_mb << 20) / ((long long)BN * row_stride_floats * 4));
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof cfg);
+    cfg.gridDim = dim3((unsigned)(groups * CG));
+    cfg.blockDim = dim3(tc::QS_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = h->stream;
+    cudaLaunchAttribute attr;
+    memset(&attr, 0, sizeof attr);
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = (unsigned)CG; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = 1;
+    void *args[4] = {(void *)&map_q, (void *)&map_x, (void *)&fp, (void *)&SB};
+    return cudaLaunchKernelExC(&cfg, kern, args);
 }
 
 template <int METRIC>
 static cudaError_t launch_filter_m(MuninnCudaIndex *h, const CUtensorMap maps[4], const tc::FilterParams &fp) {
     const bool three = h->exact_mode_run == MUNINN_EXACT_TC_3XTF32;
     if (!three && !fp.dbg_panel && h->tc_tile_rows == 256 && h->tc_qs && fp.nq >= h->tc_qs_min_nq && fp.kblocks <= tc::QS_MAX_KBLOCKS)
-        return launch_filter_qs<METRIC>(h, maps[0], maps[2], fp, h->tc_x_stride);
+        return launch_filter_qs<METRIC>(h, maps[0], h->tc_pair ? h->tc_map_xh : maps[2], fp, h->tc_x_stride, h->tc_pair != 0);
     if (fp.dbg_panel) return three ? launch_filter<METRIC, 3, 256, true>(h, maps, fp) : launch_filter<METRIC, 1, 256, true>(h, maps, fp);
     if (h->tc_tile_rows == 128)
         return three ? launch_filter<METRIC, 3, 128>(h, maps, fp) : launch_filter<METRIC, 1, 128>(h, maps, fp);
@@ -1121,6 +1139,7 @@ static int exact_knn_tc(MuninnCudaIndex *h, const float *d_queries, int nq, int 
         if (raw_x) {
             rc = make_slab_map(h, &maps[2], h->d_vec + (size_t)done * h->ld, h->ld, chunk, bn);
             maps[3] = maps[2];
+            if (!rc && h->tc_pair) rc = make_slab_map(h, &h->tc_map_xh, h->d_vec + (size_t)done * h->ld, h->ld, chunk, 128);
         } else {
             tc::tc_split_rows<<<h->num_sms * 8, 256, 0, st>>>(h->d_vec + (size_t)done * h->ld, h->ld, h->dim, chunk, kp, x_hi,
                                                               three ? x_lo : nullptr);

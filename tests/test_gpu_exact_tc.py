@@ -87,13 +87,14 @@ def test_query_stationary_filter_equals_oracle(cuda, oracle, metric, dim, n, nq,
     i_o, d_o, c_o, _ = oracle.exact_knn(base, q, k, metric, deleted=deleted, threads=8)
     with cuda.HnswIndexCuda.from_graph(flat(base, metric, deleted)) as idx:
         idx.set_option("exact_superblock_mb", sb_mb)
-        for qs in (1, 0):
+        for qs, pair in ((1, 0), (1, 1), (0, 0)):  # query-stationary, the same on CTA pairs (cta_group::2, M = 256), streaming
             idx.set_option("exact_qs", qs)
+            idx.set_option("exact_pair", pair)
             idx.set_exact_mode(cuda.EXACT_TC_AUTO, 0)
             i_g, d_g, c_g = idx.exact_knn(q, k)
             st = idx.exact_stats()
             assert st["mode"] == cuda.EXACT_TC_1XTF32 and st["overflow_queries"] == 0
-            assert np.array_equal(c_g, c_o) and d_g.tobytes() == d_o.tobytes() and np.array_equal(i_g, i_o), qs
+            assert np.array_equal(c_g, c_o) and d_g.tobytes() == d_o.tobytes() and np.array_equal(i_g, i_o), (qs, pair)
 
 
 def test_filter_prunes(cuda, oracle):

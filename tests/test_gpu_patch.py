@@ -125,11 +125,11 @@ def test_lists_longer_than_capacity_after_heavy_deletion(reference, oracle):
     ref = reference.build(base, ids=np.arange(n, dtype=np.int64) + 1, metric=0, M=M, efc=40)
     g0 = ref.export()
     dev = HnswIndexCuda.from_graph(g0)
+    g_dev = g0  # the state the device copy holds
     over, refused = False, 0
     for step, i in enumerate(np.random.default_rng(3).permutation(n)[:450]):
-        g_prev = ref.export() if step % 50 == 0 else None
         assert ref.delete(int(i) + 1) == 0
-        if g_prev is None:
+        if step % 50 != 0:
             continue
         g = ref.export()
         first = g.first_list()
@@ -139,11 +139,12 @@ def test_lists_longer_than_capacity_after_heavy_deletion(reference, oracle):
         upper[first[:-1]] = False
         over = over or bool(lens0.max() > 2 * M or (upper.any() and lens_all[upper].max() > M))
         try:
-            dev.patch(g, changed_slots(g_prev, g))
+            dev.patch(g, changed_slots(g_dev, g))  # everything the deletes since the last sync touched
         except MuninnCudaError as e:  # outgrew the device rows: a clean refusal, then the fallback the glue takes
             assert "upload again" in str(e)
             refused += 1
             dev.upload(g)
+        g_dev = g
         with HnswIndexCuda.from_graph(g) as fresh:
             for k, ef in ((10, 40), (5, 5)):
                 a, b = dev.search(q, k, ef, want_stats=True), fresh.search(q, k, ef, want_stats=True)
