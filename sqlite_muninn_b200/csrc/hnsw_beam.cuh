@@ -376,6 +376,9 @@ __global__ void __launch_bounds__(32 * W, MinBlocks<W>::v) hnsw_beam_kernel(cons
                                 spec_t[ch] = (c2 >= 0 && pos0 < p.M0) ? __ldg(l2 + pos0) : -1;
                             }
                         }
+                        /* lists of more than 32 entries: the second chunk's visited buckets move towards L2 while the first is probed */
+                        if (SPEC_CH > 1 && p.M0 > 32 && t[1] >= 0)
+                            prefetch_l2(tab + (size_t)((((unsigned)t[1] * 2654435761u) >> p.vis_shift) & ~3u));
                         /* visited filter → fresh slots */
                         nf = 0;
                         for (int base = 0; base < p.M0; base += 32) {

@@ -54,6 +54,9 @@ namespace muninn {
 #ifndef MUNINN_VIS_EVICT_LAST
 #define MUNINN_VIS_EVICT_LAST 0  /* L2 evict-last hint on visited-table probes and claims */
 #endif
+#ifndef MUNINN_LIST_AHEAD
+#define MUNINN_LIST_AHEAD 1      /* lists longer than 32 entries: all list lines up front, next chunk's visited buckets and this chunk's rows prefetched */
+#endif
 #ifndef MUNINN_NEXT_PREFETCH
 #define MUNINN_NEXT_PREFETCH 0   /* fetch the next candidate's neighbour list while R is being merged (measured: no gain) */
 #endif
@@ -544,7 +547,8 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
                 visited_test_and_set(p, tab, cur, lane == 0, lane, vpol);
                 __syncwarp();
                 int stale = 0, lb = 0, n_ins = 1, evicted_open = 0;
-                int pre_slot = -1, pre_t = -1; /* neighbour list fetched ahead for the expected next candidate */
+                int pre_slot = -1, pre_t = -1; /* neighbour list fetched ahead for the expected next candidate (MUNINN_NEXT_PREFETCH) */
+                (void)pre_slot; (void)pre_t;
                 for (;;) {
                     /* closest unexpanded entry of R */
                     int pos = -1;
@@ -581,14 +585,37 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
                     /* neighbour list → visited filter → fresh slots */
                     int nf = 0;
                     const int32_t *lst = p.nbr0 + (size_t)c * (size_t)p.M0;
+#if MUNINN_LIST_AHEAD
+                    /* lists of more than 32 entries (M > 16): every 32-entry chunk used to pay its own dependent chain
+                     * list line → visited probe. All list lines are requested up front (they are adjacent), and the visited
+                     * buckets of the NEXT chunk are pulled towards L2 while the current chunk is probed, so that only the
+                     * first probe of an expansion can be a DRAM round trip. */
+                    int t_next = lane < p.M0 ? lst[lane] : -1;
+#endif
                     for (int base = 0; base < p.M0; base += 32) {
                         int pos0 = base + lane;
                         int t;
+#if MUNINN_LIST_AHEAD
+                        t = t_next;
+                        if (base + 32 < p.M0) {
+                            t_next = pos0 + 32 < p.M0 ? lst[pos0 + 32] : -1;
+                            if (t_next >= 0) prefetch_l2(tab + (size_t)((((unsigned)t_next * 2654435761u) >> p.vis_shift) & ~3u));
+                        }
+#else
                         if (MUNINN_NEXT_PREFETCH && base == 0 && c == pre_slot) t = pre_t;
                         else t = pos0 < p.M0 ? lst[pos0] : -1;
+#endif
                         int fresh = visited_test_and_set(p, tab, t, t >= 0, lane, vpol);
                         unsigned fm = __ballot_sync(FULL, fresh);
                         if (fresh) sm.Fs[nf + __popc(fm & ((1u << lane) - 1))] = t;
+#if MUNINN_LIST_AHEAD && MUNINN_PREFETCH
+                        /* this chunk's fresh rows start towards L2 while the next chunk is still being probed (narrow rows only:
+                         * for 3 KB rows the 24 extra prefetches per row cost more than they hide — c3 proxy 13.68 vs 13.32 ms) */
+                        if (fresh && base + 32 < p.M0 && p.ld <= 128) {
+                            const char *rb = reinterpret_cast<const char *>(p.vec + (size_t)t * (size_t)p.ld);
+                            for (int off = 0; off < p.ld * 4; off += 128) prefetch_l2(rb + off);
+                        }
+#endif
                         nf += __popc(fm);
                     }
                     n_ins += nf;
