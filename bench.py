@@ -513,17 +513,21 @@ def run_search_job(D: Dist, idx, c, queries_job: np.ndarray, ef: int, steps: int
         def e2e_step():  # the C-ABI call a host makes: H2D + kernel + D2H inside muninn_cuda_search_batch
             idx.search_into(h_q.data_ptr(), nq, k, ef, h_ids.data_ptr(), h_dist.data_ptr(), h_cnt.data_ptr())
     else:
-        h_ids = torch.empty((D.world * pad, k), dtype=torch.int64).pin_memory() if D.rank == 0 else None
-        h_dist = torch.empty((D.world * pad, k), dtype=torch.float32).pin_memory() if D.rank == 0 else None
+        # ids (as two int32 words) and distances (as their bit patterns) travel as ONE [rows × 3k] int32 array: one gather
+        # straight into rank 0's receive buffer, one device→host copy
+        packed = torch.empty((pad, 3 * k), dtype=torch.int32, device="cuda")
+        big = torch.empty((D.world, pad, 3 * k), dtype=torch.int32, device="cuda") if D.rank == 0 else None
+        h_big = torch.empty((D.world, pad, 3 * k), dtype=torch.int32).pin_memory() if D.rank == 0 else None
         d_q2 = torch.empty_like(d_q)
 
-        def e2e_step():  # H2D of the slice, search, ids+distances gathered to rank 0 over NVLink, D2H there
+        def e2e_step():  # H2D of the slice, search, results gathered to rank 0 over NVLink, D2H there
             d_q2.copy_(h_q, non_blocking=True)
             idx.search_device(d_q2.data_ptr(), nq, k, ef, d_ids.data_ptr(), d_dist.data_ptr(), d_cnt.data_ptr(), None)
-            gi, gd = D.gather_rows(d_ids, pad), D.gather_rows(d_dist, pad)
+            packed[:nq, : 2 * k] = d_ids.view(torch.int32)
+            packed[:nq, 2 * k:] = d_dist.view(torch.int32)
+            D.dist.gather(packed, list(big.unbind(0)) if D.rank == 0 else None, dst=0)
             if D.rank == 0:
-                h_ids.copy_(torch.cat(gi, 0), non_blocking=True)
-                h_dist.copy_(torch.cat(gd, 0), non_blocking=True)
+                h_big.copy_(big, non_blocking=True)
             torch.cuda.synchronize()
     for _ in range(max(1, warmup // 2)):
         e2e_step()
@@ -543,10 +547,12 @@ def run_search_job(D: Dist, idx, c, queries_job: np.ndarray, ef: int, steps: int
             verified = bool(np.array_equal(got_ids, d_ids.cpu().numpy()) and np.array_equal(got_dist, d_dist.cpu().numpy()))
         else:
             parts_i, parts_d = [], []
+            hb = h_big.numpy()
             for r in range(D.world):
                 rl, rh = shard_range(job_q, r, D.world)
-                parts_i.append(h_ids.numpy()[r * pad: r * pad + (rh - rl)])
-                parts_d.append(h_dist.numpy()[r * pad: r * pad + (rh - rl)])
+                blk = np.ascontiguousarray(hb[r, : rh - rl])
+                parts_i.append(np.ascontiguousarray(blk[:, : 2 * k]).view(np.int64))
+                parts_d.append(np.ascontiguousarray(blk[:, 2 * k:]).view(np.float32))
             got_ids, got_dist = np.concatenate(parts_i, 0), np.concatenate(parts_d, 0)
             a_q = torch.from_numpy(queries_job).cuda()
             a_ids = torch.empty((job_q, k), dtype=torch.int64, device="cuda")

@@ -19,7 +19,8 @@
  * the deleted node and its former neighbours (src/hnsw_algo.c:520-666, :717-805), so the glue
  * remembers those ids and, on the next search, sends just their records with muninn_cuda_index_patch
  * (SURVEY.md §8f N4). It falls back to a full upload when an inserted rowid is not above every stored
- * one (slots would shift) or when the pending set has grown past a quarter of the index. There is no
+ * one (slots would shift), when the pending change records outnumber the stored nodes, or when a list has
+ * outgrown the device rows (hnsw_delete's reconnection has no capacity check: the library refuses the patch). There is no
  * CPU fallback: a failure of the device path is reported through zErrMsg and the query fails.
  */
 #include "hnsw_algo.h" /* the reference's header, -I<reference>/src */

@@ -245,3 +245,25 @@ def test_single_product_stays_exact_on_adversarial_rows(cuda, oracle, metric):
             idx.set_exact_mode(mode, 256)
             i_g, d_g, c_g = idx.exact_knn(q, k)
             assert np.array_equal(c_g, c_o) and d_g.tobytes() == d_o.tobytes() and np.array_equal(i_g, i_o), mode
+
+
+def test_rows_only_handle_from_host_and_device_memory(cuda, oracle):
+    """muninn_cuda_index_upload_rows: a shard of base rows without a graph (BASELINE config 5), adopted from host OR
+    device memory; exact k-NN equals the oracle, search and patch refuse the handle."""
+    import torch
+    n, dim, nq, k = 30000, 128, 1100, 20
+    base, q = latent(71, n, dim), latent(72, nq, dim)
+    i_o, d_o, c_o, _ = oracle.exact_knn(base, q, k, L2, threads=8)
+    for where in ("host", "device"):
+        with cuda.HnswIndexCuda(dim, L2, 8) as idx:
+            if where == "host":
+                idx.upload_rows(base.ctypes.data, n)
+            else:
+                d_rows = torch.from_numpy(base).cuda()
+                torch.cuda.synchronize()
+                idx.upload_rows(d_rows.data_ptr(), n)
+                del d_rows  # the handle owns its copy
+            i_g, d_g, c_g = idx.exact_knn(q, k, index_base=5)
+            assert np.array_equal(c_g, c_o) and d_g.tobytes() == d_o.tobytes() and np.array_equal(i_g, i_o + 5), where
+            with pytest.raises(cuda.MuninnCudaError, match="rows only"):
+                idx.search(q[:4], 5, 10)

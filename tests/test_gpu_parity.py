@@ -185,6 +185,23 @@ def test_full_size_properties(cuda, oracle, team):
         assert np.array_equal(st["n_dist"][:200], o[3]["n_dist"])
 
 
+def test_large_host_batches_are_sliced_and_identical(cuda, oracle):
+    """muninn_cuda_search_batch cuts host-buffer batches of >= 32 768 queries into up to four slices so that the copies
+    ride under the kernels: same ids, distances, counts and counters as the unsliced call, in batch order."""
+    from sqlite_muninn_b200.builder import build_graph
+    base, q = uniform(91, 5000, 32), uniform(92, 2500, 32)
+    g = build_graph(base, L2, 8, 60)
+    big = np.ascontiguousarray(np.tile(q, (17, 1))[:40001])  # 40 001 queries: four slices, the last one ragged
+    with cuda.HnswIndexCuda.from_graph(g) as idx:
+        ids, dist, cnt, st = idx.search(q, 10, 48, want_stats=True)
+        b_ids, b_dist, b_cnt, b_st = idx.search(big, 10, 48, want_stats=True)
+    rep = lambda a: np.tile(a, (17,) + (1,) * (a.ndim - 1))[:40001]
+    assert np.array_equal(b_ids, rep(ids)) and np.array_equal(b_dist, rep(dist)) and np.array_equal(b_cnt, rep(cnt))
+    assert np.array_equal(b_st["n_dist"], rep(st["n_dist"])) and np.array_equal(b_st["n_expand"], rep(st["n_expand"]))
+    o = oracle.graph(g).search(q, 10, 48, canonical=True)
+    assert np.array_equal(ids, o[0]) and np.array_equal(dist, o[1])
+
+
 @pytest.mark.parametrize("cfg", [3, 4])
 @pytest.mark.parametrize("kernel", ["auto", "8-w1", "8-w2"])
 def test_bench_shapes_at_size_equal_oracle(cuda, oracle, cfg, kernel, monkeypatch):
