@@ -412,7 +412,9 @@ class Dist:
         if world > 1:
             import torch.distributed as dist
             self.dist = dist
-            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+            import datetime
+            # rank 0 may spend minutes building a 10M-node graph while the others wait at a barrier
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank), timeout=datetime.timedelta(minutes=90))
         self.stream = torch.cuda.Stream()  # a real stream: the legacy default stream (0) means "handle's own" to the ABI
         torch.cuda.set_stream(self.stream)
 

@@ -54,7 +54,6 @@ struct MuninnCudaIndex {
     int64_t *d_ids = nullptr;
     /* launch state */
     cudaStream_t own_stream = nullptr, stream = nullptr;
-    cudaStream_t copy_in = nullptr, copy_out = nullptr; cudaEvent_t ev_in[4] = {}, ev_k[4] = {}; /* sliced host-buffer batches */
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool have_timing = false;
     int num_sms = 0, teams_per_sm = 0, warps_per_query = 0;
@@ -205,7 +204,6 @@ extern "C" void muninn_cuda_index_destroy(MuninnCudaIndex *h) {
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
-    if (h->copy_in) { cudaStreamDestroy(h->copy_in); cudaStreamDestroy(h->copy_out); for (int i = 0; i < 4; i++) { cudaEventDestroy(h->ev_in[i]); cudaEventDestroy(h->ev_k[i]); } }
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     delete h;
 }
@@ -875,38 +873,9 @@ extern "C" int muninn_cuda_search_batch(MuninnCudaIndex *h, const float *queries
         memcpy(out_count, res + bi + bd, (size_t)nq * 4);
         return MUNINN_CUDA_OK;
     }
-    /* large batches: the copies ride under the kernels. The batch is cut into up to four slices; slice c+1's queries
-     * arrive (copy engine, own stream) while slice c is searched, slice c's results leave while slice c+1 is searched.
-     * One slice is still ≥ 16k queries, i.e. several rounds of the 3 552 resident teams. */
-    const int n_slices = nq >= 32768 ? std::min(4, nq / 16384) : 1;
-    if (n_slices > 1) {
-        if (!h->copy_in) {
-            CK(h, cudaStreamCreateWithFlags(&h->copy_in, cudaStreamNonBlocking));
-            CK(h, cudaStreamCreateWithFlags(&h->copy_out, cudaStreamNonBlocking));
-            for (int i = 0; i < 4; i++) { CK(h, cudaEventCreateWithFlags(&h->ev_in[i], cudaEventDisableTiming)); CK(h, cudaEventCreateWithFlags(&h->ev_k[i], cudaEventDisableTiming)); }
-        }
-        const int per = (nq + n_slices - 1) / n_slices;
-        for (int c = 0; c < n_slices; c++) {
-            const int q0 = c * per, qn = std::min(per, nq - q0);
-            CK(h, cudaMemcpyAsync(dq + (size_t)q0 * h->dim, queries + (size_t)q0 * h->dim, (size_t)qn * h->dim * 4, cudaMemcpyHostToDevice, h->copy_in));
-            CK(h, cudaEventRecord(h->ev_in[c], h->copy_in));
-        }
-        for (int c = 0; c < n_slices; c++) {
-            const int q0 = c * per, qn = std::min(per, nq - q0);
-            CK(h, cudaStreamWaitEvent(h->stream, h->ev_in[c], 0));
-            rc = muninn_cuda_search_batch_device(h, dq + (size_t)q0 * h->dim, qn, k, ef, di + (size_t)q0 * k, dd + (size_t)q0 * k, dc + q0, ds ? ds + q0 : nullptr);
-            if (rc) return rc;
-            CK(h, cudaEventRecord(h->ev_k[c], h->stream));
-            CK(h, cudaStreamWaitEvent(h->copy_out, h->ev_k[c], 0));
-            CK(h, cudaMemcpyAsync(out_ids + (size_t)q0 * k, di + (size_t)q0 * k, (size_t)qn * k * 8, cudaMemcpyDeviceToHost, h->copy_out));
-            CK(h, cudaMemcpyAsync(out_dist + (size_t)q0 * k, dd + (size_t)q0 * k, (size_t)qn * k * 4, cudaMemcpyDeviceToHost, h->copy_out));
-            CK(h, cudaMemcpyAsync(out_count + q0, dc + q0, (size_t)qn * 4, cudaMemcpyDeviceToHost, h->copy_out));
-            if (out_stats) CK(h, cudaMemcpyAsync(out_stats + q0, ds + q0, (size_t)qn * sizeof(MuninnSearchStats), cudaMemcpyDeviceToHost, h->copy_out));
-        }
-        CK(h, cudaStreamSynchronize(h->copy_out));
-        CK(h, cudaStreamSynchronize(h->stream));
-        return MUNINN_CUDA_OK;
-    }
+    /* (Cutting large batches into slices so that the copies ride under the kernels was measured and dropped: every
+     * extra launch pays its own ≈ 0.25 ms drain — the last queries of a launch run on a thinning GPU — which cancels the
+     * ≈ 0.8 ms of copies it hides at 80 000 queries: e2e/value 0.927 with four slices, 0.924 with one.) */
     CK(h, cudaMemcpyAsync(dq, queries, (size_t)nq * h->dim * 4, cudaMemcpyHostToDevice, h->stream));
     rc = muninn_cuda_search_batch_device(h, dq, nq, k, ef, di, dd, dc, ds);
     if (rc) return rc;

@@ -185,13 +185,13 @@ def test_full_size_properties(cuda, oracle, team):
         assert np.array_equal(st["n_dist"][:200], o[3]["n_dist"])
 
 
-def test_large_host_batches_are_sliced_and_identical(cuda, oracle):
-    """muninn_cuda_search_batch cuts host-buffer batches of >= 32 768 queries into up to four slices so that the copies
-    ride under the kernels: same ids, distances, counts and counters as the unsliced call, in batch order."""
+def test_large_host_batches_keep_batch_order(cuda, oracle):
+    """40 001 queries through the host-buffer entry: same ids, distances, counts and counters as the small batch they
+    repeat, in batch order (staging buffers regrown, several rounds of resident teams, retry lists sized by nq)."""
     from sqlite_muninn_b200.builder import build_graph
     base, q = uniform(91, 5000, 32), uniform(92, 2500, 32)
     g = build_graph(base, L2, 8, 60)
-    big = np.ascontiguousarray(np.tile(q, (17, 1))[:40001])  # 40 001 queries: four slices, the last one ragged
+    big = np.ascontiguousarray(np.tile(q, (17, 1))[:40001])
     with cuda.HnswIndexCuda.from_graph(g) as idx:
         ids, dist, cnt, st = idx.search(q, 10, 48, want_stats=True)
         b_ids, b_dist, b_cnt, b_st = idx.search(big, 10, 48, want_stats=True)
