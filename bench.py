@@ -14,6 +14,8 @@ job alone (`verified`).
 
 Blocks under `extra` (each timed the same way at the current N, with its own roofline and `verified`):
   split_10k  the literal 10k-query batch of configs[1] split over the N ranks (the latency-bound end of the split)
+  config1    configs[0] by the reference's own methodology: 10k x 128, one MATCH per statement through the vtab, the
+             unmodified extension on the host vs the patched extension vs hnsw_knn_batch (tools/bench_config1.py, rank 0)
   config3    1M x 768 cosine, M=32, 10k-query batch split over the ranks
   config4    10M x 96 inner product, M=32, 10k-query batch split over the ranks
   config5    exact brute-force k-NN, 50M x 128 L2, k=100: base rows sharded over the ranks, ONE ncclAllGather of
@@ -865,6 +867,17 @@ def run_gpu_arm(args, rank: int, local_rank: int, world: int) -> None:
             except Exception as e:  # an extra block must never take the headline line down
                 log(f"[bench] extra config{num} failed: {e!r}")
                 extra[f"config{num}"] = {"error": repr(e)}
+    if "1" in extras and rank == 0:
+        # BASELINE configs[0], the reference's own vtab methodology (one MATCH per statement; tools/bench_config1.py):
+        # unmodified extension on the host vs the patched extension on GPU 0 vs hnsw_knn_batch, same database file
+        try:
+            r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "bench_config1.py"), "--repeats", "3"],
+                               capture_output=True, text=True, timeout=900)
+            line = [l for l in r.stdout.splitlines() if l.startswith("{")]
+            extra["config1"] = json.loads(line[-1]) if line else {"error": (r.stderr or "no output")[-400:]}
+        except Exception as e:
+            extra["config1"] = {"error": repr(e)}
+    D.barrier()
     if "5" in extras:
         try:
             extra["config5"] = run_exact_block(D, args, 3, 3, want_cpu)
@@ -896,8 +909,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", type=int, default=2, choices=sorted(CONFIGS),
                     help="BASELINE.json config (1-based) timed as the headline; 2 = the bench line the driver reads")
-    ap.add_argument("--extras", default=os.environ.get("MUNINN_BENCH_EXTRAS", "split10k,3,4,5"),
-                    help="comma list of extra blocks: split10k, 3, 4, 5, or none")
+    ap.add_argument("--extras", default=os.environ.get("MUNINN_BENCH_EXTRAS", "split10k,1,3,4,5"),
+                    help="comma list of extra blocks: split10k, 1, 3, 4, 5, or none")
     ap.add_argument("--n", type=int, default=None, help="override the headline config's size (dry runs)")
     ap.add_argument("--dim", type=int, default=None)
     ap.add_argument("--M", type=int, default=None)
