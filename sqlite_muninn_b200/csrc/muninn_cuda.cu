@@ -767,6 +767,10 @@ extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *
     int teams[3];
     unsigned caps[3];
     teams[0] = (int)std::min<long long>((long long)h->num_sms * tps, nq);
+    /* (Sizing the grid to ⌈nq / rounds⌉ teams so that every "round" of queries is full — 3 334 instead of 3 552 teams for
+     * a 10k batch — was measured and dropped: 1.543 vs 1.492 ms at ef = 64, 46.8 vs 42.6 ms at config 3. Query lengths vary
+     * enough that the work queue, not a round structure, decides; every resident slot is worth having.
+     * profiles/r2_bench/ab_balance_rounds.jsonl) */
     const unsigned cap_all = pow2_at_least(2ull * (unsigned long long)(h->n + h->W0 + 1));
     /* first-level table: 2·ef·2M slots. A search visits ≈ 0.8·ef·2M nodes on the bench graphs, so the table
      * runs at ≈ 40 % load at the end of a typical query and the whole arena (teams × cap × 4 B = 58 MB at

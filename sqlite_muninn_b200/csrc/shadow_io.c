@@ -254,7 +254,7 @@ int muninn_shadow_write(sqlite3 *db, const char *table, const MuninnShadowGraph 
          * stored directly: running xCreate would start an empty index over the tables just written */
         static const char *names[3] = {"l2", "cosine", "inner_product"};
         if (g->metric < 0 || g->metric > 2) FAIL(MUNINN_SHADOW_E_ARG);
-        char *decl = sqlite3_mprintf("CREATE VIRTUAL TABLE %s USING hnsw_index(dimensions=%d, metric='%s', m=%d, ef_construction=%d)",
+        char *decl = sqlite3_mprintf("CREATE VIRTUAL TABLE \"%w\" USING hnsw_index(dimensions=%d, metric='%s', m=%d, ef_construction=%d)",
                                      table, g->dim, names[g->metric], g->M, g->ef_construction);
         if (!decl) FAIL(MUNINN_SHADOW_E_NOMEM);
         rc = sqlite3_exec(db, "PRAGMA writable_schema=ON", NULL, NULL, NULL);
