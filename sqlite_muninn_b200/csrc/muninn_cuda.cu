@@ -54,6 +54,7 @@ struct MuninnCudaIndex {
     int64_t *d_ids = nullptr;
     /* launch state */
     cudaStream_t own_stream = nullptr, stream = nullptr;
+    cudaStream_t copy_in = nullptr; cudaEvent_t ev_first = nullptr; unsigned *d_arrived = nullptr, *h_arrived = nullptr; /* large host batches stream in behind the launch */
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool have_timing = false;
     int num_sms = 0, teams_per_sm = 0, warps_per_query = 0;
@@ -204,6 +205,7 @@ extern "C" void muninn_cuda_index_destroy(MuninnCudaIndex *h) {
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->copy_in) { cudaStreamDestroy(h->copy_in); cudaEventDestroy(h->ev_first); cudaFree(h->d_arrived); cudaFreeHost(h->h_arrived); }
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     delete h;
 }
@@ -723,9 +725,19 @@ static cudaError_t occupancy_cached(MuninnCudaIndex *h, const KernelSel &k, int 
 
 static const size_t SEARCH_SMEM_LIMIT = 200 * 1024;
 
+static int search_device_impl(MuninnCudaIndex *h, const float *d_queries, int nq, int k, int ef, int64_t *d_ids, float *d_dist,
+                              int32_t *d_count, MuninnSearchStats *d_stats, const unsigned *d_arrived);
+
 extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *d_queries, int nq, int k, int ef,
                                                int64_t *d_ids, float *d_dist, int32_t *d_count,
                                                MuninnSearchStats *d_stats) {
+    return search_device_impl(h, d_queries, nq, k, ef, d_ids, d_dist, d_count, d_stats, nullptr);
+}
+
+/* d_arrived: NULL, or a device word that the copy engine raises to the number of queries already present in d_queries
+ * (muninn_cuda_search_batch streams a large batch in behind the kernel's back; SearchParams::q_arrived) */
+static int search_device_impl(MuninnCudaIndex *h, const float *d_queries, int nq, int k, int ef, int64_t *d_ids, float *d_dist,
+                              int32_t *d_count, MuninnSearchStats *d_stats, const unsigned *d_arrived) {
     if (!h) return MUNINN_CUDA_E_ARG;
     if (!h->uploaded) return fail(h, MUNINN_CUDA_E_STATE, "search before muninn_cuda_index_upload");
     if (h->rows_only) return fail(h, MUNINN_CUDA_E_STATE, "this handle holds rows only (muninn_cuda_index_upload_rows): no graph to search");
@@ -806,6 +818,7 @@ extern "C" int muninn_cuda_search_batch_device(MuninnCudaIndex *h, const float *
     p.patience_max = std::max(ef / 4, 10); /* src/hnsw_algo.c:372-374 */
     p.out_ids = d_ids; p.out_dist = d_dist; p.out_count = d_count; p.stats = d_stats;
     p.vis = h->d_vis;
+    p.q_arrived = d_arrived;
 
     CK(h, cudaEventRecord(h->ev0, h->stream));
     for (int lv = 0; lv < nlevels; lv++) {
@@ -877,9 +890,37 @@ extern "C" int muninn_cuda_search_batch(MuninnCudaIndex *h, const float *queries
         memcpy(out_count, res + bi + bd, (size_t)nq * 4);
         return MUNINN_CUDA_OK;
     }
-    /* (Cutting large batches into slices so that the copies ride under the kernels was measured and dropped: every
-     * extra launch pays its own ≈ 0.25 ms drain — the last queries of a launch run on a thinning GPU — which cancels the
-     * ≈ 0.8 ms of copies it hides at 80 000 queries: e2e/value 0.927 with four slices, 0.924 with one.) */
+    /* Large batches: ONE launch that starts on the first 8 192 queries while the rest of the batch is still crossing
+     * PCIe. The copy engine (own stream) raises a device word behind each slice of the copy; a team that draws a query
+     * beyond it waits (SearchParams::q_arrived) — in practice never: the resident teams need several milliseconds to
+     * reach query 8 192, the copy of 80 000 × 512 B takes 0.8. (Cutting the batch into several LAUNCHES instead was
+     * measured and dropped: every launch pays ≈ 0.25 ms of drain at its end, which cancelled what the copies gained.) */
+    if (nq >= 16384) {
+        if (!h->copy_in) {
+            CK(h, cudaStreamCreateWithFlags(&h->copy_in, cudaStreamNonBlocking));
+            CK(h, cudaEventCreateWithFlags(&h->ev_first, cudaEventDisableTiming));
+            CK(h, cudaMalloc((void **)&h->d_arrived, 64));
+            CK(h, cudaMallocHost((void **)&h->h_arrived, 64));
+        }
+        const int first = 8192;
+        h->h_arrived[0] = (unsigned)first; h->h_arrived[1] = (unsigned)nq;
+        const size_t row = (size_t)h->dim * 4;
+        CK(h, cudaMemcpyAsync(dq, queries, (size_t)first * row, cudaMemcpyHostToDevice, h->copy_in));
+        CK(h, cudaMemcpyAsync(h->d_arrived, &h->h_arrived[0], 4, cudaMemcpyHostToDevice, h->copy_in));
+        CK(h, cudaEventRecord(h->ev_first, h->copy_in));
+        CK(h, cudaMemcpyAsync(dq + (size_t)first * h->dim, queries + (size_t)first * h->dim, (size_t)(nq - first) * row, cudaMemcpyHostToDevice, h->copy_in));
+        CK(h, cudaMemcpyAsync(h->d_arrived, &h->h_arrived[1], 4, cudaMemcpyHostToDevice, h->copy_in));
+        CK(h, cudaStreamWaitEvent(h->stream, h->ev_first, 0));
+        rc = search_device_impl(h, dq, nq, k, ef, di, dd, dc, ds, h->d_arrived);
+        if (rc) { cudaStreamSynchronize(h->copy_in); return rc; }
+        CK(h, cudaMemcpyAsync(out_ids, di, (size_t)nq * k * 8, cudaMemcpyDeviceToHost, h->stream));
+        CK(h, cudaMemcpyAsync(out_dist, dd, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, h->stream));
+        CK(h, cudaMemcpyAsync(out_count, dc, (size_t)nq * 4, cudaMemcpyDeviceToHost, h->stream));
+        if (out_stats) CK(h, cudaMemcpyAsync(out_stats, ds, (size_t)nq * sizeof(MuninnSearchStats), cudaMemcpyDeviceToHost, h->stream));
+        CK(h, cudaStreamSynchronize(h->stream));
+        CK(h, cudaStreamSynchronize(h->copy_in));
+        return MUNINN_CUDA_OK;
+    }
     CK(h, cudaMemcpyAsync(dq, queries, (size_t)nq * h->dim * 4, cudaMemcpyHostToDevice, h->stream));
     rc = muninn_cuda_search_batch_device(h, dq, nq, k, ef, di, dd, dc, ds);
     if (rc) return rc;
