@@ -22,13 +22,11 @@
  *     batch of rows — are in flight while the current one is walked. Everything the ring does not
  *     hold yet is pulled into L2 up front with one bulk prefetch per row.
  *
- *  3. SPECULATION ON THE NEXT CANDIDATE. When a candidate is popped, the runner-up (the next open
- *     entry of R) is almost always the one popped next. Its neighbour list is requested at once
- *     (into registers), and while the current expansion's rows are in flight its entries are
- *     looked up (read-only) in the visited table and the rows of the unvisited ones are pulled into
- *     L2. If the prediction holds the next expansion starts with its list in registers and its
- *     rows L2-resident: two of the three dependent memory round trips of an expansion disappear.
- *     A wrong guess costs nothing but the prefetched lines (no state is changed by speculation).
+ * Tried here and removed (round 2, profiles/r2_bench/ab_a_ring_spec_teams.jsonl): speculation on the next
+ * candidate — requesting the runner-up's neighbour list at pop time, looking its entries up read-only in
+ * the visited table and pulling the unvisited rows into L2. Slower everywhere (ef=64: 2.18 vs 1.88 ms,
+ * 3 KB rows: 26.5 vs 18.8 ms, a lone query 0.436 vs 0.383 ms): the runner-up is often overtaken by a fresh
+ * neighbour and the kernel is bandwidth-bound enough that speculative rows cost more than they hide.
  */
 #pragma once
 #include "hnsw_search.cuh"
@@ -37,11 +35,7 @@ namespace muninn {
 namespace beam {
 
 constexpr int RB = 16;     /* rows per batch: two lanes per row, chains (2h, 2h+1) packed as f32x2 */
-constexpr int SPEC_CH = 2; /* 32-entry chunks of a neighbour list held in registers ahead of time (M0 ≤ 64) */
-
-#ifndef MUNINN_SPEC
-#define MUNINN_SPEC 0 /* 0 = off (default: measured slower everywhere, profiles/r2_bench/ab_a_ring_spec_teams.jsonl), 1 = next candidate's list only, 2 = list + visited peek + row prefetch */
-#endif
+constexpr int LIST_CH = 2; /* 32-entry chunks of a neighbour list requested up front (M0 ≤ 64; longer lists read the rest in the loop) */
 
 __host__ __device__ inline size_t a16(size_t v) { return (v + 15) & ~(size_t)15; }
 
@@ -58,14 +52,6 @@ __host__ __device__ inline size_t smem_bytes(int ef, int ld, int M0, int U, int 
 /* whole row (or its tail) towards L2 with one TMA prefetch */
 __device__ __forceinline__ void l2_prefetch_bytes(const void *g, unsigned bytes) {
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(g), "r"(bytes) : "memory");
-}
-
-static_assert(MUNINN_VIS_BUCKET == 4, "visited_peek reads one 4-entry bucket");
-/* read-only look-up in the visited table: false only when t is certainly marked already */
-__device__ __forceinline__ bool visited_peek(const SearchParams &p, const unsigned *tab, int t) {
-    const unsigned b = (((unsigned)t * 2654435761u) >> p.vis_shift) >> 2;
-    const uint4 e = __ldcg(reinterpret_cast<const uint4 *>(tab + ((size_t)b << 2)));
-    return !(e.x == (unsigned)t || e.y == (unsigned)t || e.z == (unsigned)t || e.w == (unsigned)t);
 }
 
 /*
@@ -258,9 +244,6 @@ __global__ void __launch_bounds__(32 * W, MinBlocks<W>::v) hnsw_beam_kernel(cons
         bool overflow = false;
         /* leader state of the beam */
         int stale = 0, lb = 0, n_ins = 1, evicted_open = 0;
-        int spec_c = -1, spec_t[SPEC_CH];
-#pragma unroll
-        for (int ch = 0; ch < SPEC_CH; ch++) spec_t[ch] = -1;
         bool run_beam = false;
 
         if (leader && p.entry_slot >= 0 && p.n_live > 0) {
@@ -339,49 +322,35 @@ __global__ void __launch_bounds__(32 * W, MinBlocks<W>::v) hnsw_beam_kernel(cons
         /* ── layer-0 beam (src/hnsw_algo.c:347-448) ── */
         while (run_beam) {
             int nf = -1;
-            bool spec_hit = false;
             if (leader) {
-                /* closest unexpanded entry of R, and the runner-up */
-                int pos = -1, pos2 = -1;
+                /* closest unexpanded entry of R */
+                int pos = -1;
                 for (int base = lb & ~31; base < size; base += 32) {
                     const int idx = base + lane;
                     const bool open = idx < size && idx >= lb && !(R[idx] & 1ull);
-                    unsigned om = __ballot_sync(FULL, open);
-                    if (om && pos < 0) { pos = base + __ffs(om) - 1; om &= om - 1; }
-                    if (om) { pos2 = base + __ffs(om) - 1; break; }
-                    if (pos >= 0 && !MUNINN_SPEC) break;
+                    const unsigned om = __ballot_sync(FULL, open);
+                    if (om) { pos = base + __ffs(om) - 1; break; }
                 }
                 if (pos < 0) term = (size >= ef && evicted_open) ? 1 : 0;
                 else if (stale >= p.patience_max && size >= ef) term = 2; /* :391-392 */
                 else {
                     const int c = (int)((unsigned)R[pos] >> 1);
-                    const int c2 = pos2 >= 0 ? (int)((unsigned)R[pos2] >> 1) : -1;
                     __syncwarp();
                     if (lane == 0) R[pos] |= 1ull;
                     lb = pos + 1;
                     n_expand++;
                     if ((unsigned)(n_ins + p.M0) > p.vis_cap - (p.vis_cap >> 2)) overflow = true; /* keep the load ≤ 3/4 */
                     else {
-                        /* neighbour list: from the registers filled ahead of time when the guess was right */
+                        /* neighbour list: all of its lines are requested up front */
                         const int32_t *lst = p.nbr0 + (size_t)c * (size_t)p.M0;
-                        spec_hit = MUNINN_SPEC && c == spec_c;
-                        int t[SPEC_CH];
+                        int t[LIST_CH];
 #pragma unroll
-                        for (int ch = 0; ch < SPEC_CH; ch++) {
+                        for (int ch = 0; ch < LIST_CH; ch++) {
                             const int pos0 = ch * 32 + lane;
-                            t[ch] = spec_hit ? spec_t[ch] : (pos0 < p.M0 ? lst[pos0] : -1);
-                        }
-                        if (MUNINN_SPEC) { /* request the runner-up's list now; it lands while this expansion runs */
-                            spec_c = c2;
-                            const int32_t *l2 = p.nbr0 + (size_t)(c2 < 0 ? 0 : c2) * (size_t)p.M0;
-#pragma unroll
-                            for (int ch = 0; ch < SPEC_CH; ch++) {
-                                const int pos0 = ch * 32 + lane;
-                                spec_t[ch] = (c2 >= 0 && pos0 < p.M0) ? __ldg(l2 + pos0) : -1;
-                            }
+                            t[ch] = pos0 < p.M0 ? lst[pos0] : -1;
                         }
                         /* lists of more than 32 entries: the second chunk's visited buckets move towards L2 while the first is probed */
-                        if (SPEC_CH > 1 && p.M0 > 32 && t[1] >= 0)
+                        if (LIST_CH > 1 && p.M0 > 32 && t[1] >= 0)
                             prefetch_l2(tab + (size_t)((((unsigned)t[1] * 2654435761u) >> p.vis_shift) & ~3u));
                         /* visited filter → fresh slots */
                         nf = 0;
@@ -389,7 +358,7 @@ __global__ void __launch_bounds__(32 * W, MinBlocks<W>::v) hnsw_beam_kernel(cons
                             const int pos0 = base + lane;
                             int tt;
                             if (base == 0) tt = t[0];
-                            else if (SPEC_CH > 1 && base == 32) tt = t[1];
+                            else if (LIST_CH > 1 && base == 32) tt = t[1];
                             else tt = pos0 < p.M0 ? lst[pos0] : -1;
                             const int fresh = visited_test_and_set(p, tab, tt, tt >= 0, lane);
                             const unsigned fm = __ballot_sync(FULL, fresh);
@@ -401,35 +370,22 @@ __global__ void __launch_bounds__(32 * W, MinBlocks<W>::v) hnsw_beam_kernel(cons
                         __syncwarp();
                     }
                 }
-                if (W > 1 && lane == 0) { ctl[0] = nf; ctl[3] = spec_hit ? 1 : 0; }
+                if (W > 1 && lane == 0) ctl[0] = nf;
             }
             if (W > 1) {
                 __syncthreads();
                 nf = ctl[0];
-                spec_hit = ctl[3] != 0;
             }
             if (nf < 0) break;
 
             if (nf > 0) {
                 ring.begin(p, Fs, nf, warp, W, lane, pol);
-                /* what the rings do not hold yet → L2, one bulk prefetch per row (all of it was requested ahead of
-                 * time when the guess was right) */
-                if (!(MUNINN_SPEC >= 2 && spec_hit && p.M0 <= 32 * SPEC_CH)) {
-                    const unsigned in_ring = (unsigned)(NST * U * 4) < row_bytes ? (unsigned)(NST * U * 4) : row_bytes;
-                    for (int r = threadIdx.x; r < nf; r += NT) {
-                        const unsigned off = r < W * RB ? in_ring : 0u;
-                        if (off < row_bytes)
-                            l2_prefetch_bytes(reinterpret_cast<const char *>(p.vec + (size_t)Fs[r] * (size_t)p.ld) + off, row_bytes - off);
-                    }
-                }
-            }
-            if (MUNINN_SPEC >= 2 && leader && spec_c >= 0) {
-                /* the runner-up's neighbours: read-only visited look-up, rows of the unvisited ones → L2 */
-#pragma unroll
-                for (int ch = 0; ch < SPEC_CH; ch++) {
-                    const int ts = spec_t[ch];
-                    if (ts >= 0 && visited_peek(p, tab, ts))
-                        l2_prefetch_bytes(p.vec + (size_t)ts * (size_t)p.ld, row_bytes);
+                /* what the rings do not hold yet → L2, one bulk prefetch per row */
+                const unsigned in_ring = (unsigned)(NST * U * 4) < row_bytes ? (unsigned)(NST * U * 4) : row_bytes;
+                for (int r = threadIdx.x; r < nf; r += NT) {
+                    const unsigned off = r < W * RB ? in_ring : 0u;
+                    if (off < row_bytes)
+                        l2_prefetch_bytes(reinterpret_cast<const char *>(p.vec + (size_t)Fs[r] * (size_t)p.ld) + off, row_bytes - off);
                 }
             }
             if (nf > 0) ring.run(p, q, Fk, qn2, lane, pol);

@@ -36,29 +36,8 @@ namespace muninn {
 #ifndef MUNINN_SEARCH_MIN_BLOCKS
 #define MUNINN_SEARCH_MIN_BLOCKS 24 /* resident query teams per SM the register budget is sized for */
 #endif
-#ifndef MUNINN_PREFETCH
-#define MUNINN_PREFETCH 1
-#endif
 #ifndef MUNINN_RB
 #define MUNINN_RB 0 /* 0 = by row width: RB_NARROW rows (24 teams/SM) for one-column-block rows, else 16 */
-#endif
-#ifndef MUNINN_ROW_EVICT_FIRST
-#define MUNINN_ROW_EVICT_FIRST 1 /* gathered rows are streamed: L2 evict-first keeps lists and visited tables resident */
-#endif
-#ifndef MUNINN_BULK_ROWS
-#define MUNINN_BULK_ROWS 1       /* rows staged by one TMA bulk copy each (lane r issues row r) instead of 16-byte LDGSTS */
-#endif
-#ifndef MUNINN_F32X2
-#define MUNINN_F32X2 1           /* the two chains a lane owns are kept as one packed f32x2 register pair */
-#endif
-#ifndef MUNINN_VIS_EVICT_LAST
-#define MUNINN_VIS_EVICT_LAST 0  /* L2 evict-last hint on visited-table probes and claims */
-#endif
-#ifndef MUNINN_LIST_AHEAD
-#define MUNINN_LIST_AHEAD 1      /* lists longer than 32 entries: all list lines up front, next chunk's visited buckets and this chunk's rows prefetched */
-#endif
-#ifndef MUNINN_NEXT_PREFETCH
-#define MUNINN_NEXT_PREFETCH 0   /* fetch the next candidate's neighbour list while R is being merged (measured: no gain) */
 #endif
 constexpr int DB = 8;             /* rows per distance batch in the greedy descent (4 lanes per row) */
 /* Rows per beam batch. Rows of ‚â§ 512 bytes are staged in one go: 13-row batches shrink the tile so
@@ -74,14 +53,6 @@ constexpr int PSTRIDE = 128 + 4;  /* floats per staged row: 32 chunks + 4 pad ‚Ü
 constexpr int MAX_M0 = 128;       /* layer-0 list capacity supported (M ‚â§ 64) */
 /* dim 96 (config 4): rows are 384 bytes, so a 16-row tile at stride 100 floats (‚â° 4 mod 32: conflict-free like 132)
  * is SMALLER than the 13-row tile at stride 132 ‚Äî the full 16-row batch at the same 24 teams/SM */
-/* Pull the neighbour list of the LIKELY next candidate towards L2 while the current one is still being worked on:
- * at pop time the second-closest open entry of R, and after the distances every fresh node that beats it. The
- * list read at the top of the next expansion is then an L2 hit instead of a DRAM round trip on the critical path
- * (prefetches only: no registers held, no effect on results). Measured at config 2 (two interleaved A/B pairs):
- * 1.687 / 1.621 ms with, 1.611 / 1.671 ms without ‚Äî inside the run-to-run noise, so it stays off. */
-#ifndef MUNINN_LIST_PREFETCH
-#define MUNINN_LIST_PREFETCH 0
-#endif
 #ifndef MUNINN_D96_WIDE
 #define MUNINN_D96_WIDE 1
 #endif
@@ -132,36 +103,19 @@ __host__ __device__ inline size_t search_smem_bytes(int ef, int ld, int M0, int 
     return b;
 }
 
-/* 16-byte asynchronous global‚Üíshared copy (LDGSTS), L2-only caching: the gathered rows are
- * streamed once and never reused by this SM */
-__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src, unsigned long long policy) {
-    unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-#if MUNINN_ROW_EVICT_FIRST
-    asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(d), "l"(gmem_src), "l"(policy) : "memory");
-#else
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src) : "memory");
-#endif
-}
+/* L2 policy for the gathered rows: streamed once and never reused by this SM */
 __device__ __forceinline__ unsigned long long l2_evict_first_policy() {
     unsigned long long pol;
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
     return pol;
-}
-__device__ __forceinline__ void cp_async_wait_all() {
-    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
 }
 
 /* TMA bulk copy global ‚Üí shared of `bytes` (multiple of 16), completion counted on an mbarrier */
 __device__ __forceinline__ void bulk_row_copy(void *smem_dst, const void *gmem_src, unsigned bytes, unsigned long long *bar,
                                               unsigned long long policy) {
     const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst), b = (unsigned)__cvta_generic_to_shared(bar);
-#if MUNINN_ROW_EVICT_FIRST
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
                  ::"r"(d), "l"(gmem_src), "r"(bytes), "r"(b), "l"(policy) : "memory");
-#else
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(d), "l"(gmem_src), "r"(bytes), "r"(b) : "memory");
-#endif
 }
 __device__ __forceinline__ void bar_init(unsigned long long *bar, unsigned count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
@@ -230,21 +184,11 @@ __device__ __forceinline__ float warp_dist_rows(const SearchParams &p, TeamSmem 
     unsigned long long s01 = 0ull; /* (s0, s1) packed, CH == 2 */
     for (int t0 = 0; t0 < cpr; t0 += 32) {
         const int tc = cpr - t0 < 32 ? cpr - t0 : 32;
-#if MUNINN_BULK_ROWS
         if (lane == 0) bar_expect_tx(sm.bar, (unsigned)(nb * tc * 16));
         __syncwarp();
         if (lane < nb) bulk_row_copy(sm.P + lane * PS, p.vec + (size_t)bs[lane] * (size_t)p.ld + 4 * t0, (unsigned)(tc * 16), sm.bar, pol);
         bar_wait(sm.bar, sm.phase);
         sm.phase ^= 1u;
-#else
-        if (lane < tc) {
-            const float *src = p.vec + 4 * (t0 + lane);
-            float *dst = sm.P + 4 * lane;
-            for (int r = 0; r < nb; r++) cp_async16(dst + r * PS, src + (size_t)bs[r] * (size_t)p.ld, pol);
-        }
-        cp_async_wait_all();
-        __syncwarp();
-#endif
         if (mine) {
             int tfull = cfull - t0;
             tfull = tfull > tc ? tc : tfull;
@@ -252,7 +196,7 @@ __device__ __forceinline__ float warp_dist_rows(const SearchParams &p, TeamSmem 
             const float *qr = sm.q + 4 * t0 + CH * h;
 #pragma unroll (CD ? (CD / 4 < 32 ? CD / 4 : 32) : 8)
             for (int cc = 0; cc < tfull; cc++) {
-                if (CH == 2 && MUNINN_F32X2) {
+                if (CH == 2) {
                     const unsigned long long x = *reinterpret_cast<const unsigned long long *>(xr + 4 * cc);
                     const unsigned long long q = *reinterpret_cast<const unsigned long long *>(qr + 4 * cc);
                     unsigned long long pr;
@@ -261,11 +205,6 @@ __device__ __forceinline__ float warp_dist_rows(const SearchParams &p, TeamSmem 
                         pr = f2_pack(__fmul_rn(f2_lo(d), f2_lo(d)), __fmul_rn(f2_hi(d), f2_hi(d)));
                     } else pr = f2_pack(__fmul_rn(f2_lo(q), f2_lo(x)), __fmul_rn(f2_hi(q), f2_hi(x)));
                     s01 = f2_add(s01, pr);
-                } else if (CH == 2) {
-                    const float2 x = *reinterpret_cast<const float2 *>(xr + 4 * cc);
-                    const float2 q = *reinterpret_cast<const float2 *>(qr + 4 * cc);
-                    s0 = __fadd_rn(s0, prod1<METRIC>(q.x, x.x));
-                    s1 = __fadd_rn(s1, prod1<METRIC>(q.y, x.y));
                 } else {
                     s0 = __fadd_rn(s0, prod1<METRIC>(qr[4 * cc], xr[4 * cc]));
                 }
@@ -279,7 +218,7 @@ __device__ __forceinline__ float warp_dist_rows(const SearchParams &p, TeamSmem 
         }
         __syncwarp(); /* the tile is overwritten by the next column block */
     }
-    if (CH == 2 && MUNINN_F32X2) { s0 = f2_lo(s01); s1 = f2_hi(s01); }
+    if (CH == 2) { s0 = f2_lo(s01); s1 = f2_hi(s01); }
     float sum;
     if (L == 4) {
         float c0 = __shfl_sync(FULL, s0, g), c1 = __shfl_sync(FULL, s0, g + 1), c2 = __shfl_sync(FULL, s0, g + 2),
@@ -333,47 +272,19 @@ __device__ __forceinline__ float query_norm2(const float *q, int dim) {
 }
 
 /* visited test-and-set for one neighbour per lane; returns 1 if the slot was not yet visited.
- * The table is private to the team and cleared at the start of every query: 32-bit entries (eight
- * per 32-byte sector, so a probe chain usually stays in one sector), plain L2-level loads/stores,
- * intra-warp claim conflicts resolved with match.any. */
-__device__ __forceinline__ unsigned vis_load(const unsigned *a, unsigned long long pol) {
-#if MUNINN_VIS_EVICT_LAST
-    unsigned v;
-    asm volatile("ld.global.cg.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(a), "l"(pol) : "memory");
-    return v;
-#else
-    return __ldcg(a);
-#endif
-}
-__device__ __forceinline__ void vis_store(unsigned *a, unsigned v, unsigned long long pol) {
-#if MUNINN_VIS_EVICT_LAST
-    asm volatile("st.global.cg.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(a), "r"(v), "l"(pol) : "memory");
-#else
-    __stcg(a, v);
-#endif
-}
-__device__ __forceinline__ unsigned long long l2_evict_last_policy() {
-    unsigned long long pol;
-    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
-    return pol;
-}
-/* 0 = one entry per probe (linear probing), 4 / 8 = entries per bucket. Measured at config 2 (kernel ms at ef 64 / 128 /
- * 256): linear 1.625 / 3.23 / 7.07, 8-entry 1.616 / 3.42 / 7.55 (fewer round trips but twice the loads and compares: a
- * loss once the merge makes the kernel issue-bound), 4-entry 1.532 / 3.06 / 6.74 ‚Äî one 16-byte load, the best everywhere. */
-#ifndef MUNINN_VIS_BUCKET
-#define MUNINN_VIS_BUCKET 4
-#endif
-#if MUNINN_VIS_BUCKET
-/* Bucketised table: a key hashes to a BUCKET of VB (4 or 8) 32-bit entries inside one 32-byte sector, fetched with
- * 16-byte loads in one L2 round trip. Entries fill a bucket from the front and are never removed, so "found / first
+ * The table is private to the team and cleared at the start of every query: 32-bit entries, plain L2-level
+ * loads/stores, intra-warp claim conflicts resolved with match.any.
+ * Entries per bucket, measured at config 2 (kernel ms at ef 64 / 128 / 256): linear probing 1.625 / 3.23 / 7.07,
+ * 8-entry 1.616 / 3.42 / 7.55 (fewer round trips but twice the loads and compares: a loss once the merge makes the
+ * kernel issue-bound), 4-entry 1.532 / 3.06 / 6.74 ‚Äî one 16-byte load, the best everywhere.
+ * Bucketised table: a key hashes to a BUCKET of four 32-bit entries (half a 32-byte sector), fetched with
+ * one 16-byte load in one L2 round trip. Entries fill a bucket from the front and are never removed, so "found / first
  * empty slot / full" are all decided from that one fetch; only a full bucket (rare below 3/4 load: a search ends
  * near 40 %) sends the lane on to the next one. With one entry per probe every call paid ‚âà 3.5 dependent round trips
  * (32 lanes: some lane always collides); this pays ‚âà 1. Lanes claiming in the same bucket take consecutive empty
  * slots in lane order (match.any), no atomics. */
-__device__ __forceinline__ int visited_test_and_set(const SearchParams &p, unsigned *tab, int t, bool valid, int lane,
-                                                    unsigned long long vpol = 0ull) {
-    (void)vpol;
-    constexpr int VB = MUNINN_VIS_BUCKET == 4 ? 4 : 8, VBL = VB == 4 ? 2 : 3;
+__device__ __forceinline__ int visited_test_and_set(const SearchParams &p, unsigned *tab, int t, bool valid, int lane) {
+    constexpr int VB = 4, VBL = 2; /* entries per bucket, log2 */
     const unsigned bmask = (p.vis_cap >> VBL) - 1;
     unsigned b = (((unsigned)t * 2654435761u) >> p.vis_shift) >> VBL;
     bool active = valid;
@@ -384,11 +295,8 @@ __device__ __forceinline__ int visited_test_and_set(const SearchParams &p, unsig
         if (active) {
             const uint4 *bp = reinterpret_cast<const uint4 *>(tab + ((size_t)b << VBL));
             unsigned e[VB];
-            {
-                const uint4 e0 = __ldcg(bp);
-                e[0] = e0.x; e[1] = e0.y; e[2] = e0.z; e[3] = e0.w;
-                if (VB == 8) { const uint4 e1 = __ldcg(bp + 1); e[VB - 4] = e1.x; e[VB - 3] = e1.y; e[VB - 2] = e1.z; e[VB - 1] = e1.w; }
-            }
+            const uint4 e0 = __ldcg(bp);
+            e[0] = e0.x; e[1] = e0.y; e[2] = e0.z; e[3] = e0.w;
             bool found = false;
 #pragma unroll
             for (int i = VB - 1; i >= 0; i--) {
@@ -413,36 +321,6 @@ __device__ __forceinline__ int visited_test_and_set(const SearchParams &p, unsig
     }
     return fresh;
 }
-#else
-__device__ __forceinline__ int visited_test_and_set(const SearchParams &p, unsigned *tab, int t, bool valid, int lane,
-                                                    unsigned long long vpol = 0ull) {
-    unsigned h = ((unsigned)t * 2654435761u) >> p.vis_shift;
-    const unsigned mask = p.vis_cap - 1;
-    bool active = valid;
-    int fresh = 0;
-    while (__any_sync(FULL, active)) {
-        unsigned e = active ? vis_load(tab + h, vpol) : 0u;
-        bool claim = false;
-        if (active) {
-            if (e == (unsigned)t) active = false; /* already visited */
-            else if (e != VIS_EMPTY) h = (h + 1) & mask;
-            else claim = true;
-        }
-        unsigned cm = __ballot_sync(FULL, claim);
-        if (claim) {
-            unsigned peers = __match_any_sync(cm, h);
-            if ((__ffs(peers) - 1) == lane) {
-                vis_store(tab + h, (unsigned)t, vpol);
-                fresh = 1;
-                active = false;
-            } else h = (h + 1) & mask;
-        }
-        __syncwarp();
-    }
-    return fresh;
-}
-
-#endif
 
 __device__ __forceinline__ void visited_clear(unsigned *tab, unsigned cap, int lane) {
     uint4 *t4 = reinterpret_cast<uint4 *>(tab);
@@ -469,15 +347,12 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
         sm.bar = reinterpret_cast<unsigned long long *>(b);
         sm.phase = 0u;
     }
-#if MUNINN_BULK_ROWS
     if (lane == 0) bar_init(sm.bar, 1);
     __syncwarp();
-#endif
     unsigned *tab = p.vis + (size_t)blockIdx.x * (size_t)p.vis_cap;
     const int nwork = level == 0 ? p.nq : *p.in_count;
     const int ef = p.ef, FP = fs_pos(p.M0);
     const unsigned long long pol = l2_evict_first_policy();
-    const unsigned long long vpol = MUNINN_VIS_EVICT_LAST ? l2_evict_last_policy() : 0ull;
 
     for (;;) {
         int w = 0;
@@ -562,32 +437,18 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
                 if (lane == 0) sm.R[0] = make_key(cur_d, (unsigned)cur << 1);
                 size = 1;
                 visited_clear(tab, p.vis_cap, lane);
-                visited_test_and_set(p, tab, cur, lane == 0, lane, vpol);
+                visited_test_and_set(p, tab, cur, lane == 0, lane);
                 __syncwarp();
                 int stale = 0, lb = 0, n_ins = 1, evicted_open = 0;
-                int pre_slot = -1, pre_t = -1; /* neighbour list fetched ahead for the expected next candidate (MUNINN_NEXT_PREFETCH) */
-                (void)pre_slot; (void)pre_t;
                 for (;;) {
                     /* closest unexpanded entry of R */
                     int pos = -1;
-                    unsigned long long next_open = KEY_NONE; /* lower bound of the keys behind the popped entry */
-                    (void)next_open;
                     for (int base = lb & ~31; base < size; base += 32) {
                         int idx = base + lane;
                         bool open = idx < size && idx >= lb && !(sm.R[idx] & 1ull);
                         unsigned om = __ballot_sync(FULL, open);
                         if (om) {
                             pos = base + __ffs(om) - 1;
-#if MUNINN_LIST_PREFETCH
-                            /* every entry behind pos is ‚â• R[pos + 1]: a fresh node below that key is popped before any of them */
-                            next_open = pos + 1 < size ? sm.R[pos + 1] : KEY_NONE;
-                            const unsigned om2 = om & (om - 1);
-                            if (om2) {
-                                const unsigned long long second = sm.R[base + __ffs(om2) - 1];
-                                const char *nl = reinterpret_cast<const char *>(p.nbr0 + (size_t)((unsigned)second >> 1) * (size_t)p.M0);
-                                if (lane * 128 < p.M0 * 4) prefetch_l2(nl + lane * 128);
-                            }
-#endif
                             break;
                         }
                     }
@@ -603,47 +464,35 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
                     /* neighbour list ‚Üí visited filter ‚Üí fresh slots */
                     int nf = 0;
                     const int32_t *lst = p.nbr0 + (size_t)c * (size_t)p.M0;
-#if MUNINN_LIST_AHEAD
                     /* lists of more than 32 entries (M > 16): every 32-entry chunk used to pay its own dependent chain
                      * list line ‚Üí visited probe. All list lines are requested up front (they are adjacent), and the visited
                      * buckets of the NEXT chunk are pulled towards L2 while the current chunk is probed, so that only the
                      * first probe of an expansion can be a DRAM round trip. */
                     int t_next = lane < p.M0 ? lst[lane] : -1;
-#endif
                     for (int base = 0; base < p.M0; base += 32) {
                         int pos0 = base + lane;
-                        int t;
-#if MUNINN_LIST_AHEAD
-                        t = t_next;
+                        const int t = t_next;
                         if (base + 32 < p.M0) {
                             t_next = pos0 + 32 < p.M0 ? lst[pos0 + 32] : -1;
                             if (t_next >= 0) prefetch_l2(tab + (size_t)((((unsigned)t_next * 2654435761u) >> p.vis_shift) & ~3u));
                         }
-#else
-                        if (MUNINN_NEXT_PREFETCH && base == 0 && c == pre_slot) t = pre_t;
-                        else t = pos0 < p.M0 ? lst[pos0] : -1;
-#endif
-                        int fresh = visited_test_and_set(p, tab, t, t >= 0, lane, vpol);
+                        int fresh = visited_test_and_set(p, tab, t, t >= 0, lane);
                         unsigned fm = __ballot_sync(FULL, fresh);
                         if (fresh) sm.Fs[nf + __popc(fm & ((1u << lane) - 1))] = t;
-#if MUNINN_LIST_AHEAD && MUNINN_PREFETCH
                         /* this chunk's fresh rows start towards L2 while the next chunk is still being probed (narrow rows only:
                          * for 3 KB rows the 24 extra prefetches per row cost more than they hide ‚Äî c3 proxy 13.68 vs 13.32 ms) */
                         if (fresh && base + 32 < p.M0 && p.ld <= 128) {
                             const char *rb = reinterpret_cast<const char *>(p.vec + (size_t)t * (size_t)p.ld);
                             for (int off = 0; off < p.ld * 4; off += 128) prefetch_l2(rb + off);
                         }
-#endif
                         nf += __popc(fm);
                     }
                     n_ins += nf;
                     n_dist += nf;
                     __syncwarp();
-#if MUNINN_PREFETCH
                     if (nf > RB) prefetch_rows(p, sm.Fs + RB, nf - RB, lane); /* the first batch is copied right away */
                     /* wide rows: the first batch's later column blocks would each pay a DRAM round trip */
                     if (p.ld > 128) prefetch_rows(p, sm.Fs, nf < RB ? nf : RB, lane, 512);
-#endif
                     /* distances */
                     for (int b0 = 0; b0 < nf; b0 += RB) {
                         const int nb = nf - b0 < RB ? nf - b0 : RB;
@@ -658,43 +507,6 @@ __global__ void __launch_bounds__(32, MUNINN_SEARCH_MIN_BLOCKS) hnsw_search_kern
                         }
                     }
                     __syncwarp();
-#if MUNINN_LIST_PREFETCH
-                    for (int base = 0; base < nf; base += 32) { /* fresh nodes that will be popped before next_open */
-                        if (base + lane < nf) {
-                            const unsigned long long f = sm.Fk[base + lane];
-                            if (f < next_open) {
-                                const char *nl = reinterpret_cast<const char *>(p.nbr0 + (size_t)((unsigned)f >> 1) * (size_t)p.M0);
-                                for (int off = 0; off < p.M0 * 4; off += 128) prefetch_l2(nl + off);
-                            }
-                        }
-                    }
-#endif
-#if MUNINN_NEXT_PREFETCH
-                    {   /* the next pop is the smaller of (first open entry of R, best fresh key that will
-                         * enter R): start loading its neighbour list now, the merge below hides the latency */
-                        unsigned long long kmin = KEY_NONE;
-                        for (int base = lane; base < nf; base += 32) { unsigned long long f = sm.Fk[base]; kmin = f < kmin ? f : kmin; }
-#pragma unroll
-                        for (int o = 16; o > 0; o >>= 1) { unsigned long long oth = __shfl_xor_sync(FULL, kmin, o); kmin = oth < kmin ? oth : kmin; }
-                        const unsigned long long worst0 = size >= ef ? sm.R[ef - 1] : KEY_NONE;
-                        if (!(kmin < worst0)) kmin = KEY_NONE;
-                        unsigned long long rnext = KEY_NONE;
-                        for (int base = lb & ~31; base < size; base += 32) {
-                            int idx = base + lane;
-                            bool open = idx < size && idx >= lb && !(sm.R[idx] & 1ull);
-                            unsigned om = __ballot_sync(FULL, open);
-                            if (om) { rnext = sm.R[base + __ffs(om) - 1]; break; }
-                        }
-                        const unsigned long long nk = kmin < rnext ? kmin : rnext;
-                        pre_slot = -1;
-                        if (nk != KEY_NONE) {
-                            pre_slot = (int)((unsigned)nk >> 1);
-                            const int32_t *nl = p.nbr0 + (size_t)pre_slot * (size_t)p.M0;
-                            pre_t = lane < p.M0 ? nl[lane] : -1;
-                            if (p.M0 > 32 && lane == 0) prefetch_l2(nl + 32);
-                        }
-                    }
-#endif
                     /* R ‚Üê ef smallest of R ‚à™ F */
                     bool improved = false;
                     for (int base = 0; base < nf; base += 32) {
