@@ -637,8 +637,8 @@ static unsigned log2u(unsigned v) { unsigned l = 0; while ((1u << l) < v) l++; r
  * Two kernels answer the same contract and are tested for identical output in every shape: hnsw_search.cuh (one warp
  * per query, 13-row whole-row tile: 24 query teams per SM, the best throughput for full batches of narrow rows) and
  * hnsw_beam.cuh (query teams of W warps, 16-row batches through a row ring). kernel_gen 0 picks by shape from the
- * measurements in profiles/r2_bench/: teams of 2 warps whenever every query of the batch can be resident at once
- * (a lone MATCH, the 1 250-query slices of a batch split over 8 GPUs: 8-11 % faster), the 16-row kernel for
+ * measurements in profiles/r2_bench/: teams of 4 or 2 warps — the widest at which every query of the batch is resident at once
+ * (a lone MATCH: 4 warps; the 1 250-query slices of a batch split over 8 GPUs: 2 warps, 8-11 % faster than one), the 16-row kernel for
  * ef >= 192 at dim 128 (5 % faster), the 13-row kernel otherwise. MUNINN_KERNEL / muninn_cuda_set_option("kernel_gen")
  * force one for A/B runs. A kernel is picked as a plain function pointer so that occupancy query, attribute and launch
  * share one code path. Ring geometry (U floats per unit, NST stages) per constant-dimension instance: */
@@ -756,12 +756,15 @@ static int search_device_impl(MuninnCudaIndex *h, const float *d_queries, int nq
     {
         const int forced_w = h->warps_per_query, forced_gen = h->kernel_gen;
         int W = forced_w ? forced_w : 1;
-        if (!forced_w && forced_gen != 7) { /* automatic width: 2 warps when the whole batch is resident at that width */
-            KernelSel s2 = select_kernel(h, 8, 2, ef);
-            int o2 = 0;
-            if (s2.smem <= SEARCH_SMEM_LIMIT) {
-                CK(h, occupancy_cached(h, s2, &o2));
-                if (o2 >= 1 && (long long)nq <= (long long)h->num_sms * o2) W = 2;
+        if (!forced_w && forced_gen != 7) {
+            /* automatic width: the widest team at which the whole batch is still resident. 4 warps beat 2 by 2-5 % up to
+             * ≈ 600 queries and lose badly once a second wave is needed (profiles/r2_bench/ab_team_width4.jsonl) */
+            for (int w = 4; w >= 2 && W == 1; w >>= 1) {
+                KernelSel sw = select_kernel(h, 8, w, ef);
+                int ow = 0;
+                if (sw.smem > SEARCH_SMEM_LIMIT) continue;
+                CK(h, occupancy_cached(h, sw, &ow));
+                if (ow >= 1 && (long long)nq <= (long long)h->num_sms * ow) W = w;
             }
         }
         int gen = forced_gen;
