@@ -149,6 +149,27 @@ int muninn_cuda_search_batch(MuninnCudaIndex *idx, const float *queries, int nq,
 int muninn_cuda_search_batch_device(MuninnCudaIndex *idx, const float *d_queries, int nq, int k, int ef,
                                     int64_t *d_ids, float *d_dist, int32_t *d_count, MuninnSearchStats *d_stats);
 
+/*
+ * muninn_cuda_search_batch_device without any allocation. NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it). Same arguments, same results (ids, distances and counts are bit-identical to
+ * muninn_cuda_search_batch_device). The kernels' scratch — work counters, retry lists, per-team visited tables — is a
+ * file-scope device array of 17 301 760 bytes (256 + 512 KiB + 16 MiB) that every GPU which loads the library holds until
+ * the process exits; the call itself issues one 32-byte memset and the search launches on the handle's stream and calls
+ * no cudaMalloc, cudaFree or allocating library routine. Limits, rejected with MUNINN_CUDA_E_ARG and a message in
+ * muninn_cuda_last_error: nq <= 65 536 queries per call; indexes of at most 2 097 118 nodes (the last-resort visited
+ * table of 2(n + 2M + 1) entries, rounded up to a power of two, must fit the 4 Mi-entry arena). Fewer query teams are
+ * resident than with a grown arena (1 024 at ef = 64, M = 16), so large batches run slower than through
+ * muninn_cuda_search_batch_device. ALL calls on one device share the array and it keeps the previous call's contents
+ * (the call clears the counters; tables and lists are written before they are read): calls that overlap on the GPU —
+ * two streams, two handles, two threads — race; serialise them on one stream.
+ */
+int muninn_cuda_search_batch_device_static(MuninnCudaIndex *idx, const float *d_queries, int nq, int k, int ef,
+                                           int64_t *d_ids, float *d_dist, int32_t *d_count, MuninnSearchStats *d_stats);
+/* The limits above, for callers that size their batches against them (any pointer may be NULL). No counterpart in the
+ * reference; added with muninn_cuda_search_batch_device_static. */
+int muninn_cuda_static_scratch_limits(int *max_nq, int64_t *max_nodes, int64_t *bytes);
+
 /* Stream on which the handle launches (a cudaStream_t passed as void*; NULL = the handle's own). */
 int muninn_cuda_set_stream(MuninnCudaIndex *idx, void *stream);
 /* Device time of the handle's most recent search kernel, from CUDA events recorded around

@@ -30,6 +30,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -840,6 +841,143 @@ static int search_device_impl(MuninnCudaIndex *h, const float *d_queries, int nq
     CK(h, cudaEventRecord(h->ev1, h->stream));
     h->have_timing = true;
     h->last_W = sel.W; h->last_gen = sel.gen;
+    return MUNINN_CUDA_OK;
+}
+
+/* ── search without any allocation (muninn_cuda_search_batch_device_static) ──
+ * No counterpart in the reference; added for callers that cannot call cudaMalloc
+ * (CUDA graph capture, tight serving loops). The search kernels' scratch — work counters, retry lists and the per-team
+ * visited tables — lives in ONE file-scope device array of fixed size, which every GPU that loads the library holds until
+ * the process exits:
+ *     [0, 256)                          control words (work counters ×3, retry counts ×2), cleared by every call
+ *     [256, 256 + 2·MAX_NQ·4)           retry lists (queries whose visited table overflowed, per level)
+ *     [.., + VIS_ENTRIES·4)             visited arena: teams × capacity 32-bit entries; every query clears its own table
+ * Every call on a device shares the array: calls that overlap on the GPU (two streams, two handles) race. */
+#define MUNINN_STATIC_MAX_NQ 65536
+#define MUNINN_STATIC_VIS_ENTRIES (4u << 20) /* 16 MiB: 1 024 teams at ef = 64, M = 16; indexes up to 2 097 118 nodes */
+static const size_t STATIC_CTL_BYTES = 256, STATIC_RETRY_BYTES = (size_t)2 * MUNINN_STATIC_MAX_NQ * sizeof(int),
+                    STATIC_VIS_BYTES = (size_t)MUNINN_STATIC_VIS_ENTRIES * sizeof(unsigned);
+static __device__ __align__(256) unsigned char g_static_scratch[256 + (size_t)2 * MUNINN_STATIC_MAX_NQ * sizeof(int) +
+                                                                (size_t)MUNINN_STATIC_VIS_ENTRIES * sizeof(unsigned)];
+
+/* The array's name is only a stand-in on the host: its device address is resolved once per device, with that device current */
+static const int STATIC_MAX_DEVICES = 64;
+static unsigned char *g_static_ptr[STATIC_MAX_DEVICES];
+static std::mutex g_static_mu;
+
+static int static_scratch_address(MuninnCudaIndex *h, unsigned char **out) {
+    if (h->device < 0 || h->device >= STATIC_MAX_DEVICES) return fail(h, MUNINN_CUDA_E_ARG, "device %d: the static scratch is tracked for devices 0..%d", h->device, STATIC_MAX_DEVICES - 1);
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_ptr[h->device]) {
+        void *ptr = nullptr;
+        CK(h, cudaSetDevice(h->device));
+        CK(h, cudaGetSymbolAddress(&ptr, g_static_scratch));
+        if (!ptr) return fail(h, MUNINN_CUDA_E_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch");
+        g_static_ptr[h->device] = (unsigned char *)ptr;
+    }
+    *out = g_static_ptr[h->device];
+    return MUNINN_CUDA_OK;
+}
+
+extern "C" int muninn_cuda_search_batch_device_static(MuninnCudaIndex *h, const float *d_queries, int nq, int k, int ef,
+                                                      int64_t *d_ids, float *d_dist, int32_t *d_count,
+                                                      MuninnSearchStats *d_stats) {
+    if (!h) return MUNINN_CUDA_E_ARG;
+    if (!h->uploaded) return fail(h, MUNINN_CUDA_E_STATE, "search before muninn_cuda_index_upload");
+    if (h->rows_only) return fail(h, MUNINN_CUDA_E_STATE, "this handle holds rows only (muninn_cuda_index_upload_rows): no graph to search");
+    if (nq < 0 || k < 1) return fail(h, MUNINN_CUDA_E_ARG, "nq must be >= 0 and k >= 1 (nq=%d k=%d)", nq, k);
+    if (nq == 0) return MUNINN_CUDA_OK;
+    if (!d_queries || !d_ids || !d_dist || !d_count) return fail(h, MUNINN_CUDA_E_ARG, "NULL buffer");
+    if (nq > MUNINN_STATIC_MAX_NQ)
+        return fail(h, MUNINN_CUDA_E_ARG, "nq=%d exceeds the static scratch's limit of %d queries per call (use muninn_cuda_search_batch_device)", nq, MUNINN_STATIC_MAX_NQ);
+    if (ef < k) ef = k; /* src/hnsw_algo.c:673 */
+    CK(h, cudaSetDevice(h->device));
+
+    /* visited-table capacities exactly as in search_device_impl; the arena is the fixed array instead of a grown allocation */
+    const unsigned cap_all = pow2_at_least(2ull * (unsigned long long)(h->n + h->W0 + 1));
+    if (cap_all > MUNINN_STATIC_VIS_ENTRIES)
+        return fail(h, MUNINN_CUDA_E_ARG, "an index of %lld nodes needs a last-resort visited table of %u entries; the static scratch holds %u "
+                    "(indexes up to about %u nodes; use muninn_cuda_search_batch_device)", (long long)h->n, cap_all, MUNINN_STATIC_VIS_ENTRIES, MUNINN_STATIC_VIS_ENTRIES / 2 - 256);
+    unsigned caps[3];
+    caps[0] = std::min(pow2_at_least((unsigned long long)(h->vis_factor * (double)ef * h->W0)), cap_all);
+    caps[1] = (unsigned)std::min<unsigned long long>(16ull * caps[0], cap_all);
+    caps[2] = cap_all;
+    const int nlevels = caps[0] == cap_all ? 1 : (caps[1] == cap_all ? 2 : 3);
+    const long long arena_teams = MUNINN_STATIC_VIS_ENTRIES / caps[0];
+
+    /* team width and kernel by the same policy as search_device_impl, with "resident" bounded by the arena as well */
+    KernelSel sel;
+    int occ = 0;
+    {
+        const int forced_w = h->warps_per_query, forced_gen = h->kernel_gen;
+        int W = forced_w ? forced_w : 1;
+        if (!forced_w && forced_gen != 7) {
+            for (int w = 4; w >= 2 && W == 1; w >>= 1) {
+                KernelSel sw = select_kernel(h, 8, w, ef);
+                int ow = 0;
+                if (sw.smem > SEARCH_SMEM_LIMIT) continue;
+                CK(h, occupancy_cached(h, sw, &ow));
+                if (ow >= 1 && (long long)nq <= std::min((long long)h->num_sms * ow, arena_teams)) W = w;
+            }
+        }
+        int gen = forced_gen;
+        if (gen == 0) gen = W > 1 ? 8 : ((h->dim == 128 && ef >= 192) ? 8 : 7);
+        if (gen == 7 && W > 1) gen = 8;
+        sel = select_kernel(h, gen, W, ef);
+        if (sel.smem > SEARCH_SMEM_LIMIT && W > 1) { W = 1; sel = select_kernel(h, gen, W, ef); }
+        if (sel.smem > SEARCH_SMEM_LIMIT)
+            return fail(h, MUNINN_CUDA_E_ARG, "ef=%d with dim=%d needs %zu B of shared memory per query (limit 200 KiB)", ef, h->dim, sel.smem);
+        CK(h, occupancy_cached(h, sel, &occ));
+    }
+    if (occ < 1) return fail(h, MUNINN_CUDA_E_CUDA, "search kernel does not fit on an SM");
+    const int tps = h->teams_per_sm > 0 ? std::min(h->teams_per_sm, occ) : occ;
+    int teams[3];
+    teams[0] = (int)std::min<long long>(std::min<long long>((long long)h->num_sms * tps, nq), arena_teams);
+    for (int lv = 1; lv < 3; lv++)
+        teams[lv] = (int)std::max<long long>(1, std::min<long long>(MUNINN_STATIC_VIS_ENTRIES / caps[lv], teams[0]));
+
+    unsigned char *scratch = nullptr;
+    int rc = static_scratch_address(h, &scratch);
+    if (rc) return rc;
+    int *ctl = reinterpret_cast<int *>(scratch);
+    int *retry = reinterpret_cast<int *>(scratch + STATIC_CTL_BYTES);
+    unsigned *vis = reinterpret_cast<unsigned *>(scratch + STATIC_CTL_BYTES + STATIC_RETRY_BYTES);
+    /* the array keeps the previous call's contents: the counters must start at zero (tables and lists are written before read) */
+    CK(h, cudaMemsetAsync(ctl, 0, 8 * sizeof(int), h->stream));
+
+    SearchParams p;
+    memset(&p, 0, sizeof p);
+    p.vec = h->d_vec; p.norm2 = h->d_norm2; p.nbr0 = h->d_nbr0; p.upper_base = h->d_upper_base; p.nbrU = h->d_nbrU;
+    p.deleted = h->d_deleted; p.ids = h->d_ids;
+    p.dim = h->dim; p.ld = h->ld; p.M = h->WU; p.M0 = h->W0; p.entry_slot = h->entry_slot; p.max_level = h->max_level;
+    p.n_live = h->n_live;
+    p.queries = d_queries; p.nq = nq; p.k = k; p.ef = ef;
+    p.patience_max = std::max(ef / 4, 10); /* src/hnsw_algo.c:372-374 */
+    p.out_ids = d_ids; p.out_dist = d_dist; p.out_count = d_count; p.stats = d_stats;
+    p.vis = vis;
+    p.q_arrived = nullptr;
+    for (int lv = 0; lv < nlevels; lv++) {
+        p.vis_cap = caps[lv];
+        p.vis_shift = 32 - log2u(caps[lv]);
+        p.work_counter = ctl + lv;
+        p.in_list = lv == 0 ? nullptr : retry + (size_t)(lv - 1) * nq;
+        p.in_count = lv == 0 ? nullptr : ctl + 3 + (lv - 1);
+        p.out_list = retry + (size_t)(lv < 2 ? lv : 0) * nq;
+        p.out_count_retry = ctl + 3 + lv;
+        int level = lv;
+        void *args[2] = {(void *)&p, (void *)&level};
+        CK(h, cudaLaunchKernel(sel.fn, dim3((unsigned)teams[lv]), dim3((unsigned)(32 * sel.W)), args, sel.smem, h->stream));
+        h->launches++;
+    }
+    h->last_W = sel.W; h->last_gen = sel.gen;
+    return MUNINN_CUDA_OK;
+}
+
+/* limits of muninn_cuda_search_batch_device_static, for callers that size their batches against them */
+extern "C" int muninn_cuda_static_scratch_limits(int *max_nq, int64_t *max_nodes, int64_t *bytes) {
+    if (max_nq) *max_nq = MUNINN_STATIC_MAX_NQ;
+    if (max_nodes) *max_nodes = (int64_t)MUNINN_STATIC_VIS_ENTRIES / 2 - 256;
+    if (bytes) *bytes = (int64_t)(STATIC_CTL_BYTES + STATIC_RETRY_BYTES + STATIC_VIS_BYTES);
     return MUNINN_CUDA_OK;
 }
 

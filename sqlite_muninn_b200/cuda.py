@@ -26,7 +26,8 @@ STATS_DTYPE = np.dtype([("n_dist", np.int64), ("n_dist_upper", np.int64), ("n_ex
 ABI_SYMBOLS = (
     "muninn_cuda_device_count", "muninn_cuda_version", "muninn_cuda_strerror", "muninn_cuda_parse_metric",
     "muninn_cuda_index_create", "muninn_cuda_index_destroy", "muninn_cuda_last_error", "muninn_cuda_index_upload",
-    "muninn_cuda_search_batch", "muninn_cuda_search_batch_device", "muninn_cuda_set_stream",
+    "muninn_cuda_search_batch", "muninn_cuda_search_batch_device", "muninn_cuda_search_batch_device_static",
+    "muninn_cuda_static_scratch_limits", "muninn_cuda_set_stream",
     "muninn_cuda_last_kernel_ms", "muninn_cuda_launch_count", "muninn_cuda_set_tuning", "muninn_cuda_exact_knn",
     "muninn_cuda_exact_knn_device", "muninn_cuda_topk_merge_device", "muninn_cuda_distance_batch",
     "muninn_cuda_set_exact_mode", "muninn_cuda_exact_stats", "muninn_cuda_exact_filter_probe",
@@ -79,6 +80,8 @@ def lib():
         L.muninn_cuda_index_upload.argtypes = [_vp, C.c_int64, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int32, C.c_int32]
         L.muninn_cuda_search_batch.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _vp]
         L.muninn_cuda_search_batch_device.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _vp]
+        L.muninn_cuda_search_batch_device_static.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _vp]
+        L.muninn_cuda_static_scratch_limits.argtypes = [C.POINTER(C.c_int), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
         L.muninn_cuda_set_stream.argtypes = [_vp, _vp]
         L.muninn_cuda_last_kernel_ms.restype = C.c_float
         L.muninn_cuda_last_kernel_ms.argtypes = [_vp]
@@ -137,6 +140,13 @@ def gather_ceiling(row_bytes: int, slab_bytes: int = 1 << 30, device: int = 0) -
     if rc != 0:
         raise MuninnCudaError(rc, lib().muninn_cuda_strerror(rc).decode())
     return float(out.value)
+
+
+def static_scratch_limits() -> dict:
+    """Limits of HnswIndexCuda.search_device_static (muninn_cuda_static_scratch_limits; no counterpart in the reference)."""
+    nq, nodes, nbytes = C.c_int(0), C.c_int64(0), C.c_int64(0)
+    lib().muninn_cuda_static_scratch_limits(C.byref(nq), C.byref(nodes), C.byref(nbytes))
+    return {"max_nq": nq.value, "max_nodes": nodes.value, "bytes": nbytes.value}
 
 
 def comm_unique_id() -> bytes:
@@ -284,6 +294,13 @@ class HnswIndexCuda:
         """Device-resident buffers (raw device addresses), asynchronous on the handle's stream."""
         self._check(self.L.muninn_cuda_search_batch_device(self.h, q_ptr, nq, k, ef, ids_ptr, dist_ptr, cnt_ptr,
                                                            stats_ptr))
+
+    def search_device_static(self, q_ptr: int, nq: int, k: int, ef: int, ids_ptr: int, dist_ptr: int, cnt_ptr: int,
+                             stats_ptr: int | None = None):
+        """search_device on the library's fixed device scratch: allocates nothing (include/muninn_cuda.h,
+        muninn_cuda_search_batch_device_static; no counterpart in the reference). Calls on one device must not overlap."""
+        self._check(self.L.muninn_cuda_search_batch_device_static(self.h, q_ptr, nq, k, ef, ids_ptr, dist_ptr, cnt_ptr,
+                                                                  stats_ptr))
 
     def exact_knn(self, queries, k: int, index_base: int = 0):
         """Brute force over the uploaded rows, ascending (distance, row index)
