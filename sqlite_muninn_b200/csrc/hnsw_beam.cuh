@@ -66,10 +66,11 @@ struct RowRing {
     unsigned phase;
     const int *Fs;
     int nf, wid, W, upb, total, rowf;
+    int rb; /* rows per batch of this call: RB, or an even share of nf when the team has a warp for every share */
 
     __device__ __forceinline__ void issue(const SearchParams &p, int bi, int u, int s, int lane, unsigned long long pol) {
-        const int r0 = (wid + bi * W) * RB;
-        const int nb = nf - r0 < RB ? nf - r0 : RB;
+        const int r0 = (wid + bi * W) * rb;
+        const int nb = nf - r0 < rb ? nf - r0 : rb;
         const int fl = CD ? U : (rowf - u * U < U ? rowf - u * U : U);
         if (lane == 0) bar_expect_tx(bar + s, (unsigned)(nb * fl * 4));
         if (lane < nb)
@@ -82,7 +83,13 @@ struct RowRing {
         Fs = fs; nf = n; wid = warp_id; W = n_warps;
         rowf = CD ? CD : p.ld;
         upb = (rowf + U - 1) / U;
-        const int nbatch = (nf + RB - 1) / RB;
+        /* a team of several warps is there to cut the latency of ONE expansion: when its fresh rows fit one batch per warp
+         * they are dealt out evenly (21 rows over 4 warps: 6 + 6 + 6 + 3 instead of 16 + 5), so that no warp issues more
+         * than its share of the per-row TMA copies — the issue loop, not the memory, was the longest phase of a lone
+         * query's expansion (profiles/r2_bench/lone_query_phases.jsonl) */
+        rb = RB;
+        if (W > 1 && nf <= W * RB) { rb = (nf + W - 1) / W; rb = rb < 1 ? 1 : rb; }
+        const int nbatch = (nf + rb - 1) / rb;
         const int mine = wid < nbatch ? (nbatch - wid + W - 1) / W : 0;
         total = mine * upb;
         int bi = 0, u = 0;
@@ -105,8 +112,8 @@ struct RowRing {
 #pragma unroll
         for (int i = 0; i < NST; i++) { if (++nu == upb) { nu = 0; nbi++; } }
         for (int i = 0; i < total; i++) {
-            const int r0 = (wid + bi * W) * RB;
-            const int nb = nf - r0 < RB ? nf - r0 : RB;
+            const int r0 = (wid + bi * W) * rb;
+            const int nb = nf - r0 < rb ? nf - r0 : rb;
             const bool mine = row < nb;
             if (u == 0) {
                 s01 = 0ull; tl0 = tl1 = tl2 = 0.0f;

@@ -68,6 +68,7 @@ struct MuninnCudaIndex {
     void *h_pinned = nullptr; size_t pinned_bytes = 0;
     size_t occ_smem[4] = {0, 0, 0, 0}; int occ_val[4] = {0, 0, 0, 0}; /* cached occupancy per (generation, team width) */
     int kernel_gen = 0, last_W = 1, last_gen = 7; double vis_factor = MUNINN_VIS_FACTOR; /* kernel_gen 0 = by shape */
+    int tiny_zero_copy = 1; /* host-buffer calls of ≤ 64 KB: the kernel reads and writes pinned host memory directly */
     /* exact k-NN scratch */
     float *d_panel = nullptr; size_t panel_floats = 0;
     unsigned long long *d_topk = nullptr; int *d_topk_size = nullptr; size_t topk_cap = 0, topk_q = 0;
@@ -181,6 +182,7 @@ extern "C" int muninn_cuda_index_create(int device, int dim, int metric, int M, 
     }
     h->stream = h->own_stream;
     /* experiment knobs (A/B runs of one build): same meaning as muninn_cuda_set_option / _set_tuning */
+    if (const char *e = getenv("MUNINN_TINY_ZERO_COPY")) h->tiny_zero_copy = atoi(e) != 0;
     if (const char *e = getenv("MUNINN_KERNEL")) { const int g = atoi(e); if (g == 0 || g == 7 || g == 8) h->kernel_gen = g; }
     if (const char *e = getenv("MUNINN_VIS_FACTOR")) { const double f = atof(e); if (f >= 0.5 && f <= 64.0) h->vis_factor = f; }
     if (const char *e = getenv("MUNINN_WARPS")) { const int w = atoi(e); if (w == 0 || w == 1 || w == 2 || w == 4) h->warps_per_query = w; }
@@ -237,6 +239,8 @@ extern "C" int muninn_cuda_set_option(MuninnCudaIndex *h, const char *name, doub
     } else if (!strcmp(name, "vis_factor")) {
         if (!(value >= 0.5 && value <= 64.0)) return fail(h, MUNINN_CUDA_E_ARG, "vis_factor must be in [0.5, 64]");
         h->vis_factor = value;
+    } else if (!strcmp(name, "tiny_zero_copy")) { /* 0 = stage tiny host batches through copies, as larger ones */
+        h->tiny_zero_copy = value != 0;
     } else if (!strcmp(name, "exact_qs")) { /* 0 = the streaming 1xTF32 filter for every batch size */
         h->tc_qs = value != 0;
     } else if (!strcmp(name, "exact_pair")) { /* 1 = CTA pairs (tcgen05 cta_group::2) in the query-stationary filter */
@@ -1038,6 +1042,19 @@ extern "C" int muninn_cuda_search_batch(MuninnCudaIndex *h, const float *queries
     if (tiny && h->pinned_bytes >= 128 * 1024) {
         char *pin = (char *)h->h_pinned;
         memcpy(pin, queries, in_bytes);
+        if (h->tiny_zero_copy) {
+            /* no copy operations at all: pinned memory is device-visible at the same address (unified addressing), so the
+             * kernel reads the query and writes its k results straight over PCIe — two copy-engine operations and their
+             * cross-engine hand-overs less on a call that is pure latency (profiles/r2_bench/config1_zero_copy.json) */
+            char *res = pin + 64 * 1024;
+            rc = muninn_cuda_search_batch_device(h, (const float *)pin, nq, k, ef, (int64_t *)res, (float *)(res + bi), (int32_t *)(res + bi + bd), nullptr);
+            if (rc) return rc;
+            CK(h, cudaStreamSynchronize(h->stream));
+            memcpy(out_ids, res, (size_t)nq * k * 8);
+            memcpy(out_dist, res + bi, (size_t)nq * k * 4);
+            memcpy(out_count, res + bi + bd, (size_t)nq * 4);
+            return MUNINN_CUDA_OK;
+        }
         CK(h, cudaMemcpyAsync(dq, pin, in_bytes, cudaMemcpyHostToDevice, h->stream));
         rc = muninn_cuda_search_batch_device(h, dq, nq, k, ef, di, dd, dc, nullptr);
         if (rc) return rc;
