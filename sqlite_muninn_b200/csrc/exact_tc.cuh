@@ -750,6 +750,13 @@ __global__ void tc_prep_queries(const float *__restrict__ queries, int dim, int 
     cand_count[q] = 0; topk_size[q] = 0; overflow[q] = 0;
 }
 
+/* τ of every query from its current sorted top-k list (after the dense seed over the first rows, exact_knn_tc) */
+__global__ void tc_seed_tau(const unsigned long long *__restrict__ topk, const int *__restrict__ topk_size, int nq, int k,
+                            float *__restrict__ tau) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q < nq && topk_size[q] >= k) tau[q] = okey_inv((unsigned)(topk[(size_t)q * k + k - 1] >> 32));
+}
+
 /* ───────────── re-rank ───────────── */
 
 /* chained sum of the reference's loop for one (query, row) pair, computed by 4 adjacent lanes:
@@ -857,6 +864,10 @@ exact_tc_rerank(const float *__restrict__ vec, const float *__restrict__ norm2, 
                 xr[u] = vec + (size_t)row[u] * ld;
             }
             quad_chain_multi<METRIC, RU>(qv, xr, have, dim, lane, sum);
+            /* the round's ≤ 32 keys that beat the current k-th go into the list with ONE merge (one per group of 8 rows
+             * cost up to four passes over the list per round: 5.6 of 36.8 ms at k = 100 on the config-5 shard) */
+            const unsigned long long worst = size >= k ? R[k - 1] : KEY_NONE;
+            int ns = 0;
 #pragma unroll
             for (int u = 0; u < RU; u++) {
                 if (c0 + u * 8 >= cnt) break; /* warp-uniform */
@@ -865,13 +876,13 @@ exact_tc_rerank(const float *__restrict__ vec, const float *__restrict__ norm2, 
                 else if (METRIC == METRIC_IP) d = -sum[u];
                 else d = cosine_finish(sum[u], qn2, have[u] ? norm2[row[u]] : 1.0f);
                 const bool live = have[u] && (lane & 3) == 0 && !(deleted && deleted[row[u]]);
-                const unsigned long long worst = size >= k ? R[k - 1] : KEY_NONE;
                 const unsigned long long f = live ? make_key(d, (unsigned)row[u]) : KEY_NONE;
                 const bool keep = f < worst;
                 const unsigned km = __ballot_sync(FULL, keep);
-                const int ns = __popc(km);
-                if (ns == 0) continue;
-                if (keep) S[__popc(km & ((1u << lane) - 1))] = f;
+                if (keep) S[ns + __popc(km & ((1u << lane) - 1))] = f;
+                ns += __popc(km);
+            }
+            if (ns > 0) {
                 __syncwarp();
                 size = warp_merge_sorted(R, size, k, S, ns, lane, &mp, &ev);
             }

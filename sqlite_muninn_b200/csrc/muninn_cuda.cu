@@ -75,6 +75,7 @@ struct MuninnCudaIndex {
     /* exact k-NN, tensor-core filter (exact_tc.cuh) */
     int exact_mode = MUNINN_EXACT_TC_AUTO, tc_tile_rows = 256;
     int tc_qs = 1, tc_qs_min_nq = 1024, tc_superblock_mb = 32, tc_x_stride = 0; /* query-stationary 1xTF32 filter (exact_tc_filter_qs) */
+    int tc_seed_dense = 1; /* large batches: the first chunk (every row survives) is evaluated densely, not filtered + gathered */
     int tc_pair = 0; CUtensorMap tc_map_xh; /* CTA-pair form of the query-stationary filter: row-tile map with 128-row boxes */
     int tc_auto_1x_min_nq = 1 << 30; /* AUTO: batches of at least this many queries still take 3xTF32 (none by default) */
     int exact_mode_run = MUNINN_EXACT_TC_3XTF32; /* what AUTO resolved to for the current call */
@@ -182,6 +183,7 @@ extern "C" int muninn_cuda_index_create(int device, int dim, int metric, int M, 
     }
     h->stream = h->own_stream;
     /* experiment knobs (A/B runs of one build): same meaning as muninn_cuda_set_option / _set_tuning */
+    if (const char *e = getenv("MUNINN_EXACT_SEED_DENSE")) h->tc_seed_dense = atoi(e) != 0;
     if (const char *e = getenv("MUNINN_TINY_ZERO_COPY")) h->tiny_zero_copy = atoi(e) != 0;
     if (const char *e = getenv("MUNINN_KERNEL")) { const int g = atoi(e); if (g == 0 || g == 7 || g == 8) h->kernel_gen = g; }
     if (const char *e = getenv("MUNINN_VIS_FACTOR")) { const double f = atof(e); if (f >= 0.5 && f <= 64.0) h->vis_factor = f; }
@@ -243,6 +245,8 @@ extern "C" int muninn_cuda_set_option(MuninnCudaIndex *h, const char *name, doub
         h->tiny_zero_copy = value != 0;
     } else if (!strcmp(name, "exact_qs")) { /* 0 = the streaming 1xTF32 filter for every batch size */
         h->tc_qs = value != 0;
+    } else if (!strcmp(name, "exact_seed_dense")) { /* 0 = the first chunk goes through the filter and the re-rank like the others */
+        h->tc_seed_dense = value != 0;
     } else if (!strcmp(name, "exact_pair")) { /* 1 = CTA pairs (tcgen05 cta_group::2) in the query-stationary filter */
         h->tc_pair = value != 0;
     } else if (!strcmp(name, "exact_qs_min_nq")) {
@@ -1354,11 +1358,39 @@ static int exact_knn_tc(MuninnCudaIndex *h, const float *d_queries, int nq, int 
 
     int chunks = 0;
     size_t ev_used = 0;
+    const bool seed_dense = h->tc_seed_dense && !small && !d_dbg;
+    long long seeded_rows = 0; /* rows of the dense first chunk: evaluated exactly for every query, like survivors */
     for (long long done = 0; done < n;) {
         /* first chunk: every row survives (τ = +inf), so keep it small but ≥ 2k rows; then double */
         long long chunk = done == 0 ? std::min<long long>(small ? cap / 2 : std::min(cap, std::max(256, (2 * k + 255) / 256 * 256)), n)
                                     : std::min<long long>(std::min((long long)grow_c * done, chunk_max), n - done); /* ×(1+grow_c) per round */
         if (d_dbg) chunk = n;
+        if (done == 0 && seed_dense) {
+            /* Every row of the first chunk survives (τ = +inf), so filtering it is wasted work and re-ranking it row by row
+             * is a gather: evaluate it densely instead — 64 × 64 (query, row) tiles of reference-order chains, then one
+             * selection per query — and take τ from the result. 1M×128×10k: 0.46 ms (filter 0.05 + re-rank 0.42) → see
+             * DESIGN §4.2. Same keys, same order: the list after rows [0, chunk) does not depend on how it was computed. */
+            const int panel_ld = (int)((chunk + XT - 1) / XT * XT);
+            const size_t need = (size_t)nq * (size_t)panel_ld;
+            if (need > h->panel_floats) {
+                CK(h, cudaStreamSynchronize(st));
+                cudaFree(h->d_panel); h->d_panel = nullptr; h->panel_floats = 0;
+                CK(h, cudaMalloc((void **)&h->d_panel, need * 4));
+                h->panel_floats = need;
+            }
+            if (rr_smem > 48 * 1024) CK(h, cudaFuncSetAttribute(exact_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rr_smem));
+            if (h->metric == MUNINN_METRIC_L2) launch_dist_tile<METRIC_L2>(h, 0, (int)chunk, d_queries, nq, panel_ld);
+            else if (h->metric == MUNINN_METRIC_COSINE) launch_dist_tile<METRIC_COSINE>(h, 0, (int)chunk, d_queries, nq, panel_ld);
+            else launch_dist_tile<METRIC_IP>(h, 0, (int)chunk, d_queries, nq, panel_ld);
+            exact_select<<<(nq + 3) / 4, 128, rr_smem, st>>>(h->d_panel, panel_ld, (int)chunk, 0u, nq, k, h->d_topk, h->d_topk_size);
+            tc::tc_seed_tau<<<(nq + 255) / 256, 256, 0, st>>>(h->d_topk, h->d_topk_size, nq, k, h->d_tau);
+            h->launches += 3;
+            CK(h, cudaGetLastError());
+            seeded_rows = chunk;
+            done += chunk;
+            chunks++;
+            continue;
+        }
         h->tc_x_stride = raw_x ? h->ld : kp;
         if (raw_x) {
             rc = make_slab_map(h, &maps[2], h->d_vec + (size_t)done * h->ld, h->ld, chunk, bn);
@@ -1431,7 +1463,7 @@ static int exact_knn_tc(MuninnCudaIndex *h, const float *d_queries, int nq, int 
         fms += ms;
     }
     const int nflag = (int)(unsigned)ctr[1];
-    h->exact_stats.filter_ms = fms; h->exact_stats.candidates = (int64_t)ctr[0]; h->exact_stats.overflow_queries = nflag;
+    h->exact_stats.filter_ms = fms; h->exact_stats.candidates = (int64_t)ctr[0] + (int64_t)nq * seeded_rows; h->exact_stats.overflow_queries = nflag;
     if (nflag > 0) {
         CK(h, grow(&h->d_qgather, &h->qgather_floats, (size_t)nflag * h->dim, st));
         tc::tc_gather_queries<<<(unsigned)(((size_t)nflag * h->dim + 255) / 256), 256, 0, st>>>(d_queries, h->dim, h->d_qmap, nflag,
