@@ -202,6 +202,26 @@ def test_large_host_batches_keep_batch_order(cuda, oracle):
     assert np.array_equal(ids, o[0]) and np.array_equal(dist, o[1])
 
 
+def test_automatic_kernel_choice_never_changes_results(cuda, oracle):
+    """The library picks team width and kernel from the batch size (4-warp teams while every query is resident, then 2,
+    then one warp per query on the ring kernel while the batch fits one wave of it, then the 13-row kernel). Batches
+    straddling each threshold return the oracle's ids, distances, counts and work counters, whatever was picked."""
+    from sqlite_muninn_b200.builder import build_graph
+    base, q = uniform(301, 20_000, 128), uniform(302, 4000, 128)
+    g = build_graph(base, L2, 16, 48, batch=1024, warm=2048)
+    o_ids, o_dist, o_cnt, o_st, _ = oracle.graph(g).search(q, 10, 64, threads=8, canonical=True)
+    seen = set()
+    with cuda.HnswIndexCuda.from_graph(g) as idx:
+        for nq in (1, 7, 148, 592, 593, 1480, 1481, 2960, 2961, 3552, 3553, 4000):
+            ids, dist, cnt, st = idx.search(q[:nq], 10, 64, want_stats=True)
+            seen.add((idx.last_kernel_gen(), idx.last_team_width()))
+            assert np.array_equal(ids, o_ids[:nq]) and np.array_equal(dist, o_dist[:nq]) and np.array_equal(cnt, o_cnt[:nq]), nq
+            for f in ("n_dist", "n_dist_upper", "n_expand", "n_greedy_steps", "entry0"):
+                assert np.array_equal(st[f], o_st[f][:nq]), (f, nq)
+    assert seen <= {(8, 4), (8, 2), (8, 1), (7, 1)} and (8, 4) in seen and (7, 1) in seen, seen
+    assert len(seen) >= 3, seen  # on a 148-SM part all four shapes occur; fewer SMs may skip one
+
+
 @pytest.mark.parametrize("cfg", [3, 4])
 @pytest.mark.parametrize("kernel", ["auto", "8-w1", "8-w2"])
 def test_bench_shapes_at_size_equal_oracle(cuda, oracle, cfg, kernel, monkeypatch):
