@@ -75,6 +75,7 @@ struct MuninnCudaIndex {
     /* exact k-NN, tensor-core filter (exact_tc.cuh) */
     int exact_mode = MUNINN_EXACT_TC_AUTO, tc_tile_rows = 256;
     int tc_qs = 1, tc_qs_min_nq = 1024, tc_superblock_mb = 32, tc_x_stride = 0; /* query-stationary 1xTF32 filter (exact_tc_filter_qs) */
+    int tc_growth = 0; /* large batches: chunk growth factor − 1 (0 = default 2: the rows done grow ×3 per round) */
     int tc_seed_dense = 1; /* large batches: the first chunk (every row survives) is evaluated densely, not filtered + gathered */
     int tc_pair = 0; CUtensorMap tc_map_xh; /* CTA-pair form of the query-stationary filter: row-tile map with 128-row boxes */
     int tc_auto_1x_min_nq = 1 << 30; /* AUTO: batches of at least this many queries still take 3xTF32 (none by default) */
@@ -183,6 +184,7 @@ extern "C" int muninn_cuda_index_create(int device, int dim, int metric, int M, 
     }
     h->stream = h->own_stream;
     /* experiment knobs (A/B runs of one build): same meaning as muninn_cuda_set_option / _set_tuning */
+    if (const char *e = getenv("MUNINN_EXACT_GROWTH")) h->tc_growth = std::max(0, std::min(31, atoi(e)));
     if (const char *e = getenv("MUNINN_EXACT_SEED_DENSE")) h->tc_seed_dense = atoi(e) != 0;
     if (const char *e = getenv("MUNINN_TINY_ZERO_COPY")) h->tiny_zero_copy = atoi(e) != 0;
     if (const char *e = getenv("MUNINN_KERNEL")) { const int g = atoi(e); if (g == 0 || g == 7 || g == 8) h->kernel_gen = g; }
@@ -1293,7 +1295,7 @@ static int exact_knn_tc(MuninnCudaIndex *h, const float *d_queries, int nq, int 
      * chunk growth, i.e. 4-5 chunks instead of 9 over millions of rows */
     const bool small = !d_dbg && nq < 1024 && k <= 512 && h->ld <= 4096; /* the CTA re-rank's shared memory: 64 KB of keys + 132 KB of row tiles + the query */
     const int cap = d_dbg ? 256 : small ? 4096 : std::max(1024, (4 * k + 255) / 256 * 256);
-    const int grow_c = small ? std::min(31, std::max(3, 2 * cap / (5 * k))) : 3; /* expected survivors per chunk ≈ grow_c·k */
+    const int grow_c = small ? std::min(31, std::max(3, 2 * cap / (5 * k))) : (h->tc_growth > 0 ? h->tc_growth : 2); /* expected survivors per chunk ≈ grow_c·k; ×3 per round beat ×4 and ×2 */
     const long long n = d_dbg ? dbg_rows : h->n;
     /* row scratch: ≤ 1 GiB of split slabs per chunk, whole tiles (none when the slab is read raw) */
     long long chunk_max = raw_x ? (1ll << 40) : (long long)((1ull << 30) / ((size_t)kp * 4 * (three ? 2 : 1)));
