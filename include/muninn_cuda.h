@@ -188,7 +188,10 @@ int muninn_cuda_last_kernel_gen(const MuninnCudaIndex *idx);
  * shape), 7 (hnsw_search.cuh: one warp per query, 13-row tile) or 8 (hnsw_beam.cuh: teams of 1/2/4 warps, 16-row
  * batches); "vis_factor" = size of a team's
  * first-level visited table in units of ef·2M entries (default 2); "exact_qs" (1/0), "exact_qs_min_nq",
- * "exact_superblock_mb", "exact_auto_3x_min_nq": shape of the exact k-NN tensor-core filter. */
+ * "exact_superblock_mb", "exact_auto_3x_min_nq", "exact_seed_dense" (1/0: the first chunk of rows evaluated densely
+ * instead of filtered and gathered): shape of the exact k-NN path; "vis_in_smem" (1/0): teams of several warps keep
+ * their first-level visited table in shared memory when it fits; "tiny_zero_copy" (1/0): host batches of at most
+ * 64 KB are read and written by the kernel straight from pinned host memory, without copy operations. */
 int muninn_cuda_set_option(MuninnCudaIndex *idx, const char *name, double value);
 
 /*

@@ -35,18 +35,82 @@ namespace muninn {
 namespace beam {
 
 constexpr int RB = 16;     /* rows per batch: two lanes per row, chains (2h, 2h+1) packed as f32x2 */
+constexpr int DBB = 16;    /* valid entries of an upper-layer list evaluated per step of the greedy descent: a whole list at M ≤ 16, so a
+                            * step that finds no improvement is one round trip, not two (the one-warp kernel's DB = 8 suits its 4-lane rows) */
 constexpr int LIST_CH = 2; /* 32-entry chunks of a neighbour list requested up front (M0 ≤ 64; longer lists read the rest in the loop) */
 
 __host__ __device__ inline size_t a16(size_t v) { return (v + 15) & ~(size_t)15; }
 
+__host__ __device__ inline int fk_len(int M0) { return fs_pos(M0) > DBB ? fs_pos(M0) : DBB; } /* keys of one expansion, or of one descent step */
+
 __host__ __device__ inline size_t smem_bytes(int ef, int ld, int M0, int U, int NST, int W) {
-    size_t b = a16((size_t)ef * 8) + (size_t)fs_pos(M0) * 8 + 32 * 8;
+    size_t b = a16((size_t)ef * 8) + (size_t)fk_len(M0) * 8 + 32 * 8;
     b += a16((size_t)ld * 4);
     b += (size_t)W * NST * RB * (U + 4) * 4;
-    b += a16((size_t)fs_len(M0) * 4);
+    b += a16((size_t)(fs_pos(M0) + DBB) * 4);
     b += a16((size_t)W * NST * 8);
     b += 16; /* team control words */
     return b;
+}
+
+/* Visited test-and-set on a table in SHARED memory (one key per lane, open addressing, linear probing, claim by
+ * compare-and-swap): what the small-batch teams use at level 0. The global-memory table costs a lone query ≈ 1 600 of
+ * its ≈ 6 700 cycles per expansion — a warp-wide gather of 32 scattered buckets from L2 (≈ 800 cycles: the slowest of 32
+ * requests) and a match.any to order the claims (≈ 450) — profiles/r2_bench/lone_query_phases.jsonl; in shared memory
+ * both are tens of cycles. Same membership semantics, so the results cannot differ. */
+__device__ __forceinline__ int visited_test_and_set_smem(unsigned *tab, unsigned cap_mask, unsigned shift, int t, bool valid) {
+    int fresh = 0;
+    if (valid) {
+        unsigned i = ((unsigned)t * 2654435761u) >> shift;
+        for (;;) { /* ends: the caller keeps the load ≤ 3/4 */
+            const unsigned old = atomicCAS(tab + i, VIS_EMPTY, (unsigned)t);
+            if (old == VIS_EMPTY) { fresh = 1; break; }
+            if (old == (unsigned)t) break;
+            i = (i + 1) & cap_mask;
+        }
+    }
+    __syncwarp();
+    return fresh;
+}
+
+/* warp_merge_sorted (muninn_dev.cuh) for lists of at most 64 keys, as the small-batch teams use it: same contract, same
+ * result. Both 32-key halves of R sit in registers, so the rank of every new key in R comes out of two ballots per key
+ * instead of a binary search through shared memory, the shift of every old key out of the same comparisons, and nothing
+ * is read after the first write — one pass, two barriers (the general routine: ≈ 1 400 cycles per expansion of a lone
+ * query, profiles/r2_bench/lone_query_phases.jsonl). */
+__device__ __forceinline__ int warp_merge_sorted64(unsigned long long *R, int size, int cap, const unsigned long long *S,
+                                                   int ns, int lane, int *min_pos, int *evicted_open) {
+    const unsigned long long r0 = lane < size ? R[lane] : KEY_NONE, r1 = 32 + lane < size ? R[32 + lane] : KEY_NONE;
+    const unsigned long long f = lane < ns ? S[lane] : KEY_NONE;
+    int c0 = 0, c1 = 0, rF = 0, rR = 0, mp = 0x7fffffff;
+    for (int i = 0; i < ns; i++) {
+        const unsigned long long fi = S[i];
+        const int below = __popc(__ballot_sync(FULL, r0 < fi)) + __popc(__ballot_sync(FULL, r1 < fi)); /* rank of key i in R */
+        c0 += fi < r0 ? 1 : 0;
+        c1 += fi < r1 ? 1 : 0;
+        rF += fi < f ? 1 : 0;
+        if (i == lane) rR = below;
+        mp = below < mp ? below : mp;
+    }
+    __syncwarp();
+    int ev = 0;
+    if (lane < size && c0 > 0) {
+        if (lane + c0 < cap) R[lane + c0] = r0;
+        else if (!(r0 & 1ull)) ev = 1;
+    }
+    if (32 + lane < size && c1 > 0) {
+        if (32 + lane + c1 < cap) R[32 + lane + c1] = r1;
+        else if (!(r1 & 1ull)) ev = 1;
+    }
+    if (lane < ns) {
+        if (rR + rF < cap) R[rR + rF] = f;
+        else ev = 1; /* a new key that does not fit is an open candidate the reference would have queued */
+    }
+    __syncwarp();
+    if (__any_sync(FULL, ev)) *evicted_open = 1;
+    *min_pos = mp;
+    const int nsz = size + ns;
+    return nsz < cap ? nsz : cap;
 }
 
 /* whole row (or its tail) towards L2 with one TMA prefetch */
@@ -192,17 +256,19 @@ __global__ void __launch_bounds__(32 * W, MinBlocks<W>::v) hnsw_beam_kernel(cons
     float *q;
     int *Fs;
     volatile int *ctl;
+    unsigned *stab; /* the visited table in shared memory, when SearchParams::vis_smem gives it room */
     Ring ring;
     {
         unsigned char *b = smem_raw;
         R = reinterpret_cast<unsigned long long *>(b); b += a16((size_t)p.ef * 8);
-        Fk = reinterpret_cast<unsigned long long *>(b); b += (size_t)fs_pos(p.M0) * 8; /* ≥ DB keys for the descent */
+        Fk = reinterpret_cast<unsigned long long *>(b); b += (size_t)fk_len(p.M0) * 8;
         S = reinterpret_cast<unsigned long long *>(b); b += 32 * 8;
         q = reinterpret_cast<float *>(b); b += a16((size_t)p.ld * 4);
         ring.P = reinterpret_cast<float *>(b) + (size_t)warp * NST * RB * Ring::PS; b += (size_t)W * NST * RB * Ring::PS * 4;
-        Fs = reinterpret_cast<int *>(b); b += a16((size_t)fs_len(p.M0) * 4);
+        Fs = reinterpret_cast<int *>(b); b += a16((size_t)(fs_pos(p.M0) + DBB) * 4); /* fresh slots; the descent keeps list positions at Fs[FP + i] */
         ring.bar = reinterpret_cast<unsigned long long *>(b) + warp * NST; b += a16((size_t)W * NST * 8);
-        ctl = reinterpret_cast<volatile int *>(b);
+        ctl = reinterpret_cast<volatile int *>(b); b += 16;
+        stab = reinterpret_cast<unsigned *>(b);
         ring.phase = 0u;
     }
     if (lane == 0) {
@@ -211,7 +277,9 @@ __global__ void __launch_bounds__(32 * W, MinBlocks<W>::v) hnsw_beam_kernel(cons
     }
     team_sync<W>();
 
-    unsigned *tab = p.vis + (size_t)blockIdx.x * (size_t)p.vis_cap;
+    const bool svis = W > 1 && level == 0 && p.vis_smem > 0;
+    unsigned *tab = svis ? stab : p.vis + (size_t)blockIdx.x * (size_t)p.vis_cap;
+    const unsigned cap_mask = p.vis_cap - 1;
     const int nwork = level == 0 ? p.nq : *p.in_count;
     const int ef = p.ef, FP = fs_pos(p.M0);
     const unsigned long long pol = l2_evict_first_policy();
@@ -240,7 +308,8 @@ __global__ void __launch_bounds__(32 * W, MinBlocks<W>::v) hnsw_beam_kernel(cons
         {
             uint4 *t4 = reinterpret_cast<uint4 *>(tab);
             const uint4 e = make_uint4(VIS_EMPTY, VIS_EMPTY, VIS_EMPTY, VIS_EMPTY);
-            for (unsigned i = threadIdx.x; i < (p.vis_cap >> 2); i += NT) __stcg(t4 + i, e);
+            if (svis) for (unsigned i = threadIdx.x; i < (p.vis_cap >> 2); i += NT) t4[i] = e;
+            else for (unsigned i = threadIdx.x; i < (p.vis_cap >> 2); i += NT) __stcg(t4 + i, e);
         }
         team_sync<W>();
         float qn2 = 0.0f;
@@ -270,20 +339,20 @@ __global__ void __launch_bounds__(32 * W, MinBlocks<W>::v) hnsw_beam_kernel(cons
                     changed = false;
                     n_greedy++;
                     int i0 = 0;
-                    /* scan positions i0.. of cur's list in order, DB valid entries at a time; on the first
+                    /* scan positions i0.. of cur's list in order, DBB valid entries at a time; on the first
                      * improvement switch node and keep counting positions (:267-279) */
                     for (;;) {
                         const int32_t *lst = p.nbrU + ((size_t)p.upper_base[cur] + (size_t)(l - 1)) * (size_t)p.M;
                         int nb = 0, last_pos = p.M;
-                        for (int base = i0; base < p.M && nb < DB; base += 32) {
+                        for (int base = i0; base < p.M && nb < DBB; base += 32) {
                             const int pos = base + lane;
                             const int t = pos < p.M ? lst[pos] : -1;
                             const unsigned vm = __ballot_sync(FULL, t >= 0);
                             const int r = __popc(vm & ((1u << lane) - 1));
-                            if (t >= 0 && nb + r < DB) { Fs[nb + r] = t; Fs[FP + nb + r] = pos; }
+                            if (t >= 0 && nb + r < DBB) { Fs[nb + r] = t; Fs[FP + nb + r] = pos; }
                             nb += __popc(vm);
                         }
-                        if (nb > DB) nb = DB;
+                        if (nb > DBB) nb = DBB;
                         __syncwarp();
                         if (nb == 0) break;
                         last_pos = Fs[FP + nb - 1];
@@ -315,7 +384,8 @@ __global__ void __launch_bounds__(32 * W, MinBlocks<W>::v) hnsw_beam_kernel(cons
                 n_dist++;
                 if (lane == 0) R[0] = ((unsigned long long)cur_k << 32) | ((unsigned)cur << 1);
                 size = 1;
-                visited_test_and_set(p, tab, cur, lane == 0, lane);
+                if (svis) visited_test_and_set_smem(tab, cap_mask, p.vis_shift, cur, lane == 0);
+                else visited_test_and_set(p, tab, cur, lane == 0, lane);
                 __syncwarp();
                 run_beam = true;
             }
@@ -357,7 +427,7 @@ __global__ void __launch_bounds__(32 * W, MinBlocks<W>::v) hnsw_beam_kernel(cons
                             t[ch] = pos0 < p.M0 ? lst[pos0] : -1;
                         }
                         /* lists of more than 32 entries: the second chunk's visited buckets move towards L2 while the first is probed */
-                        if (LIST_CH > 1 && p.M0 > 32 && t[1] >= 0)
+                        if (!svis && LIST_CH > 1 && p.M0 > 32 && t[1] >= 0)
                             prefetch_l2(tab + (size_t)((((unsigned)t[1] * 2654435761u) >> p.vis_shift) & ~3u));
                         /* visited filter → fresh slots */
                         nf = 0;
@@ -367,7 +437,8 @@ __global__ void __launch_bounds__(32 * W, MinBlocks<W>::v) hnsw_beam_kernel(cons
                             if (base == 0) tt = t[0];
                             else if (LIST_CH > 1 && base == 32) tt = t[1];
                             else tt = pos0 < p.M0 ? lst[pos0] : -1;
-                            const int fresh = visited_test_and_set(p, tab, tt, tt >= 0, lane);
+                            const int fresh = svis ? visited_test_and_set_smem(tab, cap_mask, p.vis_shift, tt, tt >= 0)
+                                                   : visited_test_and_set(p, tab, tt, tt >= 0, lane);
                             const unsigned fm = __ballot_sync(FULL, fresh);
                             if (fresh) Fs[nf + __popc(fm & ((1u << lane) - 1))] = tt;
                             nf += __popc(fm);
@@ -412,7 +483,8 @@ __global__ void __launch_bounds__(32 * W, MinBlocks<W>::v) hnsw_beam_kernel(cons
                     if (keep) S[__popc(km & ((1u << lane) - 1))] = f;
                     __syncwarp();
                     int mp;
-                    size = warp_merge_sorted(R, size, ef, S, ns, lane, &mp, &evicted_open);
+                    size = (W > 1 && ef <= 64) ? warp_merge_sorted64(R, size, ef, S, ns, lane, &mp, &evicted_open)
+                                               : warp_merge_sorted(R, size, ef, S, ns, lane, &mp, &evicted_open);
                     lb = mp < lb ? mp : lb;
                 }
                 stale = improved ? 0 : stale + 1; /* :428-432 */

@@ -78,6 +78,9 @@ struct SearchParams {
     /* host-buffer entry, large batches: queries [0, *q_arrived) have landed in `queries` (written by the copy engine behind
      * each slice of the host→device copy); NULL = all of them. The kernel starts on the first slice while the rest streams in. */
     const unsigned *q_arrived;
+    /* team kernels (hnsw_beam.cuh, W > 1), level 0: bytes of shared memory behind the team's other buffers that hold its
+     * visited table (= vis_cap · 4), or 0 = the table lives in the global arena like everywhere else */
+    int vis_smem;
 };
 
 struct TeamSmem {

@@ -30,6 +30,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -66,7 +67,8 @@ struct MuninnCudaIndex {
     /* staging for the host-buffer entry points */
     void *d_stage = nullptr; size_t stage_bytes = 0;
     void *h_pinned = nullptr; size_t pinned_bytes = 0;
-    size_t occ_smem[4] = {0, 0, 0, 0}; int occ_val[4] = {0, 0, 0, 0}; /* cached occupancy per (generation, team width) */
+    size_t occ_smem[6] = {0, 0, 0, 0, 0, 0}; int occ_val[6] = {0, 0, 0, 0, 0, 0}; /* cached occupancy per (generation, team width[, table in shared memory]) */
+    int vis_in_smem = 1; /* small-batch teams keep their first-level visited table in shared memory when it fits */
     int kernel_gen = 0, last_W = 1, last_gen = 7; double vis_factor = MUNINN_VIS_FACTOR; /* kernel_gen 0 = by shape */
     int tiny_zero_copy = 1; /* host-buffer calls of ≤ 64 KB: the kernel reads and writes pinned host memory directly */
     /* exact k-NN scratch */
@@ -184,6 +186,7 @@ extern "C" int muninn_cuda_index_create(int device, int dim, int metric, int M, 
     }
     h->stream = h->own_stream;
     /* experiment knobs (A/B runs of one build): same meaning as muninn_cuda_set_option / _set_tuning */
+    if (const char *e = getenv("MUNINN_VIS_SMEM")) h->vis_in_smem = atoi(e) != 0;
     if (const char *e = getenv("MUNINN_EXACT_GROWTH")) h->tc_growth = std::max(0, std::min(31, atoi(e)));
     if (const char *e = getenv("MUNINN_EXACT_SEED_DENSE")) h->tc_seed_dense = atoi(e) != 0;
     if (const char *e = getenv("MUNINN_TINY_ZERO_COPY")) h->tiny_zero_copy = atoi(e) != 0;
@@ -243,6 +246,8 @@ extern "C" int muninn_cuda_set_option(MuninnCudaIndex *h, const char *name, doub
     } else if (!strcmp(name, "vis_factor")) {
         if (!(value >= 0.5 && value <= 64.0)) return fail(h, MUNINN_CUDA_E_ARG, "vis_factor must be in [0.5, 64]");
         h->vis_factor = value;
+    } else if (!strcmp(name, "vis_in_smem")) { /* 0 = the teams' visited tables stay in the global arena */
+        h->vis_in_smem = value != 0;
     } else if (!strcmp(name, "tiny_zero_copy")) { /* 0 = stage tiny host batches through copies, as larger ones */
         h->tiny_zero_copy = value != 0;
     } else if (!strcmp(name, "exact_qs")) { /* 0 = the streaming 1xTF32 filter for every batch size */
@@ -682,6 +687,7 @@ struct KernelSel {
     const void *fn = nullptr;
     int gen = 8, W = 1, U = 0, NST = 0;
     size_t smem = 0;
+    size_t vis_smem = 0; /* part of smem that holds the team's first-level visited table (SearchParams::vis_smem) */
 };
 
 template <int METRIC, int W>
@@ -722,12 +728,27 @@ static KernelSel select_kernel(const MuninnCudaIndex *h, int gen, int W, int ef)
     return k;
 }
 
+/* The dynamic shared memory a kernel function may be launched with is a property of the FUNCTION on a device, shared by
+ * every handle of the process, and one function serves launches of different sizes (other ef, with or without the
+ * visited table in shared memory): the limit is only ever raised, under a lock, and remembered per (device, function). */
+static cudaError_t allow_dynamic_smem(int device, const void *fn, size_t bytes) {
+    static std::mutex mu;
+    static std::map<std::pair<int, const void *>, size_t> allowed;
+    std::lock_guard<std::mutex> lock(mu);
+    size_t &cur = allowed[std::make_pair(device, fn)];
+    if (bytes <= cur) return cudaSuccess;
+    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e == cudaSuccess) cur = bytes;
+    return e;
+}
+
 /* resident teams per SM of a selection, cached per (generation, W, shared-memory size) */
 static cudaError_t occupancy_cached(MuninnCudaIndex *h, const KernelSel &k, int *occ) {
-    const int wi = k.gen == 7 ? 3 : (k.W == 4 ? 2 : k.W == 2 ? 1 : 0);
-    if (h->occ_smem[wi] == k.smem && h->occ_val[wi] > 0) { *occ = h->occ_val[wi]; return cudaSuccess; }
-    cudaError_t e = cudaFuncSetAttribute(k.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k.smem);
+    const int fi = k.gen == 7 ? 3 : (k.W == 4 ? 2 : k.W == 2 ? 1 : 0);
+    const int wi = k.vis_smem && k.W > 1 ? (k.W == 4 ? 4 : 5) : fi; /* the cache slot */
+    cudaError_t e = allow_dynamic_smem(h->device, k.fn, k.smem);
     if (e != cudaSuccess) return e;
+    if (h->occ_smem[wi] == k.smem && h->occ_val[wi] > 0) { *occ = h->occ_val[wi]; return cudaSuccess; }
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k.fn, 32 * k.W, k.smem);
     if (e != cudaSuccess) return e;
     h->occ_smem[wi] = k.smem; h->occ_val[wi] = *occ;
@@ -735,6 +756,7 @@ static cudaError_t occupancy_cached(MuninnCudaIndex *h, const KernelSel &k, int 
 }
 
 static const size_t SEARCH_SMEM_LIMIT = 200 * 1024;
+static const size_t VIS_SMEM_MAX = 64 * 1024; /* largest first-level visited table a team keeps in shared memory (ef = 256 at M = 16) */
 
 static int search_device_impl(MuninnCudaIndex *h, const float *d_queries, int nq, int k, int ef, int64_t *d_ids, float *d_dist,
                               int32_t *d_count, MuninnSearchStats *d_stats, const unsigned *d_arrived);
@@ -767,16 +789,28 @@ static int search_device_impl(MuninnCudaIndex *h, const float *d_queries, int nq
     {
         const int forced_w = h->warps_per_query, forced_gen = h->kernel_gen;
         int W = forced_w ? forced_w : 1;
+        /* the teams of several warps can keep their first-level visited table (sized as below) in shared memory */
+        const size_t tbl = (size_t)std::min(pow2_at_least((unsigned long long)(h->vis_factor * (double)ef * h->W0)),
+                                            pow2_at_least(2ull * (unsigned long long)(h->n + h->W0 + 1))) * 4;
+        const bool tbl_ok = h->vis_in_smem && tbl <= VIS_SMEM_MAX;
+        bool use_tbl = false;
         if (!forced_w && forced_gen != 7) {
-            /* automatic width: the widest team at which the whole batch is still resident. 4 warps beat 2 by 2-5 % up to
-             * ≈ 600 queries and lose badly once a second wave is needed (profiles/r2_bench/ab_team_width4.jsonl) */
+            /* automatic width: the widest team at which the whole batch is still resident — with the table in shared
+             * memory if the batch is still resident at the occupancy that leaves, else without. 4 warps beat 2 by 2-5 % up
+             * to ≈ 600 queries and lose badly once a second wave is needed (profiles/r2_bench/ab_team_width4.jsonl) */
             for (int w = 4; w >= 2 && W == 1; w >>= 1) {
-                KernelSel sw = select_kernel(h, 8, w, ef);
-                int ow = 0;
-                if (sw.smem > SEARCH_SMEM_LIMIT) continue;
-                CK(h, occupancy_cached(h, sw, &ow));
-                if (ow >= 1 && (long long)nq <= (long long)h->num_sms * ow) W = w;
+                for (int with_tbl = tbl_ok ? 1 : 0; with_tbl >= 0 && W == 1; with_tbl--) {
+                    KernelSel sw = select_kernel(h, 8, w, ef);
+                    if (with_tbl) { sw.vis_smem = tbl; sw.smem += tbl; }
+                    int ow = 0;
+                    if (sw.smem > SEARCH_SMEM_LIMIT) continue;
+                    CK(h, occupancy_cached(h, sw, &ow));
+                    if (ow >= 1 && (long long)nq <= (long long)h->num_sms * ow) { W = w; use_tbl = with_tbl != 0; }
+                }
             }
+        } else if (forced_w > 1 && tbl_ok) {
+            KernelSel sw = select_kernel(h, 8, forced_w, ef);
+            use_tbl = sw.smem + tbl <= SEARCH_SMEM_LIMIT;
         }
         int gen = forced_gen;
         if (gen == 0) gen = W > 1 ? 8 : ((h->dim == 128 && ef >= 192) ? 8 : 7);
@@ -795,6 +829,7 @@ static int search_device_impl(MuninnCudaIndex *h, const float *d_queries, int nq
         if (sel.smem > SEARCH_SMEM_LIMIT && W > 1) { W = 1; sel = select_kernel(h, gen, W, ef); }
         if (sel.smem > SEARCH_SMEM_LIMIT)
             return fail(h, MUNINN_CUDA_E_ARG, "ef=%d with dim=%d needs %zu B of shared memory per query (limit 200 KiB)", ef, h->dim, sel.smem);
+        if (use_tbl && sel.gen == 8 && sel.W > 1 && sel.smem + tbl <= SEARCH_SMEM_LIMIT) { sel.vis_smem = tbl; sel.smem += tbl; }
         CK(h, occupancy_cached(h, sel, &occ));
     }
     if (occ < 1) return fail(h, MUNINN_CUDA_E_CUDA, "search kernel does not fit on an SM");
@@ -843,6 +878,7 @@ static int search_device_impl(MuninnCudaIndex *h, const float *d_queries, int nq
     p.out_ids = d_ids; p.out_dist = d_dist; p.out_count = d_count; p.stats = d_stats;
     p.vis = h->d_vis;
     p.q_arrived = d_arrived;
+    p.vis_smem = (int)sel.vis_smem; /* caps[0] · 4 by construction: the kernel uses it at level 0 only */
 
     CK(h, cudaEventRecord(h->ev0, h->stream));
     for (int lv = 0; lv < nlevels; lv++) {

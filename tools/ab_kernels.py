@@ -4,7 +4,7 @@
   MUNINN_CUDA_SO=…/libmuninn_cuda_x.so python tools/ab_kernels.py --config 2 --ef 64,256 --nq 10000,1250,1 \
         --set 8:1:2:0 --set 8:2:2:0 --set 7:1:2:0 [--n 200000]
 
---set gen:W:vis_factor:teams_per_sm. For every (set, ef, nq): median / min kernel time over --reps launches
+--set gen:W:vis_factor:teams_per_sm[:vis_in_smem]. For every (set, ef, nq): median / min kernel time over --reps launches
 (CUDA events around the launch, muninn_cuda_last_kernel_ms), algorithmic GB/s from the kernel's own counters,
 and a checksum of the returned ids so that every shape can be seen to return the same answer. JSON lines.
 """
@@ -46,7 +46,8 @@ def main():
     sets = a.set or ["8:0:2:0"]
     with HnswIndexCuda.from_graph(g) as idx:
         for s in sets:
-            gen, W, vf, tps = s.split(":")
+            gen, W, vf, tps, vs = (s.split(":") + ["1"])[:5]
+            idx.set_option("vis_in_smem", int(vs))
             idx.set_option("kernel_gen", int(gen))
             idx.set_option("vis_factor", float(vf))
             idx.set_tuning(1 if int(gen) == 7 else int(W), int(tps))

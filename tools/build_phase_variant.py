@@ -77,4 +77,19 @@ rp('''                    p.out_dist[(size_t)qi * p.k + i] = d;
 ''','''                    p.out_dist[(size_t)qi * p.k + i] = i < 10 ? (float)T[i] : (float)(clock64() - tq0);
 ''')
 open(p,'w').write(s)
+if os.environ.get("PHASE_VISITED"):
+    # optional: split the visited test-and-set further (bucket load / match.any / the rest) into out_dist[11..14), k >= 14
+    p2=D+'/sqlite_muninn_b200/csrc/hnsw_search.cuh'
+    t=open(p2).read()
+    def rp2(a,b,c=1):
+        global t
+        assert t.count(a)==c,(a,t.count(a)); t=t.replace(a,b)
+    rp2('__device__ __forceinline__ int visited_test_and_set(', '__device__ long long g_vis_dbg[4];\n__device__ __forceinline__ int visited_test_and_set(')
+    rp2('    while (__any_sync(FULL, active)) {\n        bool claim = false;', '    while (__any_sync(FULL, active)) {\n        long long v0_ = clock64();\n        bool claim = false;')
+    rp2('        const unsigned cm = __ballot_sync(FULL, claim);\n        if (claim) {\n            const unsigned peers = __match_any_sync(cm, b);',
+        '        const unsigned cm = __ballot_sync(FULL, claim);\n        long long v1_ = clock64();\n        if (lane == 0) { g_vis_dbg[0] += v1_ - v0_; g_vis_dbg[3] += 1; }\n        if (claim) {\n            const unsigned peers = __match_any_sync(cm, b);\n            if (peers == 0xdeadbeefu) g_vis_dbg[2]++;\n            { long long v2_ = clock64(); if (lane == 0 || (cm & ((1u << lane) - 1)) == 0) g_vis_dbg[1] += v2_ - v1_; }')
+    open(p2,'w').write(t)
+    rp("p.out_dist[(size_t)qi * p.k + i] = i < 10 ? (float)T[i] : (float)(clock64() - tq0);",
+       "p.out_dist[(size_t)qi * p.k + i] = i < 10 ? (float)T[i] : i == 10 ? (float)(clock64() - tq0) : (float)g_vis_dbg[(i - 11) & 3];")
+    open(p,'w').write(s)
 subprocess.check_call('nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -shared -o %s/sqlite_muninn_b200/csrc/libmuninn_cuda_phase.so muninn_cuda.cu' % R, shell=True, cwd=D+'/sqlite_muninn_b200/csrc')
