@@ -157,8 +157,9 @@ int muninn_cuda_search_batch_device(MuninnCudaIndex *idx, const float *d_queries
  * file-scope device array of 17 301 760 bytes (256 + 512 KiB + 16 MiB) that every GPU which loads the library holds until
  * the process exits; the call itself issues one 32-byte memset and the search launches on the handle's stream and calls
  * no cudaMalloc, cudaFree or allocating library routine. Limits, rejected with MUNINN_CUDA_E_ARG and a message in
- * muninn_cuda_last_error: nq <= 65 536 queries per call; indexes of at most 2 097 118 nodes (the last-resort visited
- * table of 2(n + 2M + 1) entries, rounded up to a power of two, must fit the 4 Mi-entry arena). Fewer query teams are
+ * muninn_cuda_last_error: nq <= 65 536 queries per call; indexes of at most 2 097 119 nodes at M = 16, in general
+ * n + 2M + 1 <= 2 097 152 (the last-resort visited table of 2(n + 2M + 1) entries, rounded up to a power of two, must
+ * fit the 4 Mi-entry arena; muninn_cuda_static_scratch_limits reports 2 096 896, safe for every M). Fewer query teams are
  * resident than with a grown arena (1 024 at ef = 64, M = 16), so large batches run slower than through
  * muninn_cuda_search_batch_device. ALL calls on one device share the array and it keeps the previous call's contents
  * (the call clears the counters; tables and lists are written before they are read): calls that overlap on the GPU —

@@ -910,7 +910,7 @@ static int search_device_impl(MuninnCudaIndex *h, const float *d_queries, int nq
  *     [.., + VIS_ENTRIES·4)             visited arena: teams × capacity 32-bit entries; every query clears its own table
  * Every call on a device shares the array: calls that overlap on the GPU (two streams, two handles) race. */
 #define MUNINN_STATIC_MAX_NQ 65536
-#define MUNINN_STATIC_VIS_ENTRIES (4u << 20) /* 16 MiB: 1 024 teams at ef = 64, M = 16; indexes up to 2 097 118 nodes */
+#define MUNINN_STATIC_VIS_ENTRIES (4u << 20) /* 16 MiB: 1 024 teams at ef = 64, M = 16; indexes up to 2 097 119 nodes at M = 16 */
 static const size_t STATIC_CTL_BYTES = 256, STATIC_RETRY_BYTES = (size_t)2 * MUNINN_STATIC_MAX_NQ * sizeof(int),
                     STATIC_VIS_BYTES = (size_t)MUNINN_STATIC_VIS_ENTRIES * sizeof(unsigned);
 static __device__ __align__(256) unsigned char g_static_scratch[256 + (size_t)2 * MUNINN_STATIC_MAX_NQ * sizeof(int) +

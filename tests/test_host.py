@@ -193,6 +193,11 @@ def test_abi_host_only_calls():
     assert cuda.parse_metric("l2") == 0 and cuda.parse_metric("cosine") == 1
     assert cuda.parse_metric("inner_product") == 2 and cuda.parse_metric("hamming") == -1
     assert L.muninn_cuda_strerror(-2) == b"no CUDA device"
+    # limits of the allocation-free search entry point: pure host code, as documented in include/muninn_cuda.h
+    lim = cuda.static_scratch_limits()
+    assert lim == {"max_nq": 65536, "max_nodes": 2097152 - 256, "bytes": 17301760}
+    hdr = open(os.path.join(ROOT, "include", "muninn_cuda.h")).read()
+    assert "17 301 760 bytes" in hdr and "65 536 queries" in hdr and "2 097 119 nodes" in hdr
 
 
 def test_no_cpu_fallback_without_device():
