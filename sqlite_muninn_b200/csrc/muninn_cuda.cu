@@ -655,7 +655,7 @@ static unsigned log2u(unsigned v) { unsigned l = 0; while ((1u << l) < v) l++; r
  * hnsw_beam.cuh (query teams of W warps, 16-row batches through a row ring). kernel_gen 0 picks by shape from the
  * measurements in profiles/r2_bench/: teams of 4 or 2 warps — the widest at which every query of the batch is resident at once
  * (a lone MATCH: 4 warps; the 1 250-query slices of a batch split over 8 GPUs: 2 warps, 8-11 % faster than one), the 16-row kernel for
- * ef >= 192 at dim 128 (5 % faster) and for batches that fit one wave of its teams (4-15 % faster), the 13-row kernel otherwise. MUNINN_KERNEL / muninn_cuda_set_option("kernel_gen")
+ * ef >= 192 at dim 128 (5 % faster) and for batches of up to two waves that need no more waves of its teams than of the 13-row kernel's (4-15 % faster), the 13-row kernel otherwise. MUNINN_KERNEL / muninn_cuda_set_option("kernel_gen")
  * force one for A/B runs. A kernel is picked as a plain function pointer so that occupancy query, attribute and launch
  * share one code path. Ring geometry (U floats per unit, NST stages) per constant-dimension instance: */
 #ifndef MUNINN_U_D128
@@ -815,13 +815,21 @@ static int search_device_impl(MuninnCudaIndex *h, const float *d_queries, int nq
         int gen = forced_gen;
         if (gen == 0) gen = W > 1 ? 8 : ((h->dim == 128 && ef >= 192) ? 8 : 7);
         if (forced_gen == 0 && gen == 7) {
-            /* a batch that fits ONE wave of the ring kernel's teams: with nothing queued behind a team the 13-row kernel's
-             * extra residency buys nothing and the 16-row batches win by 4-15 % (profiles/r2_bench/ab_one_wave.jsonl) */
-            KernelSel s8 = select_kernel(h, 8, 1, ef);
-            int o8 = 0;
-            if (s8.smem <= SEARCH_SMEM_LIMIT) {
+            /* Up to two waves of resident teams the time of a launch is a staircase in the NUMBER of waves, and the 13-row
+             * kernel's extra residency only pays where it saves one: whenever the ring kernel needs no more waves than the
+             * 13-row kernel, its 16-row batches win — by 4-15 % on one wave (profiles/r2_bench/ab_one_wave.jsonl), by 10 % on
+             * two (5 000 queries, a 10k batch split over 2 GPUs: 0.842 vs 0.936 ms; 6 400: 1.13 vs 1.01 the other way;
+             * profiles/r2_bench/ab_two_waves.jsonl). Longer batches keep the 13-row kernel (measured at 10k and 80k). */
+            KernelSel s8 = select_kernel(h, 8, 1, ef), s7 = select_kernel(h, 7, 1, ef);
+            int o8 = 0, o7 = 0;
+            if (s8.smem <= SEARCH_SMEM_LIMIT && s7.smem <= SEARCH_SMEM_LIMIT) {
                 CK(h, occupancy_cached(h, s8, &o8));
-                if (o8 >= 1 && (long long)nq <= (long long)h->num_sms * o8) gen = 8;
+                CK(h, occupancy_cached(h, s7, &o7));
+                if (o8 >= 1 && o7 >= 1) {
+                    const long long cap8 = (long long)h->num_sms * o8, cap7 = (long long)h->num_sms * o7;
+                    const long long w8 = (nq + cap8 - 1) / cap8, w7 = (nq + cap7 - 1) / cap7;
+                    if (w7 <= 2 && w8 <= w7) gen = 8;
+                }
             }
         }
         if (gen == 7 && W > 1) gen = 8; /* the one-warp kernel has no wider shape */
