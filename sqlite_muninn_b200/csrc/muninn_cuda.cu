@@ -26,6 +26,7 @@
 #endif
 
 #include <algorithm>
+#include <climits>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -758,6 +759,75 @@ static cudaError_t occupancy_cached(MuninnCudaIndex *h, const KernelSel &k, int 
 static const size_t SEARCH_SMEM_LIMIT = 200 * 1024;
 static const size_t VIS_SMEM_MAX = 64 * 1024; /* largest first-level visited table a team keeps in shared memory (ef = 256 at M = 16) */
 
+/* Team width, kernel and shared-memory layout of one search call: the caller's choice (muninn_cuda_set_tuning, "kernel_gen"),
+ * else by shape — see "kernel selection" above. resident_cap bounds how many teams the caller's visited arena can keep
+ * resident (no bound when the arena grows with the launch); allow_tbl = the first-level table may live in shared memory. */
+static int choose_search_kernel(MuninnCudaIndex *h, int nq, int ef, long long resident_cap, bool allow_tbl, KernelSel *out_sel,
+                                int *out_occ) {
+    /* A lone query is a dependent chain of instructions: more warps take the distance evaluations of each expansion off
+     * it, as long as every query of the batch can be resident at once; a full batch wants as many independent queries
+     * per SM as fit. */
+    KernelSel sel;
+    int occ = 0;
+    {
+        const long long kept = resident_cap; /* teams the visited arena lets a launch keep resident */
+        const int forced_w = h->warps_per_query, forced_gen = h->kernel_gen;
+        int W = forced_w ? forced_w : 1;
+        /* the teams of several warps can keep their first-level visited table (sized as below) in shared memory */
+        const size_t tbl = (size_t)std::min(pow2_at_least((unsigned long long)(h->vis_factor * (double)ef * h->W0)),
+                                            pow2_at_least(2ull * (unsigned long long)(h->n + h->W0 + 1))) * 4;
+        const bool tbl_ok = allow_tbl && h->vis_in_smem && tbl <= VIS_SMEM_MAX;
+        bool use_tbl = false;
+        if (!forced_w && forced_gen != 7) {
+            /* automatic width: the widest team at which the whole batch is still resident — with the table in shared
+             * memory if the batch is still resident at the occupancy that leaves, else without. 4 warps beat 2 by 2-5 % up
+             * to ≈ 600 queries and lose badly once a second wave is needed (profiles/r2_bench/ab_team_width4.jsonl) */
+            for (int w = 4; w >= 2 && W == 1; w >>= 1) {
+                for (int with_tbl = tbl_ok ? 1 : 0; with_tbl >= 0 && W == 1; with_tbl--) {
+                    KernelSel sw = select_kernel(h, 8, w, ef);
+                    if (with_tbl) { sw.vis_smem = tbl; sw.smem += tbl; }
+                    int ow = 0;
+                    if (sw.smem > SEARCH_SMEM_LIMIT) continue;
+                    CK(h, occupancy_cached(h, sw, &ow));
+                    if (ow >= 1 && (long long)nq <= std::min((long long)h->num_sms * ow, kept)) { W = w; use_tbl = with_tbl != 0; }
+                }
+            }
+        } else if (forced_w > 1 && tbl_ok) {
+            KernelSel sw = select_kernel(h, 8, forced_w, ef);
+            use_tbl = sw.smem + tbl <= SEARCH_SMEM_LIMIT;
+        }
+        int gen = forced_gen;
+        if (gen == 0) gen = W > 1 ? 8 : ((h->dim == 128 && ef >= 192) ? 8 : 7);
+        if (forced_gen == 0 && gen == 7) {
+            /* Up to two waves of resident teams the time of a launch is a staircase in the NUMBER of waves, and the 13-row
+             * kernel's extra residency only pays where it saves one: whenever the ring kernel needs no more waves than the
+             * 13-row kernel, its 16-row batches win — by 4-15 % on one wave (profiles/r2_bench/ab_one_wave.jsonl), by 10 % on
+             * two (5 000 queries, a 10k batch split over 2 GPUs: 0.842 vs 0.936 ms; 6 400: 1.13 vs 1.01 the other way;
+             * profiles/r2_bench/ab_two_waves.jsonl). Longer batches keep the 13-row kernel (measured at 10k and 80k). */
+            KernelSel s8 = select_kernel(h, 8, 1, ef), s7 = select_kernel(h, 7, 1, ef);
+            int o8 = 0, o7 = 0;
+            if (s8.smem <= SEARCH_SMEM_LIMIT && s7.smem <= SEARCH_SMEM_LIMIT) {
+                CK(h, occupancy_cached(h, s8, &o8));
+                CK(h, occupancy_cached(h, s7, &o7));
+                if (o8 >= 1 && o7 >= 1) {
+                    const long long cap8 = std::min((long long)h->num_sms * o8, kept), cap7 = std::min((long long)h->num_sms * o7, kept);
+                    const long long w8 = (nq + cap8 - 1) / cap8, w7 = (nq + cap7 - 1) / cap7;
+                    if (w7 <= 2 && w8 <= w7) gen = 8;
+                }
+            }
+        }
+        if (gen == 7 && W > 1) gen = 8; /* the one-warp kernel has no wider shape */
+        sel = select_kernel(h, gen, W, ef);
+        if (sel.smem > SEARCH_SMEM_LIMIT && W > 1) { W = 1; sel = select_kernel(h, gen, W, ef); }
+        if (sel.smem > SEARCH_SMEM_LIMIT)
+            return fail(h, MUNINN_CUDA_E_ARG, "ef=%d with dim=%d needs %zu B of shared memory per query (limit 200 KiB)", ef, h->dim, sel.smem);
+        if (use_tbl && sel.gen == 8 && sel.W > 1 && sel.smem + tbl <= SEARCH_SMEM_LIMIT) { sel.vis_smem = tbl; sel.smem += tbl; }
+        CK(h, occupancy_cached(h, sel, &occ));
+    }
+    *out_sel = sel; *out_occ = occ;
+    return MUNINN_CUDA_OK;
+}
+
 static int search_device_impl(MuninnCudaIndex *h, const float *d_queries, int nq, int k, int ef, int64_t *d_ids, float *d_dist,
                               int32_t *d_count, MuninnSearchStats *d_stats, const unsigned *d_arrived);
 
@@ -780,65 +850,11 @@ static int search_device_impl(MuninnCudaIndex *h, const float *d_queries, int nq
     if (ef < k) ef = k; /* src/hnsw_algo.c:673 */
     CK(h, cudaSetDevice(h->device));
 
-    /* team width and kernel: the caller's choice, else by shape (see "kernel selection" above). A lone query is a
-     * dependent chain of instructions: a second warp takes half of each expansion's distance evaluations off it, as
-     * long as every query of the batch can be resident at once; a full batch wants as many independent queries per
-     * SM as fit. */
     KernelSel sel;
     int occ = 0;
     {
-        const int forced_w = h->warps_per_query, forced_gen = h->kernel_gen;
-        int W = forced_w ? forced_w : 1;
-        /* the teams of several warps can keep their first-level visited table (sized as below) in shared memory */
-        const size_t tbl = (size_t)std::min(pow2_at_least((unsigned long long)(h->vis_factor * (double)ef * h->W0)),
-                                            pow2_at_least(2ull * (unsigned long long)(h->n + h->W0 + 1))) * 4;
-        const bool tbl_ok = h->vis_in_smem && tbl <= VIS_SMEM_MAX;
-        bool use_tbl = false;
-        if (!forced_w && forced_gen != 7) {
-            /* automatic width: the widest team at which the whole batch is still resident — with the table in shared
-             * memory if the batch is still resident at the occupancy that leaves, else without. 4 warps beat 2 by 2-5 % up
-             * to ≈ 600 queries and lose badly once a second wave is needed (profiles/r2_bench/ab_team_width4.jsonl) */
-            for (int w = 4; w >= 2 && W == 1; w >>= 1) {
-                for (int with_tbl = tbl_ok ? 1 : 0; with_tbl >= 0 && W == 1; with_tbl--) {
-                    KernelSel sw = select_kernel(h, 8, w, ef);
-                    if (with_tbl) { sw.vis_smem = tbl; sw.smem += tbl; }
-                    int ow = 0;
-                    if (sw.smem > SEARCH_SMEM_LIMIT) continue;
-                    CK(h, occupancy_cached(h, sw, &ow));
-                    if (ow >= 1 && (long long)nq <= (long long)h->num_sms * ow) { W = w; use_tbl = with_tbl != 0; }
-                }
-            }
-        } else if (forced_w > 1 && tbl_ok) {
-            KernelSel sw = select_kernel(h, 8, forced_w, ef);
-            use_tbl = sw.smem + tbl <= SEARCH_SMEM_LIMIT;
-        }
-        int gen = forced_gen;
-        if (gen == 0) gen = W > 1 ? 8 : ((h->dim == 128 && ef >= 192) ? 8 : 7);
-        if (forced_gen == 0 && gen == 7) {
-            /* Up to two waves of resident teams the time of a launch is a staircase in the NUMBER of waves, and the 13-row
-             * kernel's extra residency only pays where it saves one: whenever the ring kernel needs no more waves than the
-             * 13-row kernel, its 16-row batches win — by 4-15 % on one wave (profiles/r2_bench/ab_one_wave.jsonl), by 10 % on
-             * two (5 000 queries, a 10k batch split over 2 GPUs: 0.842 vs 0.936 ms; 6 400: 1.13 vs 1.01 the other way;
-             * profiles/r2_bench/ab_two_waves.jsonl). Longer batches keep the 13-row kernel (measured at 10k and 80k). */
-            KernelSel s8 = select_kernel(h, 8, 1, ef), s7 = select_kernel(h, 7, 1, ef);
-            int o8 = 0, o7 = 0;
-            if (s8.smem <= SEARCH_SMEM_LIMIT && s7.smem <= SEARCH_SMEM_LIMIT) {
-                CK(h, occupancy_cached(h, s8, &o8));
-                CK(h, occupancy_cached(h, s7, &o7));
-                if (o8 >= 1 && o7 >= 1) {
-                    const long long cap8 = (long long)h->num_sms * o8, cap7 = (long long)h->num_sms * o7;
-                    const long long w8 = (nq + cap8 - 1) / cap8, w7 = (nq + cap7 - 1) / cap7;
-                    if (w7 <= 2 && w8 <= w7) gen = 8;
-                }
-            }
-        }
-        if (gen == 7 && W > 1) gen = 8; /* the one-warp kernel has no wider shape */
-        sel = select_kernel(h, gen, W, ef);
-        if (sel.smem > SEARCH_SMEM_LIMIT && W > 1) { W = 1; sel = select_kernel(h, gen, W, ef); }
-        if (sel.smem > SEARCH_SMEM_LIMIT)
-            return fail(h, MUNINN_CUDA_E_ARG, "ef=%d with dim=%d needs %zu B of shared memory per query (limit 200 KiB)", ef, h->dim, sel.smem);
-        if (use_tbl && sel.gen == 8 && sel.W > 1 && sel.smem + tbl <= SEARCH_SMEM_LIMIT) { sel.vis_smem = tbl; sel.smem += tbl; }
-        CK(h, occupancy_cached(h, sel, &occ));
+        const int rc_sel = choose_search_kernel(h, nq, ef, LLONG_MAX, true, &sel, &occ);
+        if (rc_sel) return rc_sel;
     }
     if (occ < 1) return fail(h, MUNINN_CUDA_E_CUDA, "search kernel does not fit on an SM");
     const size_t smem = sel.smem;
@@ -969,37 +985,13 @@ extern "C" int muninn_cuda_search_batch_device_static(MuninnCudaIndex *h, const 
     const int nlevels = caps[0] == cap_all ? 1 : (caps[1] == cap_all ? 2 : 3);
     const long long arena_teams = MUNINN_STATIC_VIS_ENTRIES / caps[0];
 
-    /* team width and kernel by the same policy as search_device_impl, with "resident" bounded by the arena as well */
+    /* team width and kernel by the same policy as search_device_impl, with "resident" bounded by the arena as well and
+     * every visited table in the static array */
     KernelSel sel;
     int occ = 0;
     {
-        const int forced_w = h->warps_per_query, forced_gen = h->kernel_gen;
-        int W = forced_w ? forced_w : 1;
-        if (!forced_w && forced_gen != 7) {
-            for (int w = 4; w >= 2 && W == 1; w >>= 1) {
-                KernelSel sw = select_kernel(h, 8, w, ef);
-                int ow = 0;
-                if (sw.smem > SEARCH_SMEM_LIMIT) continue;
-                CK(h, occupancy_cached(h, sw, &ow));
-                if (ow >= 1 && (long long)nq <= std::min((long long)h->num_sms * ow, arena_teams)) W = w;
-            }
-        }
-        int gen = forced_gen;
-        if (gen == 0) gen = W > 1 ? 8 : ((h->dim == 128 && ef >= 192) ? 8 : 7);
-        if (forced_gen == 0 && gen == 7) {
-            KernelSel s8 = select_kernel(h, 8, 1, ef);
-            int o8 = 0;
-            if (s8.smem <= SEARCH_SMEM_LIMIT) {
-                CK(h, occupancy_cached(h, s8, &o8));
-                if (o8 >= 1 && (long long)nq <= std::min((long long)h->num_sms * o8, arena_teams)) gen = 8;
-            }
-        }
-        if (gen == 7 && W > 1) gen = 8;
-        sel = select_kernel(h, gen, W, ef);
-        if (sel.smem > SEARCH_SMEM_LIMIT && W > 1) { W = 1; sel = select_kernel(h, gen, W, ef); }
-        if (sel.smem > SEARCH_SMEM_LIMIT)
-            return fail(h, MUNINN_CUDA_E_ARG, "ef=%d with dim=%d needs %zu B of shared memory per query (limit 200 KiB)", ef, h->dim, sel.smem);
-        CK(h, occupancy_cached(h, sel, &occ));
+        const int rc_sel = choose_search_kernel(h, nq, ef, arena_teams, false, &sel, &occ);
+        if (rc_sel) return rc_sel;
     }
     if (occ < 1) return fail(h, MUNINN_CUDA_E_CUDA, "search kernel does not fit on an SM");
     const int tps = h->teams_per_sm > 0 ? std::min(h->teams_per_sm, occ) : occ;
