@@ -88,3 +88,37 @@ def test_reference_arm_never_loads_the_cuda_library(tmp_path):
     out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=300)
     assert out.returncode == 0, out.stderr[-2000:]
     assert "CUDA_NOT_LOADED" in out.stdout
+
+
+def test_committed_dram_traffic_matches_the_kernel_sources_as_shipped():
+    """`roofline.traffic` comes from ncu captures keyed by the hash of the search-kernel sources: a kernel edit without a
+    fresh capture would silently turn it into null. The tree as committed must carry records for its own sources, for both
+    launches the bench reports (the 10k batch and the 80k-query job)."""
+    import json
+    sha = bench.kernel_source_sha()
+    recs = json.load(open(os.path.join(ROOT, "profiles", "search_traffic.json")))
+    mine = {r["nq"]: r for r in recs if r["kernel_src_sha"] == sha and r["config"] == 2 and r["ef"] == 64}
+    assert set(mine) >= {10000, 80000}, f"no ncu traffic record for kernel sources {sha}: run tools/capture_final.sh + tools/ncu_traffic.py"
+    for r in mine.values():
+        assert r["dram_bytes"] == r["dram_bytes_read"] + r["dram_bytes_write"] > 0
+        assert os.path.exists(os.path.join(ROOT, r["source"])), r["source"]
+    assert bench.ncu_traffic(2, 64, 10000) == mine[10000]["dram_bytes"]
+
+
+def test_documents_cite_files_that_exist():
+    """Every profile / tool / source file that DESIGN.md, INTEGRATION.md and the READMEs name in backticks is in the tree
+    (paths of the reference — src/, test/, benchmarks/, pytests/ — are not ours to check)."""
+    import glob
+    import re
+    where = ["", "profiles/", "profiles/r2_bench/", "profiles/r2_ncu/", "profiles/r1_bench/", "sqlite_muninn_b200/",
+             "sqlite_muninn_b200/csrc/", "tools/", "integration/", "include/", "tests/", "tests/golden/", "oracle/"]
+    reference_files = {"hnsw_algo.c", "priority_queue.c", "vec_math.c", "hnsw_vtab.c", "muninn.c"}
+    missing = []
+    for doc in ("DESIGN.md", "INTEGRATION.md", "README.md", os.path.join("profiles", "README.md")):
+        text = open(os.path.join(ROOT, doc)).read()
+        for m in re.findall(r"`([A-Za-z0-9_./*-]+\.(?:json|jsonl|csv|log|py|sh|cuh|cu|c|h|md))`", text):
+            if m.startswith(("src/", "test/", "benchmarks/", "pytests/")) or m in reference_files or "/_" in m or m.startswith("r1_"):
+                continue
+            if not any(glob.glob(os.path.join(ROOT, w + m)) for w in where):
+                missing.append((doc, m))
+    assert not missing, missing
